@@ -1,0 +1,205 @@
+// oracle/ref_wrap.cpp -- TEST INFRASTRUCTURE ONLY.
+//
+// A thin extern "C" wrapper (our code) around the UNMODIFIED reference classes compiled from
+// /root/reference/source/MRMesh (see oracle/Makefile, target `ref`).  It lets tests/ and bench.py's
+// cpu_baseline / --impl reference leg drive the reference's own CPU (TBB) implementation of the path:
+//   MR::FastWindingNumber::{calcFromVector,calcSelfIntersections,calcFromGrid,calcFromGridWithDistances}
+//     (source/MRMesh/MRFastWindingNumber.cpp:28-94)
+//   MR::AABBTree / MR::calcDipoles (source/MRMesh/MRAABBTree.cpp:31-60, MRDipole.cpp:23-71)
+//   MR::makeTorus / MR::makeUVSphere (source/MRMesh/MRTorus.cpp:9-59, MRMakeSphereMesh.cpp:35-102)
+// Nothing under meshlib_b200/ may link or load this file's output.
+#include "MRMesh/MRMesh.h"
+#include "MRMesh/MRAABBTree.h"
+#include "MRMesh/MRDipole.h"
+#include "MRMesh/MRFastWindingNumber.h"
+#include "MRMesh/MRDistanceToMeshOptions.h"
+#include "MRMesh/MRMeshProject.h"
+#include "MRMesh/MRTorus.h"
+#include "MRMesh/MRMakeSphereMesh.h"
+#include "MRMesh/MRBitSet.h"
+#include "MRMesh/MRTimer.h"
+#include <cstring>
+#include <thread>
+
+// MRTimer.cpp needs the (absent) spdlog submodule; the path only uses the RAII start/finish pair.
+namespace MR
+{
+void Timer::restart( std::string ) {}
+void Timer::start( std::string ) {}
+void Timer::start( const char* ) {}
+void Timer::finish() {}
+}
+
+using namespace MR;
+
+struct RefMesh
+{
+    Mesh mesh;
+    Triangulation tris; // reference vertex order per face (getTriangulation), -1 for invalid faces
+};
+
+static AffineXf3f toXf( const float* xf12 )
+{
+    AffineXf3f xf;
+    xf.A.x = Vector3f( xf12[0], xf12[1], xf12[2] );
+    xf.A.y = Vector3f( xf12[3], xf12[4], xf12[5] );
+    xf.A.z = Vector3f( xf12[6], xf12[7], xf12[8] );
+    xf.b = Vector3f( xf12[9], xf12[10], xf12[11] );
+    return xf;
+}
+
+extern "C"
+{
+
+int mrref_hardware_threads() { return (int)std::thread::hardware_concurrency(); }
+
+void* mrref_create( const float* pts, size_t nVerts, const int* tris, size_t nFaces )
+{
+    VertCoords points( nVerts );
+    std::memcpy( (void*)points.data(), pts, nVerts * sizeof( Vector3f ) );
+    Triangulation t( nFaces );
+    for ( size_t i = 0; i < nFaces; ++i )
+        t.vec_[i] = { VertId( tris[3 * i] ), VertId( tris[3 * i + 1] ), VertId( tris[3 * i + 2] ) };
+    auto* r = new RefMesh;
+    r->mesh = Mesh::fromTriangles( std::move( points ), t );
+    r->tris = r->mesh.topology.getTriangulation();
+    return r;
+}
+
+void* mrref_make_torus( float R, float r, int pRes, int sRes )
+{
+    auto* m = new RefMesh;
+    m->mesh = makeTorus( R, r, pRes, sRes );
+    m->tris = m->mesh.topology.getTriangulation();
+    return m;
+}
+
+void* mrref_make_uv_sphere( float radius, int hRes, int vRes )
+{
+    auto* m = new RefMesh;
+    m->mesh = makeUVSphere( radius, hRes, vRes );
+    m->tris = m->mesh.topology.getTriangulation();
+    return m;
+}
+
+void mrref_destroy( void* h ) { delete (RefMesh*)h; }
+
+size_t mrref_num_verts( void* h ) { return ( (RefMesh*)h )->mesh.points.size(); }
+size_t mrref_num_faces( void* h ) { return ( (RefMesh*)h )->tris.size(); }
+int mrref_num_valid_faces( void* h ) { return ( (RefMesh*)h )->mesh.topology.numValidFaces(); }
+
+void mrref_get_points( void* h, float* out )
+{
+    auto& m = ( (RefMesh*)h )->mesh;
+    std::memcpy( out, m.points.data(), m.points.size() * sizeof( Vector3f ) );
+}
+
+void mrref_get_tris( void* h, int* out )
+{
+    auto& t = ( (RefMesh*)h )->tris;
+    for ( size_t i = 0; i < t.size(); ++i )
+        for ( int k = 0; k < 3; ++k )
+            out[3 * i + k] = (int)t.vec_[i][k];
+}
+
+/// number of AABB tree nodes (builds the tree on first use, as Mesh::getAABBTree does)
+size_t mrref_num_nodes( void* h ) { return ( (RefMesh*)h )->mesh.getAABBTree().nodes().size(); }
+
+/// nodes: 8 x 4 bytes each = box.min xyz, box.max xyz (float), l, r (int32)
+void mrref_get_nodes( void* h, void* out )
+{
+    const auto& nodes = ( (RefMesh*)h )->mesh.getAABBTree().nodes();
+    static_assert( sizeof( nodes.vec_[0] ) == 32 );
+    std::memcpy( out, nodes.vec_.data(), nodes.size() * 32 );
+}
+
+/// dipoles: 8 floats each = pos xyz, area, dirArea xyz, rr
+void mrref_get_dipoles( void* h, float* out )
+{
+    const auto& d = ( (RefMesh*)h )->mesh.getDipoles();
+    std::memcpy( out, d.vec_.data(), d.size() * sizeof( Dipole ) );
+}
+
+int mrref_calc_from_vector( void* h, const float* pts, size_t n, float beta, int skipFace, float* out )
+{
+    FastWindingNumber fwn( ( (RefMesh*)h )->mesh );
+    std::vector<Vector3f> points( n );
+    std::memcpy( (void*)points.data(), pts, n * sizeof( Vector3f ) );
+    std::vector<float> res;
+    auto e = fwn.calcFromVector( res, points, beta, FaceId( skipFace ), {} );
+    if ( !e )
+        return 1;
+    std::memcpy( out, res.data(), n * sizeof( float ) );
+    return 0;
+}
+
+/// out_bits: ceil(faceSize/64) 64-bit words
+int mrref_calc_self_intersections( void* h, float beta, uint64_t* out_bits )
+{
+    auto& m = ( (RefMesh*)h )->mesh;
+    FastWindingNumber fwn( m );
+    FaceBitSet res;
+    auto e = fwn.calcSelfIntersections( res, beta, {} );
+    if ( !e )
+        return 1;
+    const size_t nf = m.topology.faceSize();
+    const size_t words = ( nf + 63 ) / 64;
+    for ( size_t w = 0; w < words; ++w )
+        out_bits[w] = 0;
+    for ( auto f : res )
+        out_bits[size_t( f ) / 64] |= uint64_t( 1 ) << ( size_t( f ) % 64 );
+    return 0;
+}
+
+int mrref_calc_from_grid( void* h, const int* dims, const float* xf12, float beta, float* out )
+{
+    FastWindingNumber fwn( ( (RefMesh*)h )->mesh );
+    std::vector<float> res;
+    auto e = fwn.calcFromGrid( res, Vector3i( dims[0], dims[1], dims[2] ), toXf( xf12 ), beta, {} );
+    if ( !e )
+        return 1;
+    std::memcpy( out, res.data(), res.size() * sizeof( float ) );
+    return 0;
+}
+
+int mrref_calc_from_grid_with_distances( void* h, const int* dims, const float* xf12,
+    float minDistSq, float maxDistSq, int nullOutsideMinMax, float threshold, float beta, float* out )
+{
+    FastWindingNumber fwn( ( (RefMesh*)h )->mesh );
+    DistanceToMeshOptions o;
+    o.minDistSq = minDistSq;
+    o.maxDistSq = maxDistSq;
+    o.nullOutsideMinMax = nullOutsideMinMax != 0;
+    o.windingNumberThreshold = threshold;
+    o.windingNumberBeta = beta;
+    std::vector<float> res;
+    auto e = fwn.calcFromGridWithDistances( res, Vector3i( dims[0], dims[1], dims[2] ), toXf( xf12 ), o, {} );
+    if ( !e )
+        return 1;
+    std::memcpy( out, res.data(), res.size() * sizeof( float ) );
+    return 0;
+}
+
+/// same per-voxel function on an arbitrary sub-range of z layers [z0, z1) -- used to time bounded samples
+int mrref_calc_grid_with_distances_layers( void* h, const int* dims, const float* xf12,
+    float minDistSq, float maxDistSq, int nullOutsideMinMax, float threshold, float beta, int z0, int z1, float* out )
+{
+    // a z-range of the full grid is itself a grid whose transform has b shifted by A*(0,0,z0)
+    AffineXf3f xf = toXf( xf12 );
+    xf.b = xf( Vector3f( 0, 0, float( z0 ) ) );
+    float x2[12] = { xf.A.x.x, xf.A.x.y, xf.A.x.z, xf.A.y.x, xf.A.y.y, xf.A.y.z, xf.A.z.x, xf.A.z.y, xf.A.z.z, xf.b.x, xf.b.y, xf.b.z };
+    int d2[3] = { dims[0], dims[1], z1 - z0 };
+    return mrref_calc_from_grid_with_distances( h, d2, x2, minDistSq, maxDistSq, nullOutsideMinMax, threshold, beta, out );
+}
+
+/// unsigned squared distances (findProjection) for a vector of points
+int mrref_find_projection_dist_sq( void* h, const float* pts, size_t n, float upDistLimitSq, float loDistLimitSq, float* out )
+{
+    auto& m = ( (RefMesh*)h )->mesh;
+    (void)m.getAABBTree();
+    for ( size_t i = 0; i < n; ++i )
+        out[i] = findProjection( Vector3f( pts[3 * i], pts[3 * i + 1], pts[3 * i + 2] ), m, upDistLimitSq, nullptr, loDistLimitSq ).distSq;
+    return 0;
+}
+
+} // extern "C"

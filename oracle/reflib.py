@@ -1,0 +1,157 @@
+"""oracle/reflib.py -- TEST INFRASTRUCTURE ONLY (imported by tests/, __graft_entry__.smoke(), bench.py's
+cpu_baseline / --impl reference leg; never by meshlib_b200/).
+
+ctypes loader for oracle/_ref/libmrref.so = the UNMODIFIED reference CPU/TBB implementation of the path
+(MR::FastWindingNumber, MR::AABBTree, MR::calcDipoles; /root/reference/source/MRMesh) behind our C wrapper
+oracle/ref_wrap.cpp.  Built by `make -C oracle ref` in the build container; the .so travels to the GPU box.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_PATH = os.path.join(_HERE, "_ref", "libmrref.so")
+_lib = None
+
+_f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+_i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+_u64p = np.ctypeslib.ndpointer(np.uint64, flags="C_CONTIGUOUS")
+
+
+def available():
+    return os.path.exists(_PATH)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        L = C.CDLL(_PATH)
+        L.mrref_hardware_threads.restype = C.c_int
+        L.mrref_create.restype = C.c_void_p
+        L.mrref_create.argtypes = [_f32p, C.c_size_t, _i32p, C.c_size_t]
+        L.mrref_make_torus.restype = C.c_void_p
+        L.mrref_make_torus.argtypes = [C.c_float, C.c_float, C.c_int, C.c_int]
+        L.mrref_make_uv_sphere.restype = C.c_void_p
+        L.mrref_make_uv_sphere.argtypes = [C.c_float, C.c_int, C.c_int]
+        L.mrref_destroy.argtypes = [C.c_void_p]
+        for n in ("mrref_num_verts", "mrref_num_faces", "mrref_num_nodes"):
+            getattr(L, n).restype = C.c_size_t
+            getattr(L, n).argtypes = [C.c_void_p]
+        L.mrref_num_valid_faces.restype = C.c_int
+        L.mrref_num_valid_faces.argtypes = [C.c_void_p]
+        L.mrref_get_points.argtypes = [C.c_void_p, _f32p]
+        L.mrref_get_tris.argtypes = [C.c_void_p, _i32p]
+        L.mrref_get_nodes.argtypes = [C.c_void_p, C.c_void_p]
+        L.mrref_get_dipoles.argtypes = [C.c_void_p, _f32p]
+        L.mrref_calc_from_vector.argtypes = [C.c_void_p, _f32p, C.c_size_t, C.c_float, C.c_int, _f32p]
+        L.mrref_calc_self_intersections.argtypes = [C.c_void_p, C.c_float, _u64p]
+        L.mrref_calc_from_grid.argtypes = [C.c_void_p, _i32p, _f32p, C.c_float, _f32p]
+        L.mrref_calc_from_grid_with_distances.argtypes = [
+            C.c_void_p, _i32p, _f32p, C.c_float, C.c_float, C.c_int, C.c_float, C.c_float, _f32p]
+        L.mrref_calc_grid_with_distances_layers.argtypes = [
+            C.c_void_p, _i32p, _f32p, C.c_float, C.c_float, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int, _f32p]
+        L.mrref_find_projection_dist_sq.argtypes = [C.c_void_p, _f32p, C.c_size_t, C.c_float, C.c_float, _f32p]
+        _lib = L
+    return _lib
+
+
+NODE_DTYPE = np.dtype([("bmin", np.float32, 3), ("bmax", np.float32, 3), ("l", np.int32), ("r", np.int32)])
+DIPOLE_DTYPE = np.dtype([("pos", np.float32, 3), ("area", np.float32), ("dirArea", np.float32, 3), ("rr", np.float32)])
+FLT_MAX = float(np.finfo(np.float32).max)
+
+
+class RefMesh:
+    """The reference's MR::Mesh + MR::FastWindingNumber, driven from numpy."""
+
+    def __init__(self, handle):
+        self.h = C.c_void_p(handle)
+
+    @classmethod
+    def from_arrays(cls, points, tris):
+        points = np.ascontiguousarray(points, np.float32)
+        tris = np.ascontiguousarray(tris, np.int32)
+        return cls(lib().mrref_create(points, len(points), tris, len(tris)))
+
+    @classmethod
+    def torus(cls, R, r, p_res, s_res):
+        return cls(lib().mrref_make_torus(R, r, p_res, s_res))
+
+    @classmethod
+    def uv_sphere(cls, radius, h_res, v_res):
+        return cls(lib().mrref_make_uv_sphere(radius, h_res, v_res))
+
+    def __del__(self):
+        if getattr(self, "h", None) and _lib is not None:
+            _lib.mrref_destroy(self.h)
+            self.h = None
+
+    @property
+    def points(self):
+        out = np.empty((lib().mrref_num_verts(self.h), 3), np.float32)
+        lib().mrref_get_points(self.h, out)
+        return out
+
+    @property
+    def tris(self):
+        """triangulation in the reference's per-face vertex order (MeshTopology::getTriangulation)"""
+        out = np.empty((lib().mrref_num_faces(self.h), 3), np.int32)
+        lib().mrref_get_tris(self.h, out)
+        return out
+
+    def nodes(self):
+        out = np.empty(lib().mrref_num_nodes(self.h), NODE_DTYPE)
+        lib().mrref_get_nodes(self.h, out.ctypes.data_as(C.c_void_p))
+        return out
+
+    def dipoles(self):
+        n = lib().mrref_num_nodes(self.h)
+        out = np.empty((n, 8), np.float32)
+        lib().mrref_get_dipoles(self.h, out)
+        return out.view(DIPOLE_DTYPE).reshape(n)
+
+    def calc_from_vector(self, pts, beta=2.0, skip_face=-1):
+        pts = np.ascontiguousarray(pts, np.float32)
+        out = np.empty(len(pts), np.float32)
+        assert lib().mrref_calc_from_vector(self.h, pts, len(pts), beta, skip_face, out) == 0
+        return out
+
+    def calc_self_intersections(self, beta=2.0):
+        nf = lib().mrref_num_faces(self.h)
+        out = np.zeros((nf + 63) // 64, np.uint64)
+        assert lib().mrref_calc_self_intersections(self.h, beta, out) == 0
+        return out
+
+    def calc_from_grid(self, dims, xf12, beta=2.0):
+        dims = np.asarray(dims, np.int32)
+        out = np.empty(int(np.prod(dims.astype(np.int64))), np.float32)
+        assert lib().mrref_calc_from_grid(self.h, dims, np.asarray(xf12, np.float32), beta, out) == 0
+        return out
+
+    def calc_from_grid_with_distances(self, dims, xf12, min_dist_sq=0.0, max_dist_sq=FLT_MAX, null_outside=True,
+                                      threshold=0.5, beta=2.0):
+        dims = np.asarray(dims, np.int32)
+        out = np.empty(int(np.prod(dims.astype(np.int64))), np.float32)
+        assert lib().mrref_calc_from_grid_with_distances(
+            self.h, dims, np.asarray(xf12, np.float32), min_dist_sq, max_dist_sq, int(null_outside), threshold, beta,
+            out) == 0
+        return out
+
+    def calc_grid_with_distances_layers(self, dims, xf12, z0, z1, min_dist_sq=0.0, max_dist_sq=FLT_MAX,
+                                        null_outside=True, threshold=0.5, beta=2.0):
+        dims = np.asarray(dims, np.int32)
+        out = np.empty(int(dims[0]) * int(dims[1]) * (z1 - z0), np.float32)
+        assert lib().mrref_calc_grid_with_distances_layers(
+            self.h, dims, np.asarray(xf12, np.float32), min_dist_sq, max_dist_sq, int(null_outside), threshold, beta,
+            z0, z1, out) == 0
+        return out
+
+    def find_projection_dist_sq(self, pts, up=FLT_MAX, lo=0.0):
+        pts = np.ascontiguousarray(pts, np.float32)
+        out = np.empty(len(pts), np.float32)
+        lib().mrref_find_projection_dist_sq(self.h, pts, len(pts), up, lo, out)
+        return out
+
+
+def hardware_threads():
+    return lib().mrref_hardware_threads()
