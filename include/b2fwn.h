@@ -1,0 +1,149 @@
+/* b2fwn.h -- C ABI of libb2fwn.so: the B200-native (sm_100a) implementation of MeshLib's
+ * mesh -> signed-distance-volume hot path (fast winding number + closest-point distance + marching cubes).
+ *
+ * The reference has NO C/FFI boundary for this path: the plug-in point is the C++ virtual interface
+ * MR::IFastWindingNumber / MR::IFastWindingNumberByParts (source/MRMesh/MRFastWindingNumber.h:11-45, 74-107),
+ * whose GPU implementation is MR::Cuda::FastWindingNumber (source/MRCuda/MRCudaFastWindingNumber.h:17-38).
+ * Every entry point below states the reference method it replaces.  The C++ adapter that derives from the
+ * reference interface and forwards to these calls is meshlib_b200/host/b2fwn_meshlib_adapter.hpp
+ * (see INTEGRATION.md).
+ *
+ * Conventions
+ *  - plain pointers and sizes only; every call returns B2FWN_OK (0) or an error code; the message of the
+ *    last error of the calling thread is b2fwn_last_error().  CUDA failures read "NVIDIA GPU error: <text>"
+ *    (reference: source/MRCuda/MRCudaBasic.cpp:109-112); cancellation reads "Operation was canceled"
+ *    (reference: source/MRMesh/MRExpected.h:42-51).
+ *  - "host" calls take host pointers and copy; "_device" calls take device pointers of the handle's GPU
+ *    and only enqueue + synchronise the handle's stream.
+ *  - grid linearisation id = x + dx*(y + dy*z) (source/MRMesh/MRVolumeIndexer.h:132-140); the query point of
+ *    voxel (x,y,z) is A*(x,y,z)+b with xf = {A row-major (9), b (3)} (source/MRMesh/MRAffineXf.h:46).
+ *  - there is no CPU fallback: without a CUDA device b2fwn_create fails.
+ */
+#ifndef B2FWN_H
+#define B2FWN_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2FWN_OK 0
+#define B2FWN_ERR_CUDA 1
+#define B2FWN_ERR_CANCELED 2
+#define B2FWN_ERR_INVALID 3
+
+typedef struct b2fwn_ctx* b2fwn_handle;
+
+/* progress callback: value in [0,1]; return 0 to cancel (MR::ProgressCallback, source/MRMesh/MRProgressCallback.h:14) */
+typedef int ( *b2fwn_progress )( float progress, void* user );
+
+/* by-parts consumer: data = dims[0]*dims[1]*dims[2] floats (host), z_offset = first layer of the part;
+ * return 0 to continue, non-zero to abort (GridByPartsFunc, source/MRMesh/MRFastWindingNumber.h:88) */
+typedef int ( *b2fwn_part_cb )( const float* data, const int32_t dims[3], int32_t z_offset, void* user );
+
+typedef struct b2fwn_config
+{
+    int32_t device;        /* CUDA device ordinal; reference always uses 0 (MRCudaFastWindingNumber.cpp:48) */
+    int32_t reserved[7];
+} b2fwn_config;
+
+/* mirrors MR::DistanceToMeshOptions (source/MRMesh/MRDistanceToMeshOptions.h:10-33) */
+typedef struct b2fwn_dist_options
+{
+    float min_dist_sq;            /* default 0 */
+    float max_dist_sq;            /* default FLT_MAX */
+    int32_t null_outside_min_max; /* default 1 */
+    float winding_number_threshold; /* default 0.5 */
+    float winding_number_beta;      /* default 2 */
+} b2fwn_dist_options;
+
+typedef struct b2fwn_stats
+{
+    double tree_build_ms;     /* device AABB tree + dipoles, last build */
+    double last_kernel_ms;    /* device time of the last traversal launch(es), CUDA events */
+    uint64_t num_nodes;
+    uint64_t num_leaves;
+    uint64_t kernel_launches; /* launches of our __global__ kernels since create */
+    uint64_t reserved[3];
+} b2fwn_stats;
+
+const char* b2fwn_last_error( void );
+int b2fwn_device_count( void );
+
+/* replaces MR::Cuda::FastWindingNumber::FastWindingNumber(const Mesh&) + prepareData_
+ * (source/MRCuda/MRCudaFastWindingNumber.cpp:42-85): uploads points (nVerts*3 floats) and the triangulation
+ * (nFaces*3 int32, any negative id = deleted face, as MeshTopology::getTriangulation yields), then builds the
+ * AABB tree (reference CPU: source/MRMesh/MRAABBTree.cpp:31-60, MRAABBTreeMaker.hpp:51-171) and the dipoles
+ * (source/MRMesh/MRDipole.cpp:23-71) ON THE DEVICE.  cfg may be NULL. */
+int b2fwn_create( const float* points_xyz, size_t n_verts, const int32_t* tris_abc, size_t n_faces,
+                  const b2fwn_config* cfg, b2fwn_handle* out );
+void b2fwn_destroy( b2fwn_handle h );
+
+/* IFastWindingNumber::calcFromVector (MRFastWindingNumber.h:26; CPU MRFastWindingNumber.cpp:28-38;
+ * GPU MRCudaFastWindingNumber.cpp:87-127).  skip_face < 0 = skip nothing. */
+int b2fwn_calc_from_vector( b2fwn_handle h, const float* pts_xyz, size_t n, float beta, int32_t skip_face,
+                            float* out_w, b2fwn_progress cb, void* user );
+int b2fwn_calc_from_vector_device( b2fwn_handle h, const float* d_pts_xyz, size_t n, float beta, int32_t skip_face,
+                                   float* d_out_w );
+
+/* IFastWindingNumber::calcSelfIntersections (MRFastWindingNumber.h:31; CPU .cpp:40-52; GPU
+ * MRCudaFastWindingNumber.cpp:129-173).  out_bits: ceil(n_faces/64) words, bit f set iff w<0 || w>1. */
+int b2fwn_calc_self_intersections( b2fwn_handle h, float beta, uint64_t* out_bits, b2fwn_progress cb, void* user );
+int b2fwn_calc_self_intersections_device( b2fwn_handle h, float beta, uint64_t* d_out_bits, float* d_out_w_or_null );
+
+/* IFastWindingNumber::calcFromGrid (MRFastWindingNumber.h:38; CPU .cpp:54-67; GPU .cpp:175-228) */
+int b2fwn_calc_from_grid( b2fwn_handle h, const int32_t dims[3], const float xf[12], float beta, float* out,
+                          b2fwn_progress cb, void* user );
+int b2fwn_calc_from_grid_device( b2fwn_handle h, const int32_t dims[3], const float xf[12], float beta,
+                                 int32_t z_begin, int32_t z_end, float* d_out );
+
+/* IFastWindingNumber::calcFromGridWithDistances (MRFastWindingNumber.h:44; CPU .cpp:69-94; GPU .cpp:230-283).
+ * The _device form computes layers [z_begin, z_end) of the dims grid into d_out (first value = voxel
+ * (0,0,z_begin)): the z-slab of one rank in the multi-GPU run. */
+int b2fwn_calc_from_grid_with_distances( b2fwn_handle h, const int32_t dims[3], const float xf[12],
+                                         const b2fwn_dist_options* opt, float* out, b2fwn_progress cb, void* user );
+int b2fwn_calc_from_grid_with_distances_device( b2fwn_handle h, const int32_t dims[3], const float xf[12],
+                                                const b2fwn_dist_options* opt, int32_t z_begin, int32_t z_end,
+                                                float* d_out );
+
+/* IFastWindingNumberByParts::calcFromGridByParts / calcFromGridWithDistancesByParts
+ * (MRFastWindingNumber.h:96-106; GPU MRCudaFastWindingNumber.cpp:285-429).  Parts are whole z-layers, delivered
+ * strictly in increasing z on the calling thread, consecutive parts overlapping by layer_overlap layers
+ * (chunk maths: source/MRMesh/MRChunkIterator.cpp:25-49).  max_layers_per_part <= 0 chooses by free memory. */
+int b2fwn_calc_from_grid_by_parts( b2fwn_handle h, const int32_t dims[3], const float xf[12], float beta,
+                                   int32_t layer_overlap, int32_t max_layers_per_part, b2fwn_part_cb part, void* part_user,
+                                   b2fwn_progress cb, void* user );
+int b2fwn_calc_from_grid_with_distances_by_parts( b2fwn_handle h, const int32_t dims[3], const float xf[12],
+                                                  const b2fwn_dist_options* opt, int32_t layer_overlap,
+                                                  int32_t max_layers_per_part, b2fwn_part_cb part, void* part_user,
+                                                  b2fwn_progress cb, void* user );
+
+/* debug / parity: download the device-built tree in the reference's layouts:
+ * nodes = AABBTreeNode (32 B: box.min xyz, box.max xyz, l, r; source/MRMesh/MRAABBTreeNode.h:29-45),
+ * dipoles = Dipole (32 B: pos xyz, area, dirArea xyz, rr; source/MRMesh/MRDipole.h:10-30). */
+int b2fwn_get_tree( b2fwn_handle h, void* out_nodes_32B, void* out_dipoles_32B, size_t capacity_nodes, size_t* n_nodes );
+
+int b2fwn_get_stats( b2fwn_handle h, b2fwn_stats* out );
+
+/* marching cubes over a dense float volume (replaces MR::marchingCubes(SimpleVolume) =
+ * VolumeMesher::run, source/MRVoxels/MRMarchingCubes.cpp:382-398, 548-662, 812-1102).
+ * Two-call protocol: b2fwn_marching_cubes(...) runs on the device and returns counts; then
+ * b2fwn_marching_cubes_fetch copies vertices (n_verts*3 floats) and triangles (n_tris*3 int32). */
+typedef struct b2fwn_mc_params
+{
+    float origin[3];
+    float voxel_size[3];
+    float iso;
+    int32_t less_inside;   /* MarchingCubesParams::lessInside (MRMarchingCubes.h:33) */
+    int32_t reserved[4];
+} b2fwn_mc_params;
+int b2fwn_marching_cubes( b2fwn_handle h, const float* volume, int32_t volume_on_device, const int32_t dims[3],
+                          const b2fwn_mc_params* p, uint64_t* n_verts, uint64_t* n_tris );
+int b2fwn_marching_cubes_fetch( b2fwn_handle h, float* out_verts_xyz, int32_t* out_tris_abc );
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2FWN_H */

@@ -1,0 +1,271 @@
+"""meshlib_b200.api -- ctypes binding of libb2fwn.so (include/b2fwn.h) with the reference's operator names.
+
+`FastWindingNumber` mirrors MR::IFastWindingNumber / MR::IFastWindingNumberByParts
+(/root/reference/source/MRMesh/MRFastWindingNumber.h:11-45, 74-107) and MR::Cuda::FastWindingNumber
+(source/MRCuda/MRCudaFastWindingNumber.h:17-38): same method names (snake_case), argument meaning, output
+conventions and error strings.  It is a binding, not an implementation: every method is one C-ABI call, and the
+module raises at import-of-library time if the CUDA library is missing (there is no CPU fallback).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb2fwn.so")
+FLT_MAX = float(np.finfo(np.float32).max)
+
+_lib = None
+
+PROGRESS_CB = C.CFUNCTYPE(C.c_int, C.c_float, C.c_void_p)
+PART_CB = C.CFUNCTYPE(C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_int32), C.c_int32, C.c_void_p)
+
+
+class B2Error(RuntimeError):
+    """the C ABI returned a non-zero status; str(e) is b2fwn_last_error() (reference: Expected<void>'s error string)"""
+
+    def __init__(self, code, msg):
+        super().__init__(msg)
+        self.code = code
+
+
+class Config(C.Structure):
+    _fields_ = [("device", C.c_int32), ("reserved", C.c_int32 * 7)]
+
+
+class DistOptions(C.Structure):
+    """MR::DistanceToMeshOptions (source/MRMesh/MRDistanceToMeshOptions.h:10-33)"""
+    _fields_ = [("min_dist_sq", C.c_float), ("max_dist_sq", C.c_float), ("null_outside_min_max", C.c_int32),
+                ("winding_number_threshold", C.c_float), ("winding_number_beta", C.c_float)]
+
+    def __init__(self, min_dist_sq=0.0, max_dist_sq=FLT_MAX, null_outside_min_max=True, winding_number_threshold=0.5,
+                 winding_number_beta=2.0):
+        super().__init__(min_dist_sq, max_dist_sq, int(null_outside_min_max), winding_number_threshold,
+                         winding_number_beta)
+
+
+class Stats(C.Structure):
+    _fields_ = [("tree_build_ms", C.c_double), ("last_kernel_ms", C.c_double), ("num_nodes", C.c_uint64),
+                ("num_leaves", C.c_uint64), ("kernel_launches", C.c_uint64), ("reserved", C.c_uint64 * 3)]
+
+
+class McParams(C.Structure):
+    _fields_ = [("origin", C.c_float * 3), ("voxel_size", C.c_float * 3), ("iso", C.c_float),
+                ("less_inside", C.c_int32), ("reserved", C.c_int32 * 4)]
+
+
+EXPORTS = [
+    "b2fwn_last_error", "b2fwn_device_count", "b2fwn_create", "b2fwn_destroy", "b2fwn_calc_from_vector",
+    "b2fwn_calc_from_vector_device", "b2fwn_calc_self_intersections", "b2fwn_calc_self_intersections_device",
+    "b2fwn_calc_from_grid", "b2fwn_calc_from_grid_device", "b2fwn_calc_from_grid_with_distances",
+    "b2fwn_calc_from_grid_with_distances_device", "b2fwn_calc_from_grid_by_parts",
+    "b2fwn_calc_from_grid_with_distances_by_parts", "b2fwn_get_tree", "b2fwn_get_stats", "b2fwn_marching_cubes",
+    "b2fwn_marching_cubes_fetch",
+]
+
+
+def load_library():
+    """loads libb2fwn.so; raises (never falls back) when it is missing"""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(there is no CPU fallback)")
+    L = C.CDLL(LIB_PATH)
+    vp, f32p, i32p, u64p = C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int32), C.POINTER(C.c_uint64)
+    L.b2fwn_last_error.restype = C.c_char_p
+    L.b2fwn_device_count.restype = C.c_int
+    L.b2fwn_create.argtypes = [vp, C.c_size_t, vp, C.c_size_t, C.POINTER(Config), C.POINTER(vp)]
+    L.b2fwn_destroy.argtypes = [vp]
+    L.b2fwn_destroy.restype = None
+    L.b2fwn_calc_from_vector.argtypes = [vp, vp, C.c_size_t, C.c_float, C.c_int32, vp, PROGRESS_CB, vp]
+    L.b2fwn_calc_from_vector_device.argtypes = [vp, vp, C.c_size_t, C.c_float, C.c_int32, vp]
+    L.b2fwn_calc_self_intersections.argtypes = [vp, C.c_float, vp, PROGRESS_CB, vp]
+    L.b2fwn_calc_self_intersections_device.argtypes = [vp, C.c_float, vp, vp]
+    L.b2fwn_calc_from_grid.argtypes = [vp, i32p, f32p, C.c_float, vp, PROGRESS_CB, vp]
+    L.b2fwn_calc_from_grid_device.argtypes = [vp, i32p, f32p, C.c_float, C.c_int32, C.c_int32, vp]
+    L.b2fwn_calc_from_grid_with_distances.argtypes = [vp, i32p, f32p, C.POINTER(DistOptions), vp, PROGRESS_CB, vp]
+    L.b2fwn_calc_from_grid_with_distances_device.argtypes = [vp, i32p, f32p, C.POINTER(DistOptions), C.c_int32,
+                                                             C.c_int32, vp]
+    L.b2fwn_calc_from_grid_by_parts.argtypes = [vp, i32p, f32p, C.c_float, C.c_int32, C.c_int32, PART_CB, vp,
+                                                PROGRESS_CB, vp]
+    L.b2fwn_calc_from_grid_with_distances_by_parts.argtypes = [vp, i32p, f32p, C.POINTER(DistOptions), C.c_int32,
+                                                               C.c_int32, PART_CB, vp, PROGRESS_CB, vp]
+    L.b2fwn_get_tree.argtypes = [vp, vp, vp, C.c_size_t, C.POINTER(C.c_size_t)]
+    L.b2fwn_get_stats.argtypes = [vp, C.POINTER(Stats)]
+    L.b2fwn_marching_cubes.argtypes = [vp, vp, C.c_int32, i32p, C.POINTER(McParams), u64p, u64p]
+    L.b2fwn_marching_cubes_fetch.argtypes = [vp, vp, vp]
+    _lib = L
+    return L
+
+
+def _check(rc):
+    if rc != 0:
+        raise B2Error(rc, load_library().b2fwn_last_error().decode())
+
+
+def _dims(dims):
+    return (C.c_int32 * 3)(*[int(d) for d in dims])
+
+
+def _xf(xf12):
+    a = np.asarray(xf12, np.float32).reshape(12)
+    return (C.c_float * 12)(*a.tolist())
+
+
+def _progress(cb):
+    if cb is None:
+        return C.cast(None, PROGRESS_CB)
+    return PROGRESS_CB(lambda v, _u: 1 if cb(v) else 0)
+
+
+def make_basis_xf(origin, voxel_size):
+    """gridToMeshXf of meshToDistanceVolume: scale(voxelSize), b = origin + 0.5*voxelSize (voxel centres;
+    source/MRVoxels/MRMeshToDistanceVolume.cpp:55)"""
+    o = np.asarray(origin, np.float32)
+    v = np.asarray(voxel_size, np.float32) * np.ones(3, np.float32)
+    b = o + np.float32(0.5) * v
+    return np.array([v[0], 0, 0, 0, v[1], 0, 0, 0, v[2], b[0], b[1], b[2]], np.float32)
+
+
+NODE_DTYPE = np.dtype([("bmin", np.float32, 3), ("bmax", np.float32, 3), ("l", np.int32), ("r", np.int32)])
+DIPOLE_DTYPE = np.dtype([("pos", np.float32, 3), ("area", np.float32), ("dirArea", np.float32, 3), ("rr", np.float32)])
+
+
+class FastWindingNumber:
+    """B200 implementation of MR::IFastWindingNumber + IFastWindingNumberByParts.
+
+    points: (V,3) float32; tris: (F,3) int32 in MeshTopology::getTriangulation() order (negative ids = deleted face).
+    The mesh is uploaded and the AABB tree + dipoles are built on the device in the constructor (the reference does it
+    lazily at the first call, MRCudaFastWindingNumber.cpp:46-85)."""
+
+    def __init__(self, points, tris, device=0):
+        self._h = None
+        L = load_library()
+        self.points = np.ascontiguousarray(points, np.float32).reshape(-1, 3)
+        self.tris = np.ascontiguousarray(tris, np.int32).reshape(-1, 3)
+        cfg = Config(device=device)
+        h = C.c_void_p()
+        _check(L.b2fwn_create(self.points.ctypes.data, len(self.points), self.tris.ctypes.data, len(self.tris),
+                              C.byref(cfg), C.byref(h)))
+        self._h = h
+        self.device = device
+
+    def close(self):
+        if self._h is not None and _lib is not None:
+            _lib.b2fwn_destroy(self._h)
+        self._h = None
+
+    def __del__(self):
+        self.close()
+
+    # ---- IFastWindingNumber ----
+    def calc_from_vector(self, points, beta=2.0, skip_face=-1, cb=None, out=None):
+        pts = np.ascontiguousarray(points, np.float32).reshape(-1, 3)
+        res = out if out is not None else np.empty(len(pts), np.float32)
+        _check(_lib.b2fwn_calc_from_vector(self._h, pts.ctypes.data, len(pts), beta, skip_face, res.ctypes.data,
+                                           _progress(cb), None))
+        return res
+
+    def calc_self_intersections(self, beta=2.0, cb=None):
+        """returns the FaceBitSet as uint64 words (bit f set iff w<0 or w>1)"""
+        res = np.zeros((len(self.tris) + 63) // 64, np.uint64)
+        _check(_lib.b2fwn_calc_self_intersections(self._h, beta, res.ctypes.data, _progress(cb), None))
+        return res
+
+    def calc_from_grid(self, dims, grid_to_mesh_xf, beta=2.0, cb=None, out=None):
+        n = int(np.prod(np.asarray(dims, np.int64)))
+        res = out if out is not None else np.empty(n, np.float32)
+        _check(_lib.b2fwn_calc_from_grid(self._h, _dims(dims), _xf(grid_to_mesh_xf), beta, res.ctypes.data,
+                                         _progress(cb), None))
+        return res
+
+    def calc_from_grid_with_distances(self, dims, grid_to_mesh_xf, options=None, cb=None, out=None):
+        options = options or DistOptions()
+        n = int(np.prod(np.asarray(dims, np.int64)))
+        res = out if out is not None else np.empty(n, np.float32)
+        _check(_lib.b2fwn_calc_from_grid_with_distances(self._h, _dims(dims), _xf(grid_to_mesh_xf), C.byref(options),
+                                                        res.ctypes.data, _progress(cb), None))
+        return res
+
+    # ---- IFastWindingNumberByParts ----
+    def _part_cb(self, res_func):
+        def tramp(data, dims, z_offset, _u):
+            d = (dims[0], dims[1], dims[2])
+            arr = np.ctypeslib.as_array(data, shape=(d[0] * d[1] * d[2],))
+            try:
+                ok = res_func(arr, d, z_offset)
+            except Exception:  # exceptions must not cross the C boundary
+                return 1
+            return 0 if (ok is None or ok) else 1
+        return PART_CB(tramp)
+
+    def calc_from_grid_by_parts(self, res_func, dims, grid_to_mesh_xf, beta=2.0, layer_overlap=0, cb=None,
+                                max_layers_per_part=0):
+        _check(_lib.b2fwn_calc_from_grid_by_parts(self._h, _dims(dims), _xf(grid_to_mesh_xf), beta, layer_overlap,
+                                                  max_layers_per_part, self._part_cb(res_func), None, _progress(cb),
+                                                  None))
+
+    def calc_from_grid_with_distances_by_parts(self, res_func, dims, grid_to_mesh_xf, options=None, layer_overlap=0,
+                                               cb=None, max_layers_per_part=0):
+        options = options or DistOptions()
+        _check(_lib.b2fwn_calc_from_grid_with_distances_by_parts(
+            self._h, _dims(dims), _xf(grid_to_mesh_xf), C.byref(options), layer_overlap, max_layers_per_part,
+            self._part_cb(res_func), None, _progress(cb), None))
+
+    # ---- device-pointer forms (multi-GPU slabs, benches) ----
+    def calc_from_vector_device(self, d_points_ptr, n, d_out_ptr, beta=2.0, skip_face=-1):
+        _check(_lib.b2fwn_calc_from_vector_device(self._h, d_points_ptr, n, beta, skip_face, d_out_ptr))
+
+    def calc_self_intersections_device(self, d_bits_ptr, d_w_ptr=None, beta=2.0):
+        _check(_lib.b2fwn_calc_self_intersections_device(self._h, beta, d_bits_ptr, d_w_ptr))
+
+    def calc_from_grid_device(self, dims, grid_to_mesh_xf, d_out_ptr, beta=2.0, z_begin=0, z_end=None):
+        z_end = dims[2] if z_end is None else z_end
+        _check(_lib.b2fwn_calc_from_grid_device(self._h, _dims(dims), _xf(grid_to_mesh_xf), beta, z_begin, z_end,
+                                                d_out_ptr))
+
+    def calc_from_grid_with_distances_device(self, dims, grid_to_mesh_xf, d_out_ptr, options=None, z_begin=0,
+                                             z_end=None):
+        options = options or DistOptions()
+        z_end = dims[2] if z_end is None else z_end
+        _check(_lib.b2fwn_calc_from_grid_with_distances_device(self._h, _dims(dims), _xf(grid_to_mesh_xf),
+                                                               C.byref(options), z_begin, z_end, d_out_ptr))
+
+    # ---- parity / diagnostics ----
+    def get_tree(self):
+        n = C.c_size_t()
+        _check(_lib.b2fwn_get_tree(self._h, None, None, 0, C.byref(n)))
+        nodes = np.empty(n.value, NODE_DTYPE)
+        dip = np.empty(n.value, DIPOLE_DTYPE)
+        if n.value:
+            _check(_lib.b2fwn_get_tree(self._h, nodes.ctypes.data, dip.ctypes.data, n.value, C.byref(n)))
+        return nodes, dip
+
+    def stats(self):
+        s = Stats()
+        _check(_lib.b2fwn_get_stats(self._h, C.byref(s)))
+        return s
+
+    # ---- marching cubes ----
+    def marching_cubes(self, volume, dims, origin, voxel_size, iso, less_inside=False, on_device=False):
+        """volume: host float32 array (or a device pointer when on_device); returns (verts (n,3) f32, tris (m,3) i32)"""
+        p = McParams()
+        p.origin[:] = [float(x) for x in origin]
+        vs = np.asarray(voxel_size, np.float32) * np.ones(3, np.float32)
+        p.voxel_size[:] = [float(x) for x in vs]
+        p.iso = iso
+        p.less_inside = int(less_inside)
+        nv, nt = C.c_uint64(), C.c_uint64()
+        if on_device:
+            ptr = volume
+        else:
+            volume = np.ascontiguousarray(volume, np.float32)
+            ptr = volume.ctypes.data
+        _check(_lib.b2fwn_marching_cubes(self._h, ptr, int(on_device), _dims(dims), C.byref(p), C.byref(nv),
+                                         C.byref(nt)))
+        verts = np.empty((nv.value, 3), np.float32)
+        tris = np.empty((nt.value, 3), np.int32)
+        _check(_lib.b2fwn_marching_cubes_fetch(self._h, verts.ctypes.data, tris.ctypes.data))
+        return verts, tris

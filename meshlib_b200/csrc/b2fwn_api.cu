@@ -1,0 +1,495 @@
+// b2fwn_api.cu -- the C ABI of include/b2fwn.h: handle, memory, streams, chunking / by-parts pipelines.
+// Host-side orchestration only; all arithmetic lives in b2fwn_tree.cu / b2fwn_kernels.cu / b2fwn_mc.cu.
+// There is deliberately no CPU implementation behind any entry point.
+#include "b2fwn_internal.h"
+#include <algorithm>
+#include <cstring>
+#include <vector>
+
+namespace b2
+{
+
+static thread_local std::string g_lastError;
+
+void setError( const std::string& msg ) { g_lastError = msg; }
+
+int cudaFail( cudaError_t e, const char* where )
+{
+    // reference wording: source/MRCuda/MRCudaBasic.cpp:109-112
+    g_lastError = std::string( "NVIDIA GPU error: " ) + cudaGetErrorString( e ) + " [" + where + "]";
+    (void)cudaGetLastError();
+    return B2FWN_ERR_CUDA;
+}
+
+} // namespace b2
+
+using namespace b2;
+
+struct b2fwn_ctx
+{
+    int device = 0;
+    cudaStream_t stream = nullptr;     // compute
+    cudaStream_t copyStream = nullptr; // D2H of finished parts
+    cudaEvent_t evA = nullptr, evB = nullptr;
+    DeviceTree tree;
+    b2fwn_stats stats{};
+    McResult mc;
+    // scratch for the host-pointer entry points
+    float* dScratch[2] = { nullptr, nullptr };
+    size_t scratchFloats[2] = { 0, 0 };
+    float* hPinned[2] = { nullptr, nullptr };
+    size_t pinnedFloats[2] = { 0, 0 };
+    cudaEvent_t partDone[2] = { nullptr, nullptr };
+    cudaEvent_t computeDone[2] = { nullptr, nullptr };
+};
+
+namespace
+{
+
+const char* kCanceled = "Operation was canceled"; // source/MRMesh/MRExpected.h:42-51
+
+int ensureScratch( b2fwn_ctx* h, int slot, size_t floats )
+{
+    if ( h->scratchFloats[slot] >= floats ) return B2FWN_OK;
+    if ( h->dScratch[slot] ) cudaFree( h->dScratch[slot] );
+    h->dScratch[slot] = nullptr; h->scratchFloats[slot] = 0;
+    B2_CUDA( cudaMalloc( &h->dScratch[slot], floats * sizeof( float ) ) );
+    h->scratchFloats[slot] = floats;
+    return B2FWN_OK;
+}
+
+int ensurePinned( b2fwn_ctx* h, int slot, size_t floats )
+{
+    if ( h->pinnedFloats[slot] >= floats ) return B2FWN_OK;
+    if ( h->hPinned[slot] ) cudaFreeHost( h->hPinned[slot] );
+    h->hPinned[slot] = nullptr; h->pinnedFloats[slot] = 0;
+    B2_CUDA( cudaMallocHost( &h->hPinned[slot], floats * sizeof( float ) ) );
+    h->pinnedFloats[slot] = floats;
+    return B2FWN_OK;
+}
+
+bool report( b2fwn_progress cb, void* user, float v )
+{
+    return !cb || cb( v, user ) != 0;
+}
+
+int canceled()
+{
+    setError( kCanceled );
+    return B2FWN_ERR_CANCELED;
+}
+
+GridXf toXf( const float xf[12] )
+{
+    GridXf g;
+    for ( int i = 0; i < 9; ++i ) g.A[i] = xf[i];
+    for ( int i = 0; i < 3; ++i ) g.b[i] = xf[9 + i];
+    return g;
+}
+
+struct KernelTimer
+{
+    b2fwn_ctx* h;
+    explicit KernelTimer( b2fwn_ctx* c ) : h( c ) { cudaEventRecord( h->evA, h->stream ); }
+    void stop()
+    {
+        cudaEventRecord( h->evB, h->stream );
+        if ( cudaEventSynchronize( h->evB ) == cudaSuccess )
+        {
+            float ms = 0;
+            cudaEventElapsedTime( &ms, h->evA, h->evB );
+            h->stats.last_kernel_ms = ms;
+        }
+    }
+};
+
+// layers per chunk for the host-pointer grid calls: whole layers, about 32 Mi voxels (128 MiB) per chunk so that
+// the D2H of chunk k overlaps the kernel of chunk k+1 and cancellation is polled a few times per second
+int defaultLayersPerPart( const int32_t dims[3], int overlap )
+{
+    const size_t layer = (size_t)dims[0] * dims[1];
+    if ( layer == 0 ) return std::max( dims[2], 1 );
+    size_t layers = ( (size_t)32 << 20 ) / layer;
+    layers = std::max<size_t>( layers, (size_t)overlap + 1 );
+    layers = std::max<size_t>( layers, 2 );
+    return (int)std::min<size_t>( layers, (size_t)std::max( dims[2], 1 ) );
+}
+
+// Generic z-chunked pipeline.  launch(zBegin, zEnd, dOut) enqueues the kernel on h->stream.
+// If part != nullptr the chunks (with overlap) are handed to the consumer from pinned staging buffers, in z order, on
+// the calling thread, while the next chunk is computed (the reference's cudaPipeline, source/MRCuda/MRCudaPipeline.hpp:9-48).
+// Otherwise chunks are copied straight into hostOut.
+template <typename Launch>
+int runChunked( b2fwn_ctx* h, const int32_t dims[3], int overlap, int layersPerPart, float* hostOut, b2fwn_part_cb part,
+                void* partUser, b2fwn_progress cb, void* user, Launch launch )
+{
+    const int nz = dims[2];
+    const size_t layer = (size_t)dims[0] * dims[1];
+    if ( nz == 0 || layer == 0 ) return B2FWN_OK;
+    if ( overlap < 0 ) { setError( "negative layer overlap" ); return B2FWN_ERR_INVALID; }
+    if ( layersPerPart <= 0 ) layersPerPart = defaultLayersPerPart( dims, overlap );
+    layersPerPart = std::min( layersPerPart, nz );
+    if ( layersPerPart <= overlap ) { setError( "part must be larger than the overlap" ); return B2FWN_ERR_INVALID; }
+    // splitByChunks (source/MRMesh/MRChunkIterator.cpp:25-49): offset_k = k*(chunk-overlap), last chunk shorter
+    const int step = layersPerPart - overlap;
+    const int count = nz <= overlap ? 1 : ( nz - overlap + step - 1 ) / step;
+    if ( !report( cb, user, 0.f ) ) return canceled();
+    for ( int s = 0; s < 2; ++s )
+    {
+        if ( int e = ensureScratch( h, s, (size_t)layersPerPart * layer ) ) return e;
+        if ( part ) if ( int e = ensurePinned( h, s, (size_t)layersPerPart * layer ) ) return e;
+    }
+    double kernelMs = 0;
+    auto finishPart = [&]( int k ) -> int
+    {
+        const int s = k & 1;
+        B2_CUDA( cudaEventSynchronize( h->partDone[s] ) );
+        if ( part )
+        {
+            const int z0 = k * step, z1 = std::min( nz, z0 + layersPerPart );
+            const int32_t pd[3] = { dims[0], dims[1], z1 - z0 };
+            if ( part( h->hPinned[s], pd, z0, partUser ) != 0 )
+            {
+                setError( "by-parts consumer failed" );
+                return B2FWN_ERR_CANCELED;
+            }
+        }
+        return B2FWN_OK;
+    };
+    for ( int k = 0; k < count; ++k )
+    {
+        const int s = k & 1;
+        const int z0 = k * step, z1 = std::min( nz, z0 + layersPerPart );
+        // slot s is free again once the copy of chunk k-2 finished (finishPart(k-2) waited for it)
+        cudaEventRecord( h->evA, h->stream );
+        if ( int e = launch( z0, z1, h->dScratch[s] ) ) return e;
+        cudaEventRecord( h->evB, h->stream );
+        B2_CUDA( cudaEventRecord( h->computeDone[s], h->stream ) );
+        B2_CUDA( cudaStreamWaitEvent( h->copyStream, h->computeDone[s], 0 ) );
+        float* dst = part ? h->hPinned[s] : hostOut + (size_t)z0 * layer;
+        B2_CUDA( cudaMemcpyAsync( dst, h->dScratch[s], (size_t)( z1 - z0 ) * layer * sizeof( float ), cudaMemcpyDeviceToHost, h->copyStream ) );
+        B2_CUDA( cudaEventRecord( h->partDone[s], h->copyStream ) );
+        if ( k > 0 )
+        {
+            if ( int e = finishPart( k - 1 ) ) { cudaDeviceSynchronize(); return e; }
+            if ( !report( cb, user, float( k ) / float( count ) ) ) { cudaDeviceSynchronize(); return canceled(); }
+        }
+        // the next launch into slot (k+1)&1 must not start before its previous copy (chunk k-1) is done: ensured by
+        // finishPart(k-1) above
+        if ( cudaEventSynchronize( h->evB ) == cudaSuccess )
+        {
+            float ms = 0;
+            if ( cudaEventElapsedTime( &ms, h->evA, h->evB ) == cudaSuccess ) kernelMs += ms;
+        }
+    }
+    if ( int e = finishPart( count - 1 ) ) return e;
+    B2_CUDA( cudaStreamSynchronize( h->stream ) );
+    h->stats.last_kernel_ms = kernelMs;
+    if ( !report( cb, user, 1.f ) ) return canceled();
+    return B2FWN_OK;
+}
+
+} // anonymous namespace
+
+#pragma GCC visibility push( default )
+extern "C"
+{
+
+const char* b2fwn_last_error( void ) { return g_lastError.c_str(); }
+
+int b2fwn_device_count( void )
+{
+    int n = 0;
+    if ( cudaGetDeviceCount( &n ) != cudaSuccess ) { (void)cudaGetLastError(); return 0; }
+    return n;
+}
+
+int b2fwn_create( const float* points, size_t nVerts, const int32_t* tris, size_t nFaces, const b2fwn_config* cfg,
+                  b2fwn_handle* out )
+{
+    if ( !out || ( nVerts && !points ) || ( nFaces && !tris ) ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    *out = nullptr;
+    const int dev = cfg ? cfg->device : 0;
+    B2_CUDA( cudaSetDevice( dev ) );
+    b2fwn_ctx* h = new b2fwn_ctx;
+    h->device = dev;
+    auto fail = [&]( int e ) { b2fwn_destroy( h ); return e; };
+#define B2_TRY( expr ) do { cudaError_t _e = ( expr ); if ( _e != cudaSuccess ) return fail( cudaFail( _e, #expr ) ); } while ( 0 )
+    B2_TRY( cudaStreamCreateWithFlags( &h->stream, cudaStreamNonBlocking ) );
+    B2_TRY( cudaStreamCreateWithFlags( &h->copyStream, cudaStreamNonBlocking ) );
+    B2_TRY( cudaEventCreate( &h->evA ) );
+    B2_TRY( cudaEventCreate( &h->evB ) );
+    for ( int s = 0; s < 2; ++s )
+    {
+        B2_TRY( cudaEventCreateWithFlags( &h->partDone[s], cudaEventDisableTiming ) );
+        B2_TRY( cudaEventCreateWithFlags( &h->computeDone[s], cudaEventDisableTiming ) );
+    }
+    h->tree.numVerts = nVerts; h->tree.numFaces = nFaces;
+    if ( nVerts )
+    {
+        B2_TRY( cudaMalloc( &h->tree.points, nVerts * 3 * sizeof( float ) ) );
+        B2_TRY( cudaMemcpyAsync( h->tree.points, points, nVerts * 3 * sizeof( float ), cudaMemcpyHostToDevice, h->stream ) );
+    }
+    if ( nFaces )
+    {
+        B2_TRY( cudaMalloc( &h->tree.tris, nFaces * 3 * sizeof( int32_t ) ) );
+        B2_TRY( cudaMemcpyAsync( h->tree.tris, tris, nFaces * 3 * sizeof( int32_t ), cudaMemcpyHostToDevice, h->stream ) );
+    }
+#undef B2_TRY
+    cudaEventRecord( h->evA, h->stream );
+    if ( int e = buildTree( h->tree, h->stream, &h->stats.kernel_launches ) ) return fail( e );
+    cudaEventRecord( h->evB, h->stream );
+    cudaEventSynchronize( h->evB );
+    float ms = 0;
+    cudaEventElapsedTime( &ms, h->evA, h->evB );
+    h->stats.tree_build_ms = ms;
+    h->stats.num_nodes = h->tree.numNodes;
+    h->stats.num_leaves = h->tree.numLeaves;
+    *out = h;
+    return B2FWN_OK;
+}
+
+void b2fwn_destroy( b2fwn_handle h )
+{
+    if ( !h ) return;
+    cudaSetDevice( h->device );
+    cudaDeviceSynchronize();
+    freeTree( h->tree );
+    freeMc( h->mc );
+    for ( int s = 0; s < 2; ++s )
+    {
+        if ( h->dScratch[s] ) cudaFree( h->dScratch[s] );
+        if ( h->hPinned[s] ) cudaFreeHost( h->hPinned[s] );
+        if ( h->partDone[s] ) cudaEventDestroy( h->partDone[s] );
+        if ( h->computeDone[s] ) cudaEventDestroy( h->computeDone[s] );
+    }
+    if ( h->evA ) cudaEventDestroy( h->evA );
+    if ( h->evB ) cudaEventDestroy( h->evB );
+    if ( h->stream ) cudaStreamDestroy( h->stream );
+    if ( h->copyStream ) cudaStreamDestroy( h->copyStream );
+    delete h;
+}
+
+int b2fwn_get_stats( b2fwn_handle h, b2fwn_stats* out )
+{
+    if ( !h || !out ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    *out = h->stats;
+    return B2FWN_OK;
+}
+
+int b2fwn_get_tree( b2fwn_handle h, void* outNodes, void* outDipoles, size_t capacity, size_t* nNodes )
+{
+    if ( !h ) { setError( "null handle" ); return B2FWN_ERR_INVALID; }
+    if ( nNodes ) *nNodes = h->tree.numNodes;
+    if ( capacity < h->tree.numNodes || h->tree.numNodes == 0 ) return B2FWN_OK;
+    B2_CUDA( cudaSetDevice( h->device ) );
+    if ( outNodes ) B2_CUDA( cudaMemcpy( outNodes, h->tree.refNodes, h->tree.numNodes * sizeof( RefNode ), cudaMemcpyDeviceToHost ) );
+    if ( outDipoles ) B2_CUDA( cudaMemcpy( outDipoles, h->tree.refDipoles, h->tree.numNodes * sizeof( RefDipole ), cudaMemcpyDeviceToHost ) );
+    return B2FWN_OK;
+}
+
+// ---- winding numbers of a point vector ------------------------------------------------------------------------------
+
+int b2fwn_calc_from_vector_device( b2fwn_handle h, const float* dPts, size_t n, float beta, int32_t skipFace, float* dOut )
+{
+    if ( !h || ( n && ( !dPts || !dOut ) ) ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    KernelTimer tm( h );
+    if ( int e = launchFwnVector( h->tree, dPts, n, beta, skipFace, dOut, h->stream, &h->stats.kernel_launches ) ) return e;
+    tm.stop();
+    B2_CUDA( cudaStreamSynchronize( h->stream ) );
+    return B2FWN_OK;
+}
+
+int b2fwn_calc_from_vector( b2fwn_handle h, const float* pts, size_t n, float beta, int32_t skipFace, float* out,
+                            b2fwn_progress cb, void* user )
+{
+    if ( !h || ( n && ( !pts || !out ) ) ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    if ( !report( cb, user, 0.f ) ) return canceled();
+    if ( n == 0 ) return B2FWN_OK;
+    // chunks of 4 Mi points: H2D of chunk k+1 and D2H of chunk k-1 overlap the kernel of chunk k
+    const size_t chunk = (size_t)4 << 20;
+    const size_t count = ( n + chunk - 1 ) / chunk;
+    for ( int s = 0; s < 2; ++s )
+        if ( int e = ensureScratch( h, s, std::min( n, chunk ) * 4 ) ) return e; // 3 floats in + 1 out per point
+    double kernelMs = 0;
+    for ( size_t k = 0; k < count; ++k )
+    {
+        const int s = (int)( k & 1 );
+        const size_t o = k * chunk, m = std::min( chunk, n - o );
+        float* dIn = h->dScratch[s];
+        float* dOut = h->dScratch[s] + 3 * std::min( n, chunk );
+        if ( k >= 2 ) B2_CUDA( cudaEventSynchronize( h->partDone[s] ) );
+        B2_CUDA( cudaMemcpyAsync( dIn, pts + 3 * o, m * 3 * sizeof( float ), cudaMemcpyHostToDevice, h->stream ) );
+        cudaEventRecord( h->evA, h->stream );
+        if ( int e = launchFwnVector( h->tree, dIn, m, beta, skipFace, dOut, h->stream, &h->stats.kernel_launches ) ) return e;
+        cudaEventRecord( h->evB, h->stream );
+        B2_CUDA( cudaEventRecord( h->computeDone[s], h->stream ) );
+        B2_CUDA( cudaStreamWaitEvent( h->copyStream, h->computeDone[s], 0 ) );
+        B2_CUDA( cudaMemcpyAsync( out + o, dOut, m * sizeof( float ), cudaMemcpyDeviceToHost, h->copyStream ) );
+        B2_CUDA( cudaEventRecord( h->partDone[s], h->copyStream ) );
+        if ( cb )
+        {
+            B2_CUDA( cudaEventSynchronize( h->evB ) );
+            if ( !report( cb, user, float( k + 1 ) / float( count ) ) ) { cudaDeviceSynchronize(); return canceled(); }
+        }
+        if ( cudaEventSynchronize( h->evB ) == cudaSuccess )
+        {
+            float ms = 0;
+            if ( cudaEventElapsedTime( &ms, h->evA, h->evB ) == cudaSuccess ) kernelMs += ms;
+        }
+    }
+    B2_CUDA( cudaStreamSynchronize( h->stream ) );
+    B2_CUDA( cudaStreamSynchronize( h->copyStream ) );
+    h->stats.last_kernel_ms = kernelMs;
+    return B2FWN_OK;
+}
+
+// ---- self-intersections ----------------------------------------------------------------------------------------------
+
+int b2fwn_calc_self_intersections_device( b2fwn_handle h, float beta, uint64_t* dBits, float* dW )
+{
+    if ( !h ) { setError( "null handle" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    KernelTimer tm( h );
+    if ( int e = launchFwnFaces( h->tree, beta, dW, dBits, h->stream, &h->stats.kernel_launches ) ) return e;
+    tm.stop();
+    B2_CUDA( cudaStreamSynchronize( h->stream ) );
+    return B2FWN_OK;
+}
+
+int b2fwn_calc_self_intersections( b2fwn_handle h, float beta, uint64_t* outBits, b2fwn_progress cb, void* user )
+{
+    if ( !h ) { setError( "null handle" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    if ( !report( cb, user, 0.f ) ) return canceled();
+    const size_t words = ( h->tree.numFaces + 63 ) / 64;
+    if ( words == 0 ) return B2FWN_OK;
+    if ( !outBits ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    if ( int e = ensureScratch( h, 0, words * 2 ) ) return e;
+    uint64_t* dBits = reinterpret_cast<uint64_t*>( h->dScratch[0] );
+    if ( int e = b2fwn_calc_self_intersections_device( h, beta, dBits, nullptr ) ) return e;
+    B2_CUDA( cudaMemcpy( outBits, dBits, words * sizeof( uint64_t ), cudaMemcpyDeviceToHost ) );
+    if ( !report( cb, user, 1.f ) ) return canceled();
+    return B2FWN_OK;
+}
+
+// ---- grids -------------------------------------------------------------------------------------------------------------
+
+int b2fwn_calc_from_grid_device( b2fwn_handle h, const int32_t dims[3], const float xf[12], float beta, int32_t zBegin,
+                                 int32_t zEnd, float* dOut )
+{
+    if ( !h || !dims || !xf ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    KernelTimer tm( h );
+    if ( int e = launchFwnGrid( h->tree, dims, toXf( xf ), beta, zBegin, zEnd, dOut, h->stream, &h->stats.kernel_launches ) ) return e;
+    tm.stop();
+    B2_CUDA( cudaStreamSynchronize( h->stream ) );
+    return B2FWN_OK;
+}
+
+int b2fwn_calc_from_grid_with_distances_device( b2fwn_handle h, const int32_t dims[3], const float xf[12],
+                                                const b2fwn_dist_options* opt, int32_t zBegin, int32_t zEnd, float* dOut )
+{
+    if ( !h || !dims || !xf || !opt ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    KernelTimer tm( h );
+    if ( int e = launchSdfGrid( h->tree, dims, toXf( xf ), *opt, zBegin, zEnd, dOut, h->stream, &h->stats.kernel_launches ) ) return e;
+    tm.stop();
+    B2_CUDA( cudaStreamSynchronize( h->stream ) );
+    return B2FWN_OK;
+}
+
+int b2fwn_calc_from_grid_by_parts( b2fwn_handle h, const int32_t dims[3], const float xf[12], float beta, int32_t overlap,
+                                   int32_t maxLayers, b2fwn_part_cb part, void* partUser, b2fwn_progress cb, void* user )
+{
+    if ( !h || !dims || !xf || !part ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    const GridXf g = toXf( xf );
+    return runChunked( h, dims, overlap, maxLayers, nullptr, part, partUser, cb, user, [&]( int z0, int z1, float* d )
+        { return launchFwnGrid( h->tree, dims, g, beta, z0, z1, d, h->stream, &h->stats.kernel_launches ); } );
+}
+
+int b2fwn_calc_from_grid_with_distances_by_parts( b2fwn_handle h, const int32_t dims[3], const float xf[12],
+                                                  const b2fwn_dist_options* opt, int32_t overlap, int32_t maxLayers,
+                                                  b2fwn_part_cb part, void* partUser, b2fwn_progress cb, void* user )
+{
+    if ( !h || !dims || !xf || !opt || !part ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    const GridXf g = toXf( xf );
+    const b2fwn_dist_options o = *opt;
+    return runChunked( h, dims, overlap, maxLayers, nullptr, part, partUser, cb, user, [&]( int z0, int z1, float* d )
+        { return launchSdfGrid( h->tree, dims, g, o, z0, z1, d, h->stream, &h->stats.kernel_launches ); } );
+}
+
+int b2fwn_calc_from_grid( b2fwn_handle h, const int32_t dims[3], const float xf[12], float beta, float* out,
+                          b2fwn_progress cb, void* user )
+{
+    if ( !h || !dims || !xf ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    if ( dims[0] < 0 || dims[1] < 0 || dims[2] < 0 ) { setError( "invalid grid dimensions" ); return B2FWN_ERR_INVALID; }
+    if ( (size_t)dims[0] * dims[1] * dims[2] && !out ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    const GridXf g = toXf( xf );
+    return runChunked( h, dims, 0, 0, out, nullptr, nullptr, cb, user, [&]( int z0, int z1, float* d )
+        { return launchFwnGrid( h->tree, dims, g, beta, z0, z1, d, h->stream, &h->stats.kernel_launches ); } );
+}
+
+int b2fwn_calc_from_grid_with_distances( b2fwn_handle h, const int32_t dims[3], const float xf[12],
+                                         const b2fwn_dist_options* opt, float* out, b2fwn_progress cb, void* user )
+{
+    if ( !h || !dims || !xf || !opt ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    if ( dims[0] < 0 || dims[1] < 0 || dims[2] < 0 ) { setError( "invalid grid dimensions" ); return B2FWN_ERR_INVALID; }
+    if ( (size_t)dims[0] * dims[1] * dims[2] && !out ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    const GridXf g = toXf( xf );
+    const b2fwn_dist_options o = *opt;
+    return runChunked( h, dims, 0, 0, out, nullptr, nullptr, cb, user, [&]( int z0, int z1, float* d )
+        { return launchSdfGrid( h->tree, dims, g, o, z0, z1, d, h->stream, &h->stats.kernel_launches ); } );
+}
+
+// ---- marching cubes ------------------------------------------------------------------------------------------------------
+
+int b2fwn_marching_cubes( b2fwn_handle h, const float* volume, int32_t onDevice, const int32_t dims[3], const b2fwn_mc_params* p,
+                          uint64_t* nVerts, uint64_t* nTris )
+{
+    if ( !h || !dims || !p || !nVerts || !nTris ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    if ( dims[0] < 0 || dims[1] < 0 || dims[2] < 0 ) { setError( "invalid grid dimensions" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    const size_t total = (size_t)dims[0] * dims[1] * dims[2];
+    *nVerts = *nTris = 0;
+    freeMc( h->mc );
+    if ( total == 0 ) return B2FWN_OK;
+    if ( !volume ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    const float* dVol = volume;
+    float* dTmp = nullptr;
+    if ( !onDevice )
+    {
+        B2_CUDA( cudaMalloc( &dTmp, total * sizeof( float ) ) );
+        cudaError_t e = cudaMemcpyAsync( dTmp, volume, total * sizeof( float ), cudaMemcpyHostToDevice, h->stream );
+        if ( e != cudaSuccess ) { cudaFree( dTmp ); return cudaFail( e, "H2D volume" ); }
+        dVol = dTmp;
+    }
+    KernelTimer tm( h );
+    const int rc = marchingCubesDevice( dVol, dims, *p, h->mc, h->stream, &h->stats.kernel_launches );
+    tm.stop();
+    cudaStreamSynchronize( h->stream );
+    if ( dTmp ) cudaFree( dTmp );
+    if ( rc ) return rc;
+    *nVerts = h->mc.nVerts; *nTris = h->mc.nTris;
+    return B2FWN_OK;
+}
+
+int b2fwn_marching_cubes_fetch( b2fwn_handle h, float* outVerts, int32_t* outTris )
+{
+    if ( !h ) { setError( "null handle" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    if ( h->mc.nVerts && outVerts )
+        B2_CUDA( cudaMemcpy( outVerts, h->mc.dVerts, h->mc.nVerts * 3 * sizeof( float ), cudaMemcpyDeviceToHost ) );
+    if ( h->mc.nTris && outTris )
+        B2_CUDA( cudaMemcpy( outTris, h->mc.dTris, h->mc.nTris * 3 * sizeof( int32_t ), cudaMemcpyDeviceToHost ) );
+    return B2FWN_OK;
+}
+
+} // extern "C"
+#pragma GCC visibility pop

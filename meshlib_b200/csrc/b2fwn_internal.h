@@ -1,0 +1,101 @@
+// b2fwn_internal.h -- shared declarations between the translation units of libb2fwn.so.
+// Not part of the public boundary (that is include/b2fwn.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include <string>
+#include "../../include/b2fwn.h"
+
+namespace b2
+{
+
+// Reference-layout node, 32 B (source/MRMesh/MRAABBTreeNode.h:29-45): leaf <=> r < 0, then l = FaceId.
+struct RefNode
+{
+    float bmin[3];
+    float bmax[3];
+    int32_t l, r;
+};
+
+// Reference-layout dipole, 32 B (source/MRMesh/MRDipole.h:10-30).
+struct RefDipole
+{
+    float pos[3];
+    float area;
+    float dirArea[3];
+    float rr;
+};
+
+// Traversal node, 64 B = 4 x float4, one 128-B line holds two consecutive pre-order nodes.
+//   q0 = { bmin.x, bmin.y, bmin.z, bmax.x }
+//   q1 = { bmax.y, bmax.z, 0, link }          <- distance half (one 32-B sector)
+//   q2 = { pos.x, pos.y, pos.z, rr }
+//   q3 = { dirArea.x, dirArea.y, dirArea.z, link }   <- winding-number half (one 32-B sector)
+// link (int bits): internal node: index of the first node AFTER this node's subtree (pre-order "skip" pointer);
+//                  leaf: -(leafSlot+1), where leafSlot indexes DeviceTree::tris; a leaf's skip is i+1.
+struct __align__( 16 ) TravNode
+{
+    float4 q0, q1, q2, q3;
+};
+
+// Leaf triangle, 48 B: a.w carries the FaceId bits.
+struct __align__( 16 ) LeafTri
+{
+    float4 a, b, c;
+};
+
+struct DeviceTree
+{
+    size_t numVerts = 0, numFaces = 0, numLeaves = 0, numNodes = 0;
+    int depth = 0;
+    float* points = nullptr;     // numVerts*3
+    int32_t* tris = nullptr;     // numFaces*3
+    RefNode* refNodes = nullptr; // numNodes
+    RefDipole* refDipoles = nullptr;
+    TravNode* nodes = nullptr;   // numNodes
+    LeafTri* leafTris = nullptr; // numLeaves, in pre-order leaf order
+};
+
+struct GridXf
+{
+    float A[9];
+    float b[3];
+};
+
+// errors -------------------------------------------------------------------------------------------------------
+void setError( const std::string& msg );
+int cudaFail( cudaError_t e, const char* where );
+#define B2_CUDA( expr )                                        \
+    do {                                                       \
+        cudaError_t _e = ( expr );                             \
+        if ( _e != cudaSuccess )                               \
+            return b2::cudaFail( _e, #expr );                  \
+    } while ( 0 )
+
+// tree build (b2fwn_tree.cu) -----------------------------------------------------------------------------------
+int buildTree( DeviceTree& t, cudaStream_t stream, uint64_t* launches );
+void freeTree( DeviceTree& t );
+
+// traversal launchers (b2fwn_kernels.cu) ------------------------------------------------------------------------
+int launchFwnVector( const DeviceTree& t, const float* dPts, size_t n, float beta, int32_t skipFace, float* dOut,
+                     cudaStream_t stream, uint64_t* launches );
+int launchFwnFaces( const DeviceTree& t, float beta, float* dOutWOrNull, uint64_t* dBits, cudaStream_t stream,
+                    uint64_t* launches );
+int launchFwnGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, float beta, int zBegin, int zEnd,
+                   float* dOut, cudaStream_t stream, uint64_t* launches );
+int launchSdfGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, const b2fwn_dist_options& opt,
+                   int zBegin, int zEnd, float* dOut, cudaStream_t stream, uint64_t* launches );
+
+// marching cubes (b2fwn_mc.cu) -----------------------------------------------------------------------------------
+struct McResult
+{
+    float* dVerts = nullptr;   // nVerts*3
+    int32_t* dTris = nullptr;  // nTris*3
+    uint64_t nVerts = 0, nTris = 0;
+};
+int marchingCubesDevice( const float* dVolume, const int32_t dims[3], const b2fwn_mc_params& p, McResult& out,
+                         cudaStream_t stream, uint64_t* launches );
+void freeMc( McResult& r );
+
+} // namespace b2

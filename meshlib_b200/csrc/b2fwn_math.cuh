@@ -1,0 +1,167 @@
+// b2fwn_math.cuh -- per-query arithmetic of the path, written so that every float/double operation rounds as in
+// the reference's scalar CPU code (explicit _rn intrinsics = no FMA contraction).  With an identical tree and an
+// identical summation order this makes the winding number differ from the CPU reference only through atan2f, and
+// the distance not at all.
+//   Dipole::addIfGoodApprox        source/MRMesh/MRDipole.h:18-27
+//   triangleSolidAngle             source/MRMesh/MRDipole.cpp:81-92   (Matrix3::det: MRMatrix3.h:227-233)
+//   Box::getDistanceSq(pt)         source/MRMesh/MRBox.h:207-220
+//   closestPointInTriangle<double> source/MRMesh/MRClosestPointInTriangle.h:27-87, called at MRMeshProject.cpp:68-74
+#pragma once
+#include <cuda_runtime.h>
+
+namespace b2
+{
+
+#define FM( a, b ) __fmul_rn( ( a ), ( b ) )
+#define FA( a, b ) __fadd_rn( ( a ), ( b ) )
+#define FS( a, b ) __fsub_rn( ( a ), ( b ) )
+#define DM( a, b ) __dmul_rn( ( a ), ( b ) )
+#define DA( a, b ) __dadd_rn( ( a ), ( b ) )
+#define DS( a, b ) __dsub_rn( ( a ), ( b ) )
+
+__device__ __forceinline__ float dot3( float ax, float ay, float az, float bx, float by, float bz )
+{
+    return FA( FA( FM( ax, bx ), FM( ay, by ) ), FM( az, bz ) );
+}
+__device__ __forceinline__ double ddot3( double ax, double ay, double az, double bx, double by, double bz )
+{
+    return DA( DA( DM( ax, bx ), DM( ay, by ) ), DM( az, bz ) );
+}
+
+// AffineXf3f::operator() : A * x + b  (MRAffineXf.h:46, MRMatrix3.h:127-130)
+__device__ __forceinline__ float3 applyXf( const float* __restrict__ A, const float* __restrict__ b, float x, float y, float z )
+{
+    float3 r;
+    r.x = FA( dot3( A[0], A[1], A[2], x, y, z ), b[0] );
+    r.y = FA( dot3( A[3], A[4], A[5], x, y, z ), b[1] );
+    r.z = FA( dot3( A[6], A[7], A[8], x, y, z ), b[2] );
+    return r;
+}
+
+// squared distance from p to the box {q0.xyz, (q0.w, q1.x, q1.y)}
+__device__ __forceinline__ float boxDistSq( const float3 p, const float4 q0, const float4 q1 )
+{
+    float res = 0.f;
+    if ( p.x < q0.x ) { const float d = FS( p.x, q0.x ); res = FA( res, FM( d, d ) ); }
+    else if ( p.x > q0.w ) { const float d = FS( p.x, q0.w ); res = FA( res, FM( d, d ) ); }
+    if ( p.y < q0.y ) { const float d = FS( p.y, q0.y ); res = FA( res, FM( d, d ) ); }
+    else if ( p.y > q1.x ) { const float d = FS( p.y, q1.x ); res = FA( res, FM( d, d ) ); }
+    if ( p.z < q0.z ) { const float d = FS( p.z, q0.z ); res = FA( res, FM( d, d ) ); }
+    else if ( p.z > q1.y ) { const float d = FS( p.z, q1.y ); res = FA( res, FM( d, d ) ); }
+    return res;
+}
+
+// returns true when the dipole {q2 = pos.xyz, rr; q3 = dirArea.xyz} is a good approximation at q and adds its term
+__device__ __forceinline__ bool dipoleAddIfGoodApprox( const float3 q, const float betaSq, const float4 q2, const float4 q3, float& addTo )
+{
+    const float dx = FS( q2.x, q.x ), dy = FS( q2.y, q.y ), dz = FS( q2.z, q.z );
+    const float dd = dot3( dx, dy, dz, dx, dy, dz );
+    if ( dd <= FM( betaSq, q2.w ) )
+        return false;
+    const float d = __fsqrt_rn( dd );
+    if ( d > 0 )
+        addTo = FA( addTo, __fdiv_rn( dot3( dx, dy, dz, q3.x, q3.y, q3.z ), FM( d, dd ) ) );
+    return true;
+}
+
+__device__ __forceinline__ float triangleSolidAngle( const float3 p, const float4 ta, const float4 tb, const float4 tc )
+{
+    const float ax = FS( ta.x, p.x ), ay = FS( ta.y, p.y ), az = FS( ta.z, p.z );
+    const float bx = FS( tb.x, p.x ), by = FS( tb.y, p.y ), bz = FS( tb.z, p.z );
+    const float cx = FS( tc.x, p.x ), cy = FS( tc.y, p.y ), cz = FS( tc.z, p.z );
+    const float x = __fsqrt_rn( dot3( ax, ay, az, ax, ay, az ) );
+    const float y = __fsqrt_rn( dot3( bx, by, bz, bx, by, bz ) );
+    const float z = __fsqrt_rn( dot3( cx, cy, cz, cx, cy, cz ) );
+    // den = x*y*z + dot(a,b)*z + dot(b,c)*x + dot(c,a)*y
+    float den = FM( FM( x, y ), z );
+    den = FA( den, FM( dot3( ax, ay, az, bx, by, bz ), z ) );
+    den = FA( den, FM( dot3( bx, by, bz, cx, cy, cz ), x ) );
+    den = FA( den, FM( dot3( cx, cy, cz, ax, ay, az ), y ) );
+    // det of rows a, b, c
+    const float t0 = FM( ax, FS( FM( by, cz ), FM( bz, cy ) ) );
+    const float t1 = FM( ay, FS( FM( bx, cz ), FM( bz, cx ) ) );
+    const float t2 = FM( az, FS( FM( bx, cy ), FM( by, cx ) ) );
+    const float det = FA( FS( t0, t1 ), t2 );
+    return FM( 2.f, atan2f( det, den ) );
+}
+
+// squared distance from p to triangle (a,b,c) exactly as the reference computes it: closest point in DOUBLE,
+// rounded to float, difference and squared length in float.
+__device__ __forceinline__ float triDistSqExact( const float3 pf, const float4 ta, const float4 tb, const float4 tc )
+{
+    const double px = pf.x, py = pf.y, pz = pf.z;
+    const double ax = ta.x, ay = ta.y, az = ta.z;
+    const double bx = tb.x, by = tb.y, bz = tb.z;
+    const double cx = tc.x, cy = tc.y, cz = tc.z;
+    const double abx = DS( bx, ax ), aby = DS( by, ay ), abz = DS( bz, az );
+    const double acx = DS( cx, ax ), acy = DS( cy, ay ), acz = DS( cz, az );
+    const double apx = DS( px, ax ), apy = DS( py, ay ), apz = DS( pz, az );
+    double rx, ry, rz;
+    const double d1 = ddot3( abx, aby, abz, apx, apy, apz );
+    const double d2 = ddot3( acx, acy, acz, apx, apy, apz );
+    bool done = false;
+    if ( d1 <= 0 && d2 <= 0 ) { rx = ax; ry = ay; rz = az; done = true; } // #1
+    double d3 = 0, d4 = 0, d5 = 0, d6 = 0;
+    if ( !done )
+    {
+        const double bpx = DS( px, bx ), bpy = DS( py, by ), bpz = DS( pz, bz );
+        d3 = ddot3( abx, aby, abz, bpx, bpy, bpz );
+        d4 = ddot3( acx, acy, acz, bpx, bpy, bpz );
+        if ( d3 >= 0 && d4 <= d3 ) { rx = bx; ry = by; rz = bz; done = true; } // #2
+    }
+    if ( !done )
+    {
+        const double cpx = DS( px, cx ), cpy = DS( py, cy ), cpz = DS( pz, cz );
+        d5 = ddot3( abx, aby, abz, cpx, cpy, cpz );
+        d6 = ddot3( acx, acy, acz, cpx, cpy, cpz );
+        if ( d6 >= 0 && d5 <= d6 ) { rx = cx; ry = cy; rz = cz; done = true; } // #3
+    }
+    if ( !done )
+    {
+        const double vc = DS( DM( d1, d4 ), DM( d3, d2 ) );
+        if ( vc <= 0 && d1 >= 0 && d3 <= 0 )
+        {
+            const double v = d1 / DS( d1, d3 );
+            rx = DA( ax, DM( v, abx ) ); ry = DA( ay, DM( v, aby ) ); rz = DA( az, DM( v, abz ) ); // #4
+            done = true;
+        }
+        if ( !done )
+        {
+            const double vb = DS( DM( d5, d2 ), DM( d1, d6 ) );
+            if ( vb <= 0 && d6 <= 0 && d2 >= 0 )
+            {
+                const double v = d2 / DS( d2, d6 );
+                rx = DA( ax, DM( v, acx ) ); ry = DA( ay, DM( v, acy ) ); rz = DA( az, DM( v, acz ) ); // #5
+                done = true;
+            }
+            if ( !done )
+            {
+                const double va = DS( DM( d3, d6 ), DM( d5, d4 ) );
+                if ( va <= 0 )
+                {
+                    if ( d4 < d3 ) { rx = bx; ry = by; rz = bz; }
+                    else if ( d5 < d6 ) { rx = cx; ry = cy; rz = cz; }
+                    else
+                    {
+                        const double e = DS( d4, d3 ), g = DS( d5, d6 );
+                        const double v = e / DA( e, g );
+                        rx = DA( bx, DM( v, DS( cx, bx ) ) ); ry = DA( by, DM( v, DS( cy, by ) ) ); rz = DA( bz, DM( v, DS( cz, bz ) ) ); // #6
+                    }
+                }
+                else
+                {
+                    const double denom = 1.0 / DA( DA( va, vb ), vc );
+                    const double v = DM( vb, denom ), w = DM( vc, denom );
+                    // a + v * ab + w * ac   (left to right)
+                    rx = DA( DA( ax, DM( v, abx ) ), DM( w, acx ) );
+                    ry = DA( DA( ay, DM( v, aby ) ), DM( w, acy ) );
+                    rz = DA( DA( az, DM( v, abz ) ), DM( w, acz ) ); // #0
+                }
+            }
+        }
+    }
+    const float fx = FS( __double2float_rn( rx ), pf.x ), fy = FS( __double2float_rn( ry ), pf.y ), fz = FS( __double2float_rn( rz ), pf.z );
+    return dot3( fx, fy, fz, fx, fy, fz );
+}
+
+} // namespace b2

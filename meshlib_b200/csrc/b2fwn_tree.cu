@@ -1,0 +1,476 @@
+// b2fwn_tree.cu -- device build of the AABB tree and of the dipole (far-field) data.
+//
+// Compiled with -fmad=false: every float operation below rounds exactly like the reference's scalar CPU code
+// (no FMA contraction on baseline x86-64), so that the device-built tree and dipoles are BIT-IDENTICAL to
+//   MR::AABBTree::AABBTree(MeshPart)       source/MRMesh/MRAABBTree.cpp:15-60
+//   AABBTreeMaker::construct / partitionLeaves_ / makeNode_   source/MRMesh/MRAABBTreeMaker.hpp:51-171
+//   MR::calcDipoles                         source/MRMesh/MRDipole.cpp:11-71
+//
+// The reference splits every subtree at the median of a STRICT TOTAL ORDER (box centre along the box's
+// dimensions from longest to shortest, then leaf id), so the leaf SET of every node is independent of thread
+// count and of the selection algorithm.  We therefore build the identical tree breadth-first: one segmented
+// sort per level (all segments of a level at once), node indices in DFS pre-order computed in closed form
+// (left = i+1, right = i + 2*leftLeaves).  ceil(log2 F)+1 levels, everything stays in HBM.
+#include "b2fwn_internal.h"
+#include <cub/device/device_merge_sort.cuh>
+#include <cub/device/device_select.cuh>
+#include <thrust/iterator/counting_iterator.h>
+#include <cfloat>
+#include <vector>
+
+namespace b2
+{
+
+namespace
+{
+
+constexpr int TB = 256;
+
+// per-leaf record kept during the build
+struct LeafBox
+{
+    float mn[3];
+    float mx[3];
+    int32_t face;
+};
+
+// sort key of one leaf at one level: (segment, centre along longest, middle, shortest dim, leaf id)
+struct LevelKey
+{
+    uint32_t seg;
+    float k1, k2, k3;
+    int32_t face;
+    int32_t leaf; // index into LeafBox array
+};
+
+struct LevelKeyLess
+{
+    __device__ __forceinline__ bool operator()( const LevelKey& a, const LevelKey& b ) const
+    {
+        if ( a.seg != b.seg ) return a.seg < b.seg;
+        // MRAABBTreeMaker.hpp:56-69
+        if ( a.k1 != b.k1 ) return a.k1 < b.k1;
+        if ( a.k2 != b.k2 ) return a.k2 < b.k2;
+        if ( a.k3 != b.k3 ) return a.k3 < b.k3;
+        return a.face < b.face;
+    }
+};
+
+// segment (= subtree under construction) of one level
+struct Seg
+{
+    int32_t first; // first leaf position
+    int32_t n;     // number of leaves; 0 = empty slot
+    int32_t node;  // pre-order node index of the subtree root
+    int32_t done;  // leaf node already written
+};
+
+__device__ __forceinline__ uint32_t f2ord( float f )
+{
+    uint32_t u = __float_as_uint( f );
+    return ( u & 0x80000000u ) ? ~u : ( u | 0x80000000u );
+}
+__device__ __forceinline__ float ord2f( uint32_t u )
+{
+    return __uint_as_float( ( u & 0x80000000u ) ? ( u & 0x7fffffffu ) : ~u );
+}
+
+__global__ void kValidFlags( const int32_t* __restrict__ tris, size_t nFaces, uint8_t* __restrict__ flags )
+{
+    size_t f = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if ( f >= nFaces ) return;
+    flags[f] = ( tris[3 * f] >= 0 && tris[3 * f + 1] >= 0 && tris[3 * f + 2] >= 0 ) ? 1 : 0;
+}
+
+// computeFaceBox (MRAABBTree.cpp:15-29) + Box::insignificantlyExpanded (MRBox.h:260-270)
+__global__ void kFaceBoxes( const float* __restrict__ pts, const int32_t* __restrict__ tris,
+                            const int32_t* __restrict__ validFaces, int nLeaves, LeafBox* __restrict__ out )
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if ( i >= nLeaves ) return;
+    const int f = validFaces[i];
+    LeafBox lb;
+    lb.face = f;
+#pragma unroll
+    for ( int d = 0; d < 3; ++d )
+    {
+        const float a = pts[3 * (size_t)tris[3 * (size_t)f] + d];
+        const float b = pts[3 * (size_t)tris[3 * (size_t)f + 1] + d];
+        const float c = pts[3 * (size_t)tris[3 * (size_t)f + 2] + d];
+        // Box::include: if (pt < min) min = pt; if (pt > max) max = pt  (MRBox.h)
+        float mn = FLT_MAX, mx = -FLT_MAX;
+        if ( a < mn ) mn = a; if ( a > mx ) mx = a;
+        if ( b < mn ) mn = b; if ( b > mx ) mx = b;
+        if ( c < mn ) mn = c; if ( c > mx ) mx = c;
+        lb.mn[d] = nextafterf( mn, -FLT_MAX );
+        lb.mx[d] = nextafterf( mx, FLT_MAX );
+    }
+    out[i] = lb;
+}
+
+__global__ void kInitPerm( int nLeaves, LevelKey* __restrict__ keys, const LeafBox* __restrict__ leaves )
+{
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if ( i >= nLeaves ) return;
+    LevelKey k;
+    k.seg = 0; k.k1 = k.k2 = k.k3 = 0; k.face = leaves[i].face; k.leaf = i;
+    keys[i] = k;
+}
+
+__global__ void kClearSegBoxes( uint32_t* __restrict__ segBox, size_t nSegs )
+{
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if ( i >= nSegs * 6 ) return;
+    // min slots start at +inf-ordered, max slots at -inf-ordered
+    segBox[i] = ( i % 6 < 3 ) ? 0xFFFFFFFFu : 0u;
+}
+
+// union of the leaf boxes of every segment (makeNode_, MRAABBTreeMaker.hpp:80-83): segmented warp reduction over
+// runs of equal segment id, then one atomic per run and component on order-preserving integer images
+__global__ void kSegBoxes( int nLeaves, const LevelKey* __restrict__ keys, const LeafBox* __restrict__ leaves,
+                           uint32_t* __restrict__ segBox )
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned lane = threadIdx.x & 31;
+    const bool valid = i < nLeaves;
+    uint32_t seg = 0xFFFFFFFFu;
+    uint32_t v[6];
+#pragma unroll
+    for ( int c = 0; c < 6; ++c ) v[c] = c < 3 ? 0xFFFFFFFFu : 0u;
+    if ( valid )
+    {
+        const LevelKey k = keys[i];
+        seg = k.seg;
+        const LeafBox lb = leaves[k.leaf];
+#pragma unroll
+        for ( int c = 0; c < 3; ++c ) { v[c] = f2ord( lb.mn[c] ); v[3 + c] = f2ord( lb.mx[c] ); }
+    }
+    // segments are contiguous runs; reduce towards the head lane of each run
+#pragma unroll
+    for ( int off = 1; off < 32; off <<= 1 )
+    {
+        const uint32_t oseg = __shfl_down_sync( 0xFFFFFFFFu, seg, off );
+        uint32_t ov[6];
+#pragma unroll
+        for ( int c = 0; c < 6; ++c ) ov[c] = __shfl_down_sync( 0xFFFFFFFFu, v[c], off );
+        if ( lane + off < 32 && oseg == seg )
+        {
+#pragma unroll
+            for ( int c = 0; c < 3; ++c ) { v[c] = min( v[c], ov[c] ); v[3 + c] = max( v[3 + c], ov[3 + c] ); }
+        }
+    }
+    const uint32_t pseg = __shfl_up_sync( 0xFFFFFFFFu, seg, 1 );
+    const bool head = valid && ( lane == 0 || pseg != seg );
+    if ( head )
+    {
+        uint32_t* dst = segBox + (size_t)seg * 6;
+#pragma unroll
+        for ( int c = 0; c < 3; ++c ) { atomicMin( dst + c, v[c] ); atomicMax( dst + 3 + c, v[3 + c] ); }
+    }
+}
+
+// sort keys of a level: findSortedBoxDims (MRBox.h:376-396) + the comparator of partitionLeaves_
+__global__ void kMakeKeys( int nLeaves, LevelKey* __restrict__ keys, const LeafBox* __restrict__ leaves,
+                           const uint32_t* __restrict__ segBox, const Seg* __restrict__ segs )
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if ( i >= nLeaves ) return;
+    LevelKey k = keys[i];
+    if ( segs[k.seg].n <= 1 ) { k.k1 = k.k2 = k.k3 = 0; keys[i] = k; return; }
+    const uint32_t* sb = segBox + (size_t)k.seg * 6;
+    float ext[3]; int dim[3] = { 0, 1, 2 };
+#pragma unroll
+    for ( int c = 0; c < 3; ++c ) ext[c] = ord2f( sb[3 + c] ) - ord2f( sb[c] );
+    // bubble sort of pairs (extent, axis), ascending, std::pair operator<
+#pragma unroll
+    for ( int a = 0; a + 1 < 3; ++a )
+#pragma unroll
+        for ( int b = a + 1; b < 3; ++b )
+            if ( ext[b] < ext[a] || ( !( ext[a] < ext[b] ) && dim[b] < dim[a] ) )
+            {
+                float te = ext[a]; ext[a] = ext[b]; ext[b] = te;
+                int td = dim[a]; dim[a] = dim[b]; dim[b] = td;
+            }
+    const LeafBox lb = leaves[k.leaf];
+    float c2[3];
+#pragma unroll
+    for ( int c = 0; c < 3; ++c ) c2[c] = lb.mn[c] + lb.mx[c];
+    k.k1 = dim[2] == 0 ? c2[0] : dim[2] == 1 ? c2[1] : c2[2];
+    k.k2 = dim[1] == 0 ? c2[0] : dim[1] == 1 ? c2[1] : c2[2];
+    k.k3 = dim[0] == 0 ? c2[0] : dim[0] == 1 ? c2[1] : c2[2];
+    keys[i] = k;
+}
+
+// after the sort: move every leaf into the left or right child segment of the next level
+__global__ void kDescend( int nLeaves, LevelKey* __restrict__ keys, const Seg* __restrict__ segs )
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if ( i >= nLeaves ) return;
+    const uint32_t s = keys[i].seg;
+    const Seg sg = segs[s];
+    uint32_t ns = 2u * s;
+    if ( sg.n > 1 && i - sg.first >= sg.n / 2 ) ns += 1;
+    keys[i].seg = ns;
+}
+
+// writes the nodes of this level and the segment table of the next one
+__global__ void kEmitLevel( uint32_t nSegs, int level, const Seg* __restrict__ segs, Seg* __restrict__ next,
+                            const uint32_t* __restrict__ segBox, const LevelKey* __restrict__ keys,
+                            const LeafBox* __restrict__ leaves, RefNode* __restrict__ nodes,
+                            int32_t* __restrict__ skip, uint8_t* __restrict__ depth, int32_t* __restrict__ leafNodeOfPos )
+{
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if ( s >= nSegs ) return;
+    const Seg sg = segs[s];
+    Seg l = { 0, 0, 0, 0 }, r = { 0, 0, 0, 0 };
+    if ( sg.n == 1 )
+    {
+        if ( !sg.done )
+        {
+            const LevelKey k = keys[sg.first];
+            const LeafBox lb = leaves[k.leaf];
+            RefNode nd;
+#pragma unroll
+            for ( int c = 0; c < 3; ++c ) { nd.bmin[c] = lb.mn[c]; nd.bmax[c] = lb.mx[c]; }
+            nd.l = lb.face; nd.r = -1; // setLeafId (MRAABBTreeNode.h:41)
+            nodes[sg.node] = nd;
+            skip[sg.node] = sg.node + 1;
+            depth[sg.node] = (uint8_t)level;
+            leafNodeOfPos[sg.first] = sg.node;
+        }
+        l = { sg.first, 1, sg.node, 1 };
+    }
+    else if ( sg.n > 1 )
+    {
+        const int nl = sg.n / 2; // midLeaf = first + n/2 (MRAABBTreeMaker.hpp:71)
+        RefNode nd;
+        const uint32_t* sb = segBox + (size_t)s * 6;
+#pragma unroll
+        for ( int c = 0; c < 3; ++c ) { nd.bmin[c] = ord2f( sb[c] ); nd.bmax[c] = ord2f( sb[3 + c] ); }
+        nd.l = sg.node + 1;
+        nd.r = sg.node + 2 * nl; // root + 1 + getNumNodes(leftNumLeaves) (MRAABBTreeMaker.hpp:88-89)
+        nodes[sg.node] = nd;
+        skip[sg.node] = sg.node + 2 * sg.n - 1;
+        depth[sg.node] = (uint8_t)level;
+        l = { sg.first, nl, sg.node + 1, 0 };
+        r = { sg.first + nl, sg.n - nl, sg.node + 2 * nl, 0 };
+    }
+    next[2 * (size_t)s] = l;
+    next[2 * (size_t)s + 1] = r;
+}
+
+// ---- dipoles (MRDipole.cpp:23-71) ---------------------------------------------------------------------------------
+
+// leaves: da = 0.5f*cross(b-a, c-a); area = |da|; pos = area * ((1/3.0f)*(a+b+c))   (MRDipole.cpp:29-45,
+// MRMeshMath.cpp:119-124, 140-149)
+__global__ void kLeafDipoles( size_t nNodes, const RefNode* __restrict__ nodes, const float* __restrict__ pts,
+                              const int32_t* __restrict__ tris, RefDipole* __restrict__ dip )
+{
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if ( i >= nNodes ) return;
+    const RefNode nd = nodes[i];
+    if ( nd.r >= 0 ) return;
+    const size_t f = (size_t)nd.l;
+    float a[3], b[3], c[3];
+#pragma unroll
+    for ( int d = 0; d < 3; ++d )
+    {
+        a[d] = pts[3 * (size_t)tris[3 * f] + d];
+        b[d] = pts[3 * (size_t)tris[3 * f + 1] + d];
+        c[d] = pts[3 * (size_t)tris[3 * f + 2] + d];
+    }
+    const float ux = b[0] - a[0], uy = b[1] - a[1], uz = b[2] - a[2];
+    const float vx = c[0] - a[0], vy = c[1] - a[1], vz = c[2] - a[2];
+    const float cx = uy * vz - uz * vy, cy = uz * vx - ux * vz, cz = ux * vy - uy * vx;
+    const float dax = 0.5f * cx, day = 0.5f * cy, daz = 0.5f * cz;
+    const float area = sqrtf( dax * dax + day * day + daz * daz );
+    const float third = 1 / 3.0f;
+    const float ctrx = third * ( ( a[0] + b[0] ) + c[0] ), ctry = third * ( ( a[1] + b[1] ) + c[1] ), ctrz = third * ( ( a[2] + b[2] ) + c[2] );
+    RefDipole d;
+    d.pos[0] = area * ctrx; d.pos[1] = area * ctry; d.pos[2] = area * ctrz;
+    d.area = area;
+    d.dirArea[0] = dax; d.dirArea[1] = day; d.dirArea[2] = daz;
+    d.rr = 0;
+    dip[i] = d;
+}
+
+// inner nodes of one depth: dipole = left + right (MRDipole.cpp:48-61); deeper levels are complete already
+__global__ void kInnerDipoles( size_t nNodes, int level, const uint8_t* __restrict__ depth,
+                               const RefNode* __restrict__ nodes, RefDipole* __restrict__ dip )
+{
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if ( i >= nNodes || depth[i] != level ) return;
+    const RefNode nd = nodes[i];
+    if ( nd.r < 0 ) return;
+    const RefDipole dl = dip[nd.l], dr = dip[nd.r];
+    RefDipole d;
+#pragma unroll
+    for ( int c = 0; c < 3; ++c ) { d.pos[c] = dl.pos[c] + dr.pos[c]; d.dirArea[c] = dl.dirArea[c] + dr.dirArea[c]; }
+    d.area = dl.area + dr.area;
+    d.rr = 0;
+    dip[i] = d;
+}
+
+// pos /= area (as pos *= 1/area, MRVector3.h:131-137) and rr = distToFarthestCornerSq (MRDipole.cpp:11-21, 63-70);
+// also packs the 64-B traversal node
+__global__ void kFinishDipoles( size_t nNodes, const RefNode* __restrict__ nodes, RefDipole* __restrict__ dip,
+                                const int32_t* __restrict__ skip, const int32_t* __restrict__ leafSlotOfNode,
+                                TravNode* __restrict__ trav )
+{
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if ( i >= nNodes ) return;
+    const RefNode nd = nodes[i];
+    RefDipole d = dip[i];
+    if ( d.area > 0 )
+    {
+        const float inv = 1 / d.area;
+        d.pos[0] *= inv; d.pos[1] *= inv; d.pos[2] *= inv;
+    }
+    float rr = 0;
+#pragma unroll
+    for ( int c = 0; c < 3; ++c )
+    {
+        const float a = d.pos[c] - nd.bmin[c], b = d.pos[c] - nd.bmax[c];
+        const float toMinSq = a * a, toMaxSq = b * b;
+        rr += fmaxf( toMinSq, toMaxSq );
+    }
+    d.rr = rr;
+    dip[i] = d;
+    const int link = nd.r < 0 ? -( leafSlotOfNode[i] + 1 ) : skip[i];
+    TravNode t;
+    t.q0 = make_float4( nd.bmin[0], nd.bmin[1], nd.bmin[2], nd.bmax[0] );
+    t.q1 = make_float4( nd.bmax[1], nd.bmax[2], 0.f, __int_as_float( link ) );
+    t.q2 = make_float4( d.pos[0], d.pos[1], d.pos[2], d.rr );
+    t.q3 = make_float4( d.dirArea[0], d.dirArea[1], d.dirArea[2], __int_as_float( link ) );
+    trav[i] = t;
+}
+
+// leaf slot = leaf position in the final sorted order (= pre-order rank of the leaf)
+__global__ void kLeafSlots( int nLeaves, const int32_t* __restrict__ leafNodeOfPos, int32_t* __restrict__ leafSlotOfNode,
+                            const LevelKey* __restrict__ keys, const float* __restrict__ pts,
+                            const int32_t* __restrict__ tris, LeafTri* __restrict__ out )
+{
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if ( p >= nLeaves ) return;
+    leafSlotOfNode[leafNodeOfPos[p]] = p;
+    const size_t f = (size_t)keys[p].face;
+    const int32_t ia = tris[3 * f], ib = tris[3 * f + 1], ic = tris[3 * f + 2];
+    LeafTri t;
+    t.a = make_float4( pts[3 * (size_t)ia], pts[3 * (size_t)ia + 1], pts[3 * (size_t)ia + 2], __int_as_float( (int)f ) );
+    t.b = make_float4( pts[3 * (size_t)ib], pts[3 * (size_t)ib + 1], pts[3 * (size_t)ib + 2], 0.f );
+    t.c = make_float4( pts[3 * (size_t)ic], pts[3 * (size_t)ic + 1], pts[3 * (size_t)ic + 2], 0.f );
+    out[p] = t;
+}
+
+inline unsigned nblk( size_t n ) { return (unsigned)( ( n + TB - 1 ) / TB ); }
+
+} // anonymous namespace
+
+void freeTree( DeviceTree& t )
+{
+    cudaFree( t.points ); cudaFree( t.tris ); cudaFree( t.refNodes ); cudaFree( t.refDipoles );
+    cudaFree( t.nodes ); cudaFree( t.leafTris );
+    t = DeviceTree{};
+}
+
+int buildTree( DeviceTree& t, cudaStream_t st, uint64_t* launches )
+{
+    uint64_t nl = 0;
+    const size_t F = t.numFaces;
+    t.numLeaves = t.numNodes = 0; t.depth = 0;
+    if ( F == 0 ) return B2FWN_OK;
+    if ( F > (size_t)0x3FFFFFFF ) { setError( "too many faces" ); return B2FWN_ERR_INVALID; }
+
+    // 1. valid faces in increasing id order (MRAABBTree.cpp:35-46)
+    uint8_t* dFlags = nullptr; int32_t* dValid = nullptr; int* dNum = nullptr;
+    B2_CUDA( cudaMalloc( &dFlags, F ) );
+    B2_CUDA( cudaMalloc( &dValid, F * sizeof( int32_t ) ) );
+    B2_CUDA( cudaMalloc( &dNum, sizeof( int ) ) );
+    kValidFlags<<<nblk( F ), TB, 0, st>>>( t.tris, F, dFlags ); ++nl;
+    {
+        size_t tmpBytes = 0;
+        thrust::counting_iterator<int32_t> ids( 0 );
+        cub::DeviceSelect::Flagged( nullptr, tmpBytes, ids, dFlags, dValid, dNum, (int)F, st );
+        void* tmp = nullptr;
+        B2_CUDA( cudaMalloc( &tmp, tmpBytes ) );
+        cub::DeviceSelect::Flagged( tmp, tmpBytes, ids, dFlags, dValid, dNum, (int)F, st );
+        int num = 0;
+        B2_CUDA( cudaMemcpyAsync( &num, dNum, sizeof( int ), cudaMemcpyDeviceToHost, st ) );
+        B2_CUDA( cudaStreamSynchronize( st ) );
+        cudaFree( tmp );
+        t.numLeaves = (size_t)num;
+    }
+    cudaFree( dFlags ); cudaFree( dNum );
+    const int L = (int)t.numLeaves;
+    if ( L == 0 ) { cudaFree( dValid ); return B2FWN_OK; }
+    t.numNodes = 2 * (size_t)L - 1;
+    const size_t N = t.numNodes;
+    int levels = 0; // number of splitting levels = ceil(log2 L)
+    while ( ( (size_t)1 << levels ) < (size_t)L ) ++levels;
+    t.depth = levels;
+
+    LeafBox* dLeaves = nullptr; LevelKey *dKeys = nullptr; Seg *dSegA = nullptr, *dSegB = nullptr;
+    uint32_t* dSegBox = nullptr; int32_t *dSkip = nullptr, *dLeafNodeOfPos = nullptr, *dLeafSlotOfNode = nullptr;
+    uint8_t* dDepth = nullptr;
+    const size_t maxSegs = (size_t)1 << levels;
+    B2_CUDA( cudaMalloc( &dLeaves, (size_t)L * sizeof( LeafBox ) ) );
+    B2_CUDA( cudaMalloc( &dKeys, (size_t)L * sizeof( LevelKey ) ) );
+    B2_CUDA( cudaMalloc( &dSegA, 2 * maxSegs * sizeof( Seg ) ) );
+    B2_CUDA( cudaMalloc( &dSegB, 2 * maxSegs * sizeof( Seg ) ) );
+    B2_CUDA( cudaMalloc( &dSegBox, maxSegs * 6 * sizeof( uint32_t ) ) );
+    B2_CUDA( cudaMalloc( &dSkip, N * sizeof( int32_t ) ) );
+    B2_CUDA( cudaMalloc( &dDepth, N ) );
+    B2_CUDA( cudaMalloc( &dLeafNodeOfPos, (size_t)L * sizeof( int32_t ) ) );
+    B2_CUDA( cudaMalloc( &dLeafSlotOfNode, N * sizeof( int32_t ) ) );
+    B2_CUDA( cudaMalloc( &t.refNodes, N * sizeof( RefNode ) ) );
+    B2_CUDA( cudaMalloc( &t.refDipoles, N * sizeof( RefDipole ) ) );
+    B2_CUDA( cudaMalloc( &t.nodes, N * sizeof( TravNode ) ) );
+    B2_CUDA( cudaMalloc( &t.leafTris, (size_t)L * sizeof( LeafTri ) ) );
+
+    kFaceBoxes<<<nblk( L ), TB, 0, st>>>( t.points, t.tris, dValid, L, dLeaves ); ++nl;
+    kInitPerm<<<nblk( L ), TB, 0, st>>>( L, dKeys, dLeaves ); ++nl;
+    const Seg root = { 0, L, 0, 0 };
+    B2_CUDA( cudaMemcpyAsync( dSegA, &root, sizeof( Seg ), cudaMemcpyHostToDevice, st ) );
+
+    size_t sortTmpBytes = 0; void* sortTmp = nullptr;
+    cub::DeviceMergeSort::SortKeys( nullptr, sortTmpBytes, dKeys, L, LevelKeyLess(), st );
+    B2_CUDA( cudaMalloc( &sortTmp, sortTmpBytes ) );
+
+    // 2. breadth-first build, one segmented sort per level
+    for ( int lev = 0; lev <= levels; ++lev )
+    {
+        const size_t nSegs = (size_t)1 << lev;
+        if ( lev < levels )
+        {
+            kClearSegBoxes<<<nblk( nSegs * 6 ), TB, 0, st>>>( dSegBox, nSegs ); ++nl;
+            kSegBoxes<<<nblk( L ), TB, 0, st>>>( L, dKeys, dLeaves, dSegBox ); ++nl;
+            kMakeKeys<<<nblk( L ), TB, 0, st>>>( L, dKeys, dLeaves, dSegBox, dSegA ); ++nl;
+            B2_CUDA( cub::DeviceMergeSort::SortKeys( sortTmp, sortTmpBytes, dKeys, L, LevelKeyLess(), st ) ); nl += 2;
+        }
+        kEmitLevel<<<nblk( nSegs ), TB, 0, st>>>( (uint32_t)nSegs, lev, dSegA, dSegB, dSegBox, dKeys, dLeaves, t.refNodes,
+                                                  dSkip, dDepth, dLeafNodeOfPos ); ++nl;
+        if ( lev < levels )
+        {
+            kDescend<<<nblk( L ), TB, 0, st>>>( L, dKeys, dSegA ); ++nl;
+        }
+        Seg* tmp = dSegA; dSegA = dSegB; dSegB = tmp;
+    }
+
+    // 3. leaf triangles in pre-order leaf order, dipoles bottom-up, packed traversal nodes
+    kLeafSlots<<<nblk( L ), TB, 0, st>>>( L, dLeafNodeOfPos, dLeafSlotOfNode, dKeys, t.points, t.tris, t.leafTris ); ++nl;
+    kLeafDipoles<<<nblk( N ), TB, 0, st>>>( N, t.refNodes, t.points, t.tris, t.refDipoles ); ++nl;
+    for ( int lev = levels - 1; lev >= 0; --lev )
+    {
+        kInnerDipoles<<<nblk( N ), TB, 0, st>>>( N, lev, dDepth, t.refNodes, t.refDipoles ); ++nl;
+    }
+    kFinishDipoles<<<nblk( N ), TB, 0, st>>>( N, t.refNodes, t.refDipoles, dSkip, dLeafSlotOfNode, t.nodes ); ++nl;
+    B2_CUDA( cudaGetLastError() );
+    B2_CUDA( cudaStreamSynchronize( st ) );
+
+    cudaFree( sortTmp ); cudaFree( dValid ); cudaFree( dLeaves ); cudaFree( dKeys ); cudaFree( dSegA ); cudaFree( dSegB );
+    cudaFree( dSegBox ); cudaFree( dSkip ); cudaFree( dDepth ); cudaFree( dLeafNodeOfPos ); cudaFree( dLeafSlotOfNode );
+    if ( launches ) *launches += nl;
+    return B2FWN_OK;
+}
+
+} // namespace b2
