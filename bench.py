@@ -1,0 +1,384 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the mesh -> signed-distance-volume hot path (BASELINE.json metric:
+SDF voxels/s of calcFromGridWithDistances = fast-winding-number sign + closest-point distance).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+
+A "step" is one pass of the hot path over the whole voxel grid of the workload.
+  value  : voxels/s, result resident in HBM (the _device form of the C ABI), device time by CUDA events on the
+           launching stream (b2fwn_stats.last_kernel_ms), max over ranks.
+  e2e    : voxels/s through the reference-facing call with HOST buffers: mesh arrays on the host -> b2fwn_create
+           (H2D + device tree/dipole build) -> b2fwn_calc_from_grid_with_distances into a pinned host volume
+           (chunked D2H inside the timed region).
+  --impl reference : the reference's own CPU/TBB implementation (oracle/_ref when it was built, else the C
+           restatement) on a bounded sample of the same workload, all host threads.
+N > 1 (torchrun): the grid is sharded by z-slab, mesh and tree replicated per GPU, slabs gathered into the full volume on
+every GPU by NCCL all-gather (north_star); total work is fixed => "scaling": "strong".
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from meshlib_b200 import meshgen  # noqa: E402
+
+METRIC = "sdf_voxels_per_sec"
+UNIT = "voxels/s"
+
+# name -> (mesh spec, grid n, options); C-numbers refer to BASELINE.json configs / SURVEY.md 8(d)
+WORKLOADS = {
+    # C5: noisy UV sphere (1, 3162, 1581) -> 9,998,244 faces, 2048^3, narrow band (maxDist = 3 voxels, no NaN)
+    "c5_band": dict(mesh=("noisy_sphere", 3162, 1581, 1e-3), grid=2048, band_voxels=3.0, null_outside=False),
+    # same mesh, exact distance everywhere (default options)
+    "c5_full": dict(mesh=("noisy_sphere", 3162, 1581, 1e-3), grid=2048, band_voxels=None, null_outside=True),
+    # C1: torus 65,536 faces on 128^3, default options (the reference's own CPU-runnable case)
+    "c1": dict(mesh=("torus", 256, 128), grid=128, band_voxels=None, null_outside=True),
+    # C3-shaped: 2M-face noisy sphere at 512^3, band
+    "c3_band": dict(mesh=("noisy_sphere", 1414, 707, 1e-3), grid=512, band_voxels=3.0, null_outside=False),
+    "c3_full": dict(mesh=("noisy_sphere", 1414, 707, 1e-3), grid=512, band_voxels=None, null_outside=True),
+}
+DEFAULT_WORKLOAD = "c5_band"
+
+
+def build_workload(name, grid_override=None):
+    w = dict(WORKLOADS[name])
+    spec = w["mesh"]
+    if spec[0] == "torus":
+        pts, tris = meshgen.make_torus(2, 1, spec[1], spec[2])
+        n = grid_override or w["grid"]
+        dims, origin, voxel = (n, n, n), np.array([-3.2, -3.2, -3.2], np.float32), np.float32(6.4 / n)
+    else:
+        pts, tris = meshgen.make_uv_sphere(1, spec[1], spec[2])
+        pts = meshgen.add_noise(pts, spec[3], seed=42)
+        n = grid_override or w["grid"]
+        dims, origin, voxel = meshgen.grid_for_bbox(pts, n, 2.0)
+    from meshlib_b200 import make_basis_xf
+    xf = make_basis_xf(origin, voxel)
+    fmax = float(np.finfo(np.float32).max)
+    max_sq = fmax if w["band_voxels"] is None else float(np.float32((w["band_voxels"] * float(voxel)) ** 2))
+    opts = dict(min_dist_sq=0.0, max_dist_sq=max_sq, null_outside=bool(w["null_outside"]), threshold=0.5, beta=2.0)
+    return dict(name=name, points=pts, tris=tris, dims=dims, xf=xf, voxel=float(voxel), opts=opts,
+                desc=f"{name}: {len(tris)} faces, grid {dims[0]}x{dims[1]}x{dims[2]}, "
+                     + ("exact distance everywhere" if w["band_voxels"] is None else f"band maxDist={w['band_voxels']} voxels")
+                     + f", nullOutsideMinMax={w['null_outside']}")
+
+
+class ClockSampler:
+    """samples nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)"""
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for k, n in enumerate(names):
+                if len(r) > 3 + k and r[3 + k].lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def flops_per_voxel(c, n):
+    """8*Vf + 10*Af + 80*Lf + 12*Bd + 60*Ld, counts of the REFERENCE algorithm on the reference tree"""
+    return (8 * c["fwn_visits"] + 10 * c["fwn_accepts"] + 80 * c["fwn_leaves"] + 12 * c["box_tests"] + 60 * c["tri_tests"]) / max(n, 1)
+
+
+def sample_layers(dz, k):
+    return sorted(set(int(round((i + 0.5) * dz / k - 0.5)) for i in range(k)))
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# CPU side: the reference's own implementation (checker code; only this leg of bench.py may execute oracle/)
+# ---------------------------------------------------------------------------------------------------------------------
+
+def cpu_reference_setup(wl):
+    from oracle import portlib, reflib
+    t0 = time.perf_counter()
+    if reflib.available():
+        m = reflib.RefMesh.from_arrays(wl["points"], wl["tris"])
+        kind, cores = "reference", reflib.hardware_threads()
+        m.nodes()  # builds the AABB tree once (Mesh::getAABBTree), as the first call would
+        m.dipoles()
+    else:
+        m = portlib.PortMesh(wl["points"], wl["tris"])
+        kind, cores = "port", os.cpu_count()
+    return m, kind, cores, time.perf_counter() - t0
+
+
+def cpu_run_layers(m, wl, layers):
+    o = wl["opts"]
+    t0 = time.perf_counter()
+    for z in layers:
+        m.calc_grid_with_distances_layers(wl["dims"], wl["xf"], z, z + 1, min_dist_sq=o["min_dist_sq"], max_dist_sq=o["max_dist_sq"],
+                                          null_outside=o["null_outside"], threshold=o["threshold"], beta=o["beta"])
+    return time.perf_counter() - t0
+
+
+def choose_sample(m, wl, budget_s):
+    """evenly spaced z-layers worth about budget_s seconds of CPU work (probe: the middle layer)"""
+    dz = wl["dims"][2]
+    t1 = cpu_run_layers(m, wl, [dz // 2])
+    k = int(max(1, min(dz, 16, budget_s / max(t1, 1e-6))))
+    return sample_layers(dz, k), t1
+
+
+def cpu_baseline(wl, budget_s=15.0):
+    m, kind, cores, setup_s = cpu_reference_setup(wl)
+    layers, _ = choose_sample(m, wl, budget_s)
+    dt = cpu_run_layers(m, wl, layers)
+    nvox = len(layers) * wl["dims"][0] * wl["dims"][1]
+    return {"value": nvox / dt, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": f"{len(layers)} evenly spaced z-layers of {wl['dims'][0]}x{wl['dims'][1]} ({nvox} voxels, {dt:.2f} s); "
+                      f"mesh+tree setup {setup_s:.1f} s excluded", "layers": layers}
+
+
+def algorithmic_flops(wl, layers, max_samples=200000):
+    """operation counts of the reference algorithm (C restatement, counters) on a stride sample of the given layers"""
+    from oracle import portlib
+    m = portlib.PortMesh(wl["points"], wl["tris"])
+    o = wl["opts"]
+    per_layer = wl["dims"][0] * wl["dims"][1]
+    stride = max(1, (per_layer * len(layers)) // max_samples) | 1
+    n = 0
+    m.reset_counters()
+    for z in layers:
+        m.calc_from_grid_with_distances(wl["dims"], wl["xf"], min_dist_sq=o["min_dist_sq"], max_dist_sq=o["max_dist_sq"],
+                                        null_outside=o["null_outside"], threshold=o["threshold"], beta=o["beta"], z0=z, z1=z + 1,
+                                        stride=stride)
+        n += (per_layer + stride - 1) // stride
+    c = m.counter_dict()
+    return flops_per_voxel(c, n), {k: v / n for k, v in c.items()}, n
+
+
+def run_reference_arm(args, wl):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    m, kind, cores, setup_s = cpu_reference_setup(wl)
+    layers, _ = choose_sample(m, wl, 6.0)
+    nvox = len(layers) * wl["dims"][0] * wl["dims"][1]
+    for _ in range(args.warmup):
+        cpu_run_layers(m, wl, layers[:1])
+    t = 0.0
+    for _ in range(args.steps):
+        t += cpu_run_layers(m, wl, layers)
+    v = nvox * args.steps / t
+    sample = f"each step = {len(layers)} evenly spaced z-layers ({nvox} voxels) of the workload; mesh+tree setup {setup_s:.1f} s excluded"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl["desc"], "timing": "host wall clock, all host threads (TBB)"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------------------------------
+
+def run_ours(args, wl):
+    import torch
+    import torch.distributed as dist
+    import meshlib_b200 as mb
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun --nproc-per-node {args.gpus}")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+
+    dims, xf = wl["dims"], wl["xf"]
+    o = wl["opts"]
+    opts = mb.DistOptions(o["min_dist_sq"], o["max_dist_sq"], o["null_outside"], o["threshold"], o["beta"])
+    layer = dims[0] * dims[1]
+    total = layer * dims[2]
+    z0, z1 = rank * dims[2] // world, (rank + 1) * dims[2] // world
+    assert dims[2] % world == 0 or world == 1, "z layers must divide evenly for the in-place all-gather"
+
+    fwn = mb.FastWindingNumber(wl["points"], wl["tris"], device=local)
+    st0 = fwn.stats()
+    # full volume on every GPU (north_star: slabs gathered by NCCL all-gather); rank r writes its slab in place
+    volume = torch.empty(total, dtype=torch.float32, device=dev)
+    slab = volume[z0 * layer:z1 * layer]
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+
+    def step():
+        """returns (kernel ms on the launching stream, gather ms)"""
+        fwn.calc_from_grid_with_distances_device(dims, xf, slab.data_ptr(), opts, z_begin=z0, z_end=z1)
+        k_ms = fwn.stats().last_kernel_ms
+        g_ms = 0.0
+        if world > 1:
+            ev[0].record()
+            dist.all_gather_into_tensor(volume, slab)
+            ev[1].record()
+            ev[1].synchronize()
+            g_ms = ev[0].elapsed_time(ev[1])
+        return k_ms, g_ms
+
+    for _ in range(args.warmup):
+        step()
+    launches0 = fwn.stats().kernel_launches
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    t0 = time.perf_counter()
+    k_sum = g_sum = 0.0
+    for _ in range(args.steps):
+        k, g = step()
+        k_sum += k
+        g_sum += g
+    barrier()
+    wall_ms = 1e3 * (time.perf_counter() - t0)
+    clocks = sampler.stop() if rank == 0 else None
+    launches = fwn.stats().kernel_launches - launches0
+    t = torch.tensor([k_sum + g_sum, k_sum, g_sum, wall_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, k_ms, g_ms, wall_ms = (float(x) / args.steps for x in t.tolist())
+    checksum = float(torch.nan_to_num(volume[:: max(1, total // (1 << 22))]).double().abs().sum())
+
+    # ---- e2e: host mesh -> create (H2D + device tree build) -> host volume, all inside the timed region --------------
+    e2e = None
+    if not args.no_e2e:
+        del volume, slab
+        torch.cuda.empty_cache()
+        nslab = (z1 - z0) * layer
+        host = torch.empty(nslab, dtype=torch.float32, pin_memory=True)
+        host_np = host.numpy()
+        sub_xf = np.array(xf, np.float32)
+        # the slab as its own grid: b' = A*(0,0,z0) + b would round differently; use the by-layers host call instead
+        e_steps = max(1, min(args.steps, 3))
+        fwn.close()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e_steps):
+            f2 = mb.FastWindingNumber(wl["points"], wl["tris"], device=local)
+            f2.calc_from_grid_with_distances_layers(dims, sub_xf, z0, z1, opts, out=host_np)
+            f2.close()
+        barrier()
+        e_ms = 1e3 * (time.perf_counter() - t0) / e_steps
+        t = torch.tensor([e_ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e_ms = float(t[0])
+        e2e = {"value": total / (e_ms * 1e-3), "unit": UNIT, "ms_per_step": e_ms, "steps": e_steps,
+               "h2d_bytes_per_step": int(wl["points"].nbytes + wl["tris"].nbytes + 12 * 4 + 20),
+               "d2h_bytes_per_step": int(4 * nslab),
+               "includes": "b2fwn_create (mesh H2D + device tree/dipole build) + grid call into pinned host memory, per rank; host wall clock"}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    value = total / (dev_ms * 1e-3)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak, hbm_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json)") if "hbm_gbs" in peaks else (6650.0, "fallback")
+    fp32_peak = mb.measure_fp32_peak(local)
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dev_ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": wl["desc"], "sharding": f"z-slab x{world}, mesh+tree replicated, NCCL all-gather of slabs" if world > 1 else "single GPU",
+                   "l2": "inputs larger than L2 (tree+triangles %.0f MB, output %.0f MB per step)" % (
+                       (st0.num_nodes * 64 + st0.num_leaves * 48) / 1e6, 4 * total / 1e6),
+                   "timing": "CUDA events on the launching stream (kernel) + torch events (all-gather), max over ranks"},
+        "kernel_ms_per_step": k_ms, "gather_ms_per_step": g_ms, "wall_ms_per_step": wall_ms,
+        "tree_build_ms": st0.tree_build_ms, "num_faces": int(st0.num_leaves), "num_nodes": int(st0.num_nodes),
+        "clocks": clocks, "gpu_launches": int(launches), "checksum": checksum,
+    }
+    if e2e:
+        out["e2e"] = e2e
+    # roofline of the dominant kernel (kGridLockstep<1>): FP32 pipe, per north_star; HBM figures beside it
+    out["roofline"] = {"bound": "fp32", "achieved": None, "peak": fp32_peak, "unit": "TFLOP/s", "frac": None, "traffic": None,
+                       "peak_source": "FFMA micro-benchmark run on this GPU just now (b2fwn_measure_fp32_peak)",
+                       "hbm": {"algorithmic_bytes_per_voxel": 4.0 + (st0.num_nodes * 64 + st0.num_leaves * 48) * world / total,
+                               "peak": hbm_peak, "peak_source": hbm_src, "unit": "GB/s"}}
+    nslab0 = (dims[2] // world) * layer  # voxels of one launch (rank 0's slab)
+    out["roofline"]["hbm"]["achieved"] = (4.0 * nslab0 + st0.num_nodes * 64 + st0.num_leaves * 48) / (k_ms * 1e-3) / 1e9
+    out["roofline"]["hbm"]["frac"] = out["roofline"]["hbm"]["achieved"] / hbm_peak
+    if world == 1 and not args.no_cpu:
+        cb = cpu_baseline(wl, args.cpu_budget)
+        fpv, per_voxel, n = algorithmic_flops(wl, cb["layers"])
+        del cb["layers"]
+        out["cpu_baseline"] = cb
+        ach = fpv * nslab0 / (k_ms * 1e-3) / 1e12
+        out["roofline"].update({"achieved": ach, "frac": ach / fp32_peak, "flops_per_voxel": fpv, "ops_per_voxel": per_voxel,
+                                "ops_sample": f"{n} voxels (stride sample of the cpu_baseline layers), reference algorithm counters"})
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--grid", type=int, default=None, help="override the grid size (diagnostics only; not the headline)")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--cpu-budget", type=float, default=15.0)
+    args = ap.parse_args()
+    wl = build_workload(args.workload, args.grid)
+    if args.impl == "reference":
+        run_reference_arm(args, wl)
+    else:
+        run_ours(args, wl)
+
+
+if __name__ == "__main__":
+    main()

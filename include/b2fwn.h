@@ -108,6 +108,12 @@ int b2fwn_calc_from_grid_with_distances_device( b2fwn_handle h, const int32_t di
                                                 const b2fwn_dist_options* opt, int32_t z_begin, int32_t z_end,
                                                 float* d_out );
 
+/* host-output form of one z-range [z_begin, z_end) of the grid (out[0] = voxel (0,0,z_begin)): what one rank of a
+ * z-slab sharded run calls; b2fwn_calc_from_grid_with_distances is this with the full range */
+int b2fwn_calc_from_grid_with_distances_layers( b2fwn_handle h, const int32_t dims[3], const float xf[12],
+                                                const b2fwn_dist_options* opt, int32_t z_begin, int32_t z_end, float* out,
+                                                b2fwn_progress cb, void* user );
+
 /* IFastWindingNumberByParts::calcFromGridByParts / calcFromGridWithDistancesByParts
  * (MRFastWindingNumber.h:96-106; GPU MRCudaFastWindingNumber.cpp:285-429).  Parts are whole z-layers, delivered
  * strictly in increasing z on the calling thread, consecutive parts overlapping by layer_overlap layers
@@ -126,6 +132,10 @@ int b2fwn_calc_from_grid_with_distances_by_parts( b2fwn_handle h, const int32_t 
 int b2fwn_get_tree( b2fwn_handle h, void* out_nodes_32B, void* out_dipoles_32B, size_t capacity_nodes, size_t* n_nodes );
 
 int b2fwn_get_stats( b2fwn_handle h, b2fwn_stats* out );
+
+/* diagnostics: measured FP32 FMA throughput (TFLOP/s) of the device = the roofline denominator bench.py reports
+ * the traversal kernels against (no reference counterpart) */
+int b2fwn_measure_fp32_peak( int32_t device, double* tflops );
 
 /* marching cubes over a dense float volume (replaces MR::marchingCubes(SimpleVolume) =
  * VolumeMesher::run, source/MRVoxels/MRMarchingCubes.cpp:382-398, 548-662, 812-1102).

@@ -60,7 +60,7 @@ EXPORTS = [
     "b2fwn_calc_from_grid", "b2fwn_calc_from_grid_device", "b2fwn_calc_from_grid_with_distances",
     "b2fwn_calc_from_grid_with_distances_device", "b2fwn_calc_from_grid_by_parts",
     "b2fwn_calc_from_grid_with_distances_by_parts", "b2fwn_get_tree", "b2fwn_get_stats", "b2fwn_marching_cubes",
-    "b2fwn_marching_cubes_fetch",
+    "b2fwn_marching_cubes_fetch", "b2fwn_calc_from_grid_with_distances_layers", "b2fwn_measure_fp32_peak",
 ]
 
 
@@ -88,6 +88,9 @@ def load_library():
     L.b2fwn_calc_from_grid_with_distances.argtypes = [vp, i32p, f32p, C.POINTER(DistOptions), vp, PROGRESS_CB, vp]
     L.b2fwn_calc_from_grid_with_distances_device.argtypes = [vp, i32p, f32p, C.POINTER(DistOptions), C.c_int32,
                                                              C.c_int32, vp]
+    L.b2fwn_calc_from_grid_with_distances_layers.argtypes = [vp, i32p, f32p, C.POINTER(DistOptions), C.c_int32, C.c_int32,
+                                                             vp, PROGRESS_CB, vp]
+    L.b2fwn_measure_fp32_peak.argtypes = [C.c_int32, C.POINTER(C.c_double)]
     L.b2fwn_calc_from_grid_by_parts.argtypes = [vp, i32p, f32p, C.c_float, C.c_int32, C.c_int32, PART_CB, vp,
                                                 PROGRESS_CB, vp]
     L.b2fwn_calc_from_grid_with_distances_by_parts.argtypes = [vp, i32p, f32p, C.POINTER(DistOptions), C.c_int32,
@@ -127,6 +130,13 @@ def make_basis_xf(origin, voxel_size):
     v = np.asarray(voxel_size, np.float32) * np.ones(3, np.float32)
     b = o + np.float32(0.5) * v
     return np.array([v[0], 0, 0, 0, v[1], 0, 0, 0, v[2], b[0], b[1], b[2]], np.float32)
+
+
+def measure_fp32_peak(device=0):
+    """measured FP32 FMA throughput of the device in TFLOP/s (roofline denominator of the traversal kernels)"""
+    v = C.c_double()
+    _check(load_library().b2fwn_measure_fp32_peak(device, C.byref(v)))
+    return v.value
 
 
 NODE_DTYPE = np.dtype([("bmin", np.float32, 3), ("bmax", np.float32, 3), ("l", np.int32), ("r", np.int32)])
@@ -187,6 +197,15 @@ class FastWindingNumber:
         res = out if out is not None else np.empty(n, np.float32)
         _check(_lib.b2fwn_calc_from_grid_with_distances(self._h, _dims(dims), _xf(grid_to_mesh_xf), C.byref(options),
                                                         res.ctypes.data, _progress(cb), None))
+        return res
+
+    def calc_from_grid_with_distances_layers(self, dims, grid_to_mesh_xf, z_begin, z_end, options=None, cb=None, out=None):
+        """layers [z_begin, z_end) of the grid into host memory (one rank's z-slab)"""
+        options = options or DistOptions()
+        n = int(dims[0]) * int(dims[1]) * (z_end - z_begin)
+        res = out if out is not None else np.empty(n, np.float32)
+        _check(_lib.b2fwn_calc_from_grid_with_distances_layers(self._h, _dims(dims), _xf(grid_to_mesh_xf), C.byref(options),
+                                                               z_begin, z_end, res.ctypes.data, _progress(cb), None))
         return res
 
     # ---- IFastWindingNumberByParts ----

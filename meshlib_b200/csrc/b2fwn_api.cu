@@ -120,10 +120,11 @@ int defaultLayersPerPart( const int32_t dims[3], int overlap )
 // the calling thread, while the next chunk is computed (the reference's cudaPipeline, source/MRCuda/MRCudaPipeline.hpp:9-48).
 // Otherwise chunks are copied straight into hostOut.
 template <typename Launch>
-int runChunked( b2fwn_ctx* h, const int32_t dims[3], int overlap, int layersPerPart, float* hostOut, b2fwn_part_cb part,
-                void* partUser, b2fwn_progress cb, void* user, Launch launch )
+int runChunked( b2fwn_ctx* h, const int32_t dims[3], int zBegin, int zEnd, int overlap, int layersPerPart, float* hostOut,
+                b2fwn_part_cb part, void* partUser, b2fwn_progress cb, void* user, Launch launch )
 {
-    const int nz = dims[2];
+    if ( zBegin < 0 || zEnd > dims[2] || zBegin > zEnd ) { setError( "invalid layer range" ); return B2FWN_ERR_INVALID; }
+    const int nz = zEnd - zBegin;
     const size_t layer = (size_t)dims[0] * dims[1];
     if ( nz == 0 || layer == 0 ) return B2FWN_OK;
     if ( overlap < 0 ) { setError( "negative layer overlap" ); return B2FWN_ERR_INVALID; }
@@ -148,7 +149,7 @@ int runChunked( b2fwn_ctx* h, const int32_t dims[3], int overlap, int layersPerP
         {
             const int z0 = k * step, z1 = std::min( nz, z0 + layersPerPart );
             const int32_t pd[3] = { dims[0], dims[1], z1 - z0 };
-            if ( part( h->hPinned[s], pd, z0, partUser ) != 0 )
+            if ( part( h->hPinned[s], pd, zBegin + z0, partUser ) != 0 )
             {
                 setError( "by-parts consumer failed" );
                 return B2FWN_ERR_CANCELED;
@@ -162,7 +163,7 @@ int runChunked( b2fwn_ctx* h, const int32_t dims[3], int overlap, int layersPerP
         const int z0 = k * step, z1 = std::min( nz, z0 + layersPerPart );
         // slot s is free again once the copy of chunk k-2 finished (finishPart(k-2) waited for it)
         cudaEventRecord( h->evA, h->stream );
-        if ( int e = launch( z0, z1, h->dScratch[s] ) ) return e;
+        if ( int e = launch( zBegin + z0, zBegin + z1, h->dScratch[s] ) ) return e;
         cudaEventRecord( h->evB, h->stream );
         B2_CUDA( cudaEventRecord( h->computeDone[s], h->stream ) );
         B2_CUDA( cudaStreamWaitEvent( h->copyStream, h->computeDone[s], 0 ) );
@@ -407,7 +408,7 @@ int b2fwn_calc_from_grid_by_parts( b2fwn_handle h, const int32_t dims[3], const 
     if ( !h || !dims || !xf || !part ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
     B2_CUDA( cudaSetDevice( h->device ) );
     const GridXf g = toXf( xf );
-    return runChunked( h, dims, overlap, maxLayers, nullptr, part, partUser, cb, user, [&]( int z0, int z1, float* d )
+    return runChunked( h, dims, 0, dims[2], overlap, maxLayers, nullptr, part, partUser, cb, user, [&]( int z0, int z1, float* d )
         { return launchFwnGrid( h->tree, dims, g, beta, z0, z1, d, h->stream, &h->stats.kernel_launches ); } );
 }
 
@@ -419,7 +420,7 @@ int b2fwn_calc_from_grid_with_distances_by_parts( b2fwn_handle h, const int32_t 
     B2_CUDA( cudaSetDevice( h->device ) );
     const GridXf g = toXf( xf );
     const b2fwn_dist_options o = *opt;
-    return runChunked( h, dims, overlap, maxLayers, nullptr, part, partUser, cb, user, [&]( int z0, int z1, float* d )
+    return runChunked( h, dims, 0, dims[2], overlap, maxLayers, nullptr, part, partUser, cb, user, [&]( int z0, int z1, float* d )
         { return launchSdfGrid( h->tree, dims, g, o, z0, z1, d, h->stream, &h->stats.kernel_launches ); } );
 }
 
@@ -431,21 +432,80 @@ int b2fwn_calc_from_grid( b2fwn_handle h, const int32_t dims[3], const float xf[
     if ( (size_t)dims[0] * dims[1] * dims[2] && !out ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
     B2_CUDA( cudaSetDevice( h->device ) );
     const GridXf g = toXf( xf );
-    return runChunked( h, dims, 0, 0, out, nullptr, nullptr, cb, user, [&]( int z0, int z1, float* d )
+    return runChunked( h, dims, 0, dims[2], 0, 0, out, nullptr, nullptr, cb, user, [&]( int z0, int z1, float* d )
         { return launchFwnGrid( h->tree, dims, g, beta, z0, z1, d, h->stream, &h->stats.kernel_launches ); } );
+}
+
+int b2fwn_calc_from_grid_with_distances_layers( b2fwn_handle h, const int32_t dims[3], const float xf[12],
+                                                const b2fwn_dist_options* opt, int32_t zBegin, int32_t zEnd, float* out,
+                                                b2fwn_progress cb, void* user )
+{
+    if ( !h || !dims || !xf || !opt ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    if ( dims[0] < 0 || dims[1] < 0 || dims[2] < 0 ) { setError( "invalid grid dimensions" ); return B2FWN_ERR_INVALID; }
+    if ( zBegin < 0 || zEnd > dims[2] || zBegin > zEnd ) { setError( "invalid layer range" ); return B2FWN_ERR_INVALID; }
+    if ( (size_t)dims[0] * dims[1] * ( zEnd - zBegin ) && !out ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    const GridXf g = toXf( xf );
+    const b2fwn_dist_options o = *opt;
+    return runChunked( h, dims, zBegin, zEnd, 0, 0, out, nullptr, nullptr, cb, user, [&]( int z0, int z1, float* d )
+        { return launchSdfGrid( h->tree, dims, g, o, z0, z1, d, h->stream, &h->stats.kernel_launches ); } );
 }
 
 int b2fwn_calc_from_grid_with_distances( b2fwn_handle h, const int32_t dims[3], const float xf[12],
                                          const b2fwn_dist_options* opt, float* out, b2fwn_progress cb, void* user )
 {
-    if ( !h || !dims || !xf || !opt ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
-    if ( dims[0] < 0 || dims[1] < 0 || dims[2] < 0 ) { setError( "invalid grid dimensions" ); return B2FWN_ERR_INVALID; }
-    if ( (size_t)dims[0] * dims[1] * dims[2] && !out ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
-    B2_CUDA( cudaSetDevice( h->device ) );
-    const GridXf g = toXf( xf );
-    const b2fwn_dist_options o = *opt;
-    return runChunked( h, dims, 0, 0, out, nullptr, nullptr, cb, user, [&]( int z0, int z1, float* d )
-        { return launchSdfGrid( h->tree, dims, g, o, z0, z1, d, h->stream, &h->stats.kernel_launches ); } );
+    if ( !dims ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    return b2fwn_calc_from_grid_with_distances_layers( h, dims, xf, opt, 0, dims[2], out, cb, user );
+}
+
+// ---- diagnostics: FP32 FMA-pipe peak of this GPU (the roofline denominator of the traversal kernels) -------------------
+
+namespace
+{
+__global__ void __launch_bounds__( 256 ) kFmaPeak( float* out, int iters, float a, float b )
+{
+    float x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+    for ( int i = 0; i < iters; ++i )
+    {
+#pragma unroll
+        for ( int u = 0; u < 16; ++u )
+        {
+            x0 = fmaf( x0, a, b ); x1 = fmaf( x1, a, b ); x2 = fmaf( x2, a, b ); x3 = fmaf( x3, a, b );
+            x4 = fmaf( x4, a, b ); x5 = fmaf( x5, a, b ); x6 = fmaf( x6, a, b ); x7 = fmaf( x7, a, b );
+        }
+    }
+    const float r = ( ( x0 + x1 ) + ( x2 + x3 ) ) + ( ( x4 + x5 ) + ( x6 + x7 ) );
+    if ( r == 12345.678f ) out[0] = r; // never true; keeps the chain alive
+}
+} // namespace
+
+int b2fwn_measure_fp32_peak( int32_t device, double* tflops )
+{
+    if ( !tflops ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( device ) );
+    cudaDeviceProp prop;
+    B2_CUDA( cudaGetDeviceProperties( &prop, device ) );
+    float* d = nullptr;
+    B2_CUDA( cudaMalloc( &d, 4 ) );
+    cudaEvent_t a, b;
+    cudaEventCreate( &a ); cudaEventCreate( &b );
+    const int blocks = prop.multiProcessorCount * 8, iters = 4096;
+    double best = 0;
+    for ( int rep = 0; rep < 4; ++rep )
+    {
+        cudaEventRecord( a );
+        kFmaPeak<<<blocks, 256>>>( d, iters, 1.0000001f, 1e-9f );
+        cudaEventRecord( b );
+        if ( cudaEventSynchronize( b ) != cudaSuccess ) break;
+        float ms = 0;
+        cudaEventElapsedTime( &ms, a, b );
+        const double fl = 2.0 * 8 * 16 * (double)iters * 256.0 * blocks;
+        if ( rep > 0 && ms > 0 ) best = std::max( best, fl / ( ms * 1e-3 ) / 1e12 );
+    }
+    cudaEventDestroy( a ); cudaEventDestroy( b ); cudaFree( d );
+    B2_CUDA( cudaGetLastError() );
+    *tflops = best;
+    return B2FWN_OK;
 }
 
 // ---- marching cubes ------------------------------------------------------------------------------------------------------

@@ -1,0 +1,63 @@
+"""oracle/checker.py -- TEST INFRASTRUCTURE ONLY.  Parity rules of BASELINE.json's north_star made executable
+(SURVEY.md 8(c) "Parity rules"): sign identical outside |w_ref - threshold| < band, NaN masks identical, distances within
+rel_tol relative; winding numbers compared by absolute difference; self-intersection bits outside the bands at 0 and 1."""
+import numpy as np
+
+from . import portlib, reflib
+
+W_BAND = 1e-3
+DIST_REL_TOL = 1e-5
+
+
+def best_oracle(points, tris):
+    """the unmodified reference (oracle/_ref) where it was built, else the C restatement"""
+    if reflib.available():
+        m = reflib.RefMesh.from_arrays(points, tris)
+        m.kind = "reference"
+        return m
+    return portlib.PortMesh(points, tris)
+
+
+def compare_w(got, want, atol=2e-6):
+    got, want = np.asarray(got, np.float32), np.asarray(want, np.float32)
+    diff = np.abs(got.astype(np.float64) - want.astype(np.float64))
+    return {"ok": bool(got.shape == want.shape and (diff <= atol).all()), "max_abs_diff": float(diff.max()) if diff.size else 0.0,
+            "bit_exact_frac": float((got.view(np.uint32) == want.view(np.uint32)).mean()) if diff.size else 1.0, "n": int(diff.size)}
+
+
+def compare_sdf(got, want, w_ref=None, threshold=0.5, band=W_BAND, rel_tol=DIST_REL_TOL):
+    """got/want: signed distances with NaN; w_ref: reference winding numbers of the same voxels (None = no band excuse)"""
+    got, want = np.asarray(got, np.float32), np.asarray(want, np.float32)
+    rep = {"n": int(want.size)}
+    if got.shape != want.shape:
+        return {"ok": False, "why": f"shape {got.shape} vs {want.shape}"}
+    gn, wn = np.isnan(got), np.isnan(want)
+    rep["nan_mismatch"] = int((gn != wn).sum())
+    both = ~gn & ~wn
+    g, w = got[both], want[both]
+    sign_diff = np.signbit(g) != np.signbit(w)
+    if w_ref is not None:
+        inband = np.abs(np.asarray(w_ref, np.float32)[both].astype(np.float64) - threshold) < band
+        rep["in_band"] = int(inband.sum())
+        rep["sign_mismatch_in_band"] = int((sign_diff & inband).sum())
+        sign_diff = sign_diff & ~inband
+    rep["sign_mismatch"] = int(sign_diff.sum())
+    ad, aw = np.abs(g).astype(np.float64), np.abs(w).astype(np.float64)
+    err = np.abs(ad - aw)
+    bad = err > rel_tol * aw
+    rep["dist_mismatch"] = int(bad.sum())
+    rep["max_rel_err"] = float((err[aw > 0] / aw[aw > 0]).max()) if (aw > 0).any() else 0.0
+    rep["dist_bit_exact_frac"] = float((np.abs(g).view(np.uint32) == np.abs(w).view(np.uint32)).mean()) if g.size else 1.0
+    rep["ok"] = rep["nan_mismatch"] == 0 and rep["sign_mismatch"] == 0 and rep["dist_mismatch"] == 0
+    return rep
+
+
+def compare_bits(got_words, want_words, w_ref, n_faces, band=W_BAND):
+    """self-intersection bitsets: equal outside the bands |w| < band, |w-1| < band"""
+    got = np.unpackbits(np.asarray(got_words, np.uint64).view(np.uint8), bitorder="little")[:n_faces].astype(bool)
+    want = np.unpackbits(np.asarray(want_words, np.uint64).view(np.uint8), bitorder="little")[:n_faces].astype(bool)
+    w = np.asarray(w_ref, np.float64)
+    inband = (np.abs(w) < band) | (np.abs(w - 1) < band)
+    mism = (got != want)
+    return {"ok": bool(not (mism & ~inband).any()), "mismatch": int((mism & ~inband).sum()), "mismatch_in_band": int((mism & inband).sum()),
+            "set": int(want.sum()), "n": int(n_faces)}

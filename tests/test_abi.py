@@ -1,0 +1,69 @@
+"""CPU tests of the drop-in boundary: libb2fwn.so loads, exports every symbol include/b2fwn.h declares, and fails loudly
+(no CPU fallback) when there is no CUDA device."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+import meshlib_b200 as mb
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    src = open(os.path.join(ROOT, "include", "b2fwn.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(b2fwn_[a-z_0-9]+)\s*\(", src)))
+
+
+def test_header_symbols_exported():
+    L = mb.load_library()
+    names = _declared()
+    assert len(names) >= 18
+    for n in names:
+        assert hasattr(L, n), f"{n} declared in include/b2fwn.h but not exported"
+    assert sorted(mb.EXPORTS) == names
+
+
+def test_struct_layouts_match_header():
+    assert C.sizeof(mb.DistOptions) == 20
+    assert C.sizeof(mb.api.Config) == 32
+    assert C.sizeof(mb.api.Stats) == 64
+    assert C.sizeof(mb.api.McParams) == 48
+    o = mb.DistOptions()
+    assert (o.min_dist_sq, o.null_outside_min_max, o.winding_number_threshold, o.winding_number_beta) == (0.0, 1, 0.5, 2.0)
+    assert o.max_dist_sq == np.finfo(np.float32).max
+
+
+def test_no_cpu_fallback_without_device():
+    L = mb.load_library()
+    if L.b2fwn_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    from meshlib_b200 import meshgen
+    pts, tris = meshgen.make_uv_sphere(1, 8, 8)
+    with pytest.raises(mb.B2Error) as e:
+        mb.FastWindingNumber(pts, tris)
+    assert "NVIDIA GPU error" in str(e.value)
+
+
+def test_product_does_not_touch_oracle():
+    # the product path may not import, link, load or execute anything under oracle/
+    bad = re.compile(r"^\s*(from|import)\s+oracle|liboracle|libmrref|oracle/|from \.\. ?import oracle", re.M)
+    for dirpath, _d, files in os.walk(os.path.join(ROOT, "meshlib_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp", ".cpp")) or f == "Makefile":
+                s = open(os.path.join(dirpath, f)).read()
+                assert not bad.search(s), f"{f} references the oracle"
+
+
+def test_meshgen_shapes():
+    from meshlib_b200 import meshgen
+    p, t = meshgen.make_torus(2, 1, 256, 128)
+    assert p.shape == (32768, 3) and t.shape == (65536, 3) and t.max() == 32767
+    p, t = meshgen.make_uv_sphere(1, 1000, 500)
+    assert t.shape == (1000000, 3) and p.shape == (500002, 3)
+    q = meshgen.query_points(1000)
+    assert q.shape == (1000, 3) and q.min() >= -1.5 and q.max() <= 1.5
+    assert np.array_equal(q, meshgen.query_points(1000))

@@ -1,0 +1,255 @@
+"""GPU parity tests (run on the B200 box): the CUDA path through the C ABI against the oracle (the unmodified reference
+in oracle/_ref when it travelled with the snapshot, else the C restatement) on the same seeded inputs."""
+import os
+
+import numpy as np
+import pytest
+
+import meshlib_b200 as mb
+from meshlib_b200 import meshgen
+from oracle import checker, portlib
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _mesh(name):
+    if name == "torus":
+        return meshgen.make_torus(2, 1, 96, 48)
+    if name == "sphere":
+        return meshgen.make_uv_sphere(1, 64, 32)
+    p, t = meshgen.make_uv_sphere(1, 80, 40)
+    p = meshgen.add_noise(p, 4e-3)
+    if name == "holes":
+        t = t[np.arange(len(t)) % 9 != 4]
+    if name == "deleted":
+        t = t.copy()
+        t[::13] = -1  # deleted faces keep their slot (MeshTopology::getTriangulation)
+    return p, t
+
+
+@pytest.fixture(scope="module", params=["torus", "sphere", "noisy", "holes"])
+def pair(request):
+    pts, tris = _mesh(request.param)
+    orc = checker.best_oracle(pts, tris)
+    if orc.kind == "reference":
+        tris = orc.tris  # the reference's own per-face vertex order
+    fwn = mb.FastWindingNumber(pts, tris)
+    yield request.param, pts, tris, orc, fwn
+    fwn.close()
+
+
+def test_tree_and_dipoles_bit_exact(pair):
+    _n, _p, _t, orc, fwn = pair
+    nodes, dip = fwn.get_tree()
+    assert nodes.tobytes() == orc.nodes().tobytes()
+    assert dip.tobytes() == orc.dipoles().tobytes()
+
+
+def test_calc_from_vector(pair):
+    _n, pts, _t, orc, fwn = pair
+    q = meshgen.query_points(40000, float(pts.min()) - 0.7, float(pts.max()) + 0.7, seed=99)
+    got = fwn.calc_from_vector(q)
+    want = orc.calc_from_vector(q)
+    rep = checker.compare_w(got, want, atol=2e-6)
+    assert rep["ok"], rep
+    got = fwn.calc_from_vector(q[:3000], beta=3.0, skip_face=5)
+    rep = checker.compare_w(got, orc.calc_from_vector(q[:3000], beta=3.0, skip_face=5), atol=2e-6)
+    assert rep["ok"], rep
+    assert len(fwn.calc_from_vector(np.zeros((0, 3), np.float32))) == 0
+
+
+def test_calc_from_grid(pair):
+    _n, pts, _t, orc, fwn = pair
+    dims = (37, 29, 23)  # ragged: not multiples of the brick
+    lo, hi = pts.min(0) - 0.3, pts.max(0) + 0.3
+    xf = mb.make_basis_xf(lo, (hi - lo) / np.asarray(dims, np.float32))
+    rep = checker.compare_w(fwn.calc_from_grid(dims, xf), orc.calc_from_grid(dims, xf), atol=2e-6)
+    assert rep["ok"], rep
+
+
+def test_calc_from_grid_with_distances(pair):
+    _n, pts, _t, orc, fwn = pair
+    dims = (40, 33, 26)
+    lo, hi = pts.min(0) - 0.3, pts.max(0) + 0.3
+    xf = mb.make_basis_xf(lo, (hi - lo) / np.asarray(dims, np.float32))
+    w = orc.calc_from_grid(dims, xf)
+    got = fwn.calc_from_grid_with_distances(dims, xf)
+    rep = checker.compare_sdf(got, orc.calc_from_grid_with_distances(dims, xf), w)
+    assert rep["ok"], rep
+    assert rep["dist_bit_exact_frac"] > 0.999, rep
+    # narrow band with NaN outside (mcOffsetMesh's call, MROffset.cpp:176-183); minDistSq > 0 makes the reference's
+    # early exit order dependent, so in-band distances only have to agree where the reference did not stop early
+    lo2, hi2 = 0.02 ** 2, 0.35 ** 2
+    got = fwn.calc_from_grid_with_distances(dims, xf, mb.DistOptions(lo2, hi2, True))
+    want = orc.calc_from_grid_with_distances(dims, xf, min_dist_sq=lo2, max_dist_sq=hi2, null_outside=True)
+    rep = checker.compare_sdf(got, want, w)
+    assert rep["ok"], rep
+    assert np.isnan(want).any() and not np.isnan(want).all()
+    # no NaN, custom threshold and beta
+    got = fwn.calc_from_grid_with_distances(dims, xf, mb.DistOptions(0.0, hi2, False, 0.3, 2.5))
+    want = orc.calc_from_grid_with_distances(dims, xf, min_dist_sq=0.0, max_dist_sq=hi2, null_outside=False, threshold=0.3, beta=2.5)
+    w2 = orc.calc_from_grid(dims, xf, beta=2.5)
+    rep = checker.compare_sdf(got, want, w2, threshold=0.3)
+    assert rep["ok"], rep
+
+
+def test_self_intersections(pair):
+    _n, _p, tris, orc, fwn = pair
+    got = fwn.calc_self_intersections()
+    port = portlib.PortMesh(orc.points if hasattr(orc, "points") else _p, tris)
+    want, w = port.calc_self_intersections(return_w=True)
+    rep = checker.compare_bits(got, want, w, len(tris))
+    assert rep["ok"], rep
+    if orc.kind == "reference":
+        rep = checker.compare_bits(got, orc.calc_self_intersections(), w, len(tris))
+        assert rep["ok"], rep
+
+
+def test_two_tori_self_intersections_flagged():
+    pts, tris = meshgen.two_tori(2, 0.7, 96, 48)
+    fwn = mb.FastWindingNumber(pts, tris)
+    port = portlib.PortMesh(pts, tris)
+    got = fwn.calc_self_intersections()
+    want, w = port.calc_self_intersections(return_w=True)
+    rep = checker.compare_bits(got, want, w, len(tris))
+    assert rep["ok"], rep
+    assert rep["set"] > 100  # faces of each torus inside the other have w ~ 2
+
+
+def test_deleted_faces_and_empty_mesh():
+    pts, tris = _mesh("deleted")
+    orc = portlib.PortMesh(pts, tris)
+    fwn = mb.FastWindingNumber(pts, tris)
+    nodes, dip = fwn.get_tree()
+    assert nodes.tobytes() == orc.nodes().tobytes() and dip.tobytes() == orc.dipoles().tobytes()
+    q = meshgen.query_points(5000, -1.5, 1.5, seed=3)
+    assert checker.compare_w(fwn.calc_from_vector(q), orc.calc_from_vector(q))["ok"]
+    got = fwn.calc_self_intersections()
+    want, w = orc.calc_self_intersections(return_w=True)
+    assert checker.compare_bits(got, want, w, len(tris))["ok"]
+    # empty mesh: no tree; winding numbers are 0, distances stay at maxDistSq => NaN with the default options
+    e = mb.FastWindingNumber(np.zeros((0, 3), np.float32), np.zeros((0, 3), np.int32))
+    assert (e.calc_from_vector(q[:10]) == 0).all()
+    assert len(e.calc_self_intersections()) == 0
+    # zero-sized grids
+    assert len(fwn.calc_from_grid((0, 5, 5), mb.make_basis_xf((0, 0, 0), 1))) == 0
+    assert len(fwn.calc_from_grid_with_distances((4, 4, 0), mb.make_basis_xf((0, 0, 0), 1))) == 0
+
+
+def test_golden_fixture_from_reference():
+    g = np.load(os.path.join(GOLD, "ref_golden.npz"))
+    for name in ("torus", "noisy_sphere"):
+        fwn = mb.FastWindingNumber(g[f"{name}_points"], g[f"{name}_tris"])
+        nodes, dip = fwn.get_tree()
+        assert nodes.tobytes() == g[f"{name}_nodes"].tobytes()
+        assert dip.tobytes() == g[f"{name}_dipoles"].tobytes()
+        assert checker.compare_w(fwn.calc_from_vector(g[f"{name}_q"]), g[f"{name}_w"])["ok"]
+        dims, xf = tuple(int(x) for x in g[f"{name}_dims"]), g[f"{name}_xf"]
+        assert checker.compare_w(fwn.calc_from_grid(dims, xf), g[f"{name}_wgrid"])["ok"]
+        rep = checker.compare_sdf(fwn.calc_from_grid_with_distances(dims, xf), g[f"{name}_sdf"], g[f"{name}_wgrid"])
+        assert rep["ok"], rep
+        o = g[f"{name}_band_opts"]
+        got = fwn.calc_from_grid_with_distances(dims, xf, mb.DistOptions(float(o[0]), float(o[1]), True))
+        rep = checker.compare_sdf(got, g[f"{name}_sdf_band"], g[f"{name}_wgrid"])
+        assert rep["ok"], rep
+
+
+def test_by_parts_contract():
+    pts, tris = _mesh("torus")
+    fwn = mb.FastWindingNumber(pts, tris)
+    dims = (24, 20, 19)
+    xf = mb.make_basis_xf((-3.2, -3.2, -1.3), (0.27, 0.32, 0.14))
+    full = fwn.calc_from_grid_with_distances(dims, xf)
+    layer = dims[0] * dims[1]
+    for overlap, per_part in ((0, 4), (1, 4), (1, 19), (2, 5), (1, 2)):
+        seen = []
+        vol = np.full(layer * dims[2], np.float32(7e33))
+
+        def part(data, d, z0):
+            assert d[0] == dims[0] and d[1] == dims[1] and len(data) == layer * d[2]
+            seen.append((z0, d[2]))
+            vol[z0 * layer:(z0 + d[2]) * layer] = data
+            return True
+
+        fwn.calc_from_grid_with_distances_by_parts(part, dims, xf, layer_overlap=overlap, max_layers_per_part=per_part)
+        want = [(o, s) for o, s in portlib.split_by_chunks(dims[2], per_part, overlap)]  # MRChunkIterator.cpp:25-49
+        assert seen == want, (seen, want)
+        assert vol.tobytes() == full.tobytes()
+    w = fwn.calc_from_grid(dims, xf)
+    got = np.empty_like(w)
+
+    def part_w(data, d, z0):
+        got[z0 * layer:(z0 + d[2]) * layer] = data
+        return True
+
+    fwn.calc_from_grid_by_parts(part_w, dims, xf, layer_overlap=1, max_layers_per_part=6)
+    assert got.tobytes() == w.tobytes()
+    # consumer failure and cancellation surface as errors, reference wording for cancel (MRExpected.h:42-51)
+    with pytest.raises(mb.B2Error):
+        fwn.calc_from_grid_by_parts(lambda *a: False, dims, xf, max_layers_per_part=4)
+    with pytest.raises(mb.B2Error) as e:
+        fwn.calc_from_grid_with_distances(dims, xf, cb=lambda v: False)
+    assert str(e.value) == "Operation was canceled"
+    prog = []
+    fwn.calc_from_grid(dims, xf, cb=lambda v: prog.append(v) or True)
+    assert prog[0] == 0.0 and prog[-1] == 1.0 and prog == sorted(prog)
+
+
+def test_z_slab_device_form_matches_full_grid():
+    import torch
+    pts, tris = _mesh("sphere")
+    fwn = mb.FastWindingNumber(pts, tris)
+    dims = (32, 32, 30)
+    xf = mb.make_basis_xf((-1.3, -1.3, -1.3), (2.6 / 32, 2.6 / 32, 2.6 / 30))
+    full = fwn.calc_from_grid_with_distances(dims, xf)
+    out = torch.empty(dims[0] * dims[1] * dims[2], dtype=torch.float32, device="cuda")
+    layer = dims[0] * dims[1]
+    for z0, z1 in ((0, 7), (7, 8), (8, 30)):
+        fwn.calc_from_grid_with_distances_device(dims, xf, out.data_ptr() + 4 * z0 * layer, z_begin=z0, z_end=z1)
+    assert out.cpu().numpy().tobytes() == full.tobytes()
+
+
+@pytest.mark.parametrize("n", [1, 31, 33, 100000])
+def test_vector_sizes(n):
+    pts, tris = _mesh("sphere")
+    fwn = mb.FastWindingNumber(pts, tris)
+    orc = portlib.PortMesh(pts, tris)
+    q = meshgen.query_points(n, -1.5, 1.5, seed=n)
+    assert checker.compare_w(fwn.calc_from_vector(q), orc.calc_from_vector(q))["ok"]
+
+
+def test_c1_full_size_properties():
+    """BASELINE config 1 at full size (torus 65k faces, 128^3): sampled parity + size-independent properties"""
+    pts, tris = meshgen.make_torus(2, 1, 256, 128)
+    fwn = mb.FastWindingNumber(pts, tris)
+    dims = (128, 128, 128)
+    xf = mb.make_basis_xf((-3.2, -3.2, -3.2), 0.05)
+    sdf = fwn.calc_from_grid_with_distances(dims, xf)
+    assert not np.isnan(sdf).any()
+    vol = (sdf < 0).sum() * 0.05 ** 3  # torus volume 2*pi^2*R*r^2 = 39.48
+    assert abs(vol - 2 * np.pi ** 2 * 2) / 39.48 < 0.01
+    g = sdf.reshape(128, 128, 128)
+    # |grad| <= 1: neighbouring voxels differ by at most one voxel size (distance is 1-Lipschitz)
+    for ax in range(3):
+        assert np.abs(np.diff(g, axis=ax)).max() <= 0.05 * 1.0001
+    # mirror symmetry of the input in z
+    assert np.abs(np.abs(g) - np.abs(g[::-1])).max() < 1e-4
+    port = portlib.PortMesh(pts, tris)
+    stride = 97
+    want = port.calc_from_grid_with_distances(dims, xf, stride=stride)
+    idx = np.arange(0, sdf.size, stride)
+    wref = port.calc_from_vector(_voxel_points(idx, dims, xf))
+    rep = checker.compare_sdf(sdf[idx], want[idx], wref)
+    assert rep["ok"], rep
+
+
+def _voxel_points(idx, dims, xf):
+    x = (idx % dims[0]).astype(np.float32)
+    y = ((idx // dims[0]) % dims[1]).astype(np.float32)
+    z = (idx // (dims[0] * dims[1])).astype(np.float32)
+    xf = np.asarray(xf, np.float32)
+    out = np.empty((len(idx), 3), np.float32)
+    for r in range(3):
+        out[:, r] = (xf[3 * r] * x + xf[3 * r + 1] * y + xf[3 * r + 2] * z) + xf[9 + r]
+    return out

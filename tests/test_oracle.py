@@ -1,0 +1,116 @@
+"""CPU tests: the C restatement (oracle/port.c) against the unmodified reference (oracle/_ref, when built), the
+reference's own known-answer tests for this path, and the committed golden fixtures."""
+import os
+
+import numpy as np
+import pytest
+
+from meshlib_b200 import make_basis_xf, meshgen
+from oracle import portlib, reflib
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+needs_ref = pytest.mark.skipif(not reflib.available(), reason="oracle/_ref not built (needs /root/reference)")
+
+
+def test_triangle_solid_angle_known_answers():
+    # /root/reference/source/MRTest/MRDipoleTests.cpp:12-51
+    tri = [[0, 0, 0], [1, 0, 0], [0, 1, 0]]
+    x = portlib.triangle_solid_angle([1 / 3, 1 / 3, 1e-6], tri)
+    assert abs(x + 2 * np.pi) < 1e-3 or abs(x - 2 * np.pi) < 1e-3
+    y = portlib.triangle_solid_angle([1 / 3, 1 / 3, -1e-6], tri)
+    assert abs(x + y) < 1e-3 and x * y < 0
+    # in the plane of the triangle, outside it: exactly zero
+    for p in ([-1, -1, 0], [2, 2, 0], [0.5, -1, 0]):
+        assert portlib.triangle_solid_angle(p, tri) == 0.0
+    # exactly at a vertex: zero
+    for p in tri:
+        assert portlib.triangle_solid_angle(p, tri) == 0.0
+
+
+def test_tree_known_answers():
+    # MRAABBTreeTests.cpp:10-27: node count = 2F-1, root box = mesh bbox (insignificantly expanded)
+    pts, tris = meshgen.make_uv_sphere(1, 8, 8)
+    m = portlib.PortMesh(pts, tris)
+    nodes = m.nodes()
+    assert len(nodes) == 2 * len(tris) - 1
+    assert (nodes["bmin"][0] <= pts.min(0)).all() and (nodes["bmax"][0] >= pts.max(0)).all()
+    assert np.allclose(nodes["bmin"][0], pts.min(0), atol=1e-6) and np.allclose(nodes["bmax"][0], pts.max(0), atol=1e-6)
+    leaves = nodes[nodes["r"] < 0]
+    assert sorted(leaves["l"].tolist()) == list(range(len(tris)))
+    inner = np.nonzero(nodes["r"] >= 0)[0]
+    assert (nodes["l"][inner] == inner + 1).all() and (nodes["r"][inner] > inner + 1).all()
+
+
+def test_chunk_iterator_known_answers():
+    # /root/reference/source/MRMesh/MRChunkIterator.cpp:52-80 (TEST(MRMesh, ChunkIterator))
+    assert portlib.split_by_chunks(0, 4, 0) == []
+    assert portlib.split_by_chunks(8, 0, 0) == []
+    assert portlib.split_by_chunks(8, 4, 4) == []
+    assert portlib.split_by_chunks(8, 4, 0) == [(0, 4), (4, 4)]
+    assert portlib.split_by_chunks(9, 4, 0) == [(0, 4), (4, 4), (8, 1)]
+    assert portlib.split_by_chunks(10, 4, 1) == [(0, 4), (3, 4), (6, 4)]
+    assert portlib.split_by_chunks(11, 4, 1) == [(0, 4), (3, 4), (6, 4), (9, 2)]
+
+
+def test_closed_mesh_winding_inside_outside():
+    # MRDipoleTests.cpp:35-39 convention: closed outward mesh => w ~ 1 inside, ~ 0 outside
+    pts, tris = meshgen.make_uv_sphere(1, 32, 32)
+    m = portlib.PortMesh(pts, tris)
+    w = m.calc_from_vector([[0, 0, 0], [0.5, 0.2, -0.3], [2, 0, 0], [0, -3, 1]])
+    # the beta=2 dipole far-field is a few-percent approximation on a coarse mesh
+    assert abs(w[0] - 1) < 0.05 and abs(w[1] - 1) < 0.05 and abs(w[2]) < 0.05 and abs(w[3]) < 0.05
+    d = m.find_projection_dist_sq([[2, 0, 0]])
+    assert abs(np.sqrt(d[0]) - 1) < 1e-2
+
+
+@needs_ref
+@pytest.mark.parametrize("mesh", ["torus", "sphere", "noisy", "holes"])
+def test_port_equals_reference_bit_exact(mesh):
+    if mesh == "torus":
+        ref = reflib.RefMesh.torus(2, 1, 48, 24)
+        pts, tris = ref.points, ref.tris
+    elif mesh == "sphere":
+        ref = reflib.RefMesh.uv_sphere(1, 40, 20)
+        pts, tris = ref.points, ref.tris
+    else:
+        pts, tris = meshgen.make_uv_sphere(1, 48, 24)
+        pts = meshgen.add_noise(pts, 5e-3)
+        if mesh == "holes":
+            tris = tris[np.arange(len(tris)) % 7 != 3]
+        ref = reflib.RefMesh.from_arrays(pts, tris)
+        tris = ref.tris
+    port = portlib.PortMesh(pts, tris)
+    assert ref.nodes().tobytes() == port.nodes().tobytes()
+    assert ref.dipoles().tobytes() == port.dipoles().tobytes()
+    q = meshgen.query_points(5000, -2.5, 2.5, seed=7)
+    assert ref.calc_from_vector(q).tobytes() == port.calc_from_vector(q).tobytes()
+    assert ref.calc_from_vector(q[:500], beta=3.0, skip_face=11).tobytes() == port.calc_from_vector(q[:500], beta=3.0, skip_face=11).tobytes()
+    assert ref.find_projection_dist_sq(q).tobytes() == port.find_projection_dist_sq(q).tobytes()
+    assert ref.find_projection_dist_sq(q, up=0.25, lo=0.01).tobytes() == port.find_projection_dist_sq(q, up=0.25, lo=0.01).tobytes()
+    assert np.array_equal(ref.calc_self_intersections(), port.calc_self_intersections())
+    dims, xf = (20, 18, 16), make_basis_xf((-2.6, -2.4, -1.4), (0.26, 0.27, 0.18))
+    assert ref.calc_from_grid(dims, xf).tobytes() == port.calc_from_grid(dims, xf).tobytes()
+    assert ref.calc_from_grid_with_distances(dims, xf).tobytes() == port.calc_from_grid_with_distances(dims, xf).tobytes()
+    a = ref.calc_from_grid_with_distances(dims, xf, min_dist_sq=0.01, max_dist_sq=0.5, null_outside=True)
+    b = port.calc_from_grid_with_distances(dims, xf, min_dist_sq=0.01, max_dist_sq=0.5, null_outside=True)
+    assert a.tobytes() == b.tobytes() and np.isnan(a).any() and not np.isnan(a).all()
+    a = ref.calc_from_grid_with_distances(dims, xf, min_dist_sq=0.01, max_dist_sq=0.5, null_outside=False, threshold=0.3)
+    b = port.calc_from_grid_with_distances(dims, xf, min_dist_sq=0.01, max_dist_sq=0.5, null_outside=False, threshold=0.3)
+    assert a.tobytes() == b.tobytes()
+
+
+def test_port_against_golden_fixture():
+    # tests/golden/ref_golden.npz was produced by the UNMODIFIED reference (tests/golden/make_golden.py)
+    g = np.load(os.path.join(GOLD, "ref_golden.npz"))
+    for name in ("torus", "noisy_sphere"):
+        pts, tris = g[f"{name}_points"], g[f"{name}_tris"]
+        port = portlib.PortMesh(pts, tris)
+        assert port.nodes().tobytes() == g[f"{name}_nodes"].tobytes()
+        assert port.dipoles().tobytes() == g[f"{name}_dipoles"].tobytes()
+        assert port.calc_from_vector(g[f"{name}_q"]).tobytes() == g[f"{name}_w"].tobytes()
+        dims, xf = tuple(int(x) for x in g[f"{name}_dims"]), g[f"{name}_xf"]
+        assert port.calc_from_grid_with_distances(dims, xf).tobytes() == g[f"{name}_sdf"].tobytes()
+        o = g[f"{name}_band_opts"]
+        got = port.calc_from_grid_with_distances(dims, xf, min_dist_sq=float(o[0]), max_dist_sq=float(o[1]), null_outside=True)
+        assert got.tobytes() == g[f"{name}_sdf_band"].tobytes()
+        assert np.array_equal(port.calc_self_intersections(), g[f"{name}_selfint"])
