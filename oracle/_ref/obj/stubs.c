@@ -50,3 +50,7 @@ void mrref_stub_23(void) __asm__("_ZNK2MR12MeshTriPoint8inVertexERKNS_12MeshTopo
 void mrref_stub_23(void) { fprintf(stderr, "oracle/_ref: unlinked reference symbol called: _ZNK2MR12MeshTriPoint8inVertexERKNS_12MeshTopologyE\n"); abort(); }
 void mrref_stub_24(void) __asm__("_ZNK2MR14AABBTreePoints9heapBytesEv");
 void mrref_stub_24(void) { fprintf(stderr, "oracle/_ref: unlinked reference symbol called: _ZNK2MR14AABBTreePoints9heapBytesEv\n"); abort(); }
+void mrref_stub_25(void) __asm__("_ZNK2MR9FloatGridcvbEv");
+void mrref_stub_25(void) { fprintf(stderr, "oracle/_ref: unlinked reference symbol called: _ZNK2MR9FloatGridcvbEv\n"); abort(); }
+void mrref_stub_26(void) __asm__("_ZNK2MR9FloatGridptEv");
+void mrref_stub_26(void) { fprintf(stderr, "oracle/_ref: unlinked reference symbol called: _ZNK2MR9FloatGridptEv\n"); abort(); }

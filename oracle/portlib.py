@@ -40,6 +40,9 @@ def lib():
         L.orc_chunk_count.restype = sz
         L.orc_chunk_count.argtypes = [sz, sz, sz]
         L.orc_chunk.argtypes = [sz, sz, sz, sz, C.POINTER(sz), C.POINTER(sz)]
+        L.orc_marching_cubes.argtypes = [vp, vp, vp, vp, C.c_float, C.c_int, C.POINTER(sz), C.POINTER(sz)]
+        L.orc_marching_cubes_fetch.argtypes = [vp, vp]
+        L.orc_mc_table.restype = C.POINTER(C.c_byte)
         _lib = L
     return _lib
 
@@ -48,6 +51,28 @@ def triangle_solid_angle(p, tri):
     p = np.ascontiguousarray(p, np.float32)
     tri = np.ascontiguousarray(tri, np.float32).reshape(9)
     return float(lib().orc_triangle_solid_angle(p.ctypes.data, tri.ctypes.data))
+
+
+def marching_cubes(volume, dims, voxel_size, origin, iso, less_inside=False):
+    """restatement of MR::marchingCubesAsTriMesh(SimpleVolume) (oracle/port_mc.c): (verts (n,3) f32, tris (m,3) i32)"""
+    vol = np.ascontiguousarray(volume, np.float32).reshape(-1)
+    d = np.ascontiguousarray(dims, np.int32)
+    assert vol.size == int(d[0]) * int(d[1]) * int(d[2])
+    vs = np.ascontiguousarray(np.asarray(voxel_size, np.float32) * np.ones(3, np.float32))
+    o = np.ascontiguousarray(origin, np.float32)
+    nv, nt = C.c_size_t(), C.c_size_t()
+    if lib().orc_marching_cubes(vol.ctypes.data, d.ctypes.data, vs.ctypes.data, o.ctypes.data, iso, int(less_inside),
+                                C.byref(nv), C.byref(nt)) != 0:
+        raise RuntimeError("a part must have at least two Z slices")
+    verts = np.empty((nv.value, 3), np.float32)
+    tris = np.empty((nt.value, 3), np.int32)
+    lib().orc_marching_cubes_fetch(verts.ctypes.data, tris.ctypes.data)
+    return verts, tris
+
+
+def mc_table():
+    """the 256 x 16 case table the restatement and the CUDA kernels share"""
+    return np.ctypeslib.as_array(lib().orc_mc_table(), shape=(256, 16)).copy()
 
 
 def split_by_chunks(total, chunk, overlap):

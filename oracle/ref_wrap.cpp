@@ -6,6 +6,7 @@
 //   MR::FastWindingNumber::{calcFromVector,calcSelfIntersections,calcFromGrid,calcFromGridWithDistances}
 //     (source/MRMesh/MRFastWindingNumber.cpp:28-94)
 //   MR::AABBTree / MR::calcDipoles (source/MRMesh/MRAABBTree.cpp:31-60, MRDipole.cpp:23-71)
+//   MR::marchingCubesAsTriMesh(SimpleVolume) (source/MRVoxels/MRMarchingCubes.cpp:1112-1115 -> VolumeMesher::run)
 //   MR::makeTorus / MR::makeUVSphere (source/MRMesh/MRTorus.cpp:9-59, MRMakeSphereMesh.cpp:35-102)
 // Nothing under meshlib_b200/ may link or load this file's output.
 #include "MRMesh/MRMesh.h"
@@ -18,6 +19,9 @@
 #include "MRMesh/MRMakeSphereMesh.h"
 #include "MRMesh/MRBitSet.h"
 #include "MRMesh/MRTimer.h"
+#include "MRMesh/MRTriMesh.h"
+#include "MRVoxels/MRMarchingCubes.h"
+#include "MRVoxels/MRVoxelsVolume.h"
 #include <cstring>
 #include <thread>
 
@@ -200,6 +204,38 @@ int mrref_find_projection_dist_sq( void* h, const float* pts, size_t n, float up
     for ( size_t i = 0; i < n; ++i )
         out[i] = findProjection( Vector3f( pts[3 * i], pts[3 * i + 1], pts[3 * i + 2] ), m, upDistLimitSq, nullptr, loDistLimitSq ).distSq;
     return 0;
+}
+
+/// marching cubes of a dense float volume by the reference's VolumeMesher (two calls: run -> counts, then fetch)
+static TriMesh g_lastMc;
+int mrref_marching_cubes( const float* vol, const int* dims, const float* voxelSize, const float* origin, float iso,
+    int lessInside, size_t* nVerts, size_t* nTris )
+{
+    SimpleVolume v;
+    v.dims = Vector3i( dims[0], dims[1], dims[2] );
+    v.voxelSize = Vector3f( voxelSize[0], voxelSize[1], voxelSize[2] );
+    v.data.resize( size_t( dims[0] ) * dims[1] * dims[2] );
+    std::memcpy( (void*)v.data.data(), vol, v.data.size() * sizeof( float ) );
+    MarchingCubesParams p;
+    p.origin = Vector3f( origin[0], origin[1], origin[2] );
+    p.iso = iso;
+    p.lessInside = lessInside != 0;
+    auto r = marchingCubesAsTriMesh( v, p );
+    if ( !r )
+        return 1;
+    g_lastMc = std::move( *r );
+    *nVerts = g_lastMc.points.size();
+    *nTris = g_lastMc.tris.size();
+    return 0;
+}
+
+void mrref_marching_cubes_fetch( float* outVerts, int* outTris )
+{
+    std::memcpy( outVerts, (const void*)g_lastMc.points.data(), g_lastMc.points.size() * sizeof( Vector3f ) );
+    for ( size_t t = 0; t < g_lastMc.tris.size(); ++t )
+        for ( int k = 0; k < 3; ++k )
+            outTris[3 * t + k] = (int)g_lastMc.tris.vec_[t][k];
+    g_lastMc = {};
 }
 
 } // extern "C"

@@ -52,6 +52,9 @@ def lib():
         L.mrref_calc_grid_with_distances_layers.argtypes = [
             C.c_void_p, _i32p, _f32p, C.c_float, C.c_float, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int, _f32p]
         L.mrref_find_projection_dist_sq.argtypes = [C.c_void_p, _f32p, C.c_size_t, C.c_float, C.c_float, _f32p]
+        L.mrref_marching_cubes.argtypes = [_f32p, _i32p, _f32p, _f32p, C.c_float, C.c_int, C.POINTER(C.c_size_t),
+                                           C.POINTER(C.c_size_t)]
+        L.mrref_marching_cubes_fetch.argtypes = [_f32p, _i32p]
         _lib = L
     return _lib
 
@@ -151,6 +154,22 @@ class RefMesh:
         out = np.empty(len(pts), np.float32)
         lib().mrref_find_projection_dist_sq(self.h, pts, len(pts), up, lo, out)
         return out
+
+
+def marching_cubes(volume, dims, voxel_size, origin, iso, less_inside=False):
+    """MR::marchingCubesAsTriMesh(SimpleVolume) (source/MRVoxels/MRMarchingCubes.cpp:1112-1115): (verts (n,3) f32, tris (m,3) i32)"""
+    vol = np.ascontiguousarray(volume, np.float32).reshape(-1)
+    d = np.asarray(dims, np.int32)
+    assert vol.size == int(d[0]) * int(d[1]) * int(d[2])
+    vs = np.ascontiguousarray(np.asarray(voxel_size, np.float32) * np.ones(3, np.float32))
+    o = np.ascontiguousarray(origin, np.float32)
+    nv, nt = C.c_size_t(), C.c_size_t()
+    if lib().mrref_marching_cubes(vol, d, vs, o, iso, int(less_inside), C.byref(nv), C.byref(nt)) != 0:
+        raise RuntimeError("reference marching cubes failed")
+    verts = np.empty((nv.value, 3), np.float32)
+    tris = np.empty((nt.value, 3), np.int32)
+    lib().mrref_marching_cubes_fetch(verts, tris)
+    return verts, tris
 
 
 def hardware_threads():
