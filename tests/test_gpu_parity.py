@@ -253,3 +253,41 @@ def _voxel_points(idx, dims, xf):
     for r in range(3):
         out[:, r] = (xf[3 * r] * x + xf[3 * r + 1] * y + xf[3 * r + 2] * z) + xf[9 + r]
     return out
+
+
+# ---- marching cubes (a20) ------------------------------------------------------------------------------------------
+def _mc_cases():
+    from test_oracle_mc import mc_cases
+    return list(mc_cases())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", _mc_cases(), ids=lambda c: c[0])
+def test_marching_cubes_identical_to_oracle(case):
+    from oracle import portlib
+    _, vol, dims, vs, org, iso, li = case
+    fwn = mb.FastWindingNumber(np.zeros((0, 3), np.float32), np.zeros((0, 3), np.int32))
+    v, t = fwn.marching_cubes(vol, dims, org, vs, iso, li)
+    wv, wt = portlib.marching_cubes(vol, dims, vs, org, iso, li)
+    assert v.shape == wv.shape and t.shape == wt.shape
+    assert np.array_equal(v.view(np.uint32), wv.view(np.uint32))
+    assert np.array_equal(t, wt)
+
+
+@pytest.mark.gpu
+def test_marching_cubes_of_device_sdf_counts_match_oracle():
+    """SDF -> MC; counts equal the oracle's MC of the oracle's SDF wherever the sign fields match (north_star)"""
+    from oracle import checker, portlib
+    pts, tris = meshgen.make_torus(2, 1, 96, 48)
+    dims = (48, 48, 40)
+    org = (-3.3, -3.3, -1.4)
+    xf = mb.make_basis_xf(org, 0.14)
+    fwn = mb.FastWindingNumber(pts, tris)
+    got = fwn.calc_from_grid_with_distances(dims, xf)
+    orc = checker.best_oracle(pts, tris)
+    want = orc.calc_from_grid_with_distances(dims, xf)
+    v, t = fwn.marching_cubes(got, dims, org, 0.14, 0.05, True)
+    wv, wt = portlib.marching_cubes(want, dims, 0.14, org, 0.05, True)
+    if np.array_equal(got < 0.05, want < 0.05):
+        assert len(v) == len(wv) and len(t) == len(wt)
+    assert len(t) > 1000 and len(v) - 3 * len(t) // 2 + len(t) == 0  # closed torus: Euler characteristic 0
