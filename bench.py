@@ -332,7 +332,7 @@ def run_ours(args, wl):
         "data": "synthetic",
         "config": {"workload": wl["desc"], "sharding": f"z-slab x{world}, mesh+tree replicated, NCCL all-gather of slabs" if world > 1 else "single GPU",
                    "l2": "inputs larger than L2 (tree+triangles %.0f MB, output %.0f MB per step)" % (
-                       (st0.num_nodes * 64 + st0.num_leaves * 48) / 1e6, 4 * total / 1e6),
+                       (st0.num_nodes * 64 + st0.num_leaves * 64) / 1e6, 4 * total / 1e6),
                    "timing": "CUDA events on the launching stream (kernel) + torch events (all-gather), max over ranks"},
         "kernel_ms_per_step": k_ms, "gather_ms_per_step": g_ms, "wall_ms_per_step": wall_ms,
         "tree_build_ms": st0.tree_build_ms, "num_faces": int(st0.num_leaves), "num_nodes": int(st0.num_nodes),
@@ -343,10 +343,10 @@ def run_ours(args, wl):
     # roofline of the dominant kernel (kGridLockstep<1>): FP32 pipe, per north_star; HBM figures beside it
     out["roofline"] = {"bound": "fp32", "achieved": None, "peak": fp32_peak, "unit": "TFLOP/s", "frac": None, "traffic": None,
                        "peak_source": "FFMA micro-benchmark run on this GPU just now (b2fwn_measure_fp32_peak)",
-                       "hbm": {"algorithmic_bytes_per_voxel": 4.0 + (st0.num_nodes * 64 + st0.num_leaves * 48) * world / total,
+                       "hbm": {"algorithmic_bytes_per_voxel": 4.0 + (st0.num_nodes * 64 + st0.num_leaves * 64) * world / total,
                                "peak": hbm_peak, "peak_source": hbm_src, "unit": "GB/s"}}
     nslab0 = (dims[2] // world) * layer  # voxels of one launch (rank 0's slab)
-    out["roofline"]["hbm"]["achieved"] = (4.0 * nslab0 + st0.num_nodes * 64 + st0.num_leaves * 48) / (k_ms * 1e-3) / 1e9
+    out["roofline"]["hbm"]["achieved"] = (4.0 * nslab0 + st0.num_nodes * 64 + st0.num_leaves * 64) / (k_ms * 1e-3) / 1e9
     out["roofline"]["hbm"]["frac"] = out["roofline"]["hbm"]["achieved"] / hbm_peak
     if world == 1 and not args.no_cpu:
         cb = cpu_baseline(wl, args.cpu_budget)

@@ -39,10 +39,12 @@ struct __align__( 16 ) TravNode
     float4 q0, q1, q2, q3;
 };
 
-// Leaf triangle, 48 B: a.w carries the FaceId bits.
+// Leaf triangle, 64 B (half a 128-B line): a.w carries the FaceId bits; n = unit normal (computed in double, rounded)
+// and n.w = 1e-6 * (largest |coordinate| of the triangle, summed over axes): the rounding allowance of the
+// plane-distance lower bound that filters candidates before the exact (double) closest-point evaluation.
 struct __align__( 16 ) LeafTri
 {
-    float4 a, b, c;
+    float4 a, b, c, n;
 };
 
 struct DeviceTree

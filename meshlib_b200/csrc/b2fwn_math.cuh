@@ -164,4 +164,42 @@ __device__ __forceinline__ float triDistSqExact( const float3 pf, const float4 t
     return dot3( fx, fy, fz, fx, fy, fz );
 }
 
+
+// ---- branch-free / throughput forms used by the brick kernel ---------------------------------------------------------
+
+// Box::getDistanceSq, branch-free and bit-identical to boxDistSq above: per axis d = max(lo - p, p - hi, 0) has the
+// same magnitude as the reference's (p - lo) or (p - hi), and adding the exact zeros of the untouched axes changes nothing
+__device__ __forceinline__ float boxDistSqBF( const float3 p, const float4 q0, const float4 q1 )
+{
+    const float dx = fmaxf( fmaxf( FS( q0.x, p.x ), FS( p.x, q0.w ) ), 0.f );
+    const float dy = fmaxf( fmaxf( FS( q0.y, p.y ), FS( p.y, q1.x ) ), 0.f );
+    const float dz = fmaxf( fmaxf( FS( q0.z, p.z ), FS( p.z, q1.y ) ), 0.f );
+    return FA( FA( FM( dx, dx ), FM( dy, dy ) ), FM( dz, dz ) );
+}
+
+// far-field test of Dipole::addIfGoodApprox with the reference's exact rounding for the DECISION (dd <= beta^2 rr),
+// and a throughput form for the accepted TERM: dot(dp, dirArea) * rsqrt(dd)^3 with one Newton step on the rsqrt
+// (relative error ~1e-7 per term against the reference's dot / (sqrt(dd) * dd); the sign contract is |w - thr| >= 1e-3)
+__device__ __forceinline__ bool dipoleFar( const float3 q, const float thr, const float4 q2, float& dx, float& dy, float& dz, float& dd )
+{
+    dx = FS( q2.x, q.x ); dy = FS( q2.y, q.y ); dz = FS( q2.z, q.z );
+    dd = dot3( dx, dy, dz, dx, dy, dz );
+    return !( dd <= thr );
+}
+__device__ __forceinline__ float dipoleTermFast( const float dx, const float dy, const float dz, const float dd, const float4 q3 )
+{
+    float r = rsqrtf( dd );
+    r = r * fmaf( -0.5f * dd, r * r, 1.5f );
+    return fmaf( dx, q3.x, fmaf( dy, q3.y, dz * q3.z ) ) * ( r * r * r );
+}
+
+// conservative test "the exact squared distance from p to the triangle cannot be below best": the distance to the
+// triangle's plane is a lower bound of the distance to the triangle; allowance = rounding of this evaluation and of the
+// reference's own float rounding of the projection (1e-6 * coordinate magnitudes, >= 8 ulp of every term involved)
+__device__ __forceinline__ bool planeBoundRejects( const float3 p, const float pmag, const float4 ta, const float4 tn, const float best )
+{
+    const float pd = fabsf( fmaf( tn.x, p.x - ta.x, fmaf( tn.y, p.y - ta.y, tn.z * ( p.z - ta.z ) ) ) ) - ( pmag + tn.w );
+    return pd > 0.f && pd * pd >= best;
+}
+
 } // namespace b2

@@ -359,6 +359,15 @@ __global__ void kLeafSlots( int nLeaves, const int32_t* __restrict__ leafNodeOfP
     t.a = make_float4( pts[3 * (size_t)ia], pts[3 * (size_t)ia + 1], pts[3 * (size_t)ia + 2], __int_as_float( (int)f ) );
     t.b = make_float4( pts[3 * (size_t)ib], pts[3 * (size_t)ib + 1], pts[3 * (size_t)ib + 2], 0.f );
     t.c = make_float4( pts[3 * (size_t)ic], pts[3 * (size_t)ic + 1], pts[3 * (size_t)ic + 2], 0.f );
+    // unit normal in double (a zero-area face keeps n = 0: its plane bound is 0 and never filters)
+    const double ux = (double)t.b.x - t.a.x, uy = (double)t.b.y - t.a.y, uz = (double)t.b.z - t.a.z;
+    const double vx = (double)t.c.x - t.a.x, vy = (double)t.c.y - t.a.y, vz = (double)t.c.z - t.a.z;
+    double nx = uy * vz - uz * vy, ny = uz * vx - ux * vz, nz = ux * vy - uy * vx;
+    const double len = sqrt( nx * nx + ny * ny + nz * nz );
+    if ( len > 0 ) { nx /= len; ny /= len; nz /= len; } else { nx = ny = nz = 0; }
+    const float mag = fmaxf( fmaxf( fabsf( t.a.x ), fabsf( t.b.x ) ), fabsf( t.c.x ) ) + fmaxf( fmaxf( fabsf( t.a.y ), fabsf( t.b.y ) ), fabsf( t.c.y ) )
+                      + fmaxf( fmaxf( fabsf( t.a.z ), fabsf( t.b.z ) ), fabsf( t.c.z ) );
+    t.n = make_float4( (float)nx, (float)ny, (float)nz, 1e-6f * mag );
     out[p] = t;
 }
 
