@@ -19,6 +19,8 @@
 #include "b2fwn_math.cuh"
 #include <cfloat>
 #include <climits>
+#include <cstdio>
+#include <cstdlib>
 
 namespace b2
 {
@@ -56,10 +58,16 @@ __device__ __forceinline__ int warpMinResume( const int ( &fR )[VX], const int (
 }
 
 // MODE 0: winding number only (calcFromGrid); MODE 1: signed distance (calcFromGridWithDistances)
-template <int MODE>
+// STATS (development only, B2FWN_STATS=1): operation counters of the walk, summed into `stats`
+//   [0] distance-half node visits (warp level)  [1] box tests by awake voxels   [2] leaf visits that loaded the triangle (warp)
+//   [3] exact closest-point evaluations (voxel)  [4] candidates rejected by the plane bound (voxel)
+//   [5] winding-half node visits (warp)          [6] far-field tests by awake voxels [7] exact solid angles (voxel)
+template <int MODE, bool STATS>
 __global__ void __launch_bounds__( GRID_TB ) kGridBrick( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
-                                                         const GridParams P, float* __restrict__ out )
+                                                         const GridParams P, float* __restrict__ out, unsigned long long* __restrict__ stats )
 {
+    unsigned long long cnt[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+#define B2_COUNT( k, n ) do { if ( STATS ) cnt[k] += ( n ); } while ( 0 )
     const unsigned lane = threadIdx.x & 31;
     const size_t brick = blockIdx.x * (size_t)( GRID_TB / 32 ) + ( threadIdx.x >> 5 );
     const size_t numBricks = (size_t)P.bricksX * P.bricksY * P.bricksZ;
@@ -157,12 +165,14 @@ __global__ void __launch_bounds__( GRID_TB ) kGridBrick( const TravNode* __restr
                 {
                     const float4 q0 = __ldg( np ), q1 = __ldg( np + 1 );
                     const int link = __float_as_int( q1.w );
+                    if ( lane == 0 ) B2_COUNT( 0, 1 );
                     if ( link >= 0 )
                     {
 #pragma unroll
                         for ( int v = 0; v < VX; ++v )
                         {
                             const bool a = i >= dR[v];
+                            B2_COUNT( 1, a );
                             const bool pr = boxDistSqBF( p[v], q0, q1 ) >= best[v]; // MRMeshProject.cpp:30, 48
                             dR[v] = ( a && pr ) ? link : dR[v];
                             descend |= a && !pr;
@@ -176,6 +186,7 @@ __global__ void __launch_bounds__( GRID_TB ) kGridBrick( const TravNode* __restr
                         {
                             const bool a = i >= dR[v];
                             go[v] = a && !( boxDistSqBF( p[v], q0, q1 ) >= best[v] );
+                            B2_COUNT( 1, a );
                             dR[v] = a ? i + 1 : dR[v];
                             need |= go[v];
                         }
@@ -183,10 +194,13 @@ __global__ void __launch_bounds__( GRID_TB ) kGridBrick( const TravNode* __restr
                         {
                             const float4* tp = reinterpret_cast<const float4*>( tris + ( -link - 1 ) );
                             const float4 ta = __ldg( tp ), tb = __ldg( tp + 1 ), tc = __ldg( tp + 2 ), tn = __ldg( tp + 3 );
+                            if ( lane == 0 ) B2_COUNT( 2, 1 );
 #pragma unroll
                             for ( int v = 0; v < VX; ++v )
                             {
-                                if ( !go[v] || planeBoundRejects( p[v], pmag[v], ta, tn, best[v] ) ) continue;
+                                if ( !go[v] ) continue;
+                                if ( planeBoundRejects( p[v], pmag[v], ta, tn, best[v] ) ) { B2_COUNT( 4, 1 ); continue; }
+                                B2_COUNT( 3, 1 );
                                 const float cand = triDistSqExact( p[v], ta, tb, tc );
                                 if ( cand < best[v] )
                                 {
@@ -208,6 +222,7 @@ __global__ void __launch_bounds__( GRID_TB ) kGridBrick( const TravNode* __restr
                 const float4 q2 = __ldg( np + 2 ), q3 = __ldg( np + 3 );
                 const int link = __float_as_int( q3.w );
                 const float thr = FM( P.betaSq, q2.w );
+                if ( lane == 0 ) B2_COUNT( 5, 1 );
                 if ( link >= 0 )
                 {
 #pragma unroll
@@ -218,6 +233,7 @@ __global__ void __launch_bounds__( GRID_TB ) kGridBrick( const TravNode* __restr
                         const bool far = dipoleFar( p[v], thr, q2, ddx, ddy, ddz, dd );
                         const float term = dipoleTermFast( ddx, ddy, ddz, dd, q3 );
                         const bool acc = a && far;
+                        B2_COUNT( 6, a );
                         sum[v] += acc ? term : 0.f;
                         fR[v] = acc ? link : fR[v];
                         descend |= a && !far;
@@ -234,6 +250,7 @@ __global__ void __launch_bounds__( GRID_TB ) kGridBrick( const TravNode* __restr
                         const bool far = dipoleFar( p[v], thr, q2, ddx, ddy, ddz, dd );
                         const float term = dipoleTermFast( ddx, ddy, ddz, dd, q3 );
                         sum[v] += ( a && far ) ? term : 0.f;
+                        B2_COUNT( 6, a );
                         go[v] = a && !far;
                         fR[v] = a ? i + 1 : fR[v];
                         need |= go[v];
@@ -244,7 +261,7 @@ __global__ void __launch_bounds__( GRID_TB ) kGridBrick( const TravNode* __restr
                         const float4 ta = __ldg( tp ), tb = __ldg( tp + 1 ), tc = __ldg( tp + 2 );
 #pragma unroll
                         for ( int v = 0; v < VX; ++v )
-                            if ( go[v] ) sum[v] += triangleSolidAngle( p[v], ta, tb, tc );
+                            if ( go[v] ) { B2_COUNT( 7, 1 ); sum[v] += triangleSolidAngle( p[v], ta, tb, tc ); }
                     }
                 }
             }
@@ -253,6 +270,16 @@ __global__ void __launch_bounds__( GRID_TB ) kGridBrick( const TravNode* __restr
         }
     }
 
+    if ( STATS )
+    {
+#pragma unroll
+        for ( int k = 0; k < 8; ++k )
+        {
+            const unsigned long long tot = __reduce_add_sync( FULL, (unsigned)cnt[k] ); // per-warp counts fit 32 bits
+            if ( lane == 0 ) atomicAdd( stats + k, tot );
+        }
+    }
+#undef B2_COUNT
     if ( !rowValid ) return;
     constexpr float INV_4PI = 1.0f / ( 4 * 3.14159265358979323846f ); // MRDipole.cpp:126
     float res[VX];
@@ -309,7 +336,23 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
     const size_t numBricks = (size_t)P.bricksX * P.bricksY * P.bricksZ;
     const size_t blocks = ( numBricks + GRID_TB / 32 - 1 ) / ( GRID_TB / 32 );
     if ( blocks > 0x7FFFFFFFull ) { setError( "grid too large for one launch" ); return B2FWN_ERR_INVALID; }
-    kGridBrick<MODE><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut );
+    static const bool wantStats = getenv( "B2FWN_STATS" ) != nullptr;
+    if ( wantStats )
+    {
+        unsigned long long* dStats = nullptr; unsigned long long h[8];
+        B2_CUDA( cudaMalloc( &dStats, sizeof( h ) ) );
+        B2_CUDA( cudaMemsetAsync( dStats, 0, sizeof( h ), st ) );
+        kGridBrick<MODE, true><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, dStats );
+        B2_CUDA( cudaMemcpyAsync( h, dStats, sizeof( h ), cudaMemcpyDeviceToHost, st ) );
+        B2_CUDA( cudaStreamSynchronize( st ) );
+        cudaFree( dStats );
+        const double nv = (double)dims[0] * dims[1] * ( zEnd - zBegin ), nb = (double)numBricks;
+        fprintf( stderr, "[b2fwn stats] voxels %.0f bricks %.0f | dist: visits/brick %.1f boxtests/voxel %.1f trileaf/brick %.1f exact/voxel %.2f "
+                 "filtered/voxel %.2f | fwn: visits/brick %.1f tests/voxel %.1f exact/voxel %.2f\n", nv, nb, h[0] / nb, h[1] / nv, h[2] / nb,
+                 h[3] / nv, h[4] / nv, h[5] / nb, h[6] / nv, h[7] / nv );
+    }
+    else
+        kGridBrick<MODE, false><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, nullptr );
     if ( launches ) ++*launches;
     B2_CUDA( cudaGetLastError() );
     return B2FWN_OK;

@@ -1,0 +1,184 @@
+// b2fwn_meshlib_adapter.hpp -- header-only C++ adapter that plugs libb2fwn.so (C ABI, include/b2fwn.h) in behind
+// MeshLib's own operator interface.  Compile it INSIDE a MeshLib build (it includes MeshLib headers); it adds no
+// dependency to libb2fwn itself.
+//
+//   MR::B200::FastWindingNumber : MR::IFastWindingNumber, MR::IFastWindingNumberByParts
+//       (interface: source/MRMesh/MRFastWindingNumber.h:11-45, 74-107;
+//        the class it stands in for: MR::Cuda::FastWindingNumber, source/MRCuda/MRCudaFastWindingNumber.h:17-38)
+//
+// Conventions preserved: outputs are caller-owned and RESIZED by the callee; by-parts chunks are moved
+// into the consumer on the calling thread in increasing z; errors travel as Expected<void> strings ("NVIDIA GPU error:
+// ...", "Operation was canceled"); device data is created lazily at the first call and cached, mesh edits afterwards are
+// not detected (MRCudaFastWindingNumber.cpp:42-54).  Unlike the reference GPU class, calcFromGrid* DO resize `res`
+// (Appendix A.11 documents the reference's omission as a defect).
+#pragma once
+
+#include "MRMesh/MRFastWindingNumber.h"
+#include "MRMesh/MRMesh.h"
+#include "MRMesh/MRBitSet.h"
+#include "MRMesh/MRAffineXf3.h"
+#include "MRMesh/MRVector3.h"
+#include "MRMesh/MRDistanceToMeshOptions.h"
+#include "b2fwn.h"
+
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+namespace MR
+{
+namespace B200
+{
+
+class FastWindingNumber final : public IFastWindingNumber, public IFastWindingNumberByParts
+{
+public:
+    /// stores a reference: the mesh must outlive this object (as MR::FastWindingNumber, MRFastWindingNumber.h:54-56)
+    explicit FastWindingNumber( const Mesh& mesh, int device = 0 ) : mesh_( mesh ), device_( device ) {}
+    ~FastWindingNumber() override { b2fwn_destroy( h_ ); }
+    FastWindingNumber( const FastWindingNumber& ) = delete;
+    FastWindingNumber& operator=( const FastWindingNumber& ) = delete;
+
+    Expected<void> calcFromVector( std::vector<float>& res, const std::vector<Vector3f>& points, float beta, FaceId skipFace = {},
+                                   const ProgressCallback& cb = {} ) override
+    {
+        if ( auto e = prepare_(); !e ) return e;
+        res.resize( points.size() ); // MRFastWindingNumber.cpp:31
+        static_assert( sizeof( Vector3f ) == 3 * sizeof( float ) );
+        return status_( b2fwn_calc_from_vector( h_, reinterpret_cast<const float*>( points.data() ), points.size(), beta,
+                                                skipFace.valid() ? int( skipFace ) : -1, res.data(), &progress_, (void*)&cb ) );
+    }
+
+    Expected<void> calcSelfIntersections( FaceBitSet& res, float beta, const ProgressCallback& cb = {} ) override
+    {
+        if ( auto e = prepare_(); !e ) return e;
+        const size_t n = mesh_.topology.faceSize();
+        res.clear();
+        res.resize( n ); // MRFastWindingNumber.cpp:43
+        std::vector<uint64_t> words( ( n + 63 ) / 64 );
+        if ( auto e = status_( b2fwn_calc_self_intersections( h_, beta, words.data(), &progress_, (void*)&cb ) ); !e ) return e;
+        for ( size_t f = 0; f < n; ++f )
+            if ( ( words[f >> 6] >> ( f & 63 ) ) & 1 )
+                res.set( FaceId( int( f ) ) );
+        return {};
+    }
+
+    Expected<void> calcFromGrid( std::vector<float>& res, const Vector3i& dims, const AffineXf3f& gridToMeshXf, float beta,
+                                 const ProgressCallback& cb = {} ) override
+    {
+        if ( auto e = prepare_(); !e ) return e;
+        res.resize( size_t( dims.x ) * dims.y * dims.z ); // MRFastWindingNumber.cpp:59
+        const int32_t d[3] = { dims.x, dims.y, dims.z };
+        float xf[12];
+        packXf_( gridToMeshXf, xf );
+        return status_( b2fwn_calc_from_grid( h_, d, xf, beta, res.data(), &progress_, (void*)&cb ) );
+    }
+
+    Expected<void> calcFromGridWithDistances( std::vector<float>& res, const Vector3i& dims, const AffineXf3f& gridToMeshXf,
+                                              const DistanceToMeshOptions& options, const ProgressCallback& cb ) override
+    {
+        if ( auto e = prepare_(); !e ) return e;
+        res.resize( size_t( dims.x ) * dims.y * dims.z ); // MRFastWindingNumber.cpp:83
+        const int32_t d[3] = { dims.x, dims.y, dims.z };
+        float xf[12];
+        packXf_( gridToMeshXf, xf );
+        const b2fwn_dist_options o = packOptions_( options );
+        return status_( b2fwn_calc_from_grid_with_distances( h_, d, xf, &o, res.data(), &progress_, (void*)&cb ) );
+    }
+
+    Expected<void> calcFromGridByParts( GridByPartsFunc resFunc, const Vector3i& dims, const AffineXf3f& gridToMeshXf, float beta,
+                                        int layerOverlap, const ProgressCallback& cb ) override
+    {
+        if ( auto e = prepare_(); !e ) return e;
+        const int32_t d[3] = { dims.x, dims.y, dims.z };
+        float xf[12];
+        packXf_( gridToMeshXf, xf );
+        PartCtx ctx{ &resFunc, {} };
+        const int rc = b2fwn_calc_from_grid_by_parts( h_, d, xf, beta, layerOverlap, 0, &part_, &ctx, &progress_, (void*)&cb );
+        return ctx.error.empty() ? status_( rc ) : unexpected( ctx.error );
+    }
+
+    Expected<void> calcFromGridWithDistancesByParts( GridByPartsFunc resFunc, const Vector3i& dims, const AffineXf3f& gridToMeshXf,
+                                                     const DistanceToMeshOptions& options, int layerOverlap, const ProgressCallback& cb ) override
+    {
+        if ( auto e = prepare_(); !e ) return e;
+        const int32_t d[3] = { dims.x, dims.y, dims.z };
+        float xf[12];
+        packXf_( gridToMeshXf, xf );
+        const b2fwn_dist_options o = packOptions_( options );
+        PartCtx ctx{ &resFunc, {} };
+        const int rc = b2fwn_calc_from_grid_with_distances_by_parts( h_, d, xf, &o, layerOverlap, 0, &part_, &ctx, &progress_, (void*)&cb );
+        return ctx.error.empty() ? status_( rc ) : unexpected( ctx.error );
+    }
+
+private:
+    struct PartCtx
+    {
+        GridByPartsFunc* func;
+        std::string error;
+    };
+
+    // lazy one-time upload + device tree/dipole build (replaces prepareData_, MRCudaFastWindingNumber.cpp:46-85:
+    // no host AABB tree, no host dipoles are needed -- only points and the triangulation)
+    Expected<void> prepare_()
+    {
+        if ( h_ ) return {};
+        const auto tris = mesh_.topology.getTriangulation(); // invalid faces come out with invalid (-1) vertex ids
+        static_assert( sizeof( ThreeVertIds ) == 3 * sizeof( int32_t ) );
+        b2fwn_config cfg{};
+        cfg.device = device_;
+        return status_( b2fwn_create( reinterpret_cast<const float*>( mesh_.points.data() ), mesh_.points.size(),
+                                      reinterpret_cast<const int32_t*>( tris.data() ), tris.size(), &cfg, &h_ ) );
+    }
+
+    static Expected<void> status_( int rc )
+    {
+        if ( rc == B2FWN_OK ) return {};
+        return unexpected( std::string( b2fwn_last_error() ) );
+    }
+
+    static int progress_( float v, void* user )
+    {
+        const auto& cb = *static_cast<const ProgressCallback*>( user );
+        return ( !cb || cb( v ) ) ? 1 : 0;
+    }
+
+    static int part_( const float* data, const int32_t dims[3], int32_t zOffset, void* user )
+    {
+        auto& ctx = *static_cast<PartCtx*>( user );
+        // the consumer receives an owned vector it may keep or discard (MRCudaFastWindingNumber.cpp:340-354)
+        std::vector<float> chunk( data, data + size_t( dims[0] ) * dims[1] * dims[2] );
+        auto r = ( *ctx.func )( std::move( chunk ), Vector3i( dims[0], dims[1], dims[2] ), zOffset );
+        if ( r ) return 0;
+        ctx.error = r.error();
+        return 1;
+    }
+
+    static void packXf_( const AffineXf3f& xf, float out[12] )
+    {
+        const Vector3f* rows[3] = { &xf.A.x, &xf.A.y, &xf.A.z };
+        for ( int r = 0; r < 3; ++r )
+            for ( int c = 0; c < 3; ++c )
+                out[3 * r + c] = ( *rows[r] )[c];
+        for ( int c = 0; c < 3; ++c ) out[9 + c] = xf.b[c];
+    }
+
+    static b2fwn_dist_options packOptions_( const DistanceToMeshOptions& o )
+    {
+        b2fwn_dist_options r{};
+        r.min_dist_sq = o.minDistSq;
+        r.max_dist_sq = o.maxDistSq;
+        r.null_outside_min_max = o.nullOutsideMinMax ? 1 : 0;
+        r.winding_number_threshold = o.windingNumberThreshold;
+        r.winding_number_beta = o.windingNumberBeta;
+        return r;
+    }
+
+    const Mesh& mesh_;
+    int device_ = 0;
+    b2fwn_handle h_ = nullptr;
+};
+
+} // namespace B200
+} // namespace MR

@@ -1,0 +1,127 @@
+// oracle/adapter_check.cpp -- TEST INFRASTRUCTURE ONLY.
+//
+// Drop-in check of meshlib_b200/host/b2fwn_meshlib_adapter.hpp against the UNMODIFIED reference classes
+// (oracle/_ref/libmrref.so): the B200 object is used exactly the way MeshLib's callers use an IFastWindingNumber
+//   * meshToDistanceVolume's call      (source/MRVoxels/MRMeshToDistanceVolume.cpp:52-56)
+//   * mcOffsetMesh's by-parts branch   (source/MRVoxels/MROffset.cpp:194-226): calcFromGridWithDistancesByParts with
+//     layerOverlap = 1 feeding the reference's own MarchingCubesByParts
+// and every result is compared with MR::FastWindingNumber (the reference CPU/TBB implementation) on the same mesh.
+// Built by `make -C oracle adapter` into oracle/_ref/adapter_check (travels to the GPU box); run by tests/ (-m gpu).
+// Prints one "key value" line per check and exits non-zero on a parity failure.
+#include "../meshlib_b200/host/b2fwn_meshlib_adapter.hpp"
+#include "MRMesh/MRTorus.h"
+#include "MRMesh/MRTriMesh.h"
+#include "MRVoxels/MRMarchingCubes.h"
+#include "MRVoxels/MRVoxelsVolume.h"
+#include <cmath>
+#include <cstdio>
+#include <memory>
+
+using namespace MR;
+
+static int g_fail = 0;
+static void check( bool ok, const char* what )
+{
+    std::printf( "%s %s\n", what, ok ? "ok" : "FAIL" );
+    if ( !ok ) ++g_fail;
+}
+
+int main()
+{
+    Mesh mesh = makeTorus( 2.f, 1.f, 64, 32 );
+    // the reference-facing handle type used by every caller (params.fwn): std::shared_ptr<IFastWindingNumber>
+    std::shared_ptr<IFastWindingNumber> ours = std::make_shared<B200::FastWindingNumber>( mesh );
+    FastWindingNumber ref( mesh );
+
+    // calcFromVector
+    std::vector<Vector3f> pts;
+    for ( int i = 0; i < 5000; ++i )
+        pts.emplace_back( 3.5f * std::sin( 0.37f * i ), 3.5f * std::cos( 0.91f * i ), 1.5f * std::sin( 1.73f * i ) );
+    std::vector<float> wa, wb;
+    if ( auto e = ours->calcFromVector( wa, pts, 2.f ); !e )
+    {
+        std::printf( "calcFromVector.call FAIL (%s)\n", e.error().c_str() ); // e.g. no CUDA device: there is no CPU fallback
+        return 2;
+    }
+    (void)ref.calcFromVector( wb, pts, 2.f, {}, {} );
+    float maxDw = 0;
+    for ( size_t i = 0; i < pts.size(); ++i ) maxDw = std::max( maxDw, std::abs( wa[i] - wb[i] ) );
+    std::printf( "calcFromVector.max_abs_dw %g\n", maxDw );
+    check( wa.size() == pts.size() && maxDw < 1e-5f, "calcFromVector.parity" );
+
+    // calcSelfIntersections
+    FaceBitSet sa, sb;
+    check( ours->calcSelfIntersections( sa, 2.f ).has_value(), "calcSelfIntersections.call" );
+    (void)ref.calcSelfIntersections( sb, 2.f, {} );
+    check( sa.size() == sb.size() && sa == sb, "calcSelfIntersections.parity" );
+
+    // calcFromGridWithDistances, as meshToDistanceVolume calls it (voxel centres)
+    const Vector3i dims( 40, 40, 24 );
+    const float voxel = 0.17f;
+    const Vector3f origin( -3.4f, -3.4f, -2.04f );
+    const AffineXf3f basis{ Matrix3f::scale( voxel ), origin + Vector3f::diagonal( 0.5f * voxel ) };
+    DistanceToMeshOptions opt;
+    std::vector<float> da, db, wgrid;
+    check( ours->calcFromGridWithDistances( da, dims, basis, opt, {} ).has_value(), "calcFromGridWithDistances.call" );
+    (void)ref.calcFromGridWithDistances( db, dims, basis, opt, {} );
+    (void)ref.calcFromGrid( wgrid, dims, basis, opt.windingNumberBeta, {} );
+    size_t signMism = 0, band = 0;
+    float maxRel = 0;
+    for ( size_t i = 0; i < db.size(); ++i )
+    {
+        if ( std::abs( wgrid[i] - opt.windingNumberThreshold ) < 1e-3f ) { ++band; continue; }
+        if ( ( da[i] < 0 ) != ( db[i] < 0 ) ) ++signMism;
+        maxRel = std::max( maxRel, std::abs( std::abs( da[i] ) - std::abs( db[i] ) ) / std::max( std::abs( db[i] ), 1e-30f ) );
+    }
+    std::printf( "calcFromGridWithDistances.sign_mismatch_outside_band %zu in_band %zu max_rel_dist_err %g\n", signMism, band, maxRel );
+    check( da.size() == db.size() && signMism == 0 && maxRel <= 1e-5f, "calcFromGridWithDistances.parity" );
+
+    // mcOffsetMesh's by-parts branch: our chunks -> the reference's MarchingCubesByParts
+    const float offset = 0.1f;
+    DistanceToMeshOptions band_;
+    band_.minDistSq = ( offset - 1.001f * voxel ) > 0 ? ( offset - 1.001f * voxel ) * ( offset - 1.001f * voxel ) : 0.f;
+    band_.maxDistSq = ( offset + 1.001f * voxel ) * ( offset + 1.001f * voxel );
+    band_.nullOutsideMinMax = true;
+    MarchingCubesParams mp;
+    mp.origin = origin;
+    mp.iso = offset;
+    mp.lessInside = true;
+    auto byParts = std::dynamic_pointer_cast<IFastWindingNumberByParts>( ours );
+    check( bool( byParts ), "byParts.dynamic_pointer_cast" );
+    MarchingCubesByParts mesher( dims, mp );
+    int parts = 0, lastZ = -1;
+    bool zOrder = true;
+    auto addPart = [&]( std::vector<float>&& data, const Vector3i& d, int zOffset ) -> Expected<void>
+    {
+        zOrder = zOrder && zOffset == mesher.nextZ() && zOffset > lastZ;
+        lastZ = zOffset;
+        ++parts;
+        SimpleVolume v;
+        v.data = std::move( data );
+        v.dims = d;
+        v.voxelSize = Vector3f::diagonal( voxel );
+        return mesher.addPart( v );
+    };
+    auto r = byParts->calcFromGridWithDistancesByParts( addPart, dims, basis, band_, 1, {} );
+    check( r.has_value() && zOrder && parts >= 1, "byParts.contract" );
+    auto triA = mesher.finalize();
+    // same through the reference CPU FastWindingNumber + whole-volume marching cubes
+    std::vector<float> full;
+    (void)ref.calcFromGridWithDistances( full, dims, basis, band_, {} );
+    SimpleVolume vol;
+    vol.data = std::move( full );
+    vol.dims = dims;
+    vol.voxelSize = Vector3f::diagonal( voxel );
+    auto triB = marchingCubesAsTriMesh( vol, mp );
+    check( triA.has_value() && triB.has_value(), "marchingCubes.call" );
+    if ( triA && triB )
+    {
+        std::printf( "offsetMesh.verts %zu %zu tris %zu %zu\n", triA->points.size(), triB->points.size(), triA->tris.size(), triB->tris.size() );
+        check( triA->points.size() == triB->points.size() && triA->tris.size() == triB->tris.size() && triA->tris.size() > 0, "offsetMesh.counts" );
+    }
+
+    // cancellation travels as the reference's error string
+    auto c = ours->calcFromGridWithDistances( da, dims, basis, opt, []( float ) { return false; } );
+    check( !c.has_value() && c.error() == "Operation was canceled", "cancel.error_string" );
+    return g_fail ? 1 : 0;
+}

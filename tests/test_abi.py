@@ -67,3 +67,15 @@ def test_meshgen_shapes():
     q = meshgen.query_points(1000)
     assert q.shape == (1000, 3) and q.min() >= -1.5 and q.max() <= 1.5
     assert np.array_equal(q, meshgen.query_points(1000))
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/source/MRMesh"), reason="reference headers not present")
+def test_cpp_adapter_compiles_against_reference_headers():
+    # the adapter derives from MR::IFastWindingNumber / IFastWindingNumberByParts (source/MRMesh/MRFastWindingNumber.h)
+    import subprocess
+    ref = "/root/reference"
+    src = os.path.join(ROOT, "meshlib_b200", "host", "b2fwn_meshlib_adapter.hpp")
+    cmd = ["g++", "-std=c++23", "-fsyntax-only", "-w", "-x", "c++", f"-I{ref}/source", f"-I{ref}/thirdparty/onetbb/include",
+           f"-I{ref}/thirdparty/parallel-hashmap", f"-I{ref}/thirdparty/expected/include", f"-I{ROOT}/include", src]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]

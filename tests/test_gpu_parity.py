@@ -291,3 +291,19 @@ def test_marching_cubes_of_device_sdf_counts_match_oracle():
     if np.array_equal(got < 0.05, want < 0.05):
         assert len(v) == len(wv) and len(t) == len(wt)
     assert len(t) > 1000 and len(v) - 3 * len(t) // 2 + len(t) == 0  # closed torus: Euler characteristic 0
+
+
+# ---- the C++ adapter behind MeshLib's own interface (8b) ------------------------------------------------------------
+@pytest.mark.gpu
+def test_cpp_adapter_is_a_drop_in_for_the_reference_interface():
+    """oracle/_ref/adapter_check (built where the reference headers exist): MR::B200::FastWindingNumber used through
+    std::shared_ptr<IFastWindingNumber> / IFastWindingNumberByParts by the reference's own callers' code paths, against
+    MR::FastWindingNumber (CPU) and the reference's MarchingCubesByParts"""
+    import subprocess
+    exe = os.path.join(os.path.dirname(GOLD), "..", "oracle", "_ref", "adapter_check")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/adapter_check was not built (needs the reference headers)")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    print(r.stdout, r.stderr)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "FAIL" not in r.stdout and "offsetMesh.counts ok" in r.stdout
