@@ -2,19 +2,26 @@
 // (source/MRMesh/MRFastWindingNumber.cpp:54-94; reference GPU kernels source/MRCuda/MRCudaFastWindingNumber.cu:175-243).
 // Hand-written for sm_100a; FP32/FP64 FMA-pipe work fed from L1/L2, no tensor cores (tree traversal, not a contraction).
 //
-// One warp owns a BRICK of 8 x 4 x 4 voxels; every lane owns 4 consecutive voxels in x (register blocking) and writes
-// them with one float4 store.  The warp walks the pre-order tree with ONE warp-uniform node index (stackless: "i+1"
+// One warp owns a BRICK of 8 x 4 x 4 voxels; every lane owns 4 consecutive voxels in x (register blocking) and moves
+// them with one float4 access.  The warp walks the pre-order tree with ONE warp-uniform node index (stackless: "i+1"
 // descends, the node's skip link leaves its subtree -- the order of calcFastWindingNumber's stack, MRDipole.cpp:104-121).
-// Every voxel keeps a "resume" index per half (winding number / distance): a voxel that accepted a dipole or pruned a box
-// at node i sleeps until the walk reaches skip[i].  The warp descends when any voxel needs to (warp vote), otherwise it
-// jumps to the minimum resume index (redux.sync).  Node fetches are warp-uniform 16-B loads (one transaction, broadcast
-// to 128 voxels), the per-voxel work is branch-free and 4-way independent per lane (ILP), and the two halves share the
-// walk (ONE traversal for sign + distance; the reference GPU does two, .cu:230,238).
+// Every voxel keeps a "resume" index: a voxel that accepted a dipole (or pruned a box) at node i sleeps until the walk
+// reaches skip[i].  The warp descends when any voxel needs to (warp vote), otherwise it jumps to the minimum resume index
+// (redux.sync).  Node fetches are warp-uniform 16-B loads (one transaction, broadcast to 128 voxels) and the per-voxel
+// work is branch-free and 4-way independent per lane (ILP).
+//
+//   kGridDist  closest-point distance of every voxel (findProjection semantics: upper/lower limits, MRMeshProject.cpp:13-103)
+//              -> writes |d| (or NaN outside [minDist, maxDist) when nullOutsideMinMax)
+//   kGridFwn   winding number of every voxel; MODE 1 reads |d|, skips NaN voxels exactly like the reference
+//              (MRFastWindingNumber.cpp:72-74) and writes the signed distance in place
+// Two walks, not one shared walk: the two halves visit different node sets (band mode: 52 vs 217 nodes per brick, full
+// mode: 5014 vs 217), and a shared walk measured 30 % slower (c3_band 83.8 ms vs 64.3 ms).  The reference GPU
+// also walks twice, but per THREAD with private stacks (.cu:230,238).
 //
 // Arithmetic contract (b2fwn_math.cuh): far-field DECISIONS and box / closest-point distances round exactly like the
 // reference's scalar code, so every voxel accepts exactly the reference's set of dipoles and the distance is the
-// reference's value bit for bit; the accepted dipole TERMS use rsqrt (1e-7 relative).  Distance candidates are first
-// filtered by a conservative plane-distance lower bound in FP32; survivors get the reference's double closest point.
+// reference's value bit for bit; the accepted dipole TERMS use MUFU rsqrt (<= 1e-6 relative).  Distance candidates are
+// first filtered by a conservative plane-distance lower bound in FP32; survivors get the reference's double closest point.
 #include "b2fwn_internal.h"
 #include "b2fwn_math.cuh"
 #include <cfloat>
@@ -44,66 +51,133 @@ struct GridParams
     float minDistSq, maxDistSq, threshold;
     int nullOutside;
     int numNodes;
-    int vecStore;        // rows are 16-B aligned: float4 stores
+    int vecStore;        // rows are 16-B aligned: float4 accesses
+    int rewalk;          // STATS experiment
 };
 
 __device__ __forceinline__ int skipOf( int link, int i ) { return link < 0 ? i + 1 : link; }
+__device__ __forceinline__ int min4( const int ( &a )[VX] ) { return min( min( a[0], a[1] ), min( a[2], a[3] ) ); }
 
-__device__ __forceinline__ int warpMinResume( const int ( &fR )[VX], const int ( &dR )[VX] )
+struct Brick
 {
-    int m = INT_MAX;
-#pragma unroll
-    for ( int v = 0; v < VX; ++v ) m = min( m, min( fR[v], dR[v] ) );
-    return __reduce_min_sync( FULL, m );
-}
+    int bx, by, bz, x0, y, z;
+    bool rowValid;
+    size_t id; // output index of the lane's first voxel
+};
 
-// MODE 0: winding number only (calcFromGrid); MODE 1: signed distance (calcFromGridWithDistances)
-// STATS (development only, B2FWN_STATS=1): operation counters of the walk, summed into `stats`
-//   [0] distance-half node visits (warp level)  [1] box tests by awake voxels   [2] leaf visits that loaded the triangle (warp)
-//   [3] exact closest-point evaluations (voxel)  [4] candidates rejected by the plane bound (voxel)
-//   [5] winding-half node visits (warp)          [6] far-field tests by awake voxels [7] exact solid angles (voxel)
-template <int MODE, bool STATS>
-__global__ void __launch_bounds__( GRID_TB ) kGridBrick( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
-                                                         const GridParams P, float* __restrict__ out, unsigned long long* __restrict__ stats )
+__device__ __forceinline__ bool brickOfWarp( const GridParams& P, Brick& B )
 {
-    unsigned long long cnt[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
-#define B2_COUNT( k, n ) do { if ( STATS ) cnt[k] += ( n ); } while ( 0 )
     const unsigned lane = threadIdx.x & 31;
     const size_t brick = blockIdx.x * (size_t)( GRID_TB / 32 ) + ( threadIdx.x >> 5 );
     const size_t numBricks = (size_t)P.bricksX * P.bricksY * P.bricksZ;
-    if ( brick >= numBricks ) return; // whole warp
+    if ( brick >= numBricks ) return false; // whole warp
+    B.bx = (int)( brick % P.bricksX );
+    B.by = (int)( ( brick / P.bricksX ) % P.bricksY );
+    B.bz = (int)( brick / ( (size_t)P.bricksX * P.bricksY ) );
+    B.x0 = B.bx * BX + (int)( lane & 1 ) * VX;
+    B.y = B.by * BY + (int)( ( lane >> 1 ) & 3 );
+    B.z = P.zBegin + B.bz * BZ + (int)( lane >> 3 );
+    B.rowValid = B.y < P.dy && B.z < P.zEnd;
+    B.id = (size_t)B.x0 + (size_t)P.dx * ( (size_t)B.y + (size_t)P.dy * (size_t)( B.z - P.zBegin ) );
+    return true;
+}
+
+// development counters (B2FWN_STATS=1): [0] node visits (warp) [1] tests by awake voxels [2] leaf visits that loaded the
+// triangle (warp) [3] exact evaluations (voxel) [4] candidates rejected by the plane bound (voxel)
+#define B2_COUNT( k, n ) do { if ( STATS ) cnt[k] += ( n ); } while ( 0 )
+template <bool STATS>
+__device__ __forceinline__ void flushCounters( const unsigned ( &cnt )[5], unsigned long long* stats )
+{
+    if ( !STATS ) return;
+#pragma unroll
+    for ( int k = 0; k < 5; ++k )
+    {
+        const unsigned tot = __reduce_add_sync( FULL, cnt[k] );
+        if ( ( threadIdx.x & 31 ) == 0 ) atomicAdd( stats + k, (unsigned long long)tot );
+    }
+}
+
+// ---- brick cull for band-limited distances ---------------------------------------------------------------------------
+// With an upper limit (maxDistSq < FLT_MAX, the offset flows) most bricks lie farther than maxDist from every triangle and
+// their voxels keep the initial value maxDistSq.  One THREAD per brick proves that with a box-box walk (brick AABB in mesh
+// space against the node boxes): about 20 instructions per visit on one thread instead of a 128-voxel warp walk.
+// Conservative: a brick is culled only if every leaf BOX is farther than maxDist * (1 + 1e-4) from the padded brick box, so
+// no triangle can produce a candidate < maxDistSq for any of its voxels (candidates must be strictly smaller,
+// MRMeshProject.cpp:78) -- the culled result is exactly what the walk would return.
+__global__ void __launch_bounds__( 256 ) kBrickCull( const TravNode* __restrict__ nodes, const GridParams P, uint8_t* __restrict__ active )
+{
+    const size_t brick = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    const size_t numBricks = (size_t)P.bricksX * P.bricksY * P.bricksZ;
+    if ( brick >= numBricks ) return;
     const int bx = (int)( brick % P.bricksX );
     const int by = (int)( ( brick / P.bricksX ) % P.bricksY );
     const int bz = (int)( brick / ( (size_t)P.bricksX * P.bricksY ) );
-    const int x0 = bx * BX + (int)( lane & 1 ) * VX;
-    const int y = by * BY + (int)( ( lane >> 1 ) & 3 );
-    const int z = P.zBegin + bz * BZ + (int)( lane >> 3 );
-    const bool rowValid = y < P.dy && z < P.zEnd;
-    const int N = P.numNodes;
+    float lo[3] = { FLT_MAX, FLT_MAX, FLT_MAX }, hi[3] = { -FLT_MAX, -FLT_MAX, -FLT_MAX };
+#pragma unroll
+    for ( int c = 0; c < 8; ++c )
+    {
+        const float3 q = applyXf( P.A, P.b, (float)( bx * BX + ( ( c & 1 ) ? BX - 1 : 0 ) ), (float)( by * BY + ( ( c & 2 ) ? BY - 1 : 0 ) ),
+                                  (float)( P.zBegin + bz * BZ + ( ( c & 4 ) ? BZ - 1 : 0 ) ) );
+        lo[0] = fminf( lo[0], q.x ); hi[0] = fmaxf( hi[0], q.x );
+        lo[1] = fminf( lo[1], q.y ); hi[1] = fmaxf( hi[1], q.y );
+        lo[2] = fminf( lo[2], q.z ); hi[2] = fmaxf( hi[2], q.z );
+    }
+#pragma unroll
+    for ( int k = 0; k < 3; ++k )
+    {
+        const float pad = 1e-5f * fmaxf( fabsf( lo[k] ), fabsf( hi[k] ) ); // interior voxels round a few ulp off the corner hull
+        lo[k] -= pad; hi[k] += pad;
+    }
+    const float lim = P.maxDistSq * 1.0001f;
+    int i = 0, hit = 0;
+    while ( i < P.numNodes )
+    {
+        const float4* np = reinterpret_cast<const float4*>( nodes + i );
+        const float4 q0 = __ldg( np ), q1 = __ldg( np + 1 );
+        const int link = __float_as_int( q1.w );
+        const float ddx = fmaxf( fmaxf( q0.x - hi[0], lo[0] - q0.w ), 0.f );
+        const float ddy = fmaxf( fmaxf( q0.y - hi[1], lo[1] - q1.x ), 0.f );
+        const float ddz = fmaxf( fmaxf( q0.z - hi[2], lo[2] - q1.y ), 0.f );
+        const float d = ddx * ddx + ddy * ddy + ddz * ddz;
+        if ( d > lim ) i = skipOf( link, i );
+        else if ( link < 0 ) { hit = 1; break; }
+        else ++i;
+    }
+    active[brick] = (uint8_t)hit;
+}
+
+// ---- distance walk -----------------------------------------------------------------------------------------------------
+template <bool STATS>
+__global__ void __launch_bounds__( GRID_TB ) kGridDist( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
+                                                        const GridParams P, float* __restrict__ out, const uint8_t* __restrict__ active,
+                                                        unsigned long long* __restrict__ stats )
+{
+    unsigned cnt[5] = { 0, 0, 0, 0, 0 };
+    const unsigned lane = threadIdx.x & 31;
+    Brick B;
+    if ( !brickOfWarp( P, B ) ) return;
+    // a culled brick keeps maxDistSq everywhere: no walk
+    const int N = ( active && !active[blockIdx.x * (size_t)( GRID_TB / 32 ) + ( threadIdx.x >> 5 )] ) ? 0 : P.numNodes;
 
     float3 p[VX];
-    float pmag[VX];
-    bool valid[VX];
-    float sum[VX], best[VX];
-    int fR[VX], dR[VX]; // resume indices of the winding-number / distance half of every voxel
+    float pmag[VX], best[VX];
+    int dR[VX]; // resume index of every voxel
 #pragma unroll
     for ( int v = 0; v < VX; ++v )
     {
-        valid[v] = rowValid && x0 + v < P.dx;
-        p[v] = applyXf( P.A, P.b, (float)( x0 + v ), (float)y, (float)z );
+        const bool valid = B.rowValid && B.x0 + v < P.dx;
+        p[v] = applyXf( P.A, P.b, (float)( B.x0 + v ), (float)B.y, (float)B.z );
         pmag[v] = 1e-6f * ( fabsf( p[v].x ) + fabsf( p[v].y ) + fabsf( p[v].z ) );
-        sum[v] = 0.f;
         best[v] = P.maxDistSq;
-        fR[v] = valid[v] ? 0 : INT_MAX;
-        dR[v] = ( MODE == 1 && valid[v] ) ? 0 : INT_MAX;
+        dR[v] = valid ? 0 : INT_MAX;
     }
-    bool isNaN[VX] = { false, false, false, false };
 
-    if ( MODE == 1 && N > 0 )
+    if ( N > 0 && P.maxDistSq == FLT_MAX )
     {
-        // greedy descent towards the brick centre: one near triangle gives every voxel a finite upper bound, which
-        // makes the order-independent pre-order walk prune like the reference's nearest-first walk
-        const float3 pc = applyXf( P.A, P.b, (float)( bx * BX ) + 3.5f, (float)( by * BY ) + 1.5f, (float)( P.zBegin + bz * BZ ) + 1.5f );
+        // no upper limit given: a greedy descent towards the brick centre finds one near triangle, which gives every
+        // voxel a finite upper bound and makes the order-independent pre-order walk prune like the reference's
+        // nearest-first walk (with a band limit the walk is pruned by maxDistSq from the start)
+        const float3 pc = applyXf( P.A, P.b, (float)( B.bx * BX ) + 3.5f, (float)( B.by * BY ) + 1.5f, (float)( P.zBegin + B.bz * BZ ) + 1.5f );
         int j = 0;
         int link = __float_as_int( __ldg( reinterpret_cast<const float4*>( nodes ) + 1 ).w );
         while ( link >= 0 )
@@ -122,7 +196,7 @@ __global__ void __launch_bounds__( GRID_TB ) kGridBrick( const TravNode* __restr
         const float4 ta = __ldg( tp ), tb = __ldg( tp + 1 ), tc = __ldg( tp + 2 );
 #pragma unroll
         for ( int v = 0; v < VX; ++v )
-            if ( valid[v] )
+            if ( dR[v] == 0 )
             {
                 const float cand = triDistSqExact( p[v], ta, tb, tc );
                 if ( cand < best[v] )
@@ -133,154 +207,191 @@ __global__ void __launch_bounds__( GRID_TB ) kGridBrick( const TravNode* __restr
             }
     }
 
-    // narrow band + NaN outside: the reference skips the winding number of NaN voxels (MRFastWindingNumber.cpp:72-74);
-    // run the distance half alone first, then the winding-number half for the surviving voxels
-    const bool twoPhase = MODE == 1 && P.nullOutside && P.maxDistSq < FLT_MAX;
-    if ( twoPhase )
+    for ( int walk = 0; walk < ( STATS && P.rewalk ? 2 : 1 ); ++walk )
     {
+    if ( walk == 1 )
+    {
+        // experiment: how many nodes would a walk visit that starts from a perfect upper bound?
 #pragma unroll
-        for ( int v = 0; v < VX; ++v ) fR[v] = INT_MAX;
+        for ( int v = 0; v < VX; ++v ) { best[v] = best[v] * 1.000001f; dR[v] = ( B.rowValid && B.x0 + v < P.dx ) ? 0 : INT_MAX; }
+#pragma unroll
+        for ( int k = 0; k < 5; ++k ) cnt[k] = 0;
     }
-    for ( int pass = 0; pass < ( twoPhase ? 2 : 1 ); ++pass )
+    int i = __reduce_min_sync( FULL, min4( dR ) );
+    while ( i < N )
     {
-        if ( pass == 1 )
+        const float4* np = reinterpret_cast<const float4*>( nodes + i );
+        const float4 q0 = __ldg( np ), q1 = __ldg( np + 1 );
+        const int link = __float_as_int( q1.w );
+        if ( lane == 0 ) B2_COUNT( 0, 1 );
+        bool descend = false;
+        if ( link >= 0 )
         {
 #pragma unroll
             for ( int v = 0; v < VX; ++v )
             {
-                dR[v] = INT_MAX;
-                isNaN[v] = best[v] < P.minDistSq || best[v] >= P.maxDistSq;
-                fR[v] = ( valid[v] && !isNaN[v] ) ? 0 : INT_MAX;
+                const bool a = i >= dR[v];
+                B2_COUNT( 1, a );
+                const bool pr = boxDistSqBF( p[v], q0, q1 ) >= best[v]; // MRMeshProject.cpp:30, 48
+                dR[v] = ( a && pr ) ? link : dR[v];
+                descend |= a && !pr;
             }
         }
-        int i = warpMinResume( fR, dR );
-        while ( i < N )
+        else
         {
-            const float4* np = reinterpret_cast<const float4*>( nodes + i );
-            bool descend = false;
-            if ( MODE == 1 )
+            bool go[VX], need = false;
+#pragma unroll
+            for ( int v = 0; v < VX; ++v )
             {
-                const int dmin = min( min( dR[0], dR[1] ), min( dR[2], dR[3] ) );
-                if ( __any_sync( FULL, i >= dmin ) )
+                const bool a = i >= dR[v];
+                B2_COUNT( 1, a );
+                go[v] = a && !( boxDistSqBF( p[v], q0, q1 ) >= best[v] );
+                dR[v] = a ? i + 1 : dR[v];
+                need |= go[v];
+            }
+            if ( __any_sync( FULL, need ) )
+            {
+                const float4* tp = reinterpret_cast<const float4*>( tris + ( -link - 1 ) );
+                const float4 ta = __ldg( tp ), tb = __ldg( tp + 1 ), tc = __ldg( tp + 2 ), tn = __ldg( tp + 3 );
+                if ( lane == 0 ) B2_COUNT( 2, 1 );
+#pragma unroll
+                for ( int v = 0; v < VX; ++v )
                 {
-                    const float4 q0 = __ldg( np ), q1 = __ldg( np + 1 );
-                    const int link = __float_as_int( q1.w );
-                    if ( lane == 0 ) B2_COUNT( 0, 1 );
-                    if ( link >= 0 )
+                    if ( !go[v] ) continue;
+                    if ( planeBoundRejects( p[v], pmag[v], ta, tn, best[v] ) ) { B2_COUNT( 4, 1 ); continue; }
+                    B2_COUNT( 3, 1 );
+                    const float cand = triDistSqExact( p[v], ta, tb, tc );
+                    if ( cand < best[v] )
                     {
-#pragma unroll
-                        for ( int v = 0; v < VX; ++v )
-                        {
-                            const bool a = i >= dR[v];
-                            B2_COUNT( 1, a );
-                            const bool pr = boxDistSqBF( p[v], q0, q1 ) >= best[v]; // MRMeshProject.cpp:30, 48
-                            dR[v] = ( a && pr ) ? link : dR[v];
-                            descend |= a && !pr;
-                        }
-                    }
-                    else
-                    {
-                        bool go[VX], need = false;
-#pragma unroll
-                        for ( int v = 0; v < VX; ++v )
-                        {
-                            const bool a = i >= dR[v];
-                            go[v] = a && !( boxDistSqBF( p[v], q0, q1 ) >= best[v] );
-                            B2_COUNT( 1, a );
-                            dR[v] = a ? i + 1 : dR[v];
-                            need |= go[v];
-                        }
-                        if ( __any_sync( FULL, need ) )
-                        {
-                            const float4* tp = reinterpret_cast<const float4*>( tris + ( -link - 1 ) );
-                            const float4 ta = __ldg( tp ), tb = __ldg( tp + 1 ), tc = __ldg( tp + 2 ), tn = __ldg( tp + 3 );
-                            if ( lane == 0 ) B2_COUNT( 2, 1 );
-#pragma unroll
-                            for ( int v = 0; v < VX; ++v )
-                            {
-                                if ( !go[v] ) continue;
-                                if ( planeBoundRejects( p[v], pmag[v], ta, tn, best[v] ) ) { B2_COUNT( 4, 1 ); continue; }
-                                B2_COUNT( 3, 1 );
-                                const float cand = triDistSqExact( p[v], ta, tb, tc );
-                                if ( cand < best[v] )
-                                {
-                                    best[v] = cand;
-                                    if ( best[v] <= P.minDistSq )
-                                    {
-                                        dR[v] = INT_MAX;
-                                        if ( !twoPhase && P.nullOutside && best[v] < P.minDistSq ) { isNaN[v] = true; fR[v] = INT_MAX; }
-                                    }
-                                }
-                            }
-                        }
+                        best[v] = cand;
+                        if ( best[v] <= P.minDistSq ) dR[v] = INT_MAX; // MRMeshProject.cpp:81-82
                     }
                 }
             }
-            const int fmin = min( min( fR[0], fR[1] ), min( fR[2], fR[3] ) );
-            if ( __any_sync( FULL, i >= fmin ) )
-            {
-                const float4 q2 = __ldg( np + 2 ), q3 = __ldg( np + 3 );
-                const int link = __float_as_int( q3.w );
-                const float thr = FM( P.betaSq, q2.w );
-                if ( lane == 0 ) B2_COUNT( 5, 1 );
-                if ( link >= 0 )
-                {
-#pragma unroll
-                    for ( int v = 0; v < VX; ++v )
-                    {
-                        const bool a = i >= fR[v];
-                        float ddx, ddy, ddz, dd;
-                        const bool far = dipoleFar( p[v], thr, q2, ddx, ddy, ddz, dd );
-                        const float term = dipoleTermFast( ddx, ddy, ddz, dd, q3 );
-                        const bool acc = a && far;
-                        B2_COUNT( 6, a );
-                        sum[v] += acc ? term : 0.f;
-                        fR[v] = acc ? link : fR[v];
-                        descend |= a && !far;
-                    }
-                }
-                else
-                {
-                    bool go[VX], need = false;
-#pragma unroll
-                    for ( int v = 0; v < VX; ++v )
-                    {
-                        const bool a = i >= fR[v];
-                        float ddx, ddy, ddz, dd;
-                        const bool far = dipoleFar( p[v], thr, q2, ddx, ddy, ddz, dd );
-                        const float term = dipoleTermFast( ddx, ddy, ddz, dd, q3 );
-                        sum[v] += ( a && far ) ? term : 0.f;
-                        B2_COUNT( 6, a );
-                        go[v] = a && !far;
-                        fR[v] = a ? i + 1 : fR[v];
-                        need |= go[v];
-                    }
-                    if ( __any_sync( FULL, need ) )
-                    {
-                        const float4* tp = reinterpret_cast<const float4*>( tris + ( -link - 1 ) );
-                        const float4 ta = __ldg( tp ), tb = __ldg( tp + 1 ), tc = __ldg( tp + 2 );
-#pragma unroll
-                        for ( int v = 0; v < VX; ++v )
-                            if ( go[v] ) { B2_COUNT( 7, 1 ); sum[v] += triangleSolidAngle( p[v], ta, tb, tc ); }
-                    }
-                }
-            }
-            if ( __any_sync( FULL, descend ) ) ++i;
-            else i = warpMinResume( fR, dR );
         }
+        if ( __any_sync( FULL, descend ) ) ++i;
+        else i = __reduce_min_sync( FULL, min4( dR ) );
     }
+    }
+    flushCounters<STATS>( cnt, stats );
 
-    if ( STATS )
+    if ( !B.rowValid ) return;
+    float res[VX];
+#pragma unroll
+    for ( int v = 0; v < VX; ++v )
+    {
+        // MRFastWindingNumber.cpp:71-73: NaN outside [minDist, maxDist) -- such voxels get no winding number at all
+        if ( P.nullOutside && ( best[v] < P.minDistSq || best[v] >= P.maxDistSq ) ) res[v] = __int_as_float( 0x7fc00000 ); // cQuietNan
+        else res[v] = __fsqrt_rn( best[v] );
+    }
+    if ( P.vecStore && B.x0 + VX <= P.dx )
+        *reinterpret_cast<float4*>( out + B.id ) = make_float4( res[0], res[1], res[2], res[3] );
+    else
     {
 #pragma unroll
-        for ( int k = 0; k < 8; ++k )
+        for ( int v = 0; v < VX; ++v )
+            if ( B.x0 + v < P.dx ) out[B.id + v] = res[v];
+    }
+}
+
+// ---- winding-number walk -------------------------------------------------------------------------------------------------
+// MODE 0: out = w (calcFromGrid).  MODE 1: out holds |d| or NaN from kGridDist; NaN voxels are skipped, the others become
+// w > threshold ? -|d| : |d| (calcWithDistances, MRFastWindingNumber.cpp:69-76)
+template <int MODE, bool STATS>
+__global__ void __launch_bounds__( GRID_TB ) kGridFwn( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
+                                                       const GridParams P, float* __restrict__ out, unsigned long long* __restrict__ stats )
+{
+    unsigned cnt[5] = { 0, 0, 0, 0, 0 };
+    const unsigned lane = threadIdx.x & 31;
+    Brick B;
+    if ( !brickOfWarp( P, B ) ) return;
+    const int N = P.numNodes;
+
+    float dist[VX] = { 0.f, 0.f, 0.f, 0.f };
+    const bool vec = P.vecStore && B.x0 + VX <= P.dx;
+    if ( MODE == 1 && B.rowValid )
+    {
+        if ( vec )
         {
-            const unsigned long long tot = __reduce_add_sync( FULL, (unsigned)cnt[k] ); // per-warp counts fit 32 bits
-            if ( lane == 0 ) atomicAdd( stats + k, tot );
+            const float4 d4 = *reinterpret_cast<const float4*>( out + B.id );
+            dist[0] = d4.x; dist[1] = d4.y; dist[2] = d4.z; dist[3] = d4.w;
+        }
+        else
+        {
+#pragma unroll
+            for ( int v = 0; v < VX; ++v )
+                if ( B.x0 + v < P.dx ) dist[v] = out[B.id + v];
         }
     }
-#undef B2_COUNT
-    if ( !rowValid ) return;
+    float3 p[VX];
+    float sum[VX];
+    int fR[VX];
+#pragma unroll
+    for ( int v = 0; v < VX; ++v )
+    {
+        const bool valid = B.rowValid && B.x0 + v < P.dx && !( dist[v] != dist[v] );
+        p[v] = applyXf( P.A, P.b, (float)( B.x0 + v ), (float)B.y, (float)B.z );
+        sum[v] = 0.f;
+        fR[v] = valid ? 0 : INT_MAX;
+    }
+
+    int i = __reduce_min_sync( FULL, min4( fR ) );
+    while ( i < N )
+    {
+        const float4* np = reinterpret_cast<const float4*>( nodes + i );
+        const float4 q2 = __ldg( np + 2 ), q3 = __ldg( np + 3 );
+        const int link = __float_as_int( q3.w );
+        const float thr = FM( P.betaSq, q2.w );
+        if ( lane == 0 ) B2_COUNT( 0, 1 );
+        bool descend = false;
+        if ( link >= 0 )
+        {
+#pragma unroll
+            for ( int v = 0; v < VX; ++v )
+            {
+                const bool a = i >= fR[v];
+                B2_COUNT( 1, a );
+                float ddx, ddy, ddz, dd;
+                const bool far = dipoleFar( p[v], thr, q2, ddx, ddy, ddz, dd );
+                const float term = dipoleTermFast( ddx, ddy, ddz, dd, q3 );
+                const bool acc = a && far;
+                sum[v] += ( acc && dd >= FLT_MIN ) ? term : 0.f;
+                fR[v] = acc ? link : fR[v];
+                descend |= a && !far;
+            }
+        }
+        else
+        {
+            bool go[VX], need = false;
+#pragma unroll
+            for ( int v = 0; v < VX; ++v )
+            {
+                const bool a = i >= fR[v];
+                B2_COUNT( 1, a );
+                float ddx, ddy, ddz, dd;
+                const bool far = dipoleFar( p[v], thr, q2, ddx, ddy, ddz, dd );
+                const float term = dipoleTermFast( ddx, ddy, ddz, dd, q3 );
+                sum[v] += ( a && far && dd >= FLT_MIN ) ? term : 0.f;
+                go[v] = a && !far;
+                fR[v] = a ? i + 1 : fR[v];
+                need |= go[v];
+            }
+            if ( __any_sync( FULL, need ) )
+            {
+                const float4* tp = reinterpret_cast<const float4*>( tris + ( -link - 1 ) );
+                const float4 ta = __ldg( tp ), tb = __ldg( tp + 1 ), tc = __ldg( tp + 2 );
+                if ( lane == 0 ) B2_COUNT( 2, 1 );
+#pragma unroll
+                for ( int v = 0; v < VX; ++v )
+                    if ( go[v] ) { B2_COUNT( 3, 1 ); sum[v] += triangleSolidAngle( p[v], ta, tb, tc ); }
+            }
+        }
+        if ( __any_sync( FULL, descend ) ) ++i;
+        else i = __reduce_min_sync( FULL, min4( fR ) );
+    }
+    flushCounters<STATS>( cnt, stats );
+
+    if ( !B.rowValid ) return;
     constexpr float INV_4PI = 1.0f / ( 4 * 3.14159265358979323846f ); // MRDipole.cpp:126
     float res[VX];
 #pragma unroll
@@ -288,19 +399,18 @@ __global__ void __launch_bounds__( GRID_TB ) kGridBrick( const TravNode* __restr
     {
         const float w = FM( INV_4PI, sum[v] );
         if ( MODE == 0 ) res[v] = w;
-        else if ( P.nullOutside && ( best[v] < P.minDistSq || best[v] >= P.maxDistSq ) ) res[v] = __int_as_float( 0x7fc00000 ); // cQuietNan
-        else res[v] = ( w > P.threshold ) ? -__fsqrt_rn( best[v] ) : __fsqrt_rn( best[v] );
+        else res[v] = ( dist[v] != dist[v] ) ? dist[v] : ( ( w > P.threshold ) ? -dist[v] : dist[v] );
     }
-    const size_t id = (size_t)x0 + (size_t)P.dx * ( (size_t)y + (size_t)P.dy * (size_t)( z - P.zBegin ) );
-    if ( P.vecStore && x0 + VX <= P.dx )
-        *reinterpret_cast<float4*>( out + id ) = make_float4( res[0], res[1], res[2], res[3] );
+    if ( vec )
+        *reinterpret_cast<float4*>( out + B.id ) = make_float4( res[0], res[1], res[2], res[3] );
     else
     {
 #pragma unroll
         for ( int v = 0; v < VX; ++v )
-            if ( valid[v] ) out[id + v] = res[v];
+            if ( B.x0 + v < P.dx ) out[B.id + v] = res[v];
     }
 }
+#undef B2_COUNT
 
 inline int checkDims( const int32_t dims[3], int zBegin, int zEnd )
 {
@@ -312,6 +422,13 @@ inline int checkDims( const int32_t dims[3], int zBegin, int zEnd )
     return B2FWN_OK;
 }
 
+void printStats( const char* what, const unsigned long long* h, double voxels, double bricks )
+{
+    fprintf( stderr, "[b2fwn stats] %s: voxels %.0f bricks %.0f | visits/brick %.1f tests/voxel %.1f leaf-loads/brick %.1f exact/voxel %.2f "
+             "plane-rejected/voxel %.2f\n", what, voxels, bricks, h[0] / bricks, h[1] / voxels, h[2] / bricks, h[3] / voxels, h[4] / voxels );
+}
+
+// MODE 0: winding numbers only; MODE 1: distance walk, then winding-number walk over the same slab
 template <int MODE>
 int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, float beta, const b2fwn_dist_options* opt,
                 int zBegin, int zEnd, float* dOut, cudaStream_t st, uint64_t* launches )
@@ -336,24 +453,36 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
     const size_t numBricks = (size_t)P.bricksX * P.bricksY * P.bricksZ;
     const size_t blocks = ( numBricks + GRID_TB / 32 - 1 ) / ( GRID_TB / 32 );
     if ( blocks > 0x7FFFFFFFull ) { setError( "grid too large for one launch" ); return B2FWN_ERR_INVALID; }
+    uint8_t* dActive = nullptr;
+    if ( MODE == 1 && P.maxDistSq < FLT_MAX && P.numNodes > 0 )
+    {
+        B2_CUDA( cudaMallocAsync( &dActive, numBricks, st ) );
+        kBrickCull<<<(unsigned)( ( numBricks + 255 ) / 256 ), 256, 0, st>>>( t.nodes, P, dActive );
+        if ( launches ) ++*launches;
+    }
     static const bool wantStats = getenv( "B2FWN_STATS" ) != nullptr;
+    P.rewalk = getenv( "B2FWN_REWALK" ) != nullptr;
     if ( wantStats )
     {
-        unsigned long long* dStats = nullptr; unsigned long long h[8];
+        unsigned long long* dStats = nullptr; unsigned long long h[10];
         B2_CUDA( cudaMalloc( &dStats, sizeof( h ) ) );
         B2_CUDA( cudaMemsetAsync( dStats, 0, sizeof( h ), st ) );
-        kGridBrick<MODE, true><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, dStats );
+        if ( MODE == 1 ) kGridDist<true><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, dActive, dStats );
+        kGridFwn<MODE, true><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, dStats + 5 );
         B2_CUDA( cudaMemcpyAsync( h, dStats, sizeof( h ), cudaMemcpyDeviceToHost, st ) );
         B2_CUDA( cudaStreamSynchronize( st ) );
         cudaFree( dStats );
         const double nv = (double)dims[0] * dims[1] * ( zEnd - zBegin ), nb = (double)numBricks;
-        fprintf( stderr, "[b2fwn stats] voxels %.0f bricks %.0f | dist: visits/brick %.1f boxtests/voxel %.1f trileaf/brick %.1f exact/voxel %.2f "
-                 "filtered/voxel %.2f | fwn: visits/brick %.1f tests/voxel %.1f exact/voxel %.2f\n", nv, nb, h[0] / nb, h[1] / nv, h[2] / nb,
-                 h[3] / nv, h[4] / nv, h[5] / nb, h[6] / nv, h[7] / nv );
+        if ( MODE == 1 ) printStats( "dist", h, nv, nb );
+        printStats( "fwn ", h + 5, nv, nb );
     }
     else
-        kGridBrick<MODE, false><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, nullptr );
-    if ( launches ) ++*launches;
+    {
+        if ( MODE == 1 ) kGridDist<false><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, dActive, nullptr );
+        kGridFwn<MODE, false><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, nullptr );
+    }
+    if ( launches ) *launches += ( MODE == 1 ? 2 : 1 );
+    if ( dActive ) B2_CUDA( cudaFreeAsync( dActive, st ) );
     B2_CUDA( cudaGetLastError() );
     return B2FWN_OK;
 }

@@ -178,18 +178,24 @@ __device__ __forceinline__ float boxDistSqBF( const float3 p, const float4 q0, c
 }
 
 // far-field test of Dipole::addIfGoodApprox with the reference's exact rounding for the DECISION (dd <= beta^2 rr),
-// and a throughput form for the accepted TERM: dot(dp, dirArea) * rsqrt(dd)^3 with one Newton step on the rsqrt
-// (relative error ~1e-7 per term against the reference's dot / (sqrt(dd) * dd); the sign contract is |w - thr| >= 1e-3)
+// and a throughput form for the accepted TERM: dot(dp, dirArea) * rsqrt(dd)^3 on the MUFU unit
+// (relative error <= ~1e-6 per term against the reference's dot / (sqrt(dd) * dd); the sign contract is |w - thr| >= 1e-3)
 __device__ __forceinline__ bool dipoleFar( const float3 q, const float thr, const float4 q2, float& dx, float& dy, float& dz, float& dd )
 {
     dx = FS( q2.x, q.x ); dy = FS( q2.y, q.y ); dz = FS( q2.z, q.z );
     dd = dot3( dx, dy, dz, dx, dy, dz );
     return !( dd <= thr );
 }
+__device__ __forceinline__ float rsqrtApprox( const float x )
+{
+    float r;
+    asm( "rsqrt.approx.ftz.f32 %0, %1;" : "=f"( r ) : "f"( x ) ); // one MUFU.RSQ, <= 2^-22 relative error
+    return r;
+}
+// only meaningful for dd >= FLT_MIN (the caller masks the rest out, as the reference's `d > 0` guard does)
 __device__ __forceinline__ float dipoleTermFast( const float dx, const float dy, const float dz, const float dd, const float4 q3 )
 {
-    float r = rsqrtf( dd );
-    r = r * fmaf( -0.5f * dd, r * r, 1.5f );
+    const float r = rsqrtApprox( dd );
     return fmaf( dx, q3.x, fmaf( dy, q3.y, dz * q3.z ) ) * ( r * r * r );
 }
 

@@ -7,6 +7,9 @@ from . import portlib, reflib
 
 W_BAND = 1e-3
 DIST_REL_TOL = 1e-5
+# grid kernels: far-field DECISIONS are exact, accepted dipole terms use MUFU rsqrt (<= 1e-6 relative each); the contract
+# is the sign outside |w - threshold| < W_BAND, this bound just documents how far w itself may drift
+W_GRID_ATOL = 1e-5
 
 
 def best_oracle(points, tris):

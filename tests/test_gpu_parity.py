@@ -64,7 +64,7 @@ def test_calc_from_grid(pair):
     dims = (37, 29, 23)  # ragged: not multiples of the brick
     lo, hi = pts.min(0) - 0.3, pts.max(0) + 0.3
     xf = mb.make_basis_xf(lo, (hi - lo) / np.asarray(dims, np.float32))
-    rep = checker.compare_w(fwn.calc_from_grid(dims, xf), orc.calc_from_grid(dims, xf), atol=2e-6)
+    rep = checker.compare_w(fwn.calc_from_grid(dims, xf), orc.calc_from_grid(dims, xf), atol=checker.W_GRID_ATOL)
     assert rep["ok"], rep
 
 
@@ -146,7 +146,7 @@ def test_golden_fixture_from_reference():
         assert dip.tobytes() == g[f"{name}_dipoles"].tobytes()
         assert checker.compare_w(fwn.calc_from_vector(g[f"{name}_q"]), g[f"{name}_w"])["ok"]
         dims, xf = tuple(int(x) for x in g[f"{name}_dims"]), g[f"{name}_xf"]
-        assert checker.compare_w(fwn.calc_from_grid(dims, xf), g[f"{name}_wgrid"])["ok"]
+        assert checker.compare_w(fwn.calc_from_grid(dims, xf), g[f"{name}_wgrid"], atol=checker.W_GRID_ATOL)["ok"]
         rep = checker.compare_sdf(fwn.calc_from_grid_with_distances(dims, xf), g[f"{name}_sdf"], g[f"{name}_wgrid"])
         assert rep["ok"], rep
         o = g[f"{name}_band_opts"]
