@@ -153,6 +153,49 @@ int b2fwn_marching_cubes( b2fwn_handle h, const float* volume, int32_t volume_on
                           const b2fwn_mc_params* p, uint64_t* n_verts, uint64_t* n_tris );
 int b2fwn_marching_cubes_fetch( b2fwn_handle h, float* out_verts_xyz, int32_t* out_tris_abc );
 
+/* ---- callers of the interface, moved onto the device (a18, a19) -------------------------------------- */
+
+/* exact bounding box of the vertices of all valid faces (min xyz, max xyz) = Mesh::computeBoundingBox() as mcOffsetMesh uses
+ * it (source/MRMesh/MRMesh.cpp:213-226); B2FWN_ERR_INVALID for a mesh without valid faces */
+int b2fwn_get_bounding_box( b2fwn_handle h, float out_min_max[6] );
+
+/* mirrors MR::DistanceVolumeParams (source/MRVoxels/MRDistanceVolumeParams.h:9-22) */
+typedef struct b2fwn_volume_params
+{
+    float origin[3];      /* corner of voxel (0,0,0); values are taken at voxel centres origin + (i + 0.5) * voxel_size */
+    float voxel_size[3];
+    int32_t dims[3];
+    int32_t reserved[3];
+} b2fwn_volume_params;
+
+/* MR::meshToDistanceVolume, SignDetectionMode::HoleWindingRule branch (source/MRVoxels/MRMeshToDistanceVolume.cpp:43-62):
+ * out = dims[0]*dims[1]*dims[2] signed distances (host), out_min / out_max = parallelMinMax over the non-NaN values
+ * (FLT_MAX / -FLT_MAX when there is none, as MinMaxArg's initial state) */
+int b2fwn_mesh_to_distance_volume( b2fwn_handle h, const b2fwn_volume_params* vol, const b2fwn_dist_options* opt, float* out,
+                                   float* out_min, float* out_max, b2fwn_progress cb, void* user );
+
+/* MR::mcOffsetMesh / generalOffsetMesh( Mode::Standard ) with SignDetectionMode::HoleWindingRule
+ * (source/MRVoxels/MROffset.cpp:117-246, grid by calcOriginAndDimensions, source/MRVoxels/MRCalcDims.h:18-27):
+ * the signed-distance band is computed into HBM and meshed there (marching cubes at iso = offset, lessInside = true);
+ * the volume never leaves the device.  Fetch the mesh with b2fwn_marching_cubes_fetch. */
+typedef struct b2fwn_offset_params
+{
+    float voxel_size;               /* OffsetParameters::voxelSize, > 0 */
+    float offset;
+    int32_t close_holes;            /* OffsetParameters::closeHolesInHoleWindingNumber (default 1) */
+    float winding_number_threshold; /* default 0.5 */
+    float winding_number_beta;      /* default 2 */
+    int32_t reserved[3];
+} b2fwn_offset_params;
+typedef struct b2fwn_offset_result
+{
+    float origin[3];
+    int32_t dims[3];
+    uint64_t n_verts, n_tris;
+    double sdf_ms, mc_ms;           /* device time of the two stages (CUDA events) */
+} b2fwn_offset_result;
+int b2fwn_mc_offset_mesh( b2fwn_handle h, const b2fwn_offset_params* p, b2fwn_offset_result* res, b2fwn_progress cb, void* user );
+
 #ifdef __cplusplus
 }
 #endif

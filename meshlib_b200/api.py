@@ -54,6 +54,22 @@ class McParams(C.Structure):
                 ("less_inside", C.c_int32), ("reserved", C.c_int32 * 4)]
 
 
+class VolumeParams(C.Structure):
+    """MR::DistanceVolumeParams (source/MRVoxels/MRDistanceVolumeParams.h:9-22)"""
+    _fields_ = [("origin", C.c_float * 3), ("voxel_size", C.c_float * 3), ("dims", C.c_int32 * 3), ("reserved", C.c_int32 * 3)]
+
+
+class OffsetParams(C.Structure):
+    """the fields of MR::OffsetParameters that mcOffsetMesh reads in HoleWindingRule mode (source/MRVoxels/MROffset.h)"""
+    _fields_ = [("voxel_size", C.c_float), ("offset", C.c_float), ("close_holes", C.c_int32),
+                ("winding_number_threshold", C.c_float), ("winding_number_beta", C.c_float), ("reserved", C.c_int32 * 3)]
+
+
+class OffsetResult(C.Structure):
+    _fields_ = [("origin", C.c_float * 3), ("dims", C.c_int32 * 3), ("n_verts", C.c_uint64), ("n_tris", C.c_uint64),
+                ("sdf_ms", C.c_double), ("mc_ms", C.c_double)]
+
+
 EXPORTS = [
     "b2fwn_last_error", "b2fwn_device_count", "b2fwn_create", "b2fwn_destroy", "b2fwn_calc_from_vector",
     "b2fwn_calc_from_vector_device", "b2fwn_calc_self_intersections", "b2fwn_calc_self_intersections_device",
@@ -61,6 +77,7 @@ EXPORTS = [
     "b2fwn_calc_from_grid_with_distances_device", "b2fwn_calc_from_grid_by_parts",
     "b2fwn_calc_from_grid_with_distances_by_parts", "b2fwn_get_tree", "b2fwn_get_stats", "b2fwn_marching_cubes",
     "b2fwn_marching_cubes_fetch", "b2fwn_calc_from_grid_with_distances_layers", "b2fwn_measure_fp32_peak",
+    "b2fwn_get_bounding_box", "b2fwn_mesh_to_distance_volume", "b2fwn_mc_offset_mesh",
 ]
 
 
@@ -99,6 +116,10 @@ def load_library():
     L.b2fwn_get_stats.argtypes = [vp, C.POINTER(Stats)]
     L.b2fwn_marching_cubes.argtypes = [vp, vp, C.c_int32, i32p, C.POINTER(McParams), u64p, u64p]
     L.b2fwn_marching_cubes_fetch.argtypes = [vp, vp, vp]
+    L.b2fwn_get_bounding_box.argtypes = [vp, f32p]
+    L.b2fwn_mesh_to_distance_volume.argtypes = [vp, C.POINTER(VolumeParams), C.POINTER(DistOptions), vp, f32p, f32p,
+                                                PROGRESS_CB, vp]
+    L.b2fwn_mc_offset_mesh.argtypes = [vp, C.POINTER(OffsetParams), C.POINTER(OffsetResult), PROGRESS_CB, vp]
     _lib = L
     return L
 
@@ -266,6 +287,43 @@ class FastWindingNumber:
         s = Stats()
         _check(_lib.b2fwn_get_stats(self._h, C.byref(s)))
         return s
+
+    # ---- callers of the interface, on the device ----
+    def bounding_box(self):
+        bb = (C.c_float * 6)()
+        _check(_lib.b2fwn_get_bounding_box(self._h, bb))
+        return np.array(bb[:3], np.float32), np.array(bb[3:], np.float32)
+
+    def mesh_to_distance_volume(self, origin, voxel_size, dims, options=None, cb=None, out=None):
+        """MR::meshToDistanceVolume, HoleWindingRule (source/MRVoxels/MRMeshToDistanceVolume.cpp:43-62):
+        returns (data, min, max) = SimpleVolumeMinMax's payload"""
+        options = options or DistOptions()
+        vp_ = VolumeParams()
+        vp_.origin[:] = [float(x) for x in origin]
+        vs = np.asarray(voxel_size, np.float32) * np.ones(3, np.float32)
+        vp_.voxel_size[:] = [float(x) for x in vs]
+        vp_.dims[:] = [int(d) for d in dims]
+        n = int(dims[0]) * int(dims[1]) * int(dims[2])
+        res = out if out is not None else np.empty(n, np.float32)
+        lo, hi = C.c_float(), C.c_float()
+        _check(_lib.b2fwn_mesh_to_distance_volume(self._h, C.byref(vp_), C.byref(options), res.ctypes.data, C.byref(lo),
+                                                  C.byref(hi), _progress(cb), None))
+        return res, lo.value, hi.value
+
+    def mc_offset_mesh(self, offset, voxel_size, close_holes=True, threshold=0.5, beta=2.0, cb=None, fetch=True):
+        """MR::mcOffsetMesh with HoleWindingRule (source/MRVoxels/MROffset.cpp:117-246), distance band and marching cubes
+        both on the device.  Returns (verts, tris, info) -- verts/tris None when fetch is False"""
+        p = OffsetParams(float(voxel_size), float(offset), int(close_holes), float(threshold), float(beta))
+        r = OffsetResult()
+        _check(_lib.b2fwn_mc_offset_mesh(self._h, C.byref(p), C.byref(r), _progress(cb), None))
+        info = dict(origin=np.array(r.origin[:], np.float32), dims=tuple(r.dims[:]), n_verts=r.n_verts, n_tris=r.n_tris,
+                    sdf_ms=r.sdf_ms, mc_ms=r.mc_ms)
+        if not fetch:
+            return None, None, info
+        verts = np.empty((r.n_verts, 3), np.float32)
+        tris = np.empty((r.n_tris, 3), np.int32)
+        _check(_lib.b2fwn_marching_cubes_fetch(self._h, verts.ctypes.data, tris.ctypes.data))
+        return verts, tris, info
 
     # ---- marching cubes ----
     def marching_cubes(self, volume, dims, origin, voxel_size, iso, less_inside=False, on_device=False):

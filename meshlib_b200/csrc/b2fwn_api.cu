@@ -3,6 +3,8 @@
 // There is deliberately no CPU implementation behind any entry point.
 #include "b2fwn_internal.h"
 #include <algorithm>
+#include <cfloat>
+#include <cmath>
 #include <cstring>
 #include <vector>
 
@@ -456,6 +458,165 @@ int b2fwn_calc_from_grid_with_distances( b2fwn_handle h, const int32_t dims[3], 
 {
     if ( !dims ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
     return b2fwn_calc_from_grid_with_distances_layers( h, dims, xf, opt, 0, dims[2], out, cb, user );
+}
+
+// ---- callers moved onto the device: meshToDistanceVolume, mcOffsetMesh --------------------------------------------------
+
+namespace
+{
+__device__ __forceinline__ unsigned ordOf( float f )
+{
+    const unsigned u = __float_as_uint( f );
+    return ( u & 0x80000000u ) ? ~u : ( u | 0x80000000u );
+}
+// parallelMinMax (source/MRMesh/MRParallelMinMax.h:14-42): NaN never passes `v < min` / `v > max`, so it is ignored
+__global__ void __launch_bounds__( 256 ) kMinMax( const float* __restrict__ v, size_t n, unsigned* __restrict__ mm )
+{
+    unsigned lo = 0xFFFFFFFFu, hi = 0u;
+    for ( size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x )
+    {
+        const float f = v[i];
+        if ( f == f ) { const unsigned o = ordOf( f ); lo = min( lo, o ); hi = max( hi, o ); }
+    }
+    lo = __reduce_min_sync( 0xFFFFFFFFu, lo );
+    hi = __reduce_max_sync( 0xFFFFFFFFu, hi );
+    if ( ( threadIdx.x & 31 ) == 0 ) { atomicMin( mm, lo ); atomicMax( mm + 1, hi ); }
+}
+float fromOrd( unsigned o )
+{
+    const unsigned u = ( o & 0x80000000u ) ? ( o & 0x7fffffffu ) : ~o;
+    float f;
+    memcpy( &f, &u, 4 );
+    return f;
+}
+} // namespace
+
+int b2fwn_get_bounding_box( b2fwn_handle h, float out[6] )
+{
+    if ( !h || !out ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    if ( h->tree.numLeaves == 0 ) { setError( "mesh has no valid faces" ); return B2FWN_ERR_INVALID; }
+    for ( int c = 0; c < 6; ++c ) out[c] = h->tree.bbox[c];
+    return B2FWN_OK;
+}
+
+int b2fwn_mesh_to_distance_volume( b2fwn_handle h, const b2fwn_volume_params* vol, const b2fwn_dist_options* opt, float* out,
+                                   float* outMin, float* outMax, b2fwn_progress cb, void* user )
+{
+    if ( !h || !vol || !opt ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    // basis = ( scale( voxelSize ), origin + 0.5f * voxelSize )   (MRMeshToDistanceVolume.cpp:55)
+    float xf[12] = { vol->voxel_size[0], 0, 0, 0, vol->voxel_size[1], 0, 0, 0, vol->voxel_size[2], 0, 0, 0 };
+    for ( int c = 0; c < 3; ++c )
+    {
+        volatile float half = 0.5f * vol->voxel_size[c];
+        xf[9 + c] = vol->origin[c] + half;
+    }
+    unsigned* dMM = nullptr;
+    B2_CUDA( cudaMalloc( &dMM, 2 * sizeof( unsigned ) ) );
+    const unsigned init[2] = { 0xFFFFFFFFu, 0u };
+    cudaMemcpyAsync( dMM, init, sizeof( init ), cudaMemcpyHostToDevice, h->stream );
+    const GridXf g = toXf( xf );
+    const b2fwn_dist_options o = *opt;
+    const int32_t* dims = vol->dims;
+    int rc = B2FWN_ERR_INVALID;
+    if ( dims[0] < 0 || dims[1] < 0 || dims[2] < 0 ) setError( "invalid grid dimensions" );
+    else if ( (size_t)dims[0] * dims[1] * dims[2] && !out ) setError( "null argument" );
+    else
+        rc = runChunked( h, dims, 0, dims[2], 0, 0, out, nullptr, nullptr, cb, user, [&]( int z0, int z1, float* d )
+        {
+            if ( int e = launchSdfGrid( h->tree, dims, g, o, z0, z1, d, h->stream, &h->stats.kernel_launches ) ) return e;
+            const size_t n = (size_t)dims[0] * dims[1] * ( z1 - z0 );
+            kMinMax<<<(unsigned)std::min<size_t>( ( n + 255 ) / 256, 148 * 8 ), 256, 0, h->stream>>>( d, n, dMM );
+            ++h->stats.kernel_launches;
+            return B2FWN_OK;
+        } );
+    unsigned mm[2] = { 0xFFFFFFFFu, 0u };
+    if ( rc == B2FWN_OK ) cudaMemcpy( mm, dMM, sizeof( mm ), cudaMemcpyDeviceToHost );
+    cudaFree( dMM );
+    if ( rc ) return rc;
+    if ( outMin ) *outMin = mm[0] == 0xFFFFFFFFu ? FLT_MAX : fromOrd( mm[0] );
+    if ( outMax ) *outMax = mm[1] == 0u ? -FLT_MAX : fromOrd( mm[1] );
+    return B2FWN_OK;
+}
+
+int b2fwn_mc_offset_mesh( b2fwn_handle h, const b2fwn_offset_params* p, b2fwn_offset_result* res, b2fwn_progress cb, void* user )
+{
+    if ( !h || !p || !res ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    if ( !( p->voxel_size > 0 ) ) { setError( "invalid voxelSize value" ); return B2FWN_ERR_INVALID; } // MROffset.cpp:122-126
+    if ( h->tree.numLeaves == 0 ) { setError( "mesh has no valid faces" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    memset( res, 0, sizeof( *res ) );
+    if ( !report( cb, user, 0.f ) ) return canceled();
+    const float v = p->voxel_size;
+    const float absOffset = fabsf( p->offset );
+    // box = bbox.expanded( |offset| ); calcOriginAndDimensions (MRCalcDims.h:18-27): origin = box.min - 2v,
+    // dims = int( ( box.max + 2v - origin ) * ( 1 / v ) ) + 1  (Vector3f / float multiplies by the reciprocal, MRVector3.h:120-126)
+    volatile float expansion = 2 * v, inv = 1 / v;
+    int32_t dims[3];
+    float origin[3];
+    for ( int c = 0; c < 3; ++c )
+    {
+        volatile float bmin = h->tree.bbox[c] - absOffset, bmax = h->tree.bbox[3 + c] + absOffset;
+        volatile float o = bmin - expansion;
+        volatile float top = bmax + expansion;
+        volatile float ext = top - o;
+        volatile float q = inv * ext;
+        origin[c] = o;
+        dims[c] = (int32_t)q + 1;
+        res->origin[c] = o; res->dims[c] = dims[c];
+    }
+    const size_t total = (size_t)dims[0] * dims[1] * dims[2];
+    size_t freeB = 0, totalB = 0;
+    B2_CUDA( cudaMemGetInfo( &freeB, &totalB ) );
+    if ( total * 6 + ( (size_t)256 << 20 ) > freeB ) // volume (4 B) + codes (1 B) + segment totals and scan scratch
+    {
+        setError( "offset volume does not fit into device memory; use calcFromGridWithDistancesByParts" );
+        return B2FWN_ERR_INVALID;
+    }
+    b2fwn_dist_options o{};
+    {
+        // MROffset.cpp:176-183 (1.001f guards against rounding, as there)
+        volatile float lo = absOffset - 1.001f * v, hi = absOffset + 1.001f * v;
+        const float lo0 = lo > 0.f ? (float)lo : 0.f;
+        o.min_dist_sq = lo0 * lo0;
+        o.max_dist_sq = hi * hi;
+        o.null_outside_min_max = p->close_holes ? 0 : 1; // !isHoleWindingRule || !closeHolesInHoleWindingNumber
+        o.winding_number_threshold = p->winding_number_threshold;
+        o.winding_number_beta = p->winding_number_beta;
+    }
+    float xf[12] = { v, 0, 0, 0, v, 0, 0, 0, v, 0, 0, 0 };
+    for ( int c = 0; c < 3; ++c )
+    {
+        volatile float half = 0.5f * v;
+        xf[9 + c] = origin[c] + half; // basis = ( scale( voxelSize ), origin + 0.5f * voxelSize ), MROffset.cpp:202
+    }
+    float* dVol = nullptr;
+    B2_CUDA( cudaMalloc( &dVol, total * sizeof( float ) ) );
+    cudaEventRecord( h->evA, h->stream );
+    int rc = launchSdfGrid( h->tree, dims, toXf( xf ), o, 0, dims[2], dVol, h->stream, &h->stats.kernel_launches );
+    cudaEventRecord( h->evB, h->stream );
+    if ( rc == B2FWN_OK && cudaEventSynchronize( h->evB ) != cudaSuccess ) rc = cudaFail( cudaGetLastError(), "offset: distance volume" );
+    if ( rc ) { cudaFree( dVol ); return rc; }
+    float ms = 0;
+    cudaEventElapsedTime( &ms, h->evA, h->evB );
+    res->sdf_ms = ms;
+    if ( !report( cb, user, 0.4f ) ) { cudaFree( dVol ); return canceled(); }
+    b2fwn_mc_params mp{};
+    for ( int c = 0; c < 3; ++c ) { mp.origin[c] = origin[c]; mp.voxel_size[c] = v; }
+    mp.iso = p->offset;
+    mp.less_inside = 1;
+    cudaEventRecord( h->evA, h->stream );
+    rc = marchingCubesDevice( dVol, dims, mp, h->mc, h->stream, &h->stats.kernel_launches );
+    cudaEventRecord( h->evB, h->stream );
+    cudaEventSynchronize( h->evB );
+    cudaEventElapsedTime( &ms, h->evA, h->evB );
+    res->mc_ms = ms;
+    h->stats.last_kernel_ms = res->sdf_ms + res->mc_ms;
+    cudaFree( dVol );
+    if ( rc ) return rc;
+    res->n_verts = h->mc.nVerts; res->n_tris = h->mc.nTris;
+    if ( !report( cb, user, 1.f ) ) return canceled();
+    return B2FWN_OK;
 }
 
 // ---- diagnostics: FP32 FMA-pipe peak of this GPU (the roofline denominator of the traversal kernels) -------------------

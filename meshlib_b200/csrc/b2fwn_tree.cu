@@ -16,6 +16,7 @@
 #include <cub/device/device_select.cuh>
 #include <thrust/iterator/counting_iterator.h>
 #include <cfloat>
+#include <cstring>
 #include <vector>
 
 namespace b2
@@ -83,11 +84,14 @@ __global__ void kValidFlags( const int32_t* __restrict__ tris, size_t nFaces, ui
 }
 
 // computeFaceBox (MRAABBTree.cpp:15-29) + Box::insignificantlyExpanded (MRBox.h:260-270)
+// also reduces the exact (unexpanded) bounding box of all valid faces into bbox6 (ordered-integer images)
 __global__ void kFaceBoxes( const float* __restrict__ pts, const int32_t* __restrict__ tris,
-                            const int32_t* __restrict__ validFaces, int nLeaves, LeafBox* __restrict__ out )
+                            const int32_t* __restrict__ validFaces, int nLeaves, LeafBox* __restrict__ out, uint32_t* __restrict__ bbox6 )
 {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if ( i >= nLeaves ) return;
+    uint32_t bb[6] = { 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u, 0u };
+    if ( i < nLeaves )
+    {
     const int f = validFaces[i];
     LeafBox lb;
     lb.face = f;
@@ -104,8 +108,19 @@ __global__ void kFaceBoxes( const float* __restrict__ pts, const int32_t* __rest
         if ( c < mn ) mn = c; if ( c > mx ) mx = c;
         lb.mn[d] = nextafterf( mn, -FLT_MAX );
         lb.mx[d] = nextafterf( mx, FLT_MAX );
+        bb[d] = f2ord( mn ); bb[3 + d] = f2ord( mx );
     }
     out[i] = lb;
+    }
+#pragma unroll
+    for ( int c = 0; c < 6; ++c )
+    {
+        const uint32_t r = c < 3 ? __reduce_min_sync( 0xFFFFFFFFu, bb[c] ) : __reduce_max_sync( 0xFFFFFFFFu, bb[c] );
+        if ( ( threadIdx.x & 31 ) == 0 )
+        {
+            if ( c < 3 ) atomicMin( bbox6 + c, r ); else atomicMax( bbox6 + c, r );
+        }
+    }
 }
 
 __global__ void kInitPerm( int nLeaves, LevelKey* __restrict__ keys, const LeafBox* __restrict__ leaves )
@@ -436,7 +451,21 @@ int buildTree( DeviceTree& t, cudaStream_t st, uint64_t* launches )
     B2_CUDA( cudaMalloc( &t.nodes, N * sizeof( TravNode ) ) );
     B2_CUDA( cudaMalloc( &t.leafTris, (size_t)L * sizeof( LeafTri ) ) );
 
-    kFaceBoxes<<<nblk( L ), TB, 0, st>>>( t.points, t.tris, dValid, L, dLeaves ); ++nl;
+    uint32_t* dBBox = nullptr;
+    B2_CUDA( cudaMalloc( &dBBox, 6 * sizeof( uint32_t ) ) );
+    kClearSegBoxes<<<1, 32, 0, st>>>( dBBox, 1 ); ++nl;
+    kFaceBoxes<<<nblk( L ), TB, 0, st>>>( t.points, t.tris, dValid, L, dLeaves, dBBox ); ++nl;
+    {
+        uint32_t hb[6];
+        B2_CUDA( cudaMemcpyAsync( hb, dBBox, sizeof( hb ), cudaMemcpyDeviceToHost, st ) );
+        B2_CUDA( cudaStreamSynchronize( st ) );
+        for ( int c = 0; c < 6; ++c )
+        {
+            const uint32_t u = ( hb[c] & 0x80000000u ) ? ( hb[c] & 0x7fffffffu ) : ~hb[c];
+            memcpy( &t.bbox[c], &u, 4 );
+        }
+        cudaFree( dBBox );
+    }
     kInitPerm<<<nblk( L ), TB, 0, st>>>( L, dKeys, dLeaves ); ++nl;
     const Seg root = { 0, L, 0, 0 };
     B2_CUDA( cudaMemcpyAsync( dSegA, &root, sizeof( Seg ), cudaMemcpyHostToDevice, st ) );

@@ -64,3 +64,51 @@ def compare_bits(got_words, want_words, w_ref, n_faces, band=W_BAND):
     mism = (got != want)
     return {"ok": bool(not (mism & ~inband).any()), "mismatch": int((mism & ~inband).sum()), "mismatch_in_band": int((mism & inband).sum()),
             "set": int(want.sum()), "n": int(n_faces)}
+
+
+# ---- callers of the interface, restated over the oracle (checker only) ------------------------------------------------
+def ref_mesh_to_distance_volume(orc, origin, voxel_size, dims, **opts):
+    """MR::meshToDistanceVolume, HoleWindingRule branch (source/MRVoxels/MRMeshToDistanceVolume.cpp:43-62):
+    basis = (scale(voxelSize), origin + 0.5f * voxelSize); min/max ignore NaN (MRParallelMinMax.h:14-42)"""
+    o = np.asarray(origin, np.float32)
+    v = np.asarray(voxel_size, np.float32) * np.ones(3, np.float32)
+    b = o + np.float32(0.5) * v
+    xf = np.array([v[0], 0, 0, 0, v[1], 0, 0, 0, v[2], b[0], b[1], b[2]], np.float32)
+    data = orc.calc_from_grid_with_distances(dims, xf, **opts)
+    ok = ~np.isnan(data)
+    fmax = np.finfo(np.float32).max
+    return data, (float(data[ok].min()) if ok.any() else float(fmax)), (float(data[ok].max()) if ok.any() else float(-fmax))
+
+
+def ref_offset_grid(points, tris, offset, voxel_size):
+    """grid of mcOffsetMesh: bbox.expanded(|offset|) -> calcOriginAndDimensions (source/MRVoxels/MROffset.cpp:163-165,
+    MRCalcDims.h:18-27), in float32 like the reference"""
+    f = np.float32
+    t = np.asarray(tris)
+    used = np.unique(t[(t >= 0).all(1)])
+    p = np.asarray(points, f)[used]
+    a = f(abs(offset))
+    bmin, bmax = p.min(0) - a, p.max(0) + a
+    exp = f(2) * f(voxel_size)
+    origin = (bmin - exp).astype(f)
+    inv = f(1) / f(voxel_size)
+    dims = ((((bmax + exp).astype(f) - origin).astype(f) * inv).astype(f)).astype(np.int32) + 1
+    return origin, tuple(int(d) for d in dims)
+
+
+def ref_mc_offset_mesh(orc, points, tris, offset, voxel_size, close_holes=True, threshold=0.5, beta=2.0):
+    """MR::mcOffsetMesh, HoleWindingRule (source/MRVoxels/MROffset.cpp:117-246) over the oracle's SDF and marching cubes:
+    returns (verts, tris, sdf, origin, dims)"""
+    from . import portlib, reflib
+    f = np.float32
+    origin, dims = ref_offset_grid(points, tris, offset, voxel_size)
+    v, a = f(voxel_size), f(abs(offset))
+    lo = max(f(a - f(f(1.001) * v)), f(0))
+    hi = f(a + f(f(1.001) * v))
+    b = origin + f(0.5) * v
+    xf = np.array([v, 0, 0, 0, v, 0, 0, 0, v, b[0], b[1], b[2]], f)
+    sdf = orc.calc_from_grid_with_distances(dims, xf, min_dist_sq=float(f(lo * lo)), max_dist_sq=float(f(hi * hi)),
+                                            null_outside=not close_holes, threshold=threshold, beta=beta)
+    mc = reflib.marching_cubes if reflib.available() else portlib.marching_cubes
+    verts, mtris = mc(sdf, dims, float(v), origin, float(offset), True)
+    return verts, mtris, sdf, origin, dims

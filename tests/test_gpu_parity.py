@@ -307,3 +307,37 @@ def test_cpp_adapter_is_a_drop_in_for_the_reference_interface():
     print(r.stdout, r.stderr)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "FAIL" not in r.stdout and "offsetMesh.counts ok" in r.stdout
+
+
+# ---- callers on the device: meshToDistanceVolume (a18), mcOffsetMesh (a19) --------------------------------------------
+def test_mesh_to_distance_volume_matches_reference_caller():
+    pts, tris = meshgen.make_torus(2, 1, 64, 32)
+    fwn = mb.FastWindingNumber(pts, tris)
+    orc = checker.best_oracle(pts, tris)
+    origin, voxel, dims = (-3.3, -3.3, -1.3), (0.21, 0.2, 0.13), (33, 34, 21)
+    got, lo, hi = fwn.mesh_to_distance_volume(origin, voxel, dims)
+    want, wlo, whi = checker.ref_mesh_to_distance_volume(orc, origin, voxel, dims)
+    b = np.asarray(origin, np.float32) + np.float32(0.5) * np.asarray(voxel, np.float32)
+    xf = np.array([voxel[0], 0, 0, 0, voxel[1], 0, 0, 0, voxel[2], b[0], b[1], b[2]], np.float32)
+    rep = checker.compare_sdf(got, want, orc.calc_from_grid(dims, xf))
+    assert rep["ok"], rep
+    assert lo == pytest.approx(wlo, rel=1e-5) and hi == pytest.approx(whi, rel=1e-5)
+    assert lo < 0 < hi
+
+
+@pytest.mark.parametrize("offset,close_holes", [(0.15, True), (0.15, False), (-0.1, True)])
+def test_mc_offset_mesh_matches_reference_pipeline(offset, close_holes):
+    """grid dims/origin identical; vertex and face counts identical wherever the sign fields match (north_star)"""
+    pts, tris = meshgen.make_torus(2, 1, 96, 48)
+    fwn = mb.FastWindingNumber(pts, tris)
+    orc = checker.best_oracle(pts, tris)
+    voxel = 0.11
+    v, t, info = fwn.mc_offset_mesh(offset, voxel, close_holes=close_holes)
+    wv, wt, wsdf, worigin, wdims = checker.ref_mc_offset_mesh(orc, pts, tris, offset, voxel, close_holes=close_holes)
+    lo, hi = fwn.bounding_box()
+    assert np.array_equal(lo, pts.min(0)) and np.array_equal(hi, pts.max(0))
+    assert info["dims"] == wdims and np.array_equal(info["origin"], worigin)
+    assert len(t) > 1000 and t.min() >= 0 and t.max() < len(v)
+    assert (len(v), len(t)) == (len(wv), len(wt))
+    assert np.abs(v - wv).max() < 1e-4  # same vertices up to the 1e-5 relative distance tolerance through the interpolation
+    assert np.array_equal(t, wt)
