@@ -28,7 +28,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-from meshlib_b200 import meshgen  # noqa: E402
+from meshlib_b200 import meshgen, slabs  # noqa: E402
 
 METRIC = "sdf_voxels_per_sec"
 UNIT = "voxels/s"
@@ -231,8 +231,7 @@ def run_ours(args, wl):
     opts = mb.DistOptions(o["min_dist_sq"], o["max_dist_sq"], o["null_outside"], o["threshold"], o["beta"])
     layer = dims[0] * dims[1]
     total = layer * dims[2]
-    z0, z1 = rank * dims[2] // world, (rank + 1) * dims[2] // world
-    assert dims[2] % world == 0 or world == 1, "z layers must divide evenly for the in-place all-gather"
+    z0, z1 = slabs.slab_range(rank, world, dims[2])
 
     fwn = mb.FastWindingNumber(wl["points"], wl["tris"], device=local)
     st0 = fwn.stats()
@@ -255,7 +254,7 @@ def run_ours(args, wl):
         g_ms = 0.0
         if world > 1:
             ev[0].record()
-            dist.all_gather_into_tensor(volume, slab)
+            slabs.gather_slabs(volume, rank, world, dims, dist)
             ev[1].record()
             ev[1].synchronize()
             g_ms = ev[0].elapsed_time(ev[1])
