@@ -21,7 +21,8 @@
 // Arithmetic contract (b2fwn_math.cuh): far-field DECISIONS and box / closest-point distances round exactly like the
 // reference's scalar code, so every voxel accepts exactly the reference's set of dipoles and the distance is the
 // reference's value bit for bit; the accepted dipole TERMS use MUFU rsqrt (<= 1e-6 relative).  Distance candidates are
-// first filtered by a conservative plane-distance lower bound in FP32; survivors get the reference's double closest point.
+// first filtered by an FP32 distance estimate in the triangle's own frame with a stated allowance (b2fwn_math.cuh);
+// survivors get the reference's double closest point.
 #include "b2fwn_internal.h"
 #include "b2fwn_math.cuh"
 #include <cfloat>
@@ -149,6 +150,7 @@ __global__ void __launch_bounds__( 256 ) kBrickCull( const TravNode* __restrict_
 // ---- distance walk -----------------------------------------------------------------------------------------------------
 template <bool STATS>
 __global__ void __launch_bounds__( GRID_TB ) kGridDist( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
+                                                        const LeafFilt* __restrict__ filt,
                                                         const GridParams P, float* __restrict__ out, const uint8_t* __restrict__ active,
                                                         unsigned long long* __restrict__ stats )
 {
@@ -160,7 +162,7 @@ __global__ void __launch_bounds__( GRID_TB ) kGridDist( const TravNode* __restri
     const int N = ( active && !active[blockIdx.x * (size_t)( GRID_TB / 32 ) + ( threadIdx.x >> 5 )] ) ? 0 : P.numNodes;
 
     float3 p[VX];
-    float pmag[VX], best[VX];
+    float pmag[VX], best[VX], sbest[VX]; // sbest = sqrt(best), for the FP32 candidate filter
     int dR[VX]; // resume index of every voxel
 #pragma unroll
     for ( int v = 0; v < VX; ++v )
@@ -169,6 +171,7 @@ __global__ void __launch_bounds__( GRID_TB ) kGridDist( const TravNode* __restri
         p[v] = applyXf( P.A, P.b, (float)( B.x0 + v ), (float)B.y, (float)B.z );
         pmag[v] = 1e-6f * ( fabsf( p[v].x ) + fabsf( p[v].y ) + fabsf( p[v].z ) );
         best[v] = P.maxDistSq;
+        sbest[v] = sqrtf( P.maxDistSq );
         dR[v] = valid ? 0 : INT_MAX;
     }
 
@@ -202,6 +205,7 @@ __global__ void __launch_bounds__( GRID_TB ) kGridDist( const TravNode* __restri
                 if ( cand < best[v] )
                 {
                     best[v] = cand;
+                    sbest[v] = sqrtf( cand );
                     if ( best[v] <= P.minDistSq ) dR[v] = INT_MAX; // MRMeshProject.cpp:81-82
                 }
             }
@@ -213,7 +217,7 @@ __global__ void __launch_bounds__( GRID_TB ) kGridDist( const TravNode* __restri
     {
         // experiment: how many nodes would a walk visit that starts from a perfect upper bound?
 #pragma unroll
-        for ( int v = 0; v < VX; ++v ) { best[v] = best[v] * 1.000001f; dR[v] = ( B.rowValid && B.x0 + v < P.dx ) ? 0 : INT_MAX; }
+        for ( int v = 0; v < VX; ++v ) { best[v] = best[v] * 1.000001f; sbest[v] = sqrtf( best[v] ); dR[v] = ( B.rowValid && B.x0 + v < P.dx ) ? 0 : INT_MAX; }
 #pragma unroll
         for ( int k = 0; k < 5; ++k ) cnt[k] = 0;
     }
@@ -251,20 +255,36 @@ __global__ void __launch_bounds__( GRID_TB ) kGridDist( const TravNode* __restri
             }
             if ( __any_sync( FULL, need ) )
             {
-                const float4* tp = reinterpret_cast<const float4*>( tris + ( -link - 1 ) );
-                const float4 ta = __ldg( tp ), tb = __ldg( tp + 1 ), tc = __ldg( tp + 2 ), tn = __ldg( tp + 3 );
+                const int slot = -link - 1;
+                const float4* fp = reinterpret_cast<const float4*>( filt + slot );
+                const float4 f0 = __ldg( fp ), f1 = __ldg( fp + 1 ), f2 = __ldg( fp + 2 ), f3 = __ldg( fp + 3 );
+                const float3 vv = make_float3( fmaf( f2.y, f1.z, -f2.z * f1.y ), fmaf( f2.z, f1.x, -f2.x * f1.z ), fmaf( f2.x, f1.y, -f2.y * f1.x ) ); // v = n x u
                 if ( lane == 0 ) B2_COUNT( 2, 1 );
+                bool ex = false;
 #pragma unroll
                 for ( int v = 0; v < VX; ++v )
                 {
-                    if ( !go[v] ) continue;
-                    if ( planeBoundRejects( p[v], pmag[v], ta, tn, best[v] ) ) { B2_COUNT( 4, 1 ); continue; }
-                    B2_COUNT( 3, 1 );
-                    const float cand = triDistSqExact( p[v], ta, tb, tc );
-                    if ( cand < best[v] )
+                    const bool rej = estimateRejects( p[v], pmag[v], sbest[v], f0, f1, f2, f3, vv );
+                    B2_COUNT( 4, go[v] && rej );
+                    go[v] = go[v] && !rej;
+                    ex |= go[v];
+                }
+                if ( __any_sync( FULL, ex ) )
+                {
+                    const float4* tp = reinterpret_cast<const float4*>( tris + slot );
+                    const float4 ta = __ldg( tp ), tb = __ldg( tp + 1 ), tc = __ldg( tp + 2 );
+#pragma unroll
+                    for ( int v = 0; v < VX; ++v )
                     {
-                        best[v] = cand;
-                        if ( best[v] <= P.minDistSq ) dR[v] = INT_MAX; // MRMeshProject.cpp:81-82
+                        if ( !go[v] ) continue;
+                        B2_COUNT( 3, 1 );
+                        const float cand = triDistSqExact( p[v], ta, tb, tc );
+                        if ( cand < best[v] )
+                        {
+                            best[v] = cand;
+                            sbest[v] = sqrtf( cand );
+                            if ( best[v] <= P.minDistSq ) dR[v] = INT_MAX; // MRMeshProject.cpp:81-82
+                        }
                     }
                 }
             }
@@ -467,7 +487,7 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
         unsigned long long* dStats = nullptr; unsigned long long h[10];
         B2_CUDA( cudaMalloc( &dStats, sizeof( h ) ) );
         B2_CUDA( cudaMemsetAsync( dStats, 0, sizeof( h ), st ) );
-        if ( MODE == 1 ) kGridDist<true><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, dActive, dStats );
+        if ( MODE == 1 ) kGridDist<true><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, dActive, dStats );
         kGridFwn<MODE, true><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, dStats + 5 );
         B2_CUDA( cudaMemcpyAsync( h, dStats, sizeof( h ), cudaMemcpyDeviceToHost, st ) );
         B2_CUDA( cudaStreamSynchronize( st ) );
@@ -478,7 +498,7 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
     }
     else
     {
-        if ( MODE == 1 ) kGridDist<false><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, dActive, nullptr );
+        if ( MODE == 1 ) kGridDist<false><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, dActive, nullptr );
         kGridFwn<MODE, false><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, nullptr );
     }
     if ( launches ) *launches += ( MODE == 1 ? 2 : 1 );

@@ -39,12 +39,22 @@ struct __align__( 16 ) TravNode
     float4 q0, q1, q2, q3;
 };
 
-// Leaf triangle, 64 B (half a 128-B line): a.w carries the FaceId bits; n = unit normal (computed in double, rounded)
-// and n.w = 1e-6 * (largest |coordinate| of the triangle, summed over axes): the rounding allowance of the
-// plane-distance lower bound that filters candidates before the exact (double) closest-point evaluation.
+// Leaf triangle, 48 B: a.w carries the FaceId bits.
 struct __align__( 16 ) LeafTri
 {
-    float4 a, b, c, n;
+    float4 a, b, c;
+};
+
+// Leaf filter record, 64 B: the triangle in its own orthonormal frame (computed in double, rounded once), used for the FP32
+// distance estimate that decides whether a candidate needs the reference's exact (double) closest point at all.
+//   f0 = { a.x, a.y, a.z, bx }        a = first vertex, bx = |b - a|
+//   f1 = { u.x, u.y, u.z, cx }        u = (b - a) / bx,        (cx, cy) = c - a in the (u, v) frame, cy > 0
+//   f2 = { n.x, n.y, n.z, cy }        n = unit normal,  v = n x u
+//   f3 = { 1/|c-b|^2, 1/|c-a|^2, allowance, 0 }   allowance = absolute error budget of the estimate that depends on the
+//        triangle alone; +inf for degenerate triangles (they always take the exact path)
+struct __align__( 16 ) LeafFilt
+{
+    float4 f0, f1, f2, f3;
 };
 
 struct DeviceTree
@@ -58,6 +68,7 @@ struct DeviceTree
     RefDipole* refDipoles = nullptr;
     TravNode* nodes = nullptr;   // numNodes
     LeafTri* leafTris = nullptr; // numLeaves, in pre-order leaf order
+    LeafFilt* leafFilt = nullptr; // numLeaves, same order
 };
 
 struct GridXf

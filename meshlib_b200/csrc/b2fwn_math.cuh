@@ -199,13 +199,43 @@ __device__ __forceinline__ float dipoleTermFast( const float dx, const float dy,
     return fmaf( dx, q3.x, fmaf( dy, q3.y, dz * q3.z ) ) * ( r * r * r );
 }
 
-// conservative test "the exact squared distance from p to the triangle cannot be below best": the distance to the
-// triangle's plane is a lower bound of the distance to the triangle; allowance = rounding of this evaluation and of the
-// reference's own float rounding of the projection (1e-6 * coordinate magnitudes, >= 8 ulp of every term involved)
-__device__ __forceinline__ bool planeBoundRejects( const float3 p, const float pmag, const float4 ta, const float4 tn, const float best )
+// FP32 estimate of the distance from p to a triangle given in its own frame (LeafFilt): decides whether a candidate can
+// possibly beat the running best before the reference's double-precision closest point is spent on it.
+//   w = p - a;  (x, y, h) = (w.u, w.v, w.n);  d^2 = h^2 + (2-D distance from (x, y) to the triangle (0,0) (bx,0) (cx,cy))^2
+// Every quantity is a first-order function of w with error <= ~4e-7 |w| (frame vectors are double-computed and rounded once;
+// no barycentric solve, so nothing is ill-conditioned for far points or thin triangles); the 2-D point-segment distances add
+// a few ulp of (|w| + edge length).  Allowance used by the caller, in DISTANCE units:
+//   m = 3e-6 |w|_1 + f3.z + pmag,  f3.z = 3e-6 (|ab| + |ac|) + 1e-6 |tri|_1,  pmag = 1e-6 |p|_1
+// (>= 3x the bound above, plus the reference's own float rounding of the projection, <= 2^-24 * coordinate magnitude per
+// axis).  A candidate is rejected only if estimate - m >= sqrt(best); rejected candidates cannot be the minimum, so the
+// result stays the reference's value bit for bit.
+__device__ __forceinline__ bool estimateRejects( const float3 p, const float pmag, const float sqrtBest,
+                                                 const float4 f0, const float4 f1, const float4 f2, const float4 f3, const float3 vv )
 {
-    const float pd = fabsf( fmaf( tn.x, p.x - ta.x, fmaf( tn.y, p.y - ta.y, tn.z * ( p.z - ta.z ) ) ) ) - ( pmag + tn.w );
-    return pd > 0.f && pd * pd >= best;
+    const float wx = p.x - f0.x, wy = p.y - f0.y, wz = p.z - f0.z;
+    const float x = fmaf( wx, f1.x, fmaf( wy, f1.y, wz * f1.z ) );
+    const float y = fmaf( wx, vv.x, fmaf( wy, vv.y, wz * vv.z ) );
+    const float h = fmaf( wx, f2.x, fmaf( wy, f2.y, wz * f2.z ) );
+    const float bx = f0.w, cx = f1.w, cy = f2.w;
+    // edge a-b (the x axis)
+    const float tab = fminf( fmaxf( x, 0.f ), bx );
+    const float dab = fmaf( x - tab, x - tab, y * y );
+    // edge b-c
+    const float ex = cx - bx, xb = x - bx;
+    const float sbc = __saturatef( fmaf( xb, ex, y * cy ) * f3.x );
+    const float rbx = fmaf( -sbc, ex, xb ), rby = fmaf( -sbc, cy, y );
+    const float dbc = fmaf( rbx, rbx, rby * rby );
+    // edge a-c
+    const float sca = __saturatef( fmaf( x, cx, y * cy ) * f3.y );
+    const float rcx = fmaf( -sca, cx, x ), rcy = fmaf( -sca, cy, y );
+    const float dca = fmaf( rcx, rcx, rcy * rcy );
+    // inside the (counter-clockwise) triangle?
+    const bool inside = y >= 0.f && fmaf( ex, y, -cy * xb ) >= 0.f && fmaf( cy, x, -cx * y ) >= 0.f;
+    const float ip = inside ? 0.f : fminf( dab, fminf( dbc, dca ) );
+    const float d2 = fmaf( h, h, ip );
+    const float m = fmaf( 3e-6f, fabsf( wx ) + fabsf( wy ) + fabsf( wz ), f3.z + pmag );
+    const float lim = sqrtBest + m;
+    return d2 >= lim * lim;
 }
 
 } // namespace b2

@@ -363,7 +363,7 @@ __global__ void kFinishDipoles( size_t nNodes, const RefNode* __restrict__ nodes
 // leaf slot = leaf position in the final sorted order (= pre-order rank of the leaf)
 __global__ void kLeafSlots( int nLeaves, const int32_t* __restrict__ leafNodeOfPos, int32_t* __restrict__ leafSlotOfNode,
                             const LevelKey* __restrict__ keys, const float* __restrict__ pts,
-                            const int32_t* __restrict__ tris, LeafTri* __restrict__ out )
+                            const int32_t* __restrict__ tris, LeafTri* __restrict__ out, LeafFilt* __restrict__ filt )
 {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if ( p >= nLeaves ) return;
@@ -374,15 +374,37 @@ __global__ void kLeafSlots( int nLeaves, const int32_t* __restrict__ leafNodeOfP
     t.a = make_float4( pts[3 * (size_t)ia], pts[3 * (size_t)ia + 1], pts[3 * (size_t)ia + 2], __int_as_float( (int)f ) );
     t.b = make_float4( pts[3 * (size_t)ib], pts[3 * (size_t)ib + 1], pts[3 * (size_t)ib + 2], 0.f );
     t.c = make_float4( pts[3 * (size_t)ic], pts[3 * (size_t)ic + 1], pts[3 * (size_t)ic + 2], 0.f );
-    // unit normal in double (a zero-area face keeps n = 0: its plane bound is 0 and never filters)
+    // the triangle in its own frame, in double, rounded once (LeafFilt, b2fwn_internal.h)
     const double ux = (double)t.b.x - t.a.x, uy = (double)t.b.y - t.a.y, uz = (double)t.b.z - t.a.z;
     const double vx = (double)t.c.x - t.a.x, vy = (double)t.c.y - t.a.y, vz = (double)t.c.z - t.a.z;
     double nx = uy * vz - uz * vy, ny = uz * vx - ux * vz, nz = ux * vy - uy * vx;
-    const double len = sqrt( nx * nx + ny * ny + nz * nz );
-    if ( len > 0 ) { nx /= len; ny /= len; nz /= len; } else { nx = ny = nz = 0; }
-    const float mag = fmaxf( fmaxf( fabsf( t.a.x ), fabsf( t.b.x ) ), fabsf( t.c.x ) ) + fmaxf( fmaxf( fabsf( t.a.y ), fabsf( t.b.y ) ), fabsf( t.c.y ) )
-                      + fmaxf( fmaxf( fabsf( t.a.z ), fabsf( t.b.z ) ), fabsf( t.c.z ) );
-    t.n = make_float4( (float)nx, (float)ny, (float)nz, 1e-6f * mag );
+    const double nlen = sqrt( nx * nx + ny * ny + nz * nz ), bx = sqrt( ux * ux + uy * uy + uz * uz );
+    const double lenCA2 = vx * vx + vy * vy + vz * vz;
+    const double ex = vx - ux, ey = vy - uy, ez = vz - uz, lenBC2 = ex * ex + ey * ey + ez * ez;
+    LeafFilt fr;
+    // slivers (sine of the angle at a below 1e-3) and degenerate triangles always take the exact path
+    const bool good = bx > 0 && lenCA2 > 0 && lenBC2 > 0 && nlen > 1e-3 * bx * sqrt( lenCA2 );
+    if ( good )
+    {
+        nx /= nlen; ny /= nlen; nz /= nlen;
+        const double e1x = ux / bx, e1y = uy / bx, e1z = uz / bx;
+        const double e2x = ny * e1z - nz * e1y, e2y = nz * e1x - nx * e1z, e2z = nx * e1y - ny * e1x; // v = n x u
+        const double cx = vx * e1x + vy * e1y + vz * e1z, cy = vx * e2x + vy * e2y + vz * e2z;
+        const float mag = fmaxf( fmaxf( fabsf( t.a.x ), fabsf( t.b.x ) ), fabsf( t.c.x ) ) + fmaxf( fmaxf( fabsf( t.a.y ), fabsf( t.b.y ) ), fabsf( t.c.y ) )
+                          + fmaxf( fmaxf( fabsf( t.a.z ), fabsf( t.b.z ) ), fabsf( t.c.z ) );
+        fr.f0 = make_float4( t.a.x, t.a.y, t.a.z, (float)bx );
+        fr.f1 = make_float4( (float)e1x, (float)e1y, (float)e1z, (float)cx );
+        fr.f2 = make_float4( (float)nx, (float)ny, (float)nz, (float)cy );
+        fr.f3 = make_float4( (float)( 1.0 / lenBC2 ), (float)( 1.0 / lenCA2 ), 3e-6f * (float)( bx + sqrt( lenCA2 ) ) + 1e-6f * mag, 0.f );
+    }
+    else
+    {
+        fr.f0 = make_float4( t.a.x, t.a.y, t.a.z, 0.f );
+        fr.f1 = make_float4( 1.f, 0.f, 0.f, 0.f );
+        fr.f2 = make_float4( 0.f, 0.f, 1.f, 1.f );
+        fr.f3 = make_float4( 1.f, 1.f, __int_as_float( 0x7f800000 ), 0.f );
+    }
+    filt[p] = fr;
     out[p] = t;
 }
 
@@ -393,7 +415,7 @@ inline unsigned nblk( size_t n ) { return (unsigned)( ( n + TB - 1 ) / TB ); }
 void freeTree( DeviceTree& t )
 {
     cudaFree( t.points ); cudaFree( t.tris ); cudaFree( t.refNodes ); cudaFree( t.refDipoles );
-    cudaFree( t.nodes ); cudaFree( t.leafTris );
+    cudaFree( t.nodes ); cudaFree( t.leafTris ); cudaFree( t.leafFilt );
     t = DeviceTree{};
 }
 
@@ -450,6 +472,7 @@ int buildTree( DeviceTree& t, cudaStream_t st, uint64_t* launches )
     B2_CUDA( cudaMalloc( &t.refDipoles, N * sizeof( RefDipole ) ) );
     B2_CUDA( cudaMalloc( &t.nodes, N * sizeof( TravNode ) ) );
     B2_CUDA( cudaMalloc( &t.leafTris, (size_t)L * sizeof( LeafTri ) ) );
+    B2_CUDA( cudaMalloc( &t.leafFilt, (size_t)L * sizeof( LeafFilt ) ) );
 
     uint32_t* dBBox = nullptr;
     B2_CUDA( cudaMalloc( &dBBox, 6 * sizeof( uint32_t ) ) );
@@ -495,7 +518,7 @@ int buildTree( DeviceTree& t, cudaStream_t st, uint64_t* launches )
     }
 
     // 3. leaf triangles in pre-order leaf order, dipoles bottom-up, packed traversal nodes
-    kLeafSlots<<<nblk( L ), TB, 0, st>>>( L, dLeafNodeOfPos, dLeafSlotOfNode, dKeys, t.points, t.tris, t.leafTris ); ++nl;
+    kLeafSlots<<<nblk( L ), TB, 0, st>>>( L, dLeafNodeOfPos, dLeafSlotOfNode, dKeys, t.points, t.tris, t.leafTris, t.leafFilt ); ++nl;
     kLeafDipoles<<<nblk( N ), TB, 0, st>>>( N, t.refNodes, t.points, t.tris, t.refDipoles ); ++nl;
     for ( int lev = levels - 1; lev >= 0; --lev )
     {
