@@ -53,7 +53,6 @@ struct GridParams
     int nullOutside;
     int numNodes;
     int vecStore;        // rows are 16-B aligned: float4 accesses
-    int rewalk;          // STATS experiment
 };
 
 __device__ __forceinline__ int skipOf( int link, int i ) { return link < 0 ? i + 1 : link; }
@@ -148,22 +147,26 @@ __global__ void __launch_bounds__( 256 ) kBrickCull( const TravNode* __restrict_
 }
 
 // ---- distance walk -----------------------------------------------------------------------------------------------------
+// Nearest-first depth-first walk with ONE warp-uniform stack (the order of findProjectionSubtree, MRMeshProject.cpp:43-100:
+// both children are box-tested at the parent, the nearer one is entered first, the other is pushed).  The stack lives in
+// registers, one entry per lane (depth <= log2 F < 32), push = predicated move, pop = one shuffle.  A child is entered when
+// ANY of the brick's 128 voxels still needs it (box distance < that voxel's running best); near/far is decided for the
+// brick centre.  No per-voxel traversal state at all: a popped subtree is simply re-tested against the (tighter) bests.
+// The result is the exact minimum over all triangles of the reference's per-triangle value, hence independent of the order.
 template <bool STATS>
 __global__ void __launch_bounds__( GRID_TB ) kGridDist( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
-                                                        const LeafFilt* __restrict__ filt,
-                                                        const GridParams P, float* __restrict__ out, const uint8_t* __restrict__ active,
-                                                        unsigned long long* __restrict__ stats )
+                                                        const LeafFilt* __restrict__ filt, const GridParams P, float* __restrict__ out,
+                                                        const uint8_t* __restrict__ active, unsigned long long* __restrict__ stats )
 {
     unsigned cnt[5] = { 0, 0, 0, 0, 0 };
     const unsigned lane = threadIdx.x & 31;
     Brick B;
     if ( !brickOfWarp( P, B ) ) return;
     // a culled brick keeps maxDistSq everywhere: no walk
-    const int N = ( active && !active[blockIdx.x * (size_t)( GRID_TB / 32 ) + ( threadIdx.x >> 5 )] ) ? 0 : P.numNodes;
+    const bool walk = P.numNodes > 0 && !( active && !active[blockIdx.x * (size_t)( GRID_TB / 32 ) + ( threadIdx.x >> 5 )] );
 
     float3 p[VX];
-    float pmag[VX], best[VX], sbest[VX]; // sbest = sqrt(best), for the FP32 candidate filter
-    int dR[VX]; // resume index of every voxel
+    float pmag[VX], best[VX], lim[VX], sbest[VX]; // lim = best while the voxel still searches, -1 once it stopped; sbest = sqrt(best)
 #pragma unroll
     for ( int v = 0; v < VX; ++v )
     {
@@ -172,101 +175,35 @@ __global__ void __launch_bounds__( GRID_TB ) kGridDist( const TravNode* __restri
         pmag[v] = 1e-6f * ( fabsf( p[v].x ) + fabsf( p[v].y ) + fabsf( p[v].z ) );
         best[v] = P.maxDistSq;
         sbest[v] = sqrtf( P.maxDistSq );
-        dR[v] = valid ? 0 : INT_MAX;
+        lim[v] = valid ? P.maxDistSq : -1.f;
     }
+    const float3 pc = applyXf( P.A, P.b, (float)( B.bx * BX ) + 3.5f, (float)( B.by * BY ) + 1.5f, (float)( P.zBegin + B.bz * BZ ) + 1.5f );
 
-    if ( N > 0 && P.maxDistSq == FLT_MAX )
+    if ( walk )
     {
-        // no upper limit given: a greedy descent towards the brick centre finds one near triangle, which gives every
-        // voxel a finite upper bound and makes the order-independent pre-order walk prune like the reference's
-        // nearest-first walk (with a band limit the walk is pruned by maxDistSq from the start)
-        const float3 pc = applyXf( P.A, P.b, (float)( B.bx * BX ) + 3.5f, (float)( B.by * BY ) + 1.5f, (float)( P.zBegin + B.bz * BZ ) + 1.5f );
-        int j = 0;
-        int link = __float_as_int( __ldg( reinterpret_cast<const float4*>( nodes ) + 1 ).w );
-        while ( link >= 0 )
+        int stN = 0, stI = 0, sp = 0; // lane k holds stack entry k
+        int n = 0;
+        // info of a node: leaf -> its (negative) link, internal -> index of its right child
+        const float4 r1 = __ldg( reinterpret_cast<const float4*>( nodes ) + 1 );
+        int info = __float_as_int( r1.w ) < 0 ? __float_as_int( r1.w ) : __float_as_int( r1.z );
+        for ( ;; )
         {
-            const int l = j + 1;
-            const float4* lp = reinterpret_cast<const float4*>( nodes + l );
-            const float4 l0 = __ldg( lp ), l1 = __ldg( lp + 1 );
-            const int llink = __float_as_int( l1.w );
-            const int r = skipOf( llink, l );
-            const float4* rp = reinterpret_cast<const float4*>( nodes + r );
-            const float4 r0 = __ldg( rp ), r1 = __ldg( rp + 1 );
-            if ( boxDistSqBF( pc, l0, l1 ) <= boxDistSqBF( pc, r0, r1 ) ) { j = l; link = llink; }
-            else { j = r; link = __float_as_int( r1.w ); }
-        }
-        const float4* tp = reinterpret_cast<const float4*>( tris + ( -link - 1 ) );
-        const float4 ta = __ldg( tp ), tb = __ldg( tp + 1 ), tc = __ldg( tp + 2 );
-#pragma unroll
-        for ( int v = 0; v < VX; ++v )
-            if ( dR[v] == 0 )
+            bool pop = true;
+            if ( info < 0 )
             {
-                const float cand = triDistSqExact( p[v], ta, tb, tc );
-                if ( cand < best[v] )
-                {
-                    best[v] = cand;
-                    sbest[v] = sqrtf( cand );
-                    if ( best[v] <= P.minDistSq ) dR[v] = INT_MAX; // MRMeshProject.cpp:81-82
-                }
-            }
-    }
-
-    for ( int walk = 0; walk < ( STATS && P.rewalk ? 2 : 1 ); ++walk )
-    {
-    if ( walk == 1 )
-    {
-        // experiment: how many nodes would a walk visit that starts from a perfect upper bound?
-#pragma unroll
-        for ( int v = 0; v < VX; ++v ) { best[v] = best[v] * 1.000001f; sbest[v] = sqrtf( best[v] ); dR[v] = ( B.rowValid && B.x0 + v < P.dx ) ? 0 : INT_MAX; }
-#pragma unroll
-        for ( int k = 0; k < 5; ++k ) cnt[k] = 0;
-    }
-    int i = __reduce_min_sync( FULL, min4( dR ) );
-    while ( i < N )
-    {
-        const float4* np = reinterpret_cast<const float4*>( nodes + i );
-        const float4 q0 = __ldg( np ), q1 = __ldg( np + 1 );
-        const int link = __float_as_int( q1.w );
-        if ( lane == 0 ) B2_COUNT( 0, 1 );
-        bool descend = false;
-        if ( link >= 0 )
-        {
-#pragma unroll
-            for ( int v = 0; v < VX; ++v )
-            {
-                const bool a = i >= dR[v];
-                B2_COUNT( 1, a );
-                const bool pr = boxDistSqBF( p[v], q0, q1 ) >= best[v]; // MRMeshProject.cpp:30, 48
-                dR[v] = ( a && pr ) ? link : dR[v];
-                descend |= a && !pr;
-            }
-        }
-        else
-        {
-            bool go[VX], need = false;
-#pragma unroll
-            for ( int v = 0; v < VX; ++v )
-            {
-                const bool a = i >= dR[v];
-                B2_COUNT( 1, a );
-                go[v] = a && !( boxDistSqBF( p[v], q0, q1 ) >= best[v] );
-                dR[v] = a ? i + 1 : dR[v];
-                need |= go[v];
-            }
-            if ( __any_sync( FULL, need ) )
-            {
-                const int slot = -link - 1;
+                // leaf: FP32 estimate first, the reference's double closest point for the survivors
+                const int slot = -info - 1;
                 const float4* fp = reinterpret_cast<const float4*>( filt + slot );
                 const float4 f0 = __ldg( fp ), f1 = __ldg( fp + 1 ), f2 = __ldg( fp + 2 ), f3 = __ldg( fp + 3 );
                 const float3 vv = make_float3( fmaf( f2.y, f1.z, -f2.z * f1.y ), fmaf( f2.z, f1.x, -f2.x * f1.z ), fmaf( f2.x, f1.y, -f2.y * f1.x ) ); // v = n x u
                 if ( lane == 0 ) B2_COUNT( 2, 1 );
-                bool ex = false;
+                bool go[VX], ex = false;
 #pragma unroll
                 for ( int v = 0; v < VX; ++v )
                 {
                     const bool rej = estimateRejects( p[v], pmag[v], sbest[v], f0, f1, f2, f3, vv );
-                    B2_COUNT( 4, go[v] && rej );
-                    go[v] = go[v] && !rej;
+                    go[v] = lim[v] >= 0.f && !rej;
+                    B2_COUNT( 4, lim[v] >= 0.f && rej );
                     ex |= go[v];
                 }
                 if ( __any_sync( FULL, ex ) )
@@ -279,19 +216,54 @@ __global__ void __launch_bounds__( GRID_TB ) kGridDist( const TravNode* __restri
                         if ( !go[v] ) continue;
                         B2_COUNT( 3, 1 );
                         const float cand = triDistSqExact( p[v], ta, tb, tc );
-                        if ( cand < best[v] )
+                        if ( cand < best[v] ) // MRMeshProject.cpp:78
                         {
                             best[v] = cand;
                             sbest[v] = sqrtf( cand );
-                            if ( best[v] <= P.minDistSq ) dR[v] = INT_MAX; // MRMeshProject.cpp:81-82
+                            lim[v] = cand <= P.minDistSq ? -1.f : cand; // MRMeshProject.cpp:81-82: this voxel stops searching
                         }
                     }
                 }
             }
+            else
+            {
+                const int l = n + 1, r = info;
+                const float4* lp = reinterpret_cast<const float4*>( nodes + l );
+                const float4* rp = reinterpret_cast<const float4*>( nodes + r );
+                const float4 l0 = __ldg( lp ), l1 = __ldg( lp + 1 ), r0 = __ldg( rp ), r1q = __ldg( rp + 1 );
+                if ( lane == 0 ) B2_COUNT( 0, 2 );
+                bool wl = false, wr = false;
+#pragma unroll
+                for ( int v = 0; v < VX; ++v )
+                {
+                    B2_COUNT( 1, lim[v] >= 0.f ? 2 : 0 );
+                    wl |= boxDistSqBF( p[v], l0, l1 ) < lim[v]; // prune on boxDistSq >= best, MRMeshProject.cpp:30, 48
+                    wr |= boxDistSqBF( p[v], r0, r1q ) < lim[v];
+                }
+                const bool WL = __any_sync( FULL, wl ), WR = __any_sync( FULL, wr );
+                const int infoL = __float_as_int( l1.w ) < 0 ? __float_as_int( l1.w ) : __float_as_int( l1.z );
+                const int infoR = __float_as_int( r1q.w ) < 0 ? __float_as_int( r1q.w ) : __float_as_int( r1q.z );
+                if ( WL || WR )
+                {
+                    pop = false;
+                    const bool leftFirst = WL && ( !WR || boxDistSqBF( pc, l0, l1 ) <= boxDistSqBF( pc, r0, r1q ) );
+                    if ( WL && WR )
+                    {
+                        if ( (int)lane == sp ) { stN = leftFirst ? r : l; stI = leftFirst ? infoR : infoL; }
+                        ++sp;
+                    }
+                    n = leftFirst ? l : r;
+                    info = leftFirst ? infoL : infoR;
+                }
+            }
+            if ( pop )
+            {
+                if ( sp == 0 ) break;
+                --sp;
+                n = __shfl_sync( FULL, stN, sp );
+                info = __shfl_sync( FULL, stI, sp );
+            }
         }
-        if ( __any_sync( FULL, descend ) ) ++i;
-        else i = __reduce_min_sync( FULL, min4( dR ) );
-    }
     }
     flushCounters<STATS>( cnt, stats );
 
@@ -481,7 +453,6 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
         if ( launches ) ++*launches;
     }
     static const bool wantStats = getenv( "B2FWN_STATS" ) != nullptr;
-    P.rewalk = getenv( "B2FWN_REWALK" ) != nullptr;
     if ( wantStats )
     {
         unsigned long long* dStats = nullptr; unsigned long long h[10];

@@ -29,7 +29,7 @@ struct RefDipole
 
 // Traversal node, 64 B = 4 x float4, one 128-B line holds two consecutive pre-order nodes.
 //   q0 = { bmin.x, bmin.y, bmin.z, bmax.x }
-//   q1 = { bmax.y, bmax.z, 0, link }          <- distance half (one 32-B sector)
+//   q1 = { bmax.y, bmax.z, right, link }      <- distance half (one 32-B sector); right = index of the right child (int bits)
 //   q2 = { pos.x, pos.y, pos.z, rr }
 //   q3 = { dirArea.x, dirArea.y, dirArea.z, link }   <- winding-number half (one 32-B sector)
 // link (int bits): internal node: index of the first node AFTER this node's subtree (pre-order "skip" pointer);

@@ -354,7 +354,7 @@ __global__ void kFinishDipoles( size_t nNodes, const RefNode* __restrict__ nodes
     const int link = nd.r < 0 ? -( leafSlotOfNode[i] + 1 ) : skip[i];
     TravNode t;
     t.q0 = make_float4( nd.bmin[0], nd.bmin[1], nd.bmin[2], nd.bmax[0] );
-    t.q1 = make_float4( nd.bmax[1], nd.bmax[2], 0.f, __int_as_float( link ) );
+    t.q1 = make_float4( nd.bmax[1], nd.bmax[2], __int_as_float( nd.r < 0 ? 0 : nd.r ), __int_as_float( link ) ); // .z = right child
     t.q2 = make_float4( d.pos[0], d.pos[1], d.pos[2], d.rr );
     t.q3 = make_float4( d.dirArea[0], d.dirArea[1], d.dirArea[2], __int_as_float( link ) );
     trav[i] = t;

@@ -341,3 +341,23 @@ def test_mc_offset_mesh_matches_reference_pipeline(offset, close_holes):
     assert (len(v), len(t)) == (len(wv), len(wt))
     assert np.abs(v - wv).max() < 1e-4  # same vertices up to the 1e-5 relative distance tolerance through the interpolation
     assert np.array_equal(t, wt)
+
+
+# ---- the reference's own CUDA kernels on this GPU (second baseline, 8d): sanity, not a parity gate ---------------------
+def test_reference_cuda_kernels_agree_with_ours():
+    from oracle import refcudalib
+    if not refcudalib.available():
+        pytest.skip("oracle/_ref/libmrrefcuda.so was not built (needs the reference sources)")
+    pts, tris = meshgen.make_torus(2, 1, 64, 32)
+    orc = checker.best_oracle(pts, tris)
+    ref = refcudalib.RefCudaFwn(orc.nodes(), orc.dipoles(), pts, tris)
+    dims = (24, 24, 16)
+    xf = mb.make_basis_xf((-3.3, -3.3, -1.3), (0.275, 0.275, 0.1625))
+    ms, want = ref.signed_distance_layers(dims, xf, 0, dims[2])
+    got = mb.FastWindingNumber(pts, tris).calc_from_grid_with_distances(dims, xf)
+    assert ms > 0
+    # the reference GPU path is float + fast-math (MRCudaMath.cuh:193-247): compare loosely
+    assert np.array_equal(np.isnan(got), np.isnan(want))
+    ok = ~np.isnan(got)
+    assert (np.sign(got[ok]) == np.sign(want[ok])).mean() > 0.999
+    assert np.abs(np.abs(got[ok]) - np.abs(want[ok])).max() < 1e-3
