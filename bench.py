@@ -165,6 +165,26 @@ def cpu_baseline(wl, budget_s=15.0):
                       f"mesh+tree setup {setup_s:.1f} s excluded", "layers": layers}
 
 
+def ref_cuda_baseline(wl, layers):
+    """SURVEY.md 8(d) second baseline: the reference's own CUDA kernels (oracle/_ref/libmrrefcuda.so, unmodified
+    MRCudaFastWindingNumber.cu for sm_100, -use_fast_math) on this GPU, fed the reference's CPU-built tree, on the same
+    bounded sample of z-layers as the CPU baseline; kernel time by CUDA events"""
+    from oracle import refcudalib, reflib
+    if not (refcudalib.available() and reflib.available()):
+        return None
+    m = reflib.RefMesh.from_arrays(wl["points"], wl["tris"])
+    ref = refcudalib.RefCudaFwn(m.nodes(), m.dipoles(), m.points, m.tris)  # what prepareData_ uploads
+    o = wl["opts"]
+    kw = dict(min_dist_sq=o["min_dist_sq"], max_dist_sq=o["max_dist_sq"], null_outside=o["null_outside"], threshold=o["threshold"],
+              beta=o["beta"], fetch=False)
+    ref.signed_distance_layers(wl["dims"], wl["xf"], layers[0], layers[0] + 1, **kw)  # warm-up, not counted
+    ms = sum(ref.signed_distance_layers(wl["dims"], wl["xf"], z, z + 1, **kw)[0] for z in layers)
+    ref.close()
+    nvox = len(layers) * wl["dims"][0] * wl["dims"][1]
+    return {"value": nvox / (ms * 1e-3), "unit": UNIT, "kind": "reference CUDA kernels (MRCudaFastWindingNumber.cu, sm_100, -use_fast_math), kernel time only",
+            "sample": f"{len(layers)} z-layers ({nvox} voxels, {ms:.1f} ms)"}
+
+
 def algorithmic_flops(wl, layers, max_samples=200000):
     """operation counts of the reference algorithm (C restatement, counters) on a stride sample of the given layers"""
     from oracle import portlib
@@ -350,8 +370,15 @@ def run_ours(args, wl):
     if world == 1 and not args.no_cpu:
         cb = cpu_baseline(wl, args.cpu_budget)
         fpv, per_voxel, n = algorithmic_flops(wl, cb["layers"])
+        layers_for_gpu_ref = cb["layers"]
         del cb["layers"]
         out["cpu_baseline"] = cb
+        try:
+            rc = ref_cuda_baseline(wl, layers_for_gpu_ref)
+            if rc:
+                out["ref_cuda_baseline"] = rc
+        except Exception as e:  # a baseline, never a reason to lose the bench line
+            out["ref_cuda_baseline"] = {"error": str(e)[:200]}
         ach = fpv * nslab0 / (k_ms * 1e-3) / 1e12
         out["roofline"].update({"achieved": ach, "frac": ach / fp32_peak, "flops_per_voxel": fpv, "ops_per_voxel": per_voxel,
                                 "ops_sample": f"{n} voxels (stride sample of the cpu_baseline layers), reference algorithm counters"})
