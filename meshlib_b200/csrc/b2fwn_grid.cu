@@ -153,7 +153,7 @@ __global__ void __launch_bounds__( 256 ) kBrickCull( const TravNode* __restrict_
 // ANY of the brick's 128 voxels still needs it (box distance < that voxel's running best); near/far is decided for the
 // brick centre.  No per-voxel traversal state at all: a popped subtree is simply re-tested against the (tighter) bests.
 // The result is the exact minimum over all triangles of the reference's per-triangle value, hence independent of the order.
-template <bool STATS>
+template <bool AA, bool STATS>
 __global__ void __launch_bounds__( GRID_TB ) kGridDist( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
                                                         const LeafFilt* __restrict__ filt, const GridParams P, float* __restrict__ out,
                                                         const uint8_t* __restrict__ active, unsigned long long* __restrict__ stats )
@@ -172,6 +172,7 @@ __global__ void __launch_bounds__( GRID_TB ) kGridDist( const TravNode* __restri
     {
         const bool valid = B.rowValid && B.x0 + v < P.dx;
         p[v] = applyXf( P.A, P.b, (float)( B.x0 + v ), (float)B.y, (float)B.z );
+        if ( AA ) { p[v].y = p[0].y; p[v].z = p[0].z; } // axis-aligned grid: the lane's voxels share y, z (see kGridFwn)
         pmag[v] = 1e-6f * ( fabsf( p[v].x ) + fabsf( p[v].y ) + fabsf( p[v].z ) );
         best[v] = P.maxDistSq;
         sbest[v] = sqrtf( P.maxDistSq );
@@ -289,7 +290,9 @@ __global__ void __launch_bounds__( GRID_TB ) kGridDist( const TravNode* __restri
 // ---- winding-number walk -------------------------------------------------------------------------------------------------
 // MODE 0: out = w (calcFromGrid).  MODE 1: out holds |d| or NaN from kGridDist; NaN voxels are skipped, the others become
 // w > threshold ? -|d| : |d| (calcWithDistances, MRFastWindingNumber.cpp:69-76)
-template <int MODE, bool STATS>
+// AA: the grid is axis-aligned in mesh space (A diagonal, every MeshLib caller): the 4 voxels of a lane share y and z, so
+// the y/z differences and squares of the far-field test are computed once per lane instead of four times (same rounding).
+template <int MODE, bool AA, bool STATS>
 __global__ void __launch_bounds__( GRID_TB ) kGridFwn( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
                                                        const GridParams P, float* __restrict__ out, unsigned long long* __restrict__ stats )
 {
@@ -323,9 +326,22 @@ __global__ void __launch_bounds__( GRID_TB ) kGridFwn( const TravNode* __restric
     {
         const bool valid = B.rowValid && B.x0 + v < P.dx && !( dist[v] != dist[v] );
         p[v] = applyXf( P.A, P.b, (float)( B.x0 + v ), (float)B.y, (float)B.z );
+        if ( AA ) { p[v].y = p[0].y; p[v].z = p[0].z; } // bitwise equal anyway; lets the compiler share the y/z arithmetic
         sum[v] = 0.f;
         fR[v] = valid ? 0 : INT_MAX;
     }
+    // brick centre and radius (distance of the farthest voxel centre, padded): one warp-uniform test per node tells when
+    // EVERY voxel of the brick is inside beta * r of the node, i.e. all of them must descend -- no per-voxel work then.
+    // Conservative by 1e-5 relative against the exactly rounded per-voxel decision, so decisions are unchanged.
+    const float3 pc = applyXf( P.A, P.b, (float)( B.bx * BX ) + 3.5f, (float)( B.by * BY ) + 1.5f, (float)( P.zBegin + B.bz * BZ ) + 1.5f );
+    float rad = 0.f;
+#pragma unroll
+    for ( int v = 0; v < VX; ++v )
+    {
+        const float ex = p[v].x - pc.x, ey = p[v].y - pc.y, ez = p[v].z - pc.z;
+        rad = fmaxf( rad, ex * ex + ey * ey + ez * ez );
+    }
+    rad = sqrtf( __uint_as_float( __reduce_max_sync( FULL, __float_as_uint( rad ) ) ) ) * 1.00001f;
 
     int i = __reduce_min_sync( FULL, min4( fR ) );
     while ( i < N )
@@ -336,7 +352,16 @@ __global__ void __launch_bounds__( GRID_TB ) kGridFwn( const TravNode* __restric
         const float thr = FM( P.betaSq, q2.w );
         if ( lane == 0 ) B2_COUNT( 0, 1 );
         bool descend = false;
-        if ( link >= 0 )
+        // (|pos - centre| + radius)^2 <= thr * (1 - 1e-5)  =>  dd <= thr for every voxel of the brick
+        const float cx = q2.x - pc.x, cy = q2.y - pc.y, cz = q2.z - pc.z;
+        const float dcr = sqrtf( fmaf( cx, cx, fmaf( cy, cy, cz * cz ) ) ) * 1.00001f + rad;
+        const bool allNear = dcr * dcr <= thr * 0.99999f;
+        if ( link >= 0 && allNear )
+        {
+            if ( lane == 0 ) B2_COUNT( 4, 1 );
+            descend = true; // the walk is here because some voxel is awake, and every awake voxel descends
+        }
+        else if ( link >= 0 )
         {
 #pragma unroll
             for ( int v = 0; v < VX; ++v )
@@ -445,6 +470,7 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
     const size_t numBricks = (size_t)P.bricksX * P.bricksY * P.bricksZ;
     const size_t blocks = ( numBricks + GRID_TB / 32 - 1 ) / ( GRID_TB / 32 );
     if ( blocks > 0x7FFFFFFFull ) { setError( "grid too large for one launch" ); return B2FWN_ERR_INVALID; }
+    const bool aa = xf.A[1] == 0 && xf.A[2] == 0 && xf.A[3] == 0 && xf.A[5] == 0 && xf.A[6] == 0 && xf.A[7] == 0;
     uint8_t* dActive = nullptr;
     if ( MODE == 1 && P.maxDistSq < FLT_MAX && P.numNodes > 0 )
     {
@@ -458,8 +484,15 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
         unsigned long long* dStats = nullptr; unsigned long long h[10];
         B2_CUDA( cudaMalloc( &dStats, sizeof( h ) ) );
         B2_CUDA( cudaMemsetAsync( dStats, 0, sizeof( h ), st ) );
-        if ( MODE == 1 ) kGridDist<true><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, dActive, dStats );
-        kGridFwn<MODE, true><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, dStats + 5 );
+        if ( MODE == 1 )
+        {
+            if ( aa ) kGridDist<true, true><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, dActive, dStats );
+            else kGridDist<false, true><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, dActive, dStats );
+        }
+        {
+            if ( aa ) kGridFwn<MODE, true, true><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, dStats + 5 );
+            else kGridFwn<MODE, false, true><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, dStats + 5 );
+        }
         B2_CUDA( cudaMemcpyAsync( h, dStats, sizeof( h ), cudaMemcpyDeviceToHost, st ) );
         B2_CUDA( cudaStreamSynchronize( st ) );
         cudaFree( dStats );
@@ -469,8 +502,15 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
     }
     else
     {
-        if ( MODE == 1 ) kGridDist<false><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, dActive, nullptr );
-        kGridFwn<MODE, false><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, nullptr );
+        if ( MODE == 1 )
+        {
+            if ( aa ) kGridDist<true, false><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, dActive, nullptr );
+            else kGridDist<false, false><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, dActive, nullptr );
+        }
+        {
+            if ( aa ) kGridFwn<MODE, true, false><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, nullptr );
+            else kGridFwn<MODE, false, false><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, nullptr );
+        }
     }
     if ( launches ) *launches += ( MODE == 1 ? 2 : 1 );
     if ( dActive ) B2_CUDA( cudaFreeAsync( dActive, st ) );

@@ -361,3 +361,23 @@ def test_reference_cuda_kernels_agree_with_ours():
     ok = ~np.isnan(got)
     assert (np.sign(got[ok]) == np.sign(want[ok])).mean() > 0.999
     assert np.abs(np.abs(got[ok]) - np.abs(want[ok])).max() < 1e-3
+
+
+def test_general_affine_grid_transform():
+    """gridToMeshXf with rotation + shear (the non-axis-aligned kernel variants); same parity rules"""
+    pts, tris = meshgen.make_torus(2, 1, 48, 24)
+    fwn = mb.FastWindingNumber(pts, tris)
+    orc = checker.best_oracle(pts, tris)
+    c, s_ = np.cos(0.4), np.sin(0.4)
+    A = np.array([[c, -s_, 0.05], [s_, c, 0.0], [0.02, 0.1, 1.0]], np.float32) * np.float32(0.23)
+    xf = np.concatenate([A.reshape(9), np.array([-3.1, -3.4, -1.6], np.float32)]).astype(np.float32)
+    dims = (29, 30, 14)
+    rep = checker.compare_w(fwn.calc_from_grid(dims, xf), orc.calc_from_grid(dims, xf), atol=checker.W_GRID_ATOL)
+    assert rep["ok"], rep
+    rep = checker.compare_sdf(fwn.calc_from_grid_with_distances(dims, xf), orc.calc_from_grid_with_distances(dims, xf),
+                              orc.calc_from_grid(dims, xf))
+    assert rep["ok"], rep
+    band = dict(min_dist_sq=0.01, max_dist_sq=0.25, null_outside=True)
+    got = fwn.calc_from_grid_with_distances(dims, xf, mb.DistOptions(0.01, 0.25, True))
+    rep = checker.compare_sdf(got, orc.calc_from_grid_with_distances(dims, xf, **band), orc.calc_from_grid(dims, xf))
+    assert rep["ok"], rep
