@@ -29,6 +29,8 @@
 #include <climits>
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
+#include <type_traits>
 
 namespace b2
 {
@@ -62,15 +64,28 @@ struct Brick
 {
     int bx, by, bz, x0, y, z;
     bool rowValid;
-    size_t id; // output index of the lane's first voxel
+    size_t id;    // output index of the lane's first voxel
+    size_t brick; // linear brick index
 };
 
-__device__ __forceinline__ bool brickOfWarp( const GridParams& P, Brick& B )
+// Heavy-first dispatch.  Walk lengths are very uneven (c3_band: mean 217 node visits per brick, longest 17,845 -- the pole
+// of the UV sphere, thousands of slivers the far field cannot approximate) and the long walks used to sit wherever the
+// linear brick order put them: with the pole in the LAST z-layer one SM worked alone for the final 30 % of the kernel
+// (ncu r01: sm__cycles_active avg 45.6 M of 64.7 M elapsed).  A one-thread-per-brick estimate of the walk length picks the
+// bricks far above the mean; they take the first `cap` warp slots of the grid (started first, hidden behind the bulk), the
+// linear pass skips them.  Scheduling only: every brick is computed by the same code, results do not depend on the order.
+struct BrickOrder
+{
+    const uint32_t* heavy = nullptr; // brick indices of the heavy bricks
+    const unsigned* count = nullptr; // number of appended entries (may exceed cap: the surplus stayed in the linear pass)
+    const uint8_t* cls = nullptr;    // 1 = brick is in the heavy list
+    unsigned cap = 0;                // warp slots reserved at the front of the grid; 0 = plain linear order
+};
+
+__device__ __forceinline__ void brickFromIndex( const GridParams& P, const size_t brick, Brick& B )
 {
     const unsigned lane = threadIdx.x & 31;
-    const size_t brick = blockIdx.x * (size_t)( GRID_TB / 32 ) + ( threadIdx.x >> 5 );
-    const size_t numBricks = (size_t)P.bricksX * P.bricksY * P.bricksZ;
-    if ( brick >= numBricks ) return false; // whole warp
+    B.brick = brick;
     B.bx = (int)( brick % P.bricksX );
     B.by = (int)( ( brick / P.bricksX ) % P.bricksY );
     B.bz = (int)( brick / ( (size_t)P.bricksX * P.bricksY ) );
@@ -79,14 +94,36 @@ __device__ __forceinline__ bool brickOfWarp( const GridParams& P, Brick& B )
     B.z = P.zBegin + B.bz * BZ + (int)( lane >> 3 );
     B.rowValid = B.y < P.dy && B.z < P.zEnd;
     B.id = (size_t)B.x0 + (size_t)P.dx * ( (size_t)B.y + (size_t)P.dy * (size_t)( B.z - P.zBegin ) );
+}
+
+// warp slot -> brick.  The first `cap` slots belong to the heavy list, the rest walk the bricks in linear order and skip the
+// listed ones.  false: nothing to do for this warp.
+__device__ __forceinline__ bool brickOfWarp( const GridParams& P, const BrickOrder& O, Brick& B )
+{
+    const size_t slot = blockIdx.x * (size_t)( GRID_TB / 32 ) + ( threadIdx.x >> 5 );
+    const size_t numBricks = (size_t)P.bricksX * P.bricksY * P.bricksZ;
+    size_t brick;
+    if ( slot < O.cap )
+    {
+        if ( slot >= *O.count ) return false; // whole warp
+        brick = O.heavy[slot];
+    }
+    else
+    {
+        brick = slot - O.cap;
+        if ( brick >= numBricks ) return false;
+        if ( O.cap && O.cls[brick] ) return false;
+    }
+    brickFromIndex( P, brick, B );
     return true;
 }
 
 // development counters (B2FWN_STATS=1): [0] node visits (warp) [1] tests by awake voxels [2] leaf visits that loaded the
 // triangle (warp) [3] exact evaluations (voxel) [4] candidates rejected by the plane bound (voxel)
 #define B2_COUNT( k, n ) do { if ( STATS ) cnt[k] += ( n ); } while ( 0 )
+constexpr int STAT_HIST = 5, STAT_MAX = 38, STAT_WORDS = 40; // per kernel
 template <bool STATS>
-__device__ __forceinline__ void flushCounters( const unsigned ( &cnt )[5], unsigned long long* stats )
+__device__ __forceinline__ void flushCounters( const unsigned ( &cnt )[5], unsigned long long* stats, const size_t brickIdx )
 {
     if ( !STATS ) return;
 #pragma unroll
@@ -94,6 +131,13 @@ __device__ __forceinline__ void flushCounters( const unsigned ( &cnt )[5], unsig
     {
         const unsigned tot = __reduce_add_sync( FULL, cnt[k] );
         if ( ( threadIdx.x & 31 ) == 0 ) atomicAdd( stats + k, (unsigned long long)tot );
+    }
+    // distribution of the walk length over bricks: histogram of log2(node visits), and the longest walk with its brick
+    if ( ( threadIdx.x & 31 ) == 0 )
+    {
+        const unsigned long long brick = brickIdx;
+        atomicAdd( stats + STAT_HIST + ( cnt[0] ? 32 - __clz( cnt[0] ) : 0 ), 1ull );
+        atomicMax( stats + STAT_MAX, ( (unsigned long long)cnt[0] << 32 ) | ( brick & 0xFFFFFFFFull ) );
     }
 }
 
@@ -104,46 +148,165 @@ __device__ __forceinline__ void flushCounters( const unsigned ( &cnt )[5], unsig
 // Conservative: a brick is culled only if every leaf BOX is farther than maxDist * (1 + 1e-4) from the padded brick box, so
 // no triangle can produce a candidate < maxDistSq for any of its voxels (candidates must be strictly smaller,
 // MRMeshProject.cpp:78) -- the culled result is exactly what the walk would return.
-__global__ void __launch_bounds__( 256 ) kBrickCull( const TravNode* __restrict__ nodes, const GridParams P, uint8_t* __restrict__ active )
+// The walk does not stop at the first leaf in range: it counts the node boxes in range (leaves weighted), which is the
+// length of the distance walk the brick's warp is going to do.  cost = 0 <=> culled; the counts feed the heavy-first order.
+constexpr unsigned COST_MAX = 4096u; // estimates stop here (one thread walks them): anything longer is heavy anyway
+__global__ void __launch_bounds__( 256 ) kBrickCull( const TravNode* __restrict__ nodes, const GridParams P, uint16_t* __restrict__ cost,
+                                                     unsigned long long* __restrict__ totals )
+{
+    const size_t brick = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    const size_t numBricks = (size_t)P.bricksX * P.bricksY * P.bricksZ;
+    unsigned c = 0;
+    if ( brick < numBricks )
+    {
+        const int bx = (int)( brick % P.bricksX );
+        const int by = (int)( ( brick / P.bricksX ) % P.bricksY );
+        const int bz = (int)( brick / ( (size_t)P.bricksX * P.bricksY ) );
+        float lo[3] = { FLT_MAX, FLT_MAX, FLT_MAX }, hi[3] = { -FLT_MAX, -FLT_MAX, -FLT_MAX };
+#pragma unroll
+        for ( int k = 0; k < 8; ++k )
+        {
+            const float3 q = applyXf( P.A, P.b, (float)( bx * BX + ( ( k & 1 ) ? BX - 1 : 0 ) ), (float)( by * BY + ( ( k & 2 ) ? BY - 1 : 0 ) ),
+                                      (float)( P.zBegin + bz * BZ + ( ( k & 4 ) ? BZ - 1 : 0 ) ) );
+            lo[0] = fminf( lo[0], q.x ); hi[0] = fmaxf( hi[0], q.x );
+            lo[1] = fminf( lo[1], q.y ); hi[1] = fmaxf( hi[1], q.y );
+            lo[2] = fminf( lo[2], q.z ); hi[2] = fmaxf( hi[2], q.z );
+        }
+#pragma unroll
+        for ( int k = 0; k < 3; ++k )
+        {
+            const float pad = 1e-5f * fmaxf( fabsf( lo[k] ), fabsf( hi[k] ) ); // interior voxels round a few ulp off the corner hull
+            lo[k] -= pad; hi[k] += pad;
+        }
+        const float lim = P.maxDistSq * 1.0001f;
+        int i = 0;
+        unsigned visits = 0, leaves = 0;
+        while ( i < P.numNodes && visits < COST_MAX )
+        {
+            const float4* np = reinterpret_cast<const float4*>( nodes + i );
+            const float4 q0 = __ldg( np ), q1 = __ldg( np + 1 );
+            const int link = __float_as_int( q1.w );
+            const float ddx = fmaxf( fmaxf( q0.x - hi[0], lo[0] - q0.w ), 0.f );
+            const float ddy = fmaxf( fmaxf( q0.y - hi[1], lo[1] - q1.x ), 0.f );
+            const float ddz = fmaxf( fmaxf( q0.z - hi[2], lo[2] - q1.y ), 0.f );
+            const float d = ddx * ddx + ddy * ddy + ddz * ddz;
+            ++visits;
+            if ( d > lim ) i = skipOf( link, i );
+            else { leaves += link < 0; ++i; }
+        }
+        // a walk cut short by the cap has not seen every leaf: such a brick stays active whatever it found
+        c = ( leaves || visits >= COST_MAX ) ? min( visits + 8 * leaves, COST_MAX ) : 0;
+        cost[brick] = (uint16_t)c;
+    }
+    // totals[0] = sum of the costs, totals[1] = number of bricks with a walk
+    const unsigned sum = __reduce_add_sync( FULL, c ), cntw = __popc( __ballot_sync( FULL, c != 0 ) );
+    if ( ( threadIdx.x & 31 ) == 0 && sum ) { atomicAdd( totals, (unsigned long long)sum ); atomicAdd( totals + 1, (unsigned long long)cntw ); }
+}
+
+// Length of a winding-number walk over a ball of voxels (centre pc, radius rad), estimated by ONE thread with the kernel's
+// own brick-level tests: a node is entered when some voxel of the ball may be inside beta * r of it (centre distance minus
+// radius), otherwise every voxel accepts its dipole and the walk leaves the subtree.  Leaves that need the triangle are
+// weighted.  The estimate is monotone in the ball: a ball inside another never walks more.
+__device__ __forceinline__ unsigned fwnCostWalk( const TravNode* __restrict__ nodes, const int numNodes, const float betaSq, const float3 pc,
+                                                 const float rad )
+{
+    unsigned c = 0;
+    int i = 0;
+    while ( i < numNodes && c < COST_MAX )
+    {
+        const float4* np = reinterpret_cast<const float4*>( nodes + i );
+        const float4 q2 = __ldg( np + 2 );
+        const int link = __float_as_int( __ldg( reinterpret_cast<const float*>( np + 3 ) + 3 ) );
+        const float cx = q2.x - pc.x, cy = q2.y - pc.y, cz = q2.z - pc.z;
+        const float dn = fmaxf( sqrtf( cx * cx + cy * cy + cz * cz ) - rad, 0.f );
+        const bool near = dn * dn <= betaSq * q2.w;
+        if ( link < 0 ) { c += near ? 8 : 1; ++i; }
+        else { ++c; i = near ? i + 1 : link; }
+    }
+    return min( c, COST_MAX );
+}
+// radius in mesh space of a box of voxel centres with half extents (hx, hy, hz) in voxel units
+__device__ __forceinline__ float boxRadius( const GridParams& P, const float hx, const float hy, const float hz )
+{
+    float rad = 0.f;
+#pragma unroll
+    for ( int k = 0; k < 4; ++k )
+    {
+        const float sx = hx, sy = ( k & 1 ) ? -hy : hy, sz = ( k & 2 ) ? -hz : hz;
+        const float ex = P.A[0] * sx + P.A[1] * sy + P.A[2] * sz, ey = P.A[3] * sx + P.A[4] * sy + P.A[5] * sz,
+                    ez = P.A[6] * sx + P.A[7] * sy + P.A[8] * sz;
+        rad = fmaxf( rad, ex * ex + ey * ey + ez * ez );
+    }
+    return sqrtf( rad ) * 1.0001f;
+}
+
+// first level: one estimate per GROUP of 2 x 2 x 2 bricks (per brick the estimate cost 54 ms at c5, 5 % of the step); the
+// ball of a group contains the balls of its bricks, so a brick can only be heavy inside a heavy group
+constexpr int GRP = 2;
+__global__ void __launch_bounds__( 256 ) kGroupCostFwn( const TravNode* __restrict__ nodes, const GridParams P, const int gX, const int gY,
+                                                        const int gZ, uint16_t* __restrict__ cost, unsigned long long* __restrict__ totals )
+{
+    const size_t group = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    const size_t numGroups = (size_t)gX * gY * gZ;
+    unsigned c = 0;
+    if ( group < numGroups )
+    {
+        const int gx = (int)( group % gX ), gy = (int)( ( group / gX ) % gY ), gz = (int)( group / ( (size_t)gX * gY ) );
+        const float hx = 0.5f * ( GRP * BX - 1 ), hy = 0.5f * ( GRP * BY - 1 ), hz = 0.5f * ( GRP * BZ - 1 );
+        const float3 pc = applyXf( P.A, P.b, (float)( gx * GRP * BX ) + hx, (float)( gy * GRP * BY ) + hy, (float)( P.zBegin + gz * GRP * BZ ) + hz );
+        c = fwnCostWalk( nodes, P.numNodes, P.betaSq, pc, boxRadius( P, hx, hy, hz ) );
+        cost[group] = (uint16_t)c;
+    }
+    const unsigned sum = __reduce_add_sync( FULL, c ), cntw = __popc( __ballot_sync( FULL, c != 0 ) );
+    if ( ( threadIdx.x & 31 ) == 0 && sum ) { atomicAdd( totals, (unsigned long long)sum ); atomicAdd( totals + 1, (unsigned long long)cntw ); }
+}
+
+// Estimates far above the mean go to the heavy list (BrickOrder).  The threshold is a multiple of the mean estimate of the
+// walking bricks / groups, kept inside the range the capped estimates can express.
+constexpr unsigned HEAVY_FACTOR = 8, HEAVY_MIN = COST_MAX / 2;
+__device__ __forceinline__ unsigned heavyThreshold( const unsigned long long* __restrict__ totals )
+{
+    const unsigned long long mean = totals[1] ? totals[0] / totals[1] : 0;
+    return (unsigned)min( (unsigned long long)COST_MAX - 1, max( (unsigned long long)HEAVY_MIN, HEAVY_FACTOR * mean ) );
+}
+__global__ void __launch_bounds__( 256 ) kBrickHeavy( const uint16_t* __restrict__ cost, const size_t numBricks,
+                                                      const unsigned long long* __restrict__ totals, uint32_t* __restrict__ heavy,
+                                                      unsigned* __restrict__ count, uint8_t* __restrict__ cls, const unsigned cap )
+{
+    const size_t brick = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if ( brick >= numBricks ) return;
+    uint8_t h = 0;
+    if ( cost[brick] > heavyThreshold( totals ) )
+    {
+        const unsigned k = atomicAdd( count, 1u );
+        if ( k < cap ) { heavy[k] = (uint32_t)brick; h = 1; }
+    }
+    cls[brick] = h;
+}
+// second level: the bricks of a heavy group get their own estimate; those above the same threshold are listed
+__global__ void __launch_bounds__( 256 ) kGroupHeavy( const TravNode* __restrict__ nodes, const uint16_t* __restrict__ cost, const GridParams P,
+                                                      const int gX, const int gY, const unsigned long long* __restrict__ totals,
+                                                      uint32_t* __restrict__ heavy, unsigned* __restrict__ count, uint8_t* __restrict__ cls,
+                                                      const unsigned cap )
 {
     const size_t brick = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     const size_t numBricks = (size_t)P.bricksX * P.bricksY * P.bricksZ;
     if ( brick >= numBricks ) return;
-    const int bx = (int)( brick % P.bricksX );
-    const int by = (int)( ( brick / P.bricksX ) % P.bricksY );
-    const int bz = (int)( brick / ( (size_t)P.bricksX * P.bricksY ) );
-    float lo[3] = { FLT_MAX, FLT_MAX, FLT_MAX }, hi[3] = { -FLT_MAX, -FLT_MAX, -FLT_MAX };
-#pragma unroll
-    for ( int c = 0; c < 8; ++c )
+    const int bx = (int)( brick % P.bricksX ), by = (int)( ( brick / P.bricksX ) % P.bricksY ), bz = (int)( brick / ( (size_t)P.bricksX * P.bricksY ) );
+    const size_t group = (size_t)( bx / GRP ) + (size_t)gX * ( (size_t)( by / GRP ) + (size_t)gY * (size_t)( bz / GRP ) );
+    const unsigned thr = heavyThreshold( totals );
+    uint8_t h = 0;
+    if ( cost[group] > thr )
     {
-        const float3 q = applyXf( P.A, P.b, (float)( bx * BX + ( ( c & 1 ) ? BX - 1 : 0 ) ), (float)( by * BY + ( ( c & 2 ) ? BY - 1 : 0 ) ),
-                                  (float)( P.zBegin + bz * BZ + ( ( c & 4 ) ? BZ - 1 : 0 ) ) );
-        lo[0] = fminf( lo[0], q.x ); hi[0] = fmaxf( hi[0], q.x );
-        lo[1] = fminf( lo[1], q.y ); hi[1] = fmaxf( hi[1], q.y );
-        lo[2] = fminf( lo[2], q.z ); hi[2] = fmaxf( hi[2], q.z );
+        const float hx = 0.5f * ( BX - 1 ), hy = 0.5f * ( BY - 1 ), hz = 0.5f * ( BZ - 1 );
+        const float3 pc = applyXf( P.A, P.b, (float)( bx * BX ) + hx, (float)( by * BY ) + hy, (float)( P.zBegin + bz * BZ ) + hz );
+        if ( fwnCostWalk( nodes, P.numNodes, P.betaSq, pc, boxRadius( P, hx, hy, hz ) ) > thr )
+        {
+            const unsigned k = atomicAdd( count, 1u );
+            if ( k < cap ) { heavy[k] = (uint32_t)brick; h = 1; }
+        }
     }
-#pragma unroll
-    for ( int k = 0; k < 3; ++k )
-    {
-        const float pad = 1e-5f * fmaxf( fabsf( lo[k] ), fabsf( hi[k] ) ); // interior voxels round a few ulp off the corner hull
-        lo[k] -= pad; hi[k] += pad;
-    }
-    const float lim = P.maxDistSq * 1.0001f;
-    int i = 0, hit = 0;
-    while ( i < P.numNodes )
-    {
-        const float4* np = reinterpret_cast<const float4*>( nodes + i );
-        const float4 q0 = __ldg( np ), q1 = __ldg( np + 1 );
-        const int link = __float_as_int( q1.w );
-        const float ddx = fmaxf( fmaxf( q0.x - hi[0], lo[0] - q0.w ), 0.f );
-        const float ddy = fmaxf( fmaxf( q0.y - hi[1], lo[1] - q1.x ), 0.f );
-        const float ddz = fmaxf( fmaxf( q0.z - hi[2], lo[2] - q1.y ), 0.f );
-        const float d = ddx * ddx + ddy * ddy + ddz * ddz;
-        if ( d > lim ) i = skipOf( link, i );
-        else if ( link < 0 ) { hit = 1; break; }
-        else ++i;
-    }
-    active[brick] = (uint8_t)hit;
+    cls[brick] = h;
 }
 
 // ---- distance walk -----------------------------------------------------------------------------------------------------
@@ -156,14 +319,15 @@ __global__ void __launch_bounds__( 256 ) kBrickCull( const TravNode* __restrict_
 template <bool AA, bool STATS>
 __global__ void __launch_bounds__( GRID_TB ) kGridDist( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
                                                         const LeafFilt* __restrict__ filt, const GridParams P, float* __restrict__ out,
-                                                        const uint8_t* __restrict__ active, unsigned long long* __restrict__ stats )
+                                                        const uint16_t* __restrict__ cullCost, const BrickOrder O,
+                                                        unsigned long long* __restrict__ stats )
 {
     unsigned cnt[5] = { 0, 0, 0, 0, 0 };
     const unsigned lane = threadIdx.x & 31;
     Brick B;
-    if ( !brickOfWarp( P, B ) ) return;
-    // a culled brick keeps maxDistSq everywhere: no walk
-    const bool walk = P.numNodes > 0 && !( active && !active[blockIdx.x * (size_t)( GRID_TB / 32 ) + ( threadIdx.x >> 5 )] );
+    if ( !brickOfWarp( P, O, B ) ) return;
+    // a culled brick (kBrickCull: cost 0) keeps maxDistSq everywhere: no walk
+    const bool walk = P.numNodes > 0 && !( cullCost && !cullCost[B.brick] );
 
     float3 p[VX];
     float pmag[VX], best[VX], lim[VX], sbest[VX]; // lim = best while the voxel still searches, -1 once it stopped; sbest = sqrt(best)
@@ -266,7 +430,7 @@ __global__ void __launch_bounds__( GRID_TB ) kGridDist( const TravNode* __restri
             }
         }
     }
-    flushCounters<STATS>( cnt, stats );
+    flushCounters<STATS>( cnt, stats, B.brick );
 
     if ( !B.rowValid ) return;
     float res[VX];
@@ -294,12 +458,13 @@ __global__ void __launch_bounds__( GRID_TB ) kGridDist( const TravNode* __restri
 // the y/z differences and squares of the far-field test are computed once per lane instead of four times (same rounding).
 template <int MODE, bool AA, bool STATS>
 __global__ void __launch_bounds__( GRID_TB ) kGridFwn( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
-                                                       const GridParams P, float* __restrict__ out, unsigned long long* __restrict__ stats )
+                                                       const GridParams P, float* __restrict__ out, const BrickOrder O,
+                                                       unsigned long long* __restrict__ stats )
 {
     unsigned cnt[5] = { 0, 0, 0, 0, 0 };
     const unsigned lane = threadIdx.x & 31;
     Brick B;
-    if ( !brickOfWarp( P, B ) ) return;
+    if ( !brickOfWarp( P, O, B ) ) return;
     const int N = P.numNodes;
 
     float dist[VX] = { 0.f, 0.f, 0.f, 0.f };
@@ -406,7 +571,7 @@ __global__ void __launch_bounds__( GRID_TB ) kGridFwn( const TravNode* __restric
         if ( __any_sync( FULL, descend ) ) ++i;
         else i = __reduce_min_sync( FULL, min4( fR ) );
     }
-    flushCounters<STATS>( cnt, stats );
+    flushCounters<STATS>( cnt, stats, B.brick );
 
     if ( !B.rowValid ) return;
     constexpr float INV_4PI = 1.0f / ( 4 * 3.14159265358979323846f ); // MRDipole.cpp:126
@@ -429,6 +594,188 @@ __global__ void __launch_bounds__( GRID_TB ) kGridFwn( const TravNode* __restric
 }
 #undef B2_COUNT
 
+// ---- winding-number walk, v5 -------------------------------------------------------------------------------------------
+// Same walk and the same decisions as kGridFwn above with fewer issued instructions per node (ncu r01: 46 % of the issue
+// slots were warp-uniform per-node overhead, the ALU pipe -- compares and selects -- was the busiest pipe at 46 %):
+//  * the next node comes from ONE warp reduction: m = min over the warp of the resume indices AFTER the node was
+//    processed; an awake voxel that neither accepted nor slept keeps resume <= i, so "descend" <=> m <= i and the next node
+//    is max(m, i+1) -- no per-voxel descend predicates, no vote;
+//  * the all-near test uses one MUFU square root (sqrt.approx, 2^-22 relative, inside the test's 1e-5 margins) instead of
+//    the IEEE sqrt sequence;
+//  * the denormal guard of the reference (`d > 0`, MRDipole.h:24) can only matter when beta^2 rr < FLT_MIN; such nodes take
+//    a guarded copy of the loop body, all others carry no guard;
+//  * accepted terms are added under a predicate (one FFMA) instead of multiply + select + add.
+// (Fetching node i+1 ahead of time measured SLOWER: c5_band 1419 ms against 1182 ms -- 8 more registers, 2 more loads.
+//  Block size 32 / 64 / 128 measured the same.)
+// The walk is a function of NV voxels per lane, used with NV = 4 by the regular bricks and with NV = 1 by the slices of
+// heavy bricks (below); every term is added with the same explicit operations, so a voxel gets the same bits either way.
+__device__ __forceinline__ float sqrtApprox( const float x )
+{
+    float r;
+    asm( "sqrt.approx.ftz.f32 %0, %1;" : "=f"( r ) : "f"( x ) );
+    return r;
+}
+// the two factors of an accepted term, dot(dp, dirArea) and rsqrt(dd)^3, operation by operation; the caller adds them with
+// one explicit fmaf( dot, r3, sum ) -- no compiler-chosen contraction anywhere
+__device__ __forceinline__ void dipoleTermParts( const float dx, const float dy, const float dz, const float dd, const float4 q3, float& dot, float& r3 )
+{
+    const float r = rsqrtApprox( dd );
+    dot = fmaf( dx, q3.x, fmaf( dy, q3.y, FM( dz, q3.z ) ) );
+    r3 = FM( FM( r, r ), r );
+}
+template <int NV>
+__device__ __forceinline__ int minOf( const int ( &a )[NV] )
+{
+    int m = a[0];
+#pragma unroll
+    for ( int v = 1; v < NV; ++v ) m = min( m, a[v] );
+    return m;
+}
+
+template <bool GUARD, int NV>
+__device__ __forceinline__ void fwnInner( const int i, const int link, const float thr, const float4 q2, const float4 q3,
+                                          const float3 ( &p )[NV], float ( &sum )[NV], int ( &fR )[NV] )
+{
+#pragma unroll
+    for ( int v = 0; v < NV; ++v )
+    {
+        float ddx, ddy, ddz, dd, dot, r3;
+        const bool far = dipoleFar( p[v], thr, q2, ddx, ddy, ddz, dd );
+        dipoleTermParts( ddx, ddy, ddz, dd, q3, dot, r3 );
+        if ( i >= fR[v] && far )
+        {
+            if ( !GUARD || dd >= FLT_MIN ) sum[v] = fmaf( dot, r3, sum[v] );
+            fR[v] = link;
+        }
+    }
+}
+
+// walks the tree for the NV voxels of every lane; pc, rad = centre and padded radius of all voxels of the warp
+template <int NV>
+__device__ __forceinline__ void fwnWalk( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris, const int N, const float betaSq,
+                                         const float3 ( &p )[NV], const float3 pc, const float rad, float ( &sum )[NV], int ( &fR )[NV] )
+{
+    int i = __reduce_min_sync( FULL, minOf( fR ) );
+    while ( i < N )
+    {
+        const float4* np = reinterpret_cast<const float4*>( nodes + i );
+        const float4 q2 = __ldg( np + 2 ), q3 = __ldg( np + 3 );
+        const int link = __float_as_int( q3.w );
+        const float thr = FM( betaSq, q2.w );
+        if ( link >= 0 )
+        {
+            // (|pos - centre| + radius)^2 <= thr * (1 - 1e-5)  =>  dd <= thr for every voxel of the warp: all descend
+            const float cx = q2.x - pc.x, cy = q2.y - pc.y, cz = q2.z - pc.z;
+            const float dcr = fmaf( sqrtApprox( fmaf( cx, cx, fmaf( cy, cy, cz * cz ) ) ), 1.00001f, rad );
+            if ( dcr * dcr <= thr * 0.99999f ) { ++i; continue; }
+            if ( thr >= FLT_MIN ) fwnInner<false>( i, link, thr, q2, q3, p, sum, fR );
+            else fwnInner<true>( i, link, thr, q2, q3, p, sum, fR );
+        }
+        else
+        {
+            bool go[NV], need = false;
+#pragma unroll
+            for ( int v = 0; v < NV; ++v )
+            {
+                const bool a = i >= fR[v];
+                float ddx, ddy, ddz, dd, dot, r3;
+                const bool far = dipoleFar( p[v], thr, q2, ddx, ddy, ddz, dd );
+                dipoleTermParts( ddx, ddy, ddz, dd, q3, dot, r3 );
+                if ( a && far && dd >= FLT_MIN ) sum[v] = fmaf( dot, r3, sum[v] );
+                go[v] = a && !far;
+                fR[v] = a ? i + 1 : fR[v];
+                need |= go[v];
+            }
+            if ( __any_sync( FULL, need ) )
+            {
+                const float4* tp = reinterpret_cast<const float4*>( tris + ( -link - 1 ) );
+                const float4 ta = __ldg( tp ), tb = __ldg( tp + 1 ), tc = __ldg( tp + 2 );
+#pragma unroll
+                for ( int v = 0; v < NV; ++v )
+                    if ( go[v] ) sum[v] = FA( sum[v], triangleSolidAngle( p[v], ta, tb, tc ) );
+            }
+        }
+        i = max( __reduce_min_sync( FULL, minOf( fR ) ), i + 1 );
+    }
+}
+
+__device__ __forceinline__ float fwnResult( const int MODE, const float sum, const float dist, const float threshold )
+{
+    constexpr float INV_4PI = 1.0f / ( 4 * 3.14159265358979323846f ); // MRDipole.cpp:126
+    const float w = FM( INV_4PI, sum );
+    if ( MODE == 0 ) return w;
+    return ( dist != dist ) ? dist : ( ( w > threshold ) ? -dist : dist ); // MRFastWindingNumber.cpp:72-76
+}
+
+// Bricks of the heavy list (BrickOrder) are simply walked FIRST, by the same code.  Cutting them into 4 z-slices of one voxel
+// per lane was tried (as a branch of this kernel: ptxas then guards every warp reduction of the loop against divergence,
+// +10 % on the regular walk; as a kernel of its own on a side stream: the slices pay every node for 32 voxels instead of
+// 128, 4,195 listed bricks of c3_band cost 9 ms beside a 20 ms regular kernel) and dropped.
+template <int MODE, bool AA>
+__global__ void __launch_bounds__( GRID_TB ) kGridFwn5( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
+                                                        const GridParams P, float* __restrict__ out, const BrickOrder O )
+{
+    Brick B;
+    if ( !brickOfWarp( P, O, B ) ) return;
+    const int N = P.numNodes;
+
+    float dist[VX] = { 0.f, 0.f, 0.f, 0.f };
+    const bool vec = P.vecStore && B.x0 + VX <= P.dx;
+    if ( MODE == 1 && B.rowValid )
+    {
+        if ( vec )
+        {
+            const float4 d4 = *reinterpret_cast<const float4*>( out + B.id );
+            dist[0] = d4.x; dist[1] = d4.y; dist[2] = d4.z; dist[3] = d4.w;
+        }
+        else
+        {
+#pragma unroll
+            for ( int v = 0; v < VX; ++v )
+                if ( B.x0 + v < P.dx ) dist[v] = out[B.id + v];
+        }
+    }
+    float3 p[VX];
+    float sum[VX];
+    int fR[VX];
+#pragma unroll
+    for ( int v = 0; v < VX; ++v )
+    {
+        const bool valid = B.rowValid && B.x0 + v < P.dx && !( dist[v] != dist[v] );
+        p[v] = applyXf( P.A, P.b, (float)( B.x0 + v ), (float)B.y, (float)B.z );
+        if ( AA ) { p[v].y = p[0].y; p[v].z = p[0].z; } // bitwise equal anyway; lets the compiler share the y/z arithmetic
+        sum[v] = 0.f;
+        fR[v] = valid ? 0 : INT_MAX;
+    }
+    // brick centre and radius (distance of the farthest voxel centre, padded): one warp-uniform test per node tells when
+    // EVERY voxel of the brick is inside beta * r of the node, i.e. all of them must descend -- no per-voxel work then.
+    // Conservative by 1e-5 relative against the exactly rounded per-voxel decision, so decisions are unchanged.
+    const float3 pc = applyXf( P.A, P.b, (float)( B.bx * BX ) + 3.5f, (float)( B.by * BY ) + 1.5f, (float)( P.zBegin + B.bz * BZ ) + 1.5f );
+    float rad = 0.f;
+#pragma unroll
+    for ( int v = 0; v < VX; ++v )
+    {
+        const float ex = p[v].x - pc.x, ey = p[v].y - pc.y, ez = p[v].z - pc.z;
+        rad = fmaxf( rad, ex * ex + ey * ey + ez * ez );
+    }
+    rad = sqrtf( __uint_as_float( __reduce_max_sync( FULL, __float_as_uint( rad ) ) ) ) * 1.00001f;
+
+    fwnWalk<VX>( nodes, tris, N, P.betaSq, p, pc, rad, sum, fR );
+
+    if ( !B.rowValid ) return;
+    float res[VX];
+#pragma unroll
+    for ( int v = 0; v < VX; ++v ) res[v] = fwnResult( MODE, sum[v], dist[v], P.threshold );
+    if ( vec )
+        *reinterpret_cast<float4*>( out + B.id ) = make_float4( res[0], res[1], res[2], res[3] );
+    else
+    {
+#pragma unroll
+        for ( int v = 0; v < VX; ++v )
+            if ( B.x0 + v < P.dx ) out[B.id + v] = res[v];
+    }
+}
+
 inline int checkDims( const int32_t dims[3], int zBegin, int zEnd )
 {
     if ( dims[0] < 0 || dims[1] < 0 || dims[2] < 0 || zBegin < 0 || zEnd > dims[2] || zBegin > zEnd )
@@ -443,6 +790,10 @@ void printStats( const char* what, const unsigned long long* h, double voxels, d
 {
     fprintf( stderr, "[b2fwn stats] %s: voxels %.0f bricks %.0f | visits/brick %.1f tests/voxel %.1f leaf-loads/brick %.1f exact/voxel %.2f "
              "plane-rejected/voxel %.2f\n", what, voxels, bricks, h[0] / bricks, h[1] / voxels, h[2] / bricks, h[3] / voxels, h[4] / voxels );
+    fprintf( stderr, "[b2fwn stats] %s: longest walk %llu visits at brick %llu; bricks by log2(visits):", what, h[STAT_MAX] >> 32, h[STAT_MAX] & 0xFFFFFFFFull );
+    for ( int k = 0; k < 33; ++k )
+        if ( h[STAT_HIST + k] ) fprintf( stderr, " [<2^%d]=%llu", k, h[STAT_HIST + k] );
+    fprintf( stderr, "\n" );
 }
 
 // MODE 0: winding numbers only; MODE 1: distance walk, then winding-number walk over the same slab
@@ -471,49 +822,95 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
     const size_t blocks = ( numBricks + GRID_TB / 32 - 1 ) / ( GRID_TB / 32 );
     if ( blocks > 0x7FFFFFFFull ) { setError( "grid too large for one launch" ); return B2FWN_ERR_INVALID; }
     const bool aa = xf.A[1] == 0 && xf.A[2] == 0 && xf.A[3] == 0 && xf.A[5] == 0 && xf.A[6] == 0 && xf.A[7] == 0;
-    uint8_t* dActive = nullptr;
-    if ( MODE == 1 && P.maxDistSq < FLT_MAX && P.numNodes > 0 )
-    {
-        B2_CUDA( cudaMallocAsync( &dActive, numBricks, st ) );
-        kBrickCull<<<(unsigned)( ( numBricks + 255 ) / 256 ), 256, 0, st>>>( t.nodes, P, dActive );
-        if ( launches ) ++*launches;
-    }
     static const bool wantStats = getenv( "B2FWN_STATS" ) != nullptr;
+    static const bool heavyFirst = !( getenv( "B2FWN_LINEAR" ) && atoi( getenv( "B2FWN_LINEAR" ) ) ); // dev switch: plain linear order
+    const bool band = MODE == 1 && P.maxDistSq < FLT_MAX && P.numNodes > 0;
+    // small grids (c1: 16,384 bricks, 6.4 ms) lose more to the estimate kernels than a tail can cost them
+    const bool order = heavyFirst && !wantStats && P.numNodes > 0 && numBricks >= ( 1u << 16 ) && numBricks <= 0xFFFFFFFFull;
+
+    // scratch of this call: per-brick walk-length estimates (2 x u16), heavy lists (2 x cap u32), class bytes (2 x u8),
+    // totals (4 x u64) and list counters (2 x u32) in one stream-ordered allocation
+    const unsigned cap = order ? (unsigned)std::min<size_t>( numBricks, 1u << 16 ) : 0;
+    const size_t nbPad = ( numBricks + 15 ) & ~(size_t)15;
+    uint8_t* scratch = nullptr;
+    const size_t scratchBytes = 64 + 2 * nbPad * sizeof( uint16_t ) + 2 * nbPad + 2 * (size_t)cap * sizeof( uint32_t );
+    if ( band || order )
+    {
+        B2_CUDA( cudaMallocAsync( &scratch, scratchBytes, st ) );
+        B2_CUDA( cudaMemsetAsync( scratch, 0, 64, st ) );
+    }
+    unsigned long long* totals = reinterpret_cast<unsigned long long*>( scratch ); // [0,1] distance, [2,3] winding number
+    unsigned* counts = reinterpret_cast<unsigned*>( scratch + 32 );               // [0] distance, [1] winding number
+    uint16_t* costD = reinterpret_cast<uint16_t*>( scratch + 64 );
+    uint16_t* costF = costD + nbPad;
+    uint8_t* clsD = reinterpret_cast<uint8_t*>( costF + nbPad );
+    uint8_t* clsF = clsD + nbPad;
+    uint32_t* heavyD = reinterpret_cast<uint32_t*>( clsF + nbPad );
+    uint32_t* heavyF = heavyD + cap;
+    const unsigned nb256 = (unsigned)( ( numBricks + 255 ) / 256 );
+    BrickOrder oD, oF;
+    if ( band )
+    {
+        kBrickCull<<<nb256, 256, 0, st>>>( t.nodes, P, costD, totals );
+        if ( launches ) ++*launches;
+        if ( order )
+        {
+            kBrickHeavy<<<nb256, 256, 0, st>>>( costD, numBricks, totals, heavyD, counts, clsD, cap );
+            if ( launches ) ++*launches;
+            oD.heavy = heavyD; oD.count = counts; oD.cls = clsD; oD.cap = cap;
+        }
+    }
+    if ( order )
+    {
+        const int gX = ( P.bricksX + GRP - 1 ) / GRP, gY = ( P.bricksY + GRP - 1 ) / GRP, gZ = ( P.bricksZ + GRP - 1 ) / GRP;
+        kGroupCostFwn<<<(unsigned)( ( (size_t)gX * gY * gZ + 255 ) / 256 ), 256, 0, st>>>( t.nodes, P, gX, gY, gZ, costF, totals + 2 );
+        kGroupHeavy<<<nb256, 256, 0, st>>>( t.nodes, costF, P, gX, gY, totals + 2, heavyF, counts + 1, clsF, cap );
+        if ( launches ) *launches += 2;
+        oF.heavy = heavyF; oF.count = counts + 1; oF.cls = clsF; oF.cap = cap;
+    }
+    const uint16_t* cullCost = band ? costD : nullptr;
+    auto blocksFor = [&]( const BrickOrder& o ) { return (unsigned)( ( numBricks + o.cap + GRID_TB / 32 - 1 ) / ( GRID_TB / 32 ) ); };
     if ( wantStats )
     {
-        unsigned long long* dStats = nullptr; unsigned long long h[10];
+        unsigned long long* dStats = nullptr; unsigned long long h[2 * STAT_WORDS];
         B2_CUDA( cudaMalloc( &dStats, sizeof( h ) ) );
         B2_CUDA( cudaMemsetAsync( dStats, 0, sizeof( h ), st ) );
         if ( MODE == 1 )
         {
-            if ( aa ) kGridDist<true, true><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, dActive, dStats );
-            else kGridDist<false, true><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, dActive, dStats );
+            if ( aa ) kGridDist<true, true><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, dStats );
+            else kGridDist<false, true><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, dStats );
         }
-        {
-            if ( aa ) kGridFwn<MODE, true, true><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, dStats + 5 );
-            else kGridFwn<MODE, false, true><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, dStats + 5 );
-        }
+        if ( aa ) kGridFwn<MODE, true, true><<<blocksFor( oF ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, oF, dStats + STAT_WORDS );
+        else kGridFwn<MODE, false, true><<<blocksFor( oF ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, oF, dStats + STAT_WORDS );
         B2_CUDA( cudaMemcpyAsync( h, dStats, sizeof( h ), cudaMemcpyDeviceToHost, st ) );
         B2_CUDA( cudaStreamSynchronize( st ) );
         cudaFree( dStats );
         const double nv = (double)dims[0] * dims[1] * ( zEnd - zBegin ), nb = (double)numBricks;
         if ( MODE == 1 ) printStats( "dist", h, nv, nb );
-        printStats( "fwn ", h + 5, nv, nb );
+        printStats( "fwn ", h + STAT_WORDS, nv, nb );
     }
     else
     {
         if ( MODE == 1 )
         {
-            if ( aa ) kGridDist<true, false><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, dActive, nullptr );
-            else kGridDist<false, false><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, dActive, nullptr );
+            if ( aa ) kGridDist<true, false><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, nullptr );
+            else kGridDist<false, false><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, nullptr );
         }
-        {
-            if ( aa ) kGridFwn<MODE, true, false><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, nullptr );
-            else kGridFwn<MODE, false, false><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, nullptr );
-        }
+        if ( aa ) kGridFwn5<MODE, true><<<blocksFor( oF ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, oF );
+        else kGridFwn5<MODE, false><<<blocksFor( oF ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, oF );
     }
     if ( launches ) *launches += ( MODE == 1 ? 2 : 1 );
-    if ( dActive ) B2_CUDA( cudaFreeAsync( dActive, st ) );
+    static const bool debugOrder = getenv( "B2FWN_DEBUG" ) != nullptr;
+    if ( debugOrder && scratch )
+    {
+        unsigned long long h[8];
+        B2_CUDA( cudaMemcpyAsync( h, scratch, sizeof( h ), cudaMemcpyDeviceToHost, st ) );
+        B2_CUDA( cudaStreamSynchronize( st ) );
+        const unsigned* hc = reinterpret_cast<const unsigned*>( h + 4 );
+        fprintf( stderr, "[b2fwn order] bricks %zu cap %u | dist: cost sum %llu over %llu bricks, heavy %u | fwn: cost sum %llu over %llu groups, heavy %u\n",
+                 numBricks, cap, h[0], h[1], hc[0], h[2], h[3], hc[1] );
+    }
+    if ( scratch ) B2_CUDA( cudaFreeAsync( scratch, st ) );
     B2_CUDA( cudaGetLastError() );
     return B2FWN_OK;
 }
