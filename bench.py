@@ -12,8 +12,9 @@ A "step" is one pass of the hot path over the whole voxel grid of the workload.
            (chunked D2H inside the timed region).
   --impl reference : the reference's own CPU/TBB implementation (oracle/_ref when it was built, else the C
            restatement) on a bounded sample of the same workload, all host threads.
-N > 1 (torchrun): the grid is sharded by z-slab, mesh and tree replicated per GPU, slabs gathered into the full volume on
-every GPU by NCCL all-gather (north_star); total work is fixed => "scaling": "strong".
+N > 1 (torchrun): the grid is sharded by z (interleaved chunks of a few layers per rank, meshlib_b200/slabs.py), mesh and
+tree replicated per GPU, the slabs gathered into the full volume on every GPU by NCCL all-gather (north_star), stage by
+stage behind the kernels of the next stage; total work is fixed => "scaling": "strong".
 """
 import argparse
 import json
@@ -255,8 +256,18 @@ def run_ours(args, wl):
 
     fwn = mb.FastWindingNumber(wl["points"], wl["tris"], device=local)
     st0 = fwn.stats()
-    # full volume on every GPU (north_star: slabs gathered by NCCL all-gather); rank r writes its slab in place
-    volume = torch.empty(total, dtype=torch.float32, device=dev)
+    # full volume on every GPU (north_star: the slabs of all ranks gathered on every GPU); rank r writes its share in place
+    p2p = world > 1 and args.gather == "p2p"
+    peer_ptrs, my_ptr = [], None
+    if p2p:
+        # peer-visible volumes: every rank maps the volumes of the others; the kernels store each result into all of them
+        my_ptr, token = fwn.shared_alloc(4 * total)
+        tokens = [None] * world
+        dist.all_gather_object(tokens, token)
+        peer_ptrs = [fwn.shared_open(tokens[r]) for r in range(world) if r != rank]
+        volume = torch.as_tensor(mb.DeviceBuffer(my_ptr, total), device=dev)
+    else:
+        volume = torch.empty(total, dtype=torch.float32, device=dev)
     slab = volume[z0 * layer:z1 * layer]
 
     def barrier():
@@ -265,20 +276,42 @@ def run_ours(args, wl):
             dist.barrier()
             torch.cuda.synchronize()
 
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+
+    # N > 1: z-interleaved chunks (equal cost per rank).  --gather p2p (default): one call per step, the gather fused into the
+    # kernel (stores into every rank's volume over NVLink), then a barrier.  --gather nccl: the z-range cut into stages, the
+    # all-gather of one stage issued on NCCL's stream while the next stage is computed.  N = 1: one plain call.
+    plan = slabs.ChunkPlan(world, dims[2], chunk=args.z_chunk, stages=1 if p2p else args.stages) if world > 1 else None
+    if p2p and plan.call_args(rank, 0) is None:
+        raise SystemExit("grid too small for this many ranks")
 
     def step():
-        """returns (kernel ms on the launching stream, gather ms)"""
-        fwn.calc_from_grid_with_distances_device(dims, xf, slab.data_ptr(), opts, z_begin=z0, z_end=z1)
-        k_ms = fwn.stats().last_kernel_ms
-        g_ms = 0.0
-        if world > 1:
-            ev[0].record()
-            slabs.gather_slabs(volume, rank, world, dims, dist)
-            ev[1].record()
-            ev[1].synchronize()
-            g_ms = ev[0].elapsed_time(ev[1])
-        return k_ms, g_ms
+        """returns (kernel ms on the launching stream, ms between the last kernel's end and the last gather's end)"""
+        if world == 1:
+            fwn.calc_from_grid_with_distances_device(dims, xf, slab.data_ptr(), opts, z_begin=z0, z_end=z1)
+            return fwn.stats().last_kernel_ms, 0.0
+        if p2p:
+            zb, ze, zc, zs = plan.call_args(rank, 0)
+            off = 4 * zb * layer
+            fwn.calc_from_grid_with_distances_device_chunks_p2p(dims, xf, my_ptr + off, [q + off for q in peer_ptrs], opts, z_begin=zb,
+                                                                z_end=ze, z_chunk=zc, z_stride=zs)  # returns when the kernels are done
+            t = time.perf_counter()
+            dist.barrier()  # every rank's stores have landed: the volume is complete everywhere
+            torch.cuda.synchronize()
+            return fwn.stats().last_kernel_ms, 1e3 * (time.perf_counter() - t)
+        k_ms, works = 0.0, []
+        for s in range(plan.stages):
+            a = plan.call_args(rank, s)
+            if a:
+                zb, ze, zc, zs = a
+                fwn.calc_from_grid_with_distances_device_chunks(dims, xf, volume.data_ptr() + 4 * zb * layer, opts, z_begin=zb,
+                                                                z_end=ze, z_chunk=zc, z_stride=zs)  # returns when the kernels are done
+                k_ms += fwn.stats().last_kernel_ms
+            works += plan.gather_stage(volume, rank, s, dims, dist, async_op=True)
+        t = time.perf_counter()
+        for w in works:
+            w.wait()
+        torch.cuda.synchronize()
+        return k_ms, 1e3 * (time.perf_counter() - t)
 
     for _ in range(args.warmup):
         step()
@@ -301,12 +334,25 @@ def run_ours(args, wl):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dev_ms, k_ms, g_ms, wall_ms = (float(x) / args.steps for x in t.tolist())
+    if world > 1:
+        dev_ms = wall_ms  # gathers overlap the kernels: the step is the bracketed region (device synchronised on both sides)
     checksum = float(torch.nan_to_num(volume[:: max(1, total // (1 << 22))]).double().abs().sum())
+    if world > 1:  # every rank must hold the same, complete volume
+        c = torch.tensor([checksum, -checksum], dtype=torch.float64, device=dev)
+        dist.all_reduce(c, op=dist.ReduceOp.MAX)
+        if float(c[0]) != -float(c[1]):
+            raise SystemExit(f"volumes differ between ranks: checksum range [{-float(c[1])}, {float(c[0])}]")
 
     # ---- e2e: host mesh -> create (H2D + device tree build) -> host volume, all inside the timed region --------------
     e2e = None
     if not args.no_e2e:
         del volume, slab
+        if p2p:
+            barrier()
+            for q in peer_ptrs:
+                fwn.shared_close(q)
+            barrier()
+            fwn.shared_free(my_ptr)
         torch.cuda.empty_cache()
         nslab = (z1 - z0) * layer
         host = torch.empty(nslab, dtype=torch.float32, pin_memory=True)
@@ -349,11 +395,16 @@ def run_ours(args, wl):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dev_ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": wl["desc"], "sharding": f"z-slab x{world}, mesh+tree replicated, NCCL all-gather of slabs" if world > 1 else "single GPU",
+        "config": {"workload": wl["desc"], "sharding": "single GPU" if world == 1 else
+                   (f"z-interleaved chunks of {args.z_chunk} layers x{world} ranks, mesh+tree replicated, gather fused into the kernel "
+                    "(peer stores over NVLink into every rank's volume) + barrier") if p2p else
+                   (f"z-interleaved chunks of {args.z_chunk} layers x{world} ranks in {plan.stages} stages, mesh+tree replicated, NCCL "
+                    "all-gather of each stage issued behind the next stage's kernels"),
                    "l2": "inputs larger than L2 (tree+triangles %.0f MB, output %.0f MB per step)" % (
                        (st0.num_nodes * 64 + st0.num_leaves * 64) / 1e6, 4 * total / 1e6),
-                   "timing": "CUDA events on the launching stream (kernel) + torch events (all-gather), max over ranks"},
-        "kernel_ms_per_step": k_ms, "gather_ms_per_step": g_ms, "wall_ms_per_step": wall_ms,
+                   "timing": ("CUDA events on the launching stream" if world == 1 else
+                              "host clock around the K steps, device synchronised and ranks barriered on both sides") + ", max over ranks"},
+        "kernel_ms_per_step": k_ms, "gather_exposed_ms_per_step": g_ms, "wall_ms_per_step": wall_ms,
         "tree_build_ms": st0.tree_build_ms, "num_faces": int(st0.num_leaves), "num_nodes": int(st0.num_nodes),
         "clocks": clocks, "gpu_launches": int(launches), "checksum": checksum,
     }
@@ -395,6 +446,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument("--grid", type=int, default=None, help="override the grid size (diagnostics only; not the headline)")
+    ap.add_argument("--z-chunk", type=int, default=8, help="N > 1: layers per interleaved chunk (multiple of 4)")
+    ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"], help="N > 1: fused peer stores, or NCCL all-gather")
+    ap.add_argument("--stages", type=int, default=4, help="N > 1: compute/gather pipeline stages over z")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=15.0)

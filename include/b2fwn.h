@@ -108,6 +108,33 @@ int b2fwn_calc_from_grid_with_distances_device( b2fwn_handle h, const int32_t di
                                                 const b2fwn_dist_options* opt, int32_t z_begin, int32_t z_end,
                                                 float* d_out );
 
+/* z-interleaved form for multi-GPU runs (no counterpart in the reference, which has one GPU): computes the layers
+ * z_begin + c * z_stride + k (c = 0, 1, ...; 0 <= k < z_chunk) below z_end, and writes voxel (x, y, z) to
+ * d_volume_at_z_begin[x + dims[0] * (y + dims[1] * (z - z_begin))] -- i.e. in place into a volume that holds all layers
+ * from z_begin on.  With z_stride = n_ranks * z_chunk and z_begin = z0 + rank * z_chunk every rank gets an equal share of
+ * every part of the grid (contiguous z-slabs differ in cost).  z_chunk must be a positive multiple of 4. */
+int b2fwn_calc_from_grid_with_distances_device_chunks( b2fwn_handle h, const int32_t dims[3], const float xf[12],
+                                                       const b2fwn_dist_options* opt, int32_t z_begin, int32_t z_end,
+                                                       int32_t z_chunk, int32_t z_stride, float* d_volume_at_z_begin );
+
+/* Multi-GPU gather fused into the kernels (one process per GPU of one node; replaces the all-gather that would follow
+ * b2fwn_calc_from_grid_with_distances_device[_chunks]): every result is stored, besides d_volume_at_z_begin, at the same
+ * offset of each of the n_peers peer volumes (device memory of other GPUs, mapped with b2fwn_shared_open).  When the call
+ * has returned on every rank (barrier), every volume is complete.  n_peers <= 15. */
+int b2fwn_calc_from_grid_with_distances_device_chunks_p2p( b2fwn_handle h, const int32_t dims[3], const float xf[12],
+                                                           const b2fwn_dist_options* opt, int32_t z_begin, int32_t z_end,
+                                                           int32_t z_chunk, int32_t z_stride, float* d_volume_at_z_begin,
+                                                           int32_t n_peers, float* const* d_peer_volumes_at_z_begin );
+
+/* Peer-visible device memory for such volumes: b2fwn_shared_alloc allocates `bytes` on the handle's device and returns a
+ * 64-byte token another process of the node passes to b2fwn_shared_open to map the same memory (CUDA IPC; peer access over
+ * NVLink is enabled by the mapping).  b2fwn_shared_close unmaps, b2fwn_shared_free releases the allocation. */
+#define B2FWN_IPC_TOKEN_BYTES 64
+int b2fwn_shared_alloc( b2fwn_handle h, size_t bytes, void** d_ptr, unsigned char token_out[B2FWN_IPC_TOKEN_BYTES] );
+int b2fwn_shared_open( b2fwn_handle h, const unsigned char token[B2FWN_IPC_TOKEN_BYTES], void** d_peer_ptr );
+int b2fwn_shared_close( b2fwn_handle h, void* d_peer_ptr );
+int b2fwn_shared_free( b2fwn_handle h, void* d_ptr );
+
 /* host-output form of one z-range [z_begin, z_end) of the grid (out[0] = voxel (0,0,z_begin)): what one rank of a
  * z-slab sharded run calls; b2fwn_calc_from_grid_with_distances is this with the full range */
 int b2fwn_calc_from_grid_with_distances_layers( b2fwn_handle h, const int32_t dims[3], const float xf[12],

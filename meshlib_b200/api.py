@@ -65,6 +65,14 @@ class OffsetParams(C.Structure):
                 ("winding_number_threshold", C.c_float), ("winding_number_beta", C.c_float), ("reserved", C.c_int32 * 3)]
 
 
+class DeviceBuffer:
+    """a raw device allocation exposed through __cuda_array_interface__ (zero-copy view: torch.as_tensor(buf, device=...))"""
+
+    def __init__(self, ptr, n_floats):
+        self.ptr, self.n = ptr, n_floats
+        self.__cuda_array_interface__ = {"shape": (n_floats,), "typestr": "<f4", "data": (ptr, False), "version": 2, "strides": None}
+
+
 class OffsetResult(C.Structure):
     _fields_ = [("origin", C.c_float * 3), ("dims", C.c_int32 * 3), ("n_verts", C.c_uint64), ("n_tris", C.c_uint64),
                 ("sdf_ms", C.c_double), ("mc_ms", C.c_double)]
@@ -74,7 +82,9 @@ EXPORTS = [
     "b2fwn_last_error", "b2fwn_device_count", "b2fwn_create", "b2fwn_destroy", "b2fwn_calc_from_vector",
     "b2fwn_calc_from_vector_device", "b2fwn_calc_self_intersections", "b2fwn_calc_self_intersections_device",
     "b2fwn_calc_from_grid", "b2fwn_calc_from_grid_device", "b2fwn_calc_from_grid_with_distances",
-    "b2fwn_calc_from_grid_with_distances_device", "b2fwn_calc_from_grid_by_parts",
+    "b2fwn_calc_from_grid_with_distances_device", "b2fwn_calc_from_grid_with_distances_device_chunks",
+    "b2fwn_calc_from_grid_with_distances_device_chunks_p2p", "b2fwn_shared_alloc", "b2fwn_shared_open", "b2fwn_shared_close",
+    "b2fwn_shared_free", "b2fwn_calc_from_grid_by_parts",
     "b2fwn_calc_from_grid_with_distances_by_parts", "b2fwn_get_tree", "b2fwn_get_stats", "b2fwn_marching_cubes",
     "b2fwn_marching_cubes_fetch", "b2fwn_calc_from_grid_with_distances_layers", "b2fwn_measure_fp32_peak",
     "b2fwn_get_bounding_box", "b2fwn_mesh_to_distance_volume", "b2fwn_mc_offset_mesh",
@@ -105,6 +115,15 @@ def load_library():
     L.b2fwn_calc_from_grid_with_distances.argtypes = [vp, i32p, f32p, C.POINTER(DistOptions), vp, PROGRESS_CB, vp]
     L.b2fwn_calc_from_grid_with_distances_device.argtypes = [vp, i32p, f32p, C.POINTER(DistOptions), C.c_int32,
                                                              C.c_int32, vp]
+    L.b2fwn_calc_from_grid_with_distances_device_chunks.argtypes = [vp, i32p, f32p, C.POINTER(DistOptions), C.c_int32,
+                                                                    C.c_int32, C.c_int32, C.c_int32, vp]
+    L.b2fwn_calc_from_grid_with_distances_device_chunks_p2p.argtypes = [vp, i32p, f32p, C.POINTER(DistOptions), C.c_int32,
+                                                                        C.c_int32, C.c_int32, C.c_int32, vp, C.c_int32,
+                                                                        C.POINTER(vp)]
+    L.b2fwn_shared_alloc.argtypes = [vp, C.c_size_t, C.POINTER(vp), C.c_char_p]
+    L.b2fwn_shared_open.argtypes = [vp, C.c_char_p, C.POINTER(vp)]
+    L.b2fwn_shared_close.argtypes = [vp, vp]
+    L.b2fwn_shared_free.argtypes = [vp, vp]
     L.b2fwn_calc_from_grid_with_distances_layers.argtypes = [vp, i32p, f32p, C.POINTER(DistOptions), C.c_int32, C.c_int32,
                                                              vp, PROGRESS_CB, vp]
     L.b2fwn_measure_fp32_peak.argtypes = [C.c_int32, C.POINTER(C.c_double)]
@@ -272,6 +291,45 @@ class FastWindingNumber:
         z_end = dims[2] if z_end is None else z_end
         _check(_lib.b2fwn_calc_from_grid_with_distances_device(self._h, _dims(dims), _xf(grid_to_mesh_xf),
                                                                C.byref(options), z_begin, z_end, d_out_ptr))
+
+    def calc_from_grid_with_distances_device_chunks(self, dims, grid_to_mesh_xf, d_volume_at_z_begin, options=None, z_begin=0,
+                                                    z_end=None, z_chunk=8, z_stride=8):
+        """layers z_begin + c * z_stride + k (k < z_chunk) below z_end, written in place into the volume that starts at
+        layer z_begin (one rank's share of a z-interleaved multi-GPU partition)"""
+        options = options or DistOptions()
+        z_end = dims[2] if z_end is None else z_end
+        _check(_lib.b2fwn_calc_from_grid_with_distances_device_chunks(self._h, _dims(dims), _xf(grid_to_mesh_xf), C.byref(options),
+                                                                      z_begin, z_end, z_chunk, z_stride, d_volume_at_z_begin))
+
+    def calc_from_grid_with_distances_device_chunks_p2p(self, dims, grid_to_mesh_xf, d_volume_at_z_begin, peer_ptrs_at_z_begin,
+                                                        options=None, z_begin=0, z_end=None, z_chunk=8, z_stride=8):
+        """as ..._device_chunks, and every result is also stored into the peer volumes (other GPUs' memory opened with
+        shared_open): the all-gather of a multi-GPU run fused into the kernel"""
+        options = options or DistOptions()
+        z_end = dims[2] if z_end is None else z_end
+        n = len(peer_ptrs_at_z_begin)
+        arr = (C.c_void_p * max(n, 1))(*peer_ptrs_at_z_begin)
+        _check(_lib.b2fwn_calc_from_grid_with_distances_device_chunks_p2p(self._h, _dims(dims), _xf(grid_to_mesh_xf), C.byref(options),
+                                                                          z_begin, z_end, z_chunk, z_stride, d_volume_at_z_begin, n, arr))
+
+    # ---- peer-visible device memory (multi-GPU volumes) ----
+    def shared_alloc(self, nbytes):
+        """-> (device pointer, 64-byte token another process passes to shared_open)"""
+        ptr = C.c_void_p()
+        token = C.create_string_buffer(64)
+        _check(_lib.b2fwn_shared_alloc(self._h, nbytes, C.byref(ptr), token))
+        return ptr.value, token.raw
+
+    def shared_open(self, token):
+        ptr = C.c_void_p()
+        _check(_lib.b2fwn_shared_open(self._h, token, C.byref(ptr)))
+        return ptr.value
+
+    def shared_close(self, ptr):
+        _check(_lib.b2fwn_shared_close(self._h, ptr))
+
+    def shared_free(self, ptr):
+        _check(_lib.b2fwn_shared_free(self._h, ptr))
 
     # ---- parity / diagnostics ----
     def get_tree(self):

@@ -404,6 +404,86 @@ int b2fwn_calc_from_grid_with_distances_device( b2fwn_handle h, const int32_t di
     return B2FWN_OK;
 }
 
+int b2fwn_calc_from_grid_with_distances_device_chunks( b2fwn_handle h, const int32_t dims[3], const float xf[12],
+                                                       const b2fwn_dist_options* opt, int32_t zBegin, int32_t zEnd,
+                                                       int32_t zChunk, int32_t zStride, float* dVolumeAtZBegin )
+{
+    if ( !h || !dims || !xf || !opt ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    const ZChunks zc{ zChunk, zStride };
+    KernelTimer tm( h );
+    if ( int e = launchSdfGrid( h->tree, dims, toXf( xf ), *opt, zBegin, zEnd, dVolumeAtZBegin, h->stream, &h->stats.kernel_launches, &zc ) )
+        return e;
+    tm.stop();
+    B2_CUDA( cudaStreamSynchronize( h->stream ) );
+    return B2FWN_OK;
+}
+
+int b2fwn_calc_from_grid_with_distances_device_chunks_p2p( b2fwn_handle h, const int32_t dims[3], const float xf[12],
+                                                           const b2fwn_dist_options* opt, int32_t zBegin, int32_t zEnd,
+                                                           int32_t zChunk, int32_t zStride, float* dVolumeAtZBegin,
+                                                           int32_t nPeers, float* const* dPeerVolumesAtZBegin )
+{
+    if ( !h || !dims || !xf || !opt || ( nPeers > 0 && !dPeerVolumesAtZBegin ) ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    if ( nPeers < 0 || nPeers > MAX_PEERS ) { setError( "too many peer volumes" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    const ZChunks zc{ zChunk, zStride };
+    PeerOut po{};
+    po.n = nPeers;
+    for ( int k = 0; k < nPeers; ++k )
+    {
+        if ( !dPeerVolumesAtZBegin[k] ) { setError( "null peer volume" ); return B2FWN_ERR_INVALID; }
+        po.p[k] = dPeerVolumesAtZBegin[k];
+    }
+    KernelTimer tm( h );
+    if ( int e = launchSdfGrid( h->tree, dims, toXf( xf ), *opt, zBegin, zEnd, dVolumeAtZBegin, h->stream, &h->stats.kernel_launches, &zc, &po ) )
+        return e;
+    tm.stop();
+    B2_CUDA( cudaStreamSynchronize( h->stream ) );
+    return B2FWN_OK;
+}
+
+static_assert( sizeof( cudaIpcMemHandle_t ) == B2FWN_IPC_TOKEN_BYTES, "IPC token size" );
+
+int b2fwn_shared_alloc( b2fwn_handle h, size_t bytes, void** dPtr, unsigned char tokenOut[B2FWN_IPC_TOKEN_BYTES] )
+{
+    if ( !h || !dPtr || !tokenOut ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    *dPtr = nullptr;
+    B2_CUDA( cudaMalloc( dPtr, bytes ? bytes : 1 ) );
+    cudaIpcMemHandle_t ipc;
+    const cudaError_t e = cudaIpcGetMemHandle( &ipc, *dPtr );
+    if ( e != cudaSuccess ) { cudaFree( *dPtr ); *dPtr = nullptr; return cudaFail( e, "cudaIpcGetMemHandle" ); }
+    memcpy( tokenOut, &ipc, sizeof( ipc ) );
+    return B2FWN_OK;
+}
+
+int b2fwn_shared_open( b2fwn_handle h, const unsigned char token[B2FWN_IPC_TOKEN_BYTES], void** dPeerPtr )
+{
+    if ( !h || !token || !dPeerPtr ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    cudaIpcMemHandle_t ipc;
+    memcpy( &ipc, token, sizeof( ipc ) );
+    B2_CUDA( cudaIpcOpenMemHandle( dPeerPtr, ipc, cudaIpcMemLazyEnablePeerAccess ) );
+    return B2FWN_OK;
+}
+
+int b2fwn_shared_close( b2fwn_handle h, void* dPeerPtr )
+{
+    if ( !h ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    if ( dPeerPtr ) B2_CUDA( cudaIpcCloseMemHandle( dPeerPtr ) );
+    return B2FWN_OK;
+}
+
+int b2fwn_shared_free( b2fwn_handle h, void* dPtr )
+{
+    if ( !h ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    if ( dPtr ) B2_CUDA( cudaFree( dPtr ) );
+    return B2FWN_OK;
+}
+
 int b2fwn_calc_from_grid_by_parts( b2fwn_handle h, const int32_t dims[3], const float xf[12], float beta, int32_t overlap,
                                    int32_t maxLayers, b2fwn_part_cb part, void* partUser, b2fwn_progress cb, void* user )
 {

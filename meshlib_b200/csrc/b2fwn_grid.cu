@@ -46,7 +46,9 @@ constexpr int GRID_TB = 128;           // 4 warps = 4 bricks (adjacent in x) per
 struct GridParams
 {
     int dx, dy;          // grid dims in x, y
-    int zBegin, zEnd;    // layers computed by this launch
+    int zBegin, nz;      // first layer and number of layers computed by this launch ...
+    int zChunk, zSkip;   // ... in chunks of zChunk consecutive layers with zSkip layers left out after each chunk (z-interleaved
+                         // multi-GPU partition; a contiguous slab has zChunk >= nz, zSkip = 0).  zChunk is a multiple of BZ.
     int bricksX, bricksY, bricksZ;
     float A[9];
     float b[3];
@@ -57,6 +59,8 @@ struct GridParams
     int vecStore;        // rows are 16-B aligned: float4 accesses
 };
 
+// grid layer of local layer lz
+__device__ __forceinline__ int globalZ( const GridParams& P, const int lz ) { return P.zBegin + lz + ( lz / P.zChunk ) * P.zSkip; }
 __device__ __forceinline__ int skipOf( int link, int i ) { return link < 0 ? i + 1 : link; }
 __device__ __forceinline__ int min4( const int ( &a )[VX] ) { return min( min( a[0], a[1] ), min( a[2], a[3] ) ); }
 
@@ -91,8 +95,8 @@ __device__ __forceinline__ void brickFromIndex( const GridParams& P, const size_
     B.bz = (int)( brick / ( (size_t)P.bricksX * P.bricksY ) );
     B.x0 = B.bx * BX + (int)( lane & 1 ) * VX;
     B.y = B.by * BY + (int)( ( lane >> 1 ) & 3 );
-    B.z = P.zBegin + B.bz * BZ + (int)( lane >> 3 );
-    B.rowValid = B.y < P.dy && B.z < P.zEnd;
+    B.z = globalZ( P, B.bz * BZ ) + (int)( lane >> 3 ); // a brick never straddles two chunks
+    B.rowValid = B.y < P.dy && B.bz * BZ + (int)( lane >> 3 ) < P.nz;
     B.id = (size_t)B.x0 + (size_t)P.dx * ( (size_t)B.y + (size_t)P.dy * (size_t)( B.z - P.zBegin ) );
 }
 
@@ -167,7 +171,7 @@ __global__ void __launch_bounds__( 256 ) kBrickCull( const TravNode* __restrict_
         for ( int k = 0; k < 8; ++k )
         {
             const float3 q = applyXf( P.A, P.b, (float)( bx * BX + ( ( k & 1 ) ? BX - 1 : 0 ) ), (float)( by * BY + ( ( k & 2 ) ? BY - 1 : 0 ) ),
-                                      (float)( P.zBegin + bz * BZ + ( ( k & 4 ) ? BZ - 1 : 0 ) ) );
+                                      (float)( globalZ( P, bz * BZ ) + ( ( k & 4 ) ? BZ - 1 : 0 ) ) );
             lo[0] = fminf( lo[0], q.x ); hi[0] = fmaxf( hi[0], q.x );
             lo[1] = fminf( lo[1], q.y ); hi[1] = fmaxf( hi[1], q.y );
             lo[2] = fminf( lo[2], q.z ); hi[2] = fmaxf( hi[2], q.z );
@@ -253,7 +257,7 @@ __global__ void __launch_bounds__( 256 ) kGroupCostFwn( const TravNode* __restri
     {
         const int gx = (int)( group % gX ), gy = (int)( ( group / gX ) % gY ), gz = (int)( group / ( (size_t)gX * gY ) );
         const float hx = 0.5f * ( GRP * BX - 1 ), hy = 0.5f * ( GRP * BY - 1 ), hz = 0.5f * ( GRP * BZ - 1 );
-        const float3 pc = applyXf( P.A, P.b, (float)( gx * GRP * BX ) + hx, (float)( gy * GRP * BY ) + hy, (float)( P.zBegin + gz * GRP * BZ ) + hz );
+        const float3 pc = applyXf( P.A, P.b, (float)( gx * GRP * BX ) + hx, (float)( gy * GRP * BY ) + hy, (float)globalZ( P, gz * GRP * BZ ) + hz );
         c = fwnCostWalk( nodes, P.numNodes, P.betaSq, pc, boxRadius( P, hx, hy, hz ) );
         cost[group] = (uint16_t)c;
     }
@@ -299,7 +303,7 @@ __global__ void __launch_bounds__( 256 ) kGroupHeavy( const TravNode* __restrict
     if ( cost[group] > thr )
     {
         const float hx = 0.5f * ( BX - 1 ), hy = 0.5f * ( BY - 1 ), hz = 0.5f * ( BZ - 1 );
-        const float3 pc = applyXf( P.A, P.b, (float)( bx * BX ) + hx, (float)( by * BY ) + hy, (float)( P.zBegin + bz * BZ ) + hz );
+        const float3 pc = applyXf( P.A, P.b, (float)( bx * BX ) + hx, (float)( by * BY ) + hy, (float)globalZ( P, bz * BZ ) + hz );
         if ( fwnCostWalk( nodes, P.numNodes, P.betaSq, pc, boxRadius( P, hx, hy, hz ) ) > thr )
         {
             const unsigned k = atomicAdd( count, 1u );
@@ -342,7 +346,7 @@ __global__ void __launch_bounds__( GRID_TB ) kGridDist( const TravNode* __restri
         sbest[v] = sqrtf( P.maxDistSq );
         lim[v] = valid ? P.maxDistSq : -1.f;
     }
-    const float3 pc = applyXf( P.A, P.b, (float)( B.bx * BX ) + 3.5f, (float)( B.by * BY ) + 1.5f, (float)( P.zBegin + B.bz * BZ ) + 1.5f );
+    const float3 pc = applyXf( P.A, P.b, (float)( B.bx * BX ) + 3.5f, (float)( B.by * BY ) + 1.5f, (float)globalZ( P, B.bz * BZ ) + 1.5f );
 
     if ( walk )
     {
@@ -498,7 +502,7 @@ __global__ void __launch_bounds__( GRID_TB ) kGridFwn( const TravNode* __restric
     // brick centre and radius (distance of the farthest voxel centre, padded): one warp-uniform test per node tells when
     // EVERY voxel of the brick is inside beta * r of the node, i.e. all of them must descend -- no per-voxel work then.
     // Conservative by 1e-5 relative against the exactly rounded per-voxel decision, so decisions are unchanged.
-    const float3 pc = applyXf( P.A, P.b, (float)( B.bx * BX ) + 3.5f, (float)( B.by * BY ) + 1.5f, (float)( P.zBegin + B.bz * BZ ) + 1.5f );
+    const float3 pc = applyXf( P.A, P.b, (float)( B.bx * BX ) + 3.5f, (float)( B.by * BY ) + 1.5f, (float)globalZ( P, B.bz * BZ ) + 1.5f );
     float rad = 0.f;
 #pragma unroll
     for ( int v = 0; v < VX; ++v )
@@ -711,9 +715,14 @@ __device__ __forceinline__ float fwnResult( const int MODE, const float sum, con
 // per lane was tried (as a branch of this kernel: ptxas then guards every warp reduction of the loop against divergence,
 // +10 % on the regular walk; as a kernel of its own on a side stream: the slices pay every node for 32 voxels instead of
 // 128, 4,195 listed bricks of c3_band cost 9 ms beside a 20 ms regular kernel) and dropped.
-template <int MODE, bool AA>
+// PEERS: the multi-GPU gather fused into the kernel.  Every rank computes its own bricks and stores each result, besides
+// its own volume, straight into the volumes of the other ranks (peer memory over NVLink / NVSwitch, posted writes): when
+// the kernels of all ranks have finished, every GPU holds the whole volume -- no collective kernel competes for SMs (the
+// NCCL all-gather could not overlap this kernel: it fills every SM's register file) and nothing is left to do after the
+// last brick.  Traffic: (P-1) x 4 B per voxel leave each GPU during its step, far below the NVLink rate.
+template <int MODE, bool AA, bool PEERS>
 __global__ void __launch_bounds__( GRID_TB ) kGridFwn5( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
-                                                        const GridParams P, float* __restrict__ out, const BrickOrder O )
+                                                        const GridParams P, float* __restrict__ out, const BrickOrder O, const PeerOut peers )
 {
     Brick B;
     if ( !brickOfWarp( P, O, B ) ) return;
@@ -750,7 +759,7 @@ __global__ void __launch_bounds__( GRID_TB ) kGridFwn5( const TravNode* __restri
     // brick centre and radius (distance of the farthest voxel centre, padded): one warp-uniform test per node tells when
     // EVERY voxel of the brick is inside beta * r of the node, i.e. all of them must descend -- no per-voxel work then.
     // Conservative by 1e-5 relative against the exactly rounded per-voxel decision, so decisions are unchanged.
-    const float3 pc = applyXf( P.A, P.b, (float)( B.bx * BX ) + 3.5f, (float)( B.by * BY ) + 1.5f, (float)( P.zBegin + B.bz * BZ ) + 1.5f );
+    const float3 pc = applyXf( P.A, P.b, (float)( B.bx * BX ) + 3.5f, (float)( B.by * BY ) + 1.5f, (float)globalZ( P, B.bz * BZ ) + 1.5f );
     float rad = 0.f;
 #pragma unroll
     for ( int v = 0; v < VX; ++v )
@@ -773,6 +782,21 @@ __global__ void __launch_bounds__( GRID_TB ) kGridFwn5( const TravNode* __restri
 #pragma unroll
         for ( int v = 0; v < VX; ++v )
             if ( B.x0 + v < P.dx ) out[B.id + v] = res[v];
+    }
+    if ( PEERS )
+    {
+        for ( int k = 0; k < peers.n; ++k )
+        {
+            float* po = peers.p[k];
+            if ( vec )
+                *reinterpret_cast<float4*>( po + B.id ) = make_float4( res[0], res[1], res[2], res[3] );
+            else
+            {
+#pragma unroll
+                for ( int v = 0; v < VX; ++v )
+                    if ( B.x0 + v < P.dx ) po[B.id + v] = res[v];
+            }
+        }
     }
 }
 
@@ -799,15 +823,29 @@ void printStats( const char* what, const unsigned long long* h, double voxels, d
 // MODE 0: winding numbers only; MODE 1: distance walk, then winding-number walk over the same slab
 template <int MODE>
 int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, float beta, const b2fwn_dist_options* opt,
-                int zBegin, int zEnd, float* dOut, cudaStream_t st, uint64_t* launches )
+                int zBegin, int zEnd, const ZChunks* zc, const PeerOut* peers, float* dOut, cudaStream_t st, uint64_t* launches )
 {
     if ( int e = checkDims( dims, zBegin, zEnd ) ) return e;
+    if ( peers && peers->n > 0 && getenv( "B2FWN_STATS" ) ) { setError( "peer output is not available in stats mode" ); return B2FWN_ERR_INVALID; }
     if ( dims[0] == 0 || dims[1] == 0 || zEnd == zBegin ) return B2FWN_OK;
     GridParams P{};
-    P.dx = dims[0]; P.dy = dims[1]; P.zBegin = zBegin; P.zEnd = zEnd;
+    P.dx = dims[0]; P.dy = dims[1]; P.zBegin = zBegin;
+    if ( zc )
+    {
+        // layers zBegin + c * stride + k, k < chunk, below zEnd; dOut points at layer zBegin of a volume that has them all
+        if ( zc->chunk <= 0 || zc->chunk % BZ != 0 || zc->stride < zc->chunk )
+        {
+            setError( "invalid z-chunk layout (chunk must be a positive multiple of 4, stride >= chunk)" );
+            return B2FWN_ERR_INVALID;
+        }
+        const int span = zEnd - zBegin;
+        P.nz = ( span / zc->stride ) * zc->chunk + std::min( span % zc->stride, zc->chunk );
+        P.zChunk = zc->chunk; P.zSkip = zc->stride - zc->chunk;
+    }
+    else { P.nz = zEnd - zBegin; P.zChunk = INT_MAX / 2; P.zSkip = 0; }
     P.bricksX = ( dims[0] + BX - 1 ) / BX;
     P.bricksY = ( dims[1] + BY - 1 ) / BY;
-    P.bricksZ = ( zEnd - zBegin + BZ - 1 ) / BZ;
+    P.bricksZ = ( P.nz + BZ - 1 ) / BZ;
     for ( int k = 0; k < 9; ++k ) P.A[k] = xf.A[k];
     for ( int k = 0; k < 3; ++k ) P.b[k] = xf.b[k];
     P.betaSq = beta * beta; // sqr(beta), MRDipole.cpp:103
@@ -885,7 +923,7 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
         B2_CUDA( cudaMemcpyAsync( h, dStats, sizeof( h ), cudaMemcpyDeviceToHost, st ) );
         B2_CUDA( cudaStreamSynchronize( st ) );
         cudaFree( dStats );
-        const double nv = (double)dims[0] * dims[1] * ( zEnd - zBegin ), nb = (double)numBricks;
+        const double nv = (double)dims[0] * dims[1] * P.nz, nb = (double)numBricks;
         if ( MODE == 1 ) printStats( "dist", h, nv, nb );
         printStats( "fwn ", h + STAT_WORDS, nv, nb );
     }
@@ -896,8 +934,17 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
             if ( aa ) kGridDist<true, false><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, nullptr );
             else kGridDist<false, false><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, nullptr );
         }
-        if ( aa ) kGridFwn5<MODE, true><<<blocksFor( oF ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, oF );
-        else kGridFwn5<MODE, false><<<blocksFor( oF ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, oF );
+        PeerOut po{};
+        if ( peers && peers->n > 0 )
+        {
+            po = *peers;
+            for ( int k = 0; k < po.n; ++k )
+                if ( reinterpret_cast<uintptr_t>( po.p[k] ) % 16 != 0 ) P.vecStore = 0;
+            if ( aa ) kGridFwn5<MODE, true, true><<<blocksFor( oF ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, oF, po );
+            else kGridFwn5<MODE, false, true><<<blocksFor( oF ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, oF, po );
+        }
+        else if ( aa ) kGridFwn5<MODE, true, false><<<blocksFor( oF ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, oF, po );
+        else kGridFwn5<MODE, false, false><<<blocksFor( oF ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, oF, po );
     }
     if ( launches ) *launches += ( MODE == 1 ? 2 : 1 );
     static const bool debugOrder = getenv( "B2FWN_DEBUG" ) != nullptr;
@@ -918,15 +965,15 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
 } // anonymous namespace
 
 int launchFwnGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, float beta, int zBegin, int zEnd,
-                   float* dOut, cudaStream_t st, uint64_t* launches )
+                   float* dOut, cudaStream_t st, uint64_t* launches, const ZChunks* zc )
 {
-    return launchGrid<0>( t, dims, xf, beta, nullptr, zBegin, zEnd, dOut, st, launches );
+    return launchGrid<0>( t, dims, xf, beta, nullptr, zBegin, zEnd, zc, nullptr, dOut, st, launches );
 }
 
 int launchSdfGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, const b2fwn_dist_options& opt,
-                   int zBegin, int zEnd, float* dOut, cudaStream_t st, uint64_t* launches )
+                   int zBegin, int zEnd, float* dOut, cudaStream_t st, uint64_t* launches, const ZChunks* zc, const PeerOut* peers )
 {
-    return launchGrid<1>( t, dims, xf, opt.winding_number_beta, &opt, zBegin, zEnd, dOut, st, launches );
+    return launchGrid<1>( t, dims, xf, opt.winding_number_beta, &opt, zBegin, zEnd, zc, peers, dOut, st, launches );
 }
 
 } // namespace b2

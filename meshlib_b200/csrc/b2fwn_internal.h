@@ -96,10 +96,23 @@ int launchFwnVector( const DeviceTree& t, const float* dPts, size_t n, float bet
                      cudaStream_t stream, uint64_t* launches );
 int launchFwnFaces( const DeviceTree& t, float beta, float* dOutWOrNull, uint64_t* dBits, cudaStream_t stream,
                     uint64_t* launches );
+// z-interleaved layer set of one launch (multi-GPU partition): chunks of `chunk` consecutive layers, `stride` layers apart
+struct ZChunks
+{
+    int chunk, stride;
+};
 int launchFwnGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, float beta, int zBegin, int zEnd,
-                   float* dOut, cudaStream_t stream, uint64_t* launches );
+                   float* dOut, cudaStream_t stream, uint64_t* launches, const ZChunks* zc = nullptr );
+// volumes of the other ranks (peer device memory) that receive every result besides the rank's own volume
+constexpr int MAX_PEERS = 15;
+struct PeerOut
+{
+    int n;
+    float* p[MAX_PEERS];
+};
 int launchSdfGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, const b2fwn_dist_options& opt,
-                   int zBegin, int zEnd, float* dOut, cudaStream_t stream, uint64_t* launches );
+                   int zBegin, int zEnd, float* dOut, cudaStream_t stream, uint64_t* launches, const ZChunks* zc = nullptr,
+                   const PeerOut* peers = nullptr );
 
 // marching cubes (b2fwn_mc.cu) -----------------------------------------------------------------------------------
 struct McResult

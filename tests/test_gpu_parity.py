@@ -210,6 +210,64 @@ def test_z_slab_device_form_matches_full_grid():
     assert out.cpu().numpy().tobytes() == full.tobytes()
 
 
+@pytest.mark.parametrize("world,chunk,stages,dz", [(2, 4, 2, 30), (3, 8, 1, 50), (8, 4, 4, 64)])
+def test_z_interleaved_chunks_match_full_grid(world, chunk, stages, dz):
+    """every rank's interleaved share (slabs.ChunkPlan -> ..._device_chunks), written in place, gives the full-grid volume
+    bit for bit; band limits on, so the cull / heavy-first machinery runs on the chunked layout too"""
+    import torch
+    from meshlib_b200 import slabs
+    pts, tris = _mesh("noisy")
+    fwn = mb.FastWindingNumber(pts, tris)
+    dims = (40, 36, dz)
+    xf = mb.make_basis_xf((-1.3, -1.3, -1.3), (2.6 / 40, 2.6 / 36, 2.6 / dz))
+    for opts in (mb.DistOptions(), mb.DistOptions(0.0, 0.04, False, 0.5, 2.0), mb.DistOptions(0.0004, 0.04, True, 0.5, 2.0)):
+        full = fwn.calc_from_grid_with_distances(dims, xf, opts)
+        out = torch.full((dims[0] * dims[1] * dz,), 123.0, dtype=torch.float32, device="cuda")
+        layer = dims[0] * dims[1]
+        plan = slabs.ChunkPlan(world, dz, chunk, stages)
+        for r in range(world):
+            for s in range(plan.stages):
+                a = plan.call_args(r, s)
+                if a:
+                    zb, ze, zc, zs = a
+                    fwn.calc_from_grid_with_distances_device_chunks(dims, xf, out.data_ptr() + 4 * zb * layer, opts, z_begin=zb,
+                                                                    z_end=ze, z_chunk=zc, z_stride=zs)
+        assert out.cpu().numpy().tobytes() == full.tobytes()
+    with pytest.raises(Exception):
+        fwn.calc_from_grid_with_distances_device_chunks(dims, xf, out.data_ptr(), z_chunk=6, z_stride=12)
+
+
+def test_fused_gather_stores_every_result_into_the_peer_volumes():
+    """the _p2p form (multi-GPU gather fused into the kernel): two further volumes stand in for the other ranks' memory;
+    after all ranks' calls each of them equals the full-grid result"""
+    import torch
+    from meshlib_b200 import slabs
+    pts, tris = _mesh("noisy")
+    fwn = mb.FastWindingNumber(pts, tris)
+    dims, world = (36, 40, 48), 3
+    xf = mb.make_basis_xf((-1.3, -1.3, -1.3), (2.6 / 36, 2.6 / 40, 2.6 / 48))
+    opts = mb.DistOptions(0.0, 0.04, False, 0.5, 2.0)
+    full = fwn.calc_from_grid_with_distances(dims, xf, opts)
+    layer = dims[0] * dims[1]
+    vols = [torch.full((layer * dims[2],), 7.0, dtype=torch.float32, device="cuda") for _ in range(world)]
+    plan = slabs.ChunkPlan(world, dims[2], 4, 1)
+    for r in range(world):
+        zb, ze, zc, zs = plan.call_args(r, 0)
+        off = 4 * zb * layer
+        fwn.calc_from_grid_with_distances_device_chunks_p2p(dims, xf, vols[r].data_ptr() + off,
+                                                            [vols[q].data_ptr() + off for q in range(world) if q != r], opts,
+                                                            z_begin=zb, z_end=ze, z_chunk=zc, z_stride=zs)
+    for v in vols:
+        assert v.cpu().numpy().tobytes() == full.tobytes()
+    ptr, token = fwn.shared_alloc(1 << 20)
+    assert ptr and len(token) == 64
+    t = torch.as_tensor(mb.DeviceBuffer(ptr, 1 << 18), device="cuda")
+    t.fill_(3.0)
+    assert float(t.sum()) == 3.0 * (1 << 18)
+    del t
+    fwn.shared_free(ptr)
+
+
 @pytest.mark.parametrize("n", [1, 31, 33, 100000])
 def test_vector_sizes(n):
     pts, tris = _mesh("sphere")

@@ -60,3 +60,64 @@ def test_world2_gloo_slab_gather_equals_single_rank(tmp_path, dims):
     for r in range(2):
         got = np.load(tmp_path / f"rank{r}.npy")
         assert np.array_equal(got.view(np.uint32), full.view(np.uint32))
+
+
+# ---- z-interleaved chunks in stages (what bench.py runs for N > 1) ------------------------------------------------------------
+
+def test_chunk_plan_covers_the_grid_once():
+    for dz in (1, 7, 8, 64, 100, 2048):
+        for world in (1, 2, 3, 8):
+            for stages in (1, 4):
+                plan = slabs.ChunkPlan(world, dz, 8, stages)
+                seen = []
+                for r in range(world):
+                    mine = []
+                    for s in range(plan.stages):
+                        a = plan.call_args(r, s)
+                        if a:
+                            zb, ze, c, sd = a
+                            while zb < ze:
+                                mine += list(range(zb, min(zb + c, ze)))
+                                zb += sd
+                    assert mine == plan.layers_of(r)
+                    seen += mine
+                assert sorted(seen) == list(range(dz))
+    with pytest.raises(ValueError):
+        slabs.ChunkPlan(2, 64, 6, 1)
+
+
+def _chunk_worker(rank, world, port, dims, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from oracle import portlib
+    pts, tris = meshgen.make_torus(2, 1, 24, 12)
+    m = portlib.PortMesh(pts, tris)
+    xf = np.array([0.4, 0, 0, 0, 0.4, 0, 0, 0, 0.2, -3.0, -3.0, -1.4], np.float32)
+    layer = dims[0] * dims[1]
+    volume = torch.full((layer * dims[2],), float("nan"), dtype=torch.float32)
+    plan = slabs.ChunkPlan(world, dims[2], 4, 2)
+    works = []
+    for s in range(plan.stages):
+        for z in plan.layers_of(rank):
+            z0, z1 = plan.stage_range(s)
+            if z0 <= z < z1:
+                volume[z * layer:(z + 1) * layer] = torch.from_numpy(m.calc_grid_with_distances_layers(dims, xf, z, z + 1))
+        works += plan.gather_stage(volume, rank, s, dims, dist, async_op=True)
+    for w in works:
+        w.wait()
+    np.save(os.path.join(out_dir, f"rank{rank}.npy"), volume.numpy())
+    if rank == 0:
+        np.save(os.path.join(out_dir, "full.npy"), m.calc_from_grid_with_distances(dims, xf))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("dims", [(9, 8, 16), (9, 8, 21)], ids=["even", "ragged"])
+def test_world2_gloo_staged_chunk_gather_equals_single_rank(tmp_path, dims):
+    port = _free_port()
+    mp.spawn(_chunk_worker, args=(2, port, dims, str(tmp_path)), nprocs=2, join=True)
+    full = np.load(tmp_path / "full.npy")
+    for r in range(2):
+        got = np.load(tmp_path / f"rank{r}.npy")
+        assert np.array_equal(got.view(np.uint32), full.view(np.uint32))
