@@ -48,6 +48,13 @@ WORKLOADS = {
 }
 DEFAULT_WORKLOAD = "c5_band"
 
+# DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of ONE launch of the dominant kernel (kGridFwn5, whole grid on one
+# GPU) from an `ncu --set full` capture on B200; not measurable inside a timed run, so quoted from the committed capture
+NCU_TRAFFIC = {
+    "c5_band": (41.637380e9 + 34.415310e9, "profiles/r01/ncu_full_kGridFwn5_c5_band_v5.csv"),
+    "c3_band": (1.003856e9 + 0.503436e9, "profiles/r01/ncu_full_kGridDist_kGridFwn5_c3_band_v5.csv"),
+}
+
 
 def build_workload(name, grid_override=None):
     w = dict(WORKLOADS[name])
@@ -410,11 +417,15 @@ def run_ours(args, wl):
     }
     if e2e:
         out["e2e"] = e2e
-    # roofline of the dominant kernel (kGridLockstep<1>): FP32 pipe, per north_star; HBM figures beside it
+    # roofline of the step (kGridDist + kGridFwn5, the latter ~87 % of it): FP32 pipe, per north_star; HBM figures beside it
     out["roofline"] = {"bound": "fp32", "achieved": None, "peak": fp32_peak, "unit": "TFLOP/s", "frac": None, "traffic": None,
                        "peak_source": "FFMA micro-benchmark run on this GPU just now (b2fwn_measure_fp32_peak)",
                        "hbm": {"algorithmic_bytes_per_voxel": 4.0 + (st0.num_nodes * 64 + st0.num_leaves * 64) * world / total,
                                "peak": hbm_peak, "peak_source": hbm_src, "unit": "GB/s"}}
+    if world == 1 and wl["name"] in NCU_TRAFFIC and not args.grid:
+        out["roofline"]["traffic"], out["roofline"]["traffic_source"] = NCU_TRAFFIC[wl["name"]]
+        out["roofline"]["traffic_note"] = ("dominant kernel kGridFwn5 alone; its algorithmic bytes are 8 B/voxel (|d| read, signed d written) "
+                                           "+ one read of the tree")
     nslab0 = (dims[2] // world) * layer  # voxels of one launch (rank 0's slab)
     out["roofline"]["hbm"]["achieved"] = (4.0 * nslab0 + st0.num_nodes * 64 + st0.num_leaves * 64) / (k_ms * 1e-3) / 1e9
     out["roofline"]["hbm"]["frac"] = out["roofline"]["hbm"]["achieved"] / hbm_peak

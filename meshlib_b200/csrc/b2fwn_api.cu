@@ -105,13 +105,18 @@ struct KernelTimer
     }
 };
 
-// layers per chunk for the host-pointer grid calls: whole layers, about 32 Mi voxels (128 MiB) per chunk so that
-// the D2H of chunk k overlaps the kernel of chunk k+1 and cancellation is polled a few times per second
+// layers per chunk for the host-pointer grid calls: whole layers, one eighth of the grid but between 32 Mi and 256 Mi voxels
+// (128 MiB .. 1 GiB) per chunk, so that the D2H of chunk k overlaps the kernels of chunk k+1, the copy left over after the
+// last kernel is short, cancellation is polled many times per second -- and the per-launch costs (walk-length estimates,
+// kernel tails, stream-ordered scratch) are paid tens of times per grid, not hundreds (8-layer chunks of 2048^2 made the
+// host-output call 1.5x slower than the kernels themselves, r01)
 int defaultLayersPerPart( const int32_t dims[3], int overlap )
 {
     const size_t layer = (size_t)dims[0] * dims[1];
     if ( layer == 0 ) return std::max( dims[2], 1 );
-    size_t layers = ( (size_t)32 << 20 ) / layer;
+    const size_t total = layer * (size_t)std::max( dims[2], 1 );
+    const size_t voxels = std::min<size_t>( std::max<size_t>( total / 8, (size_t)32 << 20 ), (size_t)256 << 20 );
+    size_t layers = voxels / layer;
     layers = std::max<size_t>( layers, (size_t)overlap + 1 );
     layers = std::max<size_t>( layers, 2 );
     return (int)std::min<size_t>( layers, (size_t)std::max( dims[2], 1 ) );

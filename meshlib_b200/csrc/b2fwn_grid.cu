@@ -154,7 +154,7 @@ __device__ __forceinline__ void flushCounters( const unsigned ( &cnt )[5], unsig
 // MRMeshProject.cpp:78) -- the culled result is exactly what the walk would return.
 // The walk does not stop at the first leaf in range: it counts the node boxes in range (leaves weighted), which is the
 // length of the distance walk the brick's warp is going to do.  cost = 0 <=> culled; the counts feed the heavy-first order.
-constexpr unsigned COST_MAX = 4096u; // estimates stop here (one thread walks them): anything longer is heavy anyway
+constexpr unsigned COST_MAX = 2048u; // estimates stop here (one thread walks them): anything longer is heavy anyway
 __global__ void __launch_bounds__( 256 ) kBrickCull( const TravNode* __restrict__ nodes, const GridParams P, uint16_t* __restrict__ cost,
                                                      unsigned long long* __restrict__ totals )
 {
@@ -320,8 +320,10 @@ __global__ void __launch_bounds__( 256 ) kGroupHeavy( const TravNode* __restrict
 // ANY of the brick's 128 voxels still needs it (box distance < that voxel's running best); near/far is decided for the
 // brick centre.  No per-voxel traversal state at all: a popped subtree is simply re-tested against the (tighter) bests.
 // The result is the exact minimum over all triangles of the reference's per-triangle value, hence independent of the order.
-template <bool AA, bool STATS>
-__global__ void __launch_bounds__( GRID_TB ) kGridDist( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
+// 8 blocks per SM (64 registers, ~200 B of spills) measured faster than the spill-free 118 registers at 4 blocks: c3_full
+// 626 -> 535 ms, c5_band 1221 -> 1150 ms -- the walk is latency-bound (one dependent node fetch after another)
+template <bool AA, bool STATS, int MINB = 8>
+__global__ void __launch_bounds__( GRID_TB, MINB ) kGridDist( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
                                                         const LeafFilt* __restrict__ filt, const GridParams P, float* __restrict__ out,
                                                         const uint16_t* __restrict__ cullCost, const BrickOrder O,
                                                         unsigned long long* __restrict__ stats )
@@ -720,8 +722,9 @@ __device__ __forceinline__ float fwnResult( const int MODE, const float sum, con
 // the kernels of all ranks have finished, every GPU holds the whole volume -- no collective kernel competes for SMs (the
 // NCCL all-gather could not overlap this kernel: it fills every SM's register file) and nothing is left to do after the
 // last brick.  Traffic: (P-1) x 4 B per voxel leave each GPU during its step, far below the NVLink rate.
-template <int MODE, bool AA, bool PEERS>
-__global__ void __launch_bounds__( GRID_TB ) kGridFwn5( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
+// 9 blocks per SM (56 registers) measured 1.8 % faster than 8 (63 registers); 10 (48 registers, 60 B spills) slower again
+template <int MODE, bool AA, bool PEERS, int MINB = 9>
+__global__ void __launch_bounds__( GRID_TB, MINB ) kGridFwn5( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
                                                         const GridParams P, float* __restrict__ out, const BrickOrder O, const PeerOut peers )
 {
     Brick B;

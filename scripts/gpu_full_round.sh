@@ -15,6 +15,10 @@ done
 WL=c3_band
 CMD="python bench.py --workload $WL --steps 2 --warmup 1 --no-e2e --no-cpu"
 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/launches_$WL.csv $CMD > gpurun_out/ncu_launches_$WL.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:kGrid -c 2 -f -o gpurun_out/prof_$WL $CMD > gpurun_out/ncu_full_$WL.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:'kGridDist|kGridFwn5' -c 2 -f -o gpurun_out/prof_$WL $CMD > gpurun_out/ncu_full_$WL.log 2>&1
 tail -3 gpurun_out/ncu_full_$WL.log
+# dominant kernel at the bench workload: full capture (DRAM traffic for roofline.traffic)
+ncu --set full --clock-control none --import-source on -k regex:kGridFwn5 -c 1 -f -o gpurun_out/prof_c5_band_fwn5 python bench.py --workload c5_band --steps 1 --warmup 0 --no-e2e --no-cpu > gpurun_out/ncu_full_c5_band.log 2>&1
+tail -2 gpurun_out/ncu_full_c5_band.log
+python scripts/diag_queries.py > gpurun_out/diag_queries.txt 2>&1; tail -2 gpurun_out/diag_queries.txt
 ls -la gpurun_out
