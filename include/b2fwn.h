@@ -93,6 +93,27 @@ int b2fwn_calc_from_vector_device( b2fwn_handle h, const float* d_pts_xyz, size_
 int b2fwn_calc_self_intersections( b2fwn_handle h, float beta, uint64_t* out_bits, b2fwn_progress cb, void* user );
 int b2fwn_calc_self_intersections_device( b2fwn_handle h, float beta, uint64_t* d_out_bits, float* d_out_w_or_null );
 
+/* IPointsToMeshProjector::findProjections (source/MRMesh/MRPointsToMeshProjector.h:23-26; CPU .cpp:17-33; reference GPU
+ * source/MRCuda/MRCudaPointsToMeshProjector.cpp:51-123): the closest point of the mesh to every query point, with its face
+ * and barycentric coordinates (MeshProjectionResult, MRMeshProject.h:17-31).  point_xf / tree_xf (row-major A then b, or
+ * NULL) are MeshProjectionTransforms::rigidXfPoint / nonRigidXfTree as createProjectionTransforms (MRMeshProject.cpp:104-121)
+ * returns them: the first moves the query points, the second the tree's boxes and triangles.  No projection within
+ * up_dist_limit_sq: face = -1, dist_sq = up_dist_limit_sq.  MeshTriPoint::e is topology (edgeWithLeft(face)) and is
+ * filled by the caller, as the reference's GPU class does (MRCudaPointsToMeshProjector.cpp:117-123). */
+typedef struct b2fwn_projection
+{
+    int32_t face;      /* PointOnFace::face, -1 = none */
+    float point[3];    /* PointOnFace::point */
+    float bary_a, bary_b; /* MeshTriPoint::bary */
+    float dist_sq;     /* MeshProjectionResult::distSq */
+    int32_t reserved;
+} b2fwn_projection;
+int b2fwn_find_projections( b2fwn_handle h, const float* points_xyz, size_t n, const float point_xf[12], const float tree_xf[12],
+                            float up_dist_limit_sq, float lo_dist_limit_sq, b2fwn_projection* out, b2fwn_progress cb, void* user );
+int b2fwn_find_projections_device( b2fwn_handle h, const float* d_points_xyz, size_t n, const float point_xf[12],
+                                   const float tree_xf[12], float up_dist_limit_sq, float lo_dist_limit_sq,
+                                   b2fwn_projection* d_out );
+
 /* IFastWindingNumber::calcFromGrid (MRFastWindingNumber.h:38; CPU .cpp:54-67; GPU .cpp:175-228) */
 int b2fwn_calc_from_grid( b2fwn_handle h, const int32_t dims[3], const float xf[12], float beta, float* out,
                           b2fwn_progress cb, void* user );

@@ -65,6 +65,11 @@ class OffsetParams(C.Structure):
                 ("winding_number_threshold", C.c_float), ("winding_number_beta", C.c_float), ("reserved", C.c_int32 * 3)]
 
 
+# b2fwn_projection (include/b2fwn.h)
+PROJECTION_DTYPE = np.dtype([("face", "<i4"), ("point", "<f4", (3,)), ("a", "<f4"), ("b", "<f4"), ("dist_sq", "<f4"),
+                             ("reserved", "<i4")])
+
+
 class DeviceBuffer:
     """a raw device allocation exposed through __cuda_array_interface__ (zero-copy view: torch.as_tensor(buf, device=...))"""
 
@@ -84,7 +89,7 @@ EXPORTS = [
     "b2fwn_calc_from_grid", "b2fwn_calc_from_grid_device", "b2fwn_calc_from_grid_with_distances",
     "b2fwn_calc_from_grid_with_distances_device", "b2fwn_calc_from_grid_with_distances_device_chunks",
     "b2fwn_calc_from_grid_with_distances_device_chunks_p2p", "b2fwn_shared_alloc", "b2fwn_shared_open", "b2fwn_shared_close",
-    "b2fwn_shared_free", "b2fwn_calc_from_grid_by_parts",
+    "b2fwn_shared_free", "b2fwn_find_projections", "b2fwn_find_projections_device", "b2fwn_calc_from_grid_by_parts",
     "b2fwn_calc_from_grid_with_distances_by_parts", "b2fwn_get_tree", "b2fwn_get_stats", "b2fwn_marching_cubes",
     "b2fwn_marching_cubes_fetch", "b2fwn_calc_from_grid_with_distances_layers", "b2fwn_measure_fp32_peak",
     "b2fwn_get_bounding_box", "b2fwn_mesh_to_distance_volume", "b2fwn_mc_offset_mesh",
@@ -120,6 +125,8 @@ def load_library():
     L.b2fwn_calc_from_grid_with_distances_device_chunks_p2p.argtypes = [vp, i32p, f32p, C.POINTER(DistOptions), C.c_int32,
                                                                         C.c_int32, C.c_int32, C.c_int32, vp, C.c_int32,
                                                                         C.POINTER(vp)]
+    L.b2fwn_find_projections.argtypes = [vp, vp, C.c_size_t, vp, vp, C.c_float, C.c_float, vp, PROGRESS_CB, vp]
+    L.b2fwn_find_projections_device.argtypes = [vp, vp, C.c_size_t, vp, vp, C.c_float, C.c_float, vp]
     L.b2fwn_shared_alloc.argtypes = [vp, C.c_size_t, C.POINTER(vp), C.c_char_p]
     L.b2fwn_shared_open.argtypes = [vp, C.c_char_p, C.POINTER(vp)]
     L.b2fwn_shared_close.argtypes = [vp, vp]
@@ -311,6 +318,27 @@ class FastWindingNumber:
         arr = (C.c_void_p * max(n, 1))(*peer_ptrs_at_z_begin)
         _check(_lib.b2fwn_calc_from_grid_with_distances_device_chunks_p2p(self._h, _dims(dims), _xf(grid_to_mesh_xf), C.byref(options),
                                                                           z_begin, z_end, z_chunk, z_stride, d_volume_at_z_begin, n, arr))
+
+    # ---- IPointsToMeshProjector::findProjections ----
+    def find_projections(self, points, point_xf=None, tree_xf=None, up_dist_limit_sq=FLT_MAX, lo_dist_limit_sq=0.0, cb=None):
+        """structured array (PROJECTION_DTYPE) of the closest mesh point of every query point: face (-1 = none within the
+        limit), point, barycentrics a/b, dist_sq; point_xf / tree_xf = rigidXfPoint / nonRigidXfTree (12 floats, A then b)"""
+        pts = np.ascontiguousarray(points, np.float32).reshape(-1, 3)
+        out = np.zeros(len(pts), PROJECTION_DTYPE)
+        px = None if point_xf is None else np.ascontiguousarray(point_xf, np.float32)
+        tx = None if tree_xf is None else np.ascontiguousarray(tree_xf, np.float32)
+        _check(_lib.b2fwn_find_projections(self._h, pts.ctypes.data, len(pts), None if px is None else px.ctypes.data,
+                                           None if tx is None else tx.ctypes.data, up_dist_limit_sq, lo_dist_limit_sq,
+                                           out.ctypes.data, _progress(cb), None))
+        return out
+
+    def find_projections_device(self, d_points_ptr, n, d_out_ptr, point_xf=None, tree_xf=None, up_dist_limit_sq=FLT_MAX,
+                                lo_dist_limit_sq=0.0):
+        px = None if point_xf is None else np.ascontiguousarray(point_xf, np.float32)
+        tx = None if tree_xf is None else np.ascontiguousarray(tree_xf, np.float32)
+        _check(_lib.b2fwn_find_projections_device(self._h, d_points_ptr, n, None if px is None else px.ctypes.data,
+                                                  None if tx is None else tx.ctypes.data, up_dist_limit_sq, lo_dist_limit_sq,
+                                                  d_out_ptr))
 
     # ---- peer-visible device memory (multi-GPU volumes) ----
     def shared_alloc(self, nbytes):

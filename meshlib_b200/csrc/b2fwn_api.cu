@@ -383,6 +383,53 @@ int b2fwn_calc_self_intersections( b2fwn_handle h, float beta, uint64_t* outBits
     return B2FWN_OK;
 }
 
+// ---- closest points with face and barycentrics (IPointsToMeshProjector) ---------------------------------------------------
+
+int b2fwn_find_projections_device( b2fwn_handle h, const float* dPts, size_t n, const float pointXf[12], const float treeXf[12],
+                                   float upDistLimitSq, float loDistLimitSq, b2fwn_projection* dOut )
+{
+    if ( !h || ( n && ( !dPts || !dOut ) ) ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    KernelTimer tm( h );
+    if ( int e = launchFindProjections( h->tree, dPts, n, pointXf, treeXf, upDistLimitSq, loDistLimitSq, dOut, h->stream,
+                                        &h->stats.kernel_launches ) ) return e;
+    tm.stop();
+    B2_CUDA( cudaStreamSynchronize( h->stream ) );
+    return B2FWN_OK;
+}
+
+int b2fwn_find_projections( b2fwn_handle h, const float* pts, size_t n, const float pointXf[12], const float treeXf[12],
+                            float upDistLimitSq, float loDistLimitSq, b2fwn_projection* out, b2fwn_progress cb, void* user )
+{
+    if ( !h || ( n && ( !pts || !out ) ) ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    if ( !report( cb, user, 0.f ) ) return canceled();
+    if ( n == 0 ) return B2FWN_OK;
+    // chunks of 4 Mi points (3 floats in, 8 floats out per point), the reference's splitByChunks loop (MRCudaPointsToMeshProjector.cpp:105-113)
+    const size_t chunk = std::min<size_t>( n, (size_t)4 << 20 );
+    const size_t inFloats = ( 3 * chunk + 3 ) / 4 * 4; // records start 16-B aligned (two float4 stores each)
+    if ( int e = ensureScratch( h, 0, inFloats + 8 * chunk ) ) return e;
+    float* dIn = h->dScratch[0];
+    b2fwn_projection* dOut = reinterpret_cast<b2fwn_projection*>( h->dScratch[0] + inFloats );
+    double kernelMs = 0;
+    for ( size_t o = 0; o < n; o += chunk )
+    {
+        const size_t m = std::min( chunk, n - o );
+        B2_CUDA( cudaMemcpyAsync( dIn, pts + 3 * o, m * 3 * sizeof( float ), cudaMemcpyHostToDevice, h->stream ) );
+        cudaEventRecord( h->evA, h->stream );
+        if ( int e = launchFindProjections( h->tree, dIn, m, pointXf, treeXf, upDistLimitSq, loDistLimitSq, dOut, h->stream,
+                                            &h->stats.kernel_launches ) ) return e;
+        cudaEventRecord( h->evB, h->stream );
+        B2_CUDA( cudaMemcpyAsync( out + o, dOut, m * sizeof( b2fwn_projection ), cudaMemcpyDeviceToHost, h->stream ) );
+        B2_CUDA( cudaStreamSynchronize( h->stream ) );
+        float ms = 0;
+        if ( cudaEventElapsedTime( &ms, h->evA, h->evB ) == cudaSuccess ) kernelMs += ms;
+        if ( !report( cb, user, float( o + m ) / float( n ) ) ) return canceled();
+    }
+    h->stats.last_kernel_ms = kernelMs;
+    return B2FWN_OK;
+}
+
 // ---- grids -------------------------------------------------------------------------------------------------------------
 
 int b2fwn_calc_from_grid_device( b2fwn_handle h, const int32_t dims[3], const float xf[12], float beta, int32_t zBegin,

@@ -114,6 +114,10 @@ int launchSdfGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf,
                    int zBegin, int zEnd, float* dOut, cudaStream_t stream, uint64_t* launches, const ZChunks* zc = nullptr,
                    const PeerOut* peers = nullptr );
 
+// closest point with face and barycentrics (b2fwn_project.cu) -----------------------------------------------------------
+int launchFindProjections( const DeviceTree& t, const float* dPts, size_t n, const float* pointXf12, const float* treeXf12,
+                           float upDistLimitSq, float loDistLimitSq, b2fwn_projection* dOut, cudaStream_t stream, uint64_t* launches );
+
 // marching cubes (b2fwn_mc.cu) -----------------------------------------------------------------------------------
 struct McResult
 {

@@ -1,0 +1,210 @@
+// b2fwn_project.cu -- closest point on the mesh for a vector of points, WITH face id and barycentric coordinates:
+// the GPU back-end of MR::IPointsToMeshProjector (source/MRMesh/MRPointsToMeshProjector.h:12-31,
+// CPU: MRPointsToMeshProjector.cpp:17-33 -> findProjectionSubtree, MRMeshProject.cpp:13-103; reference GPU:
+// source/MRCuda/MRCudaPointsToMeshProjector.cu:8-97).
+//
+// One thread per point, private stack of (node, box distance) pairs, exactly the reference's visiting order: both children
+// are box-tested at the parent, the farther one is pushed first, a popped task is dropped when its distance is no longer
+// below the running best, a candidate replaces the best only when STRICTLY closer.  The face that wins a tie therefore is
+// the reference's, and with the closest point evaluated in double like the reference (MRMeshProject.cpp:67-75) the whole
+// record -- face, point, barycentrics, distSq -- is the reference's bit for bit.
+// Optional transforms (createProjectionTransforms, MRMeshProject.cpp:104-121): pointXf moves the query point, treeXf (the
+// non-rigid case) moves node boxes (hull of the 8 transformed corners, MRBox.h:336-345) and triangle vertices.
+#include "b2fwn_internal.h"
+#include "b2fwn_math.cuh"
+#include <cfloat>
+
+namespace b2
+{
+
+namespace
+{
+
+struct Xf12
+{
+    float A[9];
+    float b[3];
+};
+
+// closestPointInTriangle<double> (MRClosestPointInTriangle.h:27-87) with its barycentric pair; same operations, same order
+__device__ __forceinline__ void closestPointBary( const float3 pf, const float3 fa, const float3 fb, const float3 fc,
+                                                  double& rx, double& ry, double& rz, double& ba, double& bb )
+{
+    const double px = pf.x, py = pf.y, pz = pf.z;
+    const double ax = fa.x, ay = fa.y, az = fa.z, bx = fb.x, by = fb.y, bz = fb.z, cx = fc.x, cy = fc.y, cz = fc.z;
+    const double abx = DS( bx, ax ), aby = DS( by, ay ), abz = DS( bz, az );
+    const double acx = DS( cx, ax ), acy = DS( cy, ay ), acz = DS( cz, az );
+    const double apx = DS( px, ax ), apy = DS( py, ay ), apz = DS( pz, az );
+    const double d1 = ddot3( abx, aby, abz, apx, apy, apz );
+    const double d2 = ddot3( acx, acy, acz, apx, apy, apz );
+    if ( d1 <= 0 && d2 <= 0 ) { rx = ax; ry = ay; rz = az; ba = 0; bb = 0; return; } // #1
+    const double bpx = DS( px, bx ), bpy = DS( py, by ), bpz = DS( pz, bz );
+    const double d3 = ddot3( abx, aby, abz, bpx, bpy, bpz );
+    const double d4 = ddot3( acx, acy, acz, bpx, bpy, bpz );
+    if ( d3 >= 0 && d4 <= d3 ) { rx = bx; ry = by; rz = bz; ba = 1; bb = 0; return; } // #2
+    const double cpx = DS( px, cx ), cpy = DS( py, cy ), cpz = DS( pz, cz );
+    const double d5 = ddot3( abx, aby, abz, cpx, cpy, cpz );
+    const double d6 = ddot3( acx, acy, acz, cpx, cpy, cpz );
+    if ( d6 >= 0 && d5 <= d6 ) { rx = cx; ry = cy; rz = cz; ba = 0; bb = 1; return; } // #3
+    const double vc = DS( DM( d1, d4 ), DM( d3, d2 ) );
+    if ( vc <= 0 && d1 >= 0 && d3 <= 0 )
+    {
+        const double v = d1 / DS( d1, d3 );
+        rx = DA( ax, DM( v, abx ) ); ry = DA( ay, DM( v, aby ) ); rz = DA( az, DM( v, abz ) ); ba = v; bb = 0; return; // #4
+    }
+    const double vb = DS( DM( d5, d2 ), DM( d1, d6 ) );
+    if ( vb <= 0 && d6 <= 0 && d2 >= 0 )
+    {
+        const double v = d2 / DS( d2, d6 );
+        rx = DA( ax, DM( v, acx ) ); ry = DA( ay, DM( v, acy ) ); rz = DA( az, DM( v, acz ) ); ba = 0; bb = v; return; // #5
+    }
+    const double va = DS( DM( d3, d6 ), DM( d5, d4 ) );
+    if ( va <= 0 )
+    {
+        if ( d4 < d3 ) { rx = bx; ry = by; rz = bz; ba = 1; bb = 0; return; }
+        if ( d5 < d6 ) { rx = cx; ry = cy; rz = cz; ba = 0; bb = 1; return; }
+        const double e = DS( d4, d3 ), g = DS( d5, d6 );
+        const double v = e / DA( e, g );
+        rx = DA( bx, DM( v, DS( cx, bx ) ) ); ry = DA( by, DM( v, DS( cy, by ) ) ); rz = DA( bz, DM( v, DS( cz, bz ) ) );
+        ba = DS( 1.0, v ); bb = v; return; // #6
+    }
+    const double denom = 1.0 / DA( DA( va, vb ), vc );
+    const double v = DM( vb, denom ), w = DM( vc, denom );
+    rx = DA( DA( ax, DM( v, abx ) ), DM( w, acx ) );
+    ry = DA( DA( ay, DM( v, aby ) ), DM( w, acy ) );
+    rz = DA( DA( az, DM( v, abz ) ), DM( w, acz ) ); // #0
+    ba = v; bb = w;
+}
+
+template <bool TXF>
+__device__ __forceinline__ float nodeBoxDistSq( const TravNode* __restrict__ nodes, const int n, const Xf12& treeXf, const float3 pt, int& right, int& link )
+{
+    const float4* np = reinterpret_cast<const float4*>( nodes + n );
+    float4 q0 = __ldg( np ), q1 = __ldg( np + 1 );
+    right = __float_as_int( q1.z );
+    link = __float_as_int( q1.w );
+    if ( TXF )
+    {
+        float lo[3] = { FLT_MAX, FLT_MAX, FLT_MAX }, hi[3] = { -FLT_MAX, -FLT_MAX, -FLT_MAX };
+#pragma unroll
+        for ( int c = 0; c < 8; ++c )
+        {
+            const float3 q = applyXf( treeXf.A, treeXf.b, ( c & 1 ) ? q0.w : q0.x, ( c & 2 ) ? q1.x : q0.y, ( c & 4 ) ? q1.y : q0.z );
+            if ( q.x < lo[0] ) lo[0] = q.x; if ( q.x > hi[0] ) hi[0] = q.x; // Box::include, MRBox.h
+            if ( q.y < lo[1] ) lo[1] = q.y; if ( q.y > hi[1] ) hi[1] = q.y;
+            if ( q.z < lo[2] ) lo[2] = q.z; if ( q.z > hi[2] ) hi[2] = q.z;
+        }
+        q0 = make_float4( lo[0], lo[1], lo[2], hi[0] );
+        q1.x = hi[1]; q1.y = hi[2];
+    }
+    return boxDistSq( pt, q0, q1 );
+}
+
+template <bool TXF>
+__global__ void __launch_bounds__( 128 ) kFindProjections( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris, const int numNodes,
+                                                           const float* __restrict__ pts, const size_t n, const int hasPointXf, const Xf12 pointXf,
+                                                           const Xf12 treeXf, const float upDistLimitSq, const float loDistLimitSq,
+                                                           b2fwn_projection* __restrict__ out )
+{
+    const size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if ( idx >= n ) return;
+    float3 pt = make_float3( pts[3 * idx], pts[3 * idx + 1], pts[3 * idx + 2] );
+    if ( hasPointXf ) pt = applyXf( pointXf.A, pointXf.b, pt.x, pt.y, pt.z );
+
+    int face = -1;
+    float best = upDistLimitSq, bpx = 0.f, bpy = 0.f, bpz = 0.f, ba = 0.f, bb = 0.f;
+    int stN[32];
+    float stD[32];
+    int sp = 0;
+    if ( numNodes > 0 )
+    {
+        int right, link;
+        const float d = nodeBoxDistSq<TXF>( nodes, 0, treeXf, pt, right, link );
+        if ( d < best ) { stN[0] = 0; stD[0] = d; sp = 1; }
+    }
+    while ( sp > 0 )
+    {
+        --sp;
+        const int node = stN[sp];
+        if ( stD[sp] >= best ) continue;
+        const float4 q1 = __ldg( reinterpret_cast<const float4*>( nodes + node ) + 1 );
+        const int link = __float_as_int( q1.w );
+        if ( link < 0 )
+        {
+            const float4* tp = reinterpret_cast<const float4*>( tris + ( -link - 1 ) );
+            const float4 ta = __ldg( tp ), tb = __ldg( tp + 1 ), tc = __ldg( tp + 2 );
+            float3 a = make_float3( ta.x, ta.y, ta.z ), b = make_float3( tb.x, tb.y, tb.z ), c = make_float3( tc.x, tc.y, tc.z );
+            if ( TXF )
+            {
+                a = applyXf( treeXf.A, treeXf.b, a.x, a.y, a.z );
+                b = applyXf( treeXf.A, treeXf.b, b.x, b.y, b.z );
+                c = applyXf( treeXf.A, treeXf.b, c.x, c.y, c.z );
+            }
+            double rx, ry, rz, va, vb;
+            closestPointBary( pt, a, b, c, rx, ry, rz, va, vb );
+            const float fx = __double2float_rn( rx ), fy = __double2float_rn( ry ), fz = __double2float_rn( rz );
+            const float ex = FS( fx, pt.x ), ey = FS( fy, pt.y ), ez = FS( fz, pt.z );
+            const float cand = dot3( ex, ey, ez, ex, ey, ez );
+            if ( cand < best ) // MRMeshProject.cpp:78
+            {
+                best = cand; face = __float_as_int( ta.w ); bpx = fx; bpy = fy; bpz = fz;
+                ba = __double2float_rn( va ); bb = __double2float_rn( vb );
+                if ( best <= loDistLimitSq ) break; // MRMeshProject.cpp:81-82
+            }
+            continue;
+        }
+        const int l = node + 1, r = __float_as_int( q1.z );
+        int dummyR, dummyL;
+        const float d1 = nodeBoxDistSq<TXF>( nodes, l, treeXf, pt, dummyR, dummyL );
+        const float d2 = nodeBoxDistSq<TXF>( nodes, r, treeXf, pt, dummyR, dummyL );
+        // the task with the smaller distance is pushed last, to be entered first (MRMeshProject.cpp:90-99)
+        if ( d1 < d2 )
+        {
+            if ( d2 < best ) { stN[sp] = r; stD[sp] = d2; ++sp; }
+            if ( d1 < best ) { stN[sp] = l; stD[sp] = d1; ++sp; }
+        }
+        else
+        {
+            if ( d1 < best ) { stN[sp] = l; stD[sp] = d1; ++sp; }
+            if ( d2 < best ) { stN[sp] = r; stD[sp] = d2; ++sp; }
+        }
+    }
+    float4* o = reinterpret_cast<float4*>( out + idx );
+    o[0] = make_float4( __int_as_float( face ), bpx, bpy, bpz );
+    o[1] = make_float4( ba, bb, best, 0.f );
+}
+
+Xf12 toXf12( const float* x )
+{
+    Xf12 r{};
+    if ( x )
+    {
+        for ( int k = 0; k < 9; ++k ) r.A[k] = x[k];
+        for ( int k = 0; k < 3; ++k ) r.b[k] = x[9 + k];
+    }
+    return r;
+}
+
+} // anonymous namespace
+
+static_assert( sizeof( b2fwn_projection ) == 32, "b2fwn_projection is two float4" );
+
+int launchFindProjections( const DeviceTree& t, const float* dPts, size_t n, const float* pointXf12, const float* treeXf12,
+                           float upDistLimitSq, float loDistLimitSq, b2fwn_projection* dOut, cudaStream_t st, uint64_t* launches )
+{
+    if ( n == 0 ) return B2FWN_OK;
+    if ( t.depth > 30 ) { setError( "tree too deep for the projection stack" ); return B2FWN_ERR_INVALID; }
+    const unsigned blocks = (unsigned)( ( n + 127 ) / 128 );
+    const Xf12 pxf = toXf12( pointXf12 ), txf = toXf12( treeXf12 );
+    if ( treeXf12 )
+        kFindProjections<true><<<blocks, 128, 0, st>>>( t.nodes, t.leafTris, (int)t.numNodes, dPts, n, pointXf12 != nullptr, pxf, txf,
+                                                        upDistLimitSq, loDistLimitSq, dOut );
+    else
+        kFindProjections<false><<<blocks, 128, 0, st>>>( t.nodes, t.leafTris, (int)t.numNodes, dPts, n, pointXf12 != nullptr, pxf, txf,
+                                                         upDistLimitSq, loDistLimitSq, dOut );
+    if ( launches ) ++*launches;
+    B2_CUDA( cudaGetLastError() );
+    return B2FWN_OK;
+}
+
+} // namespace b2

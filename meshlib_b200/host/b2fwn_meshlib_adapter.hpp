@@ -2,6 +2,9 @@
 // MeshLib's own operator interface.  Compile it INSIDE a MeshLib build (it includes MeshLib headers); it adds no
 // dependency to libb2fwn itself.
 //
+//   MR::B200::PointsToMeshProjector : MR::IPointsToMeshProjector
+//       (interface: source/MRMesh/MRPointsToMeshProjector.h:12-31; stands in for MR::Cuda::PointsToMeshProjector,
+//        source/MRCuda/MRCudaPointsToMeshProjector.h)
 //   MR::B200::FastWindingNumber : MR::IFastWindingNumber, MR::IFastWindingNumberByParts
 //       (interface: source/MRMesh/MRFastWindingNumber.h:11-45, 74-107;
 //        the class it stands in for: MR::Cuda::FastWindingNumber, source/MRCuda/MRCudaFastWindingNumber.h:17-38)
@@ -19,8 +22,11 @@
 #include "MRMesh/MRAffineXf3.h"
 #include "MRMesh/MRVector3.h"
 #include "MRMesh/MRDistanceToMeshOptions.h"
+#include "MRMesh/MRPointsToMeshProjector.h"
+#include "MRMesh/MRMeshProject.h"
 #include "b2fwn.h"
 
+#include <cfloat>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -178,6 +184,92 @@ private:
     const Mesh& mesh_;
     int device_ = 0;
     b2fwn_handle h_ = nullptr;
+};
+
+/// GPU back-end of IPointsToMeshProjector: the closest point of the mesh to each given point, with face and barycentrics.
+/// Same contract as MR::Cuda::PointsToMeshProjector (source/MRCuda/MRCudaPointsToMeshProjector.cpp:30-129): updateMeshData
+/// uploads the mesh (here: builds tree and triangles on the device), findProjections resizes `result`, decomposes the two
+/// transforms with the reference's own createProjectionTransforms, and fills MeshTriPoint::e from the mesh topology.
+class PointsToMeshProjector final : public IPointsToMeshProjector
+{
+public:
+    explicit PointsToMeshProjector( int device = 0 ) : device_( device ) {}
+    ~PointsToMeshProjector() override { b2fwn_destroy( h_ ); }
+    PointsToMeshProjector( const PointsToMeshProjector& ) = delete;
+    PointsToMeshProjector& operator=( const PointsToMeshProjector& ) = delete;
+
+    void updateMeshData( const Mesh* mesh ) override
+    {
+        b2fwn_destroy( h_ );
+        h_ = nullptr;
+        mesh_ = mesh;
+        if ( !mesh_ ) return;
+        const auto tris = mesh_->topology.getTriangulation();
+        b2fwn_config cfg{};
+        cfg.device = device_;
+        if ( b2fwn_create( reinterpret_cast<const float*>( mesh_->points.data() ), mesh_->points.size(),
+                           reinterpret_cast<const int32_t*>( tris.data() ), tris.size(), &cfg, &h_ ) != B2FWN_OK )
+        {
+            lastError_ = std::string( "NVIDIA GPU error: " ) + b2fwn_last_error();
+            h_ = nullptr;
+        }
+    }
+
+    void findProjections( std::vector<MeshProjectionResult>& result, const std::vector<Vector3f>& points,
+                          const AffineXf3f* worldXf = nullptr, const AffineXf3f* worldRefXf = nullptr,
+                          float upDistLimitSq = FLT_MAX, float loDistLimitSq = 0.0f ) override
+    {
+        if ( !mesh_ || !h_ ) return; // as the reference: nothing without mesh data (MRPointsToMeshProjector.cpp:19-20)
+        result.resize( points.size() );
+        AffineXf3f storage;
+        const auto xfs = createProjectionTransforms( storage, worldXf, worldRefXf ); // MRMeshProject.cpp:104-121
+        float pxf[12], txf[12];
+        if ( xfs.rigidXfPoint ) packXf12_( *xfs.rigidXfPoint, pxf );
+        if ( xfs.nonRigidXfTree ) packXf12_( *xfs.nonRigidXfTree, txf );
+        std::vector<b2fwn_projection> raw( points.size() );
+        if ( b2fwn_find_projections( h_, reinterpret_cast<const float*>( points.data() ), points.size(), xfs.rigidXfPoint ? pxf : nullptr,
+                                     xfs.nonRigidXfTree ? txf : nullptr, upDistLimitSq, loDistLimitSq, raw.data(), nullptr, nullptr ) != B2FWN_OK )
+        {
+            lastError_ = b2fwn_last_error();
+            return;
+        }
+        for ( size_t i = 0; i < raw.size(); ++i )
+        {
+            const auto& r = raw[i];
+            MeshProjectionResult m;
+            m.distSq = r.dist_sq;
+            if ( r.face >= 0 )
+            {
+                m.proj.face = FaceId( r.face );
+                m.proj.point = Vector3f( r.point[0], r.point[1], r.point[2] );
+                m.mtp.e = mesh_->topology.edgeWithLeft( m.proj.face ); // MRCudaPointsToMeshProjector.cpp:117-123
+                m.mtp.bary = TriPointf( r.bary_a, r.bary_b );
+            }
+            result[i] = m;
+        }
+    }
+
+    size_t projectionsHeapBytes( size_t numProjections ) const override
+    {
+        return numProjections * ( 3 * sizeof( float ) + sizeof( b2fwn_projection ) ); // device staging per projection
+    }
+
+    const std::string& lastError() const { return lastError_; }
+
+private:
+    static void packXf12_( const AffineXf3f& xf, float out[12] )
+    {
+        const Vector3f* rows[3] = { &xf.A.x, &xf.A.y, &xf.A.z };
+        for ( int r = 0; r < 3; ++r )
+            for ( int c = 0; c < 3; ++c )
+                out[3 * r + c] = ( *rows[r] )[c];
+        for ( int c = 0; c < 3; ++c ) out[9 + c] = xf.b[c];
+    }
+
+    const Mesh* mesh_ = nullptr;
+    int device_ = 0;
+    b2fwn_handle h_ = nullptr;
+    std::string lastError_;
 };
 
 } // namespace B200

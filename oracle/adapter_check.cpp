@@ -123,5 +123,32 @@ int main()
     // cancellation travels as the reference's error string
     auto c = ours->calcFromGridWithDistances( da, dims, basis, opt, []( float ) { return false; } );
     check( !c.has_value() && c.error() == "Operation was canceled", "cancel.error_string" );
+
+    // IPointsToMeshProjector: our back-end against the reference's CPU class through the interface pointer,
+    // the way findSignedDistances receives it (MRPointsToMeshProjector.cpp:35-62); rigid and non-rigid transform cases
+    {
+        std::unique_ptr<IPointsToMeshProjector> oursP = std::make_unique<B200::PointsToMeshProjector>();
+        PointsToMeshProjector refP;
+        oursP->updateMeshData( &mesh );
+        refP.updateMeshData( &mesh );
+        const AffineXf3f rigid( Matrix3f::rotation( Vector3f( 0.3f, 0.5f, 0.8f ).normalized(), 0.7f ), Vector3f( 0.2f, -0.1f, 0.3f ) );
+        const AffineXf3f shear( Matrix3f( Vector3f( 1.2f, 0.1f, 0.f ), Vector3f( 0.f, 0.9f, 0.2f ), Vector3f( 0.05f, 0.f, 1.1f ) ), Vector3f( 0.3f, 0.1f, -0.2f ) );
+        struct Case { const char* name; const AffineXf3f* xf; const AffineXf3f* refXf; float up, lo; };
+        const Case cases[] = { { "plain", nullptr, nullptr, FLT_MAX, 0.f }, { "limits", nullptr, nullptr, 0.5f, 0.01f },
+                               { "pointXf", &rigid, nullptr, FLT_MAX, 0.f }, { "rigidRefXf", &shear, &rigid, FLT_MAX, 0.f },
+                               { "nonRigidRefXf", &rigid, &shear, 2.f, 0.f } };
+        for ( const auto& c : cases )
+        {
+            std::vector<MeshProjectionResult> ra, rb;
+            oursP->findProjections( ra, pts, c.xf, c.refXf, c.up, c.lo );
+            refP.findProjections( rb, pts, c.xf, c.refXf, c.up, c.lo );
+            bool same = ra.size() == rb.size() && ra.size() == pts.size();
+            for ( size_t i = 0; same && i < ra.size(); ++i )
+                same = ra[i].proj.face == rb[i].proj.face && ra[i].mtp.e == rb[i].mtp.e && ra[i].distSq == rb[i].distSq &&
+                       ( !rb[i].proj.face.valid() || ( ra[i].proj.point == rb[i].proj.point && ra[i].mtp.bary.a == rb[i].mtp.bary.a && ra[i].mtp.bary.b == rb[i].mtp.bary.b ) );
+            check( same, ( std::string( "findProjections." ) + c.name ).c_str() );
+        }
+        check( oursP->projectionsHeapBytes( 10 ) == 10 * ( 12 + 32 ), "projectionsHeapBytes" );
+    }
     return g_fail ? 1 : 0;
 }

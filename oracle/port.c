@@ -401,7 +401,135 @@ static float findProjectionDistSq( const OMesh* m, const float* pt, float upDist
     return best;
 }
 
+/* ---- full projection result: IPointsToMeshProjector::findProjections ----------------------------------
+ * MRPointsToMeshProjector.cpp:17-33 -> findProjection -> findProjectionSubtree (MRMeshProject.cpp:13-103) with the optional
+ * transforms of createProjectionTransforms (MRMeshProject.cpp:104-121): pointXf moves the query point, treeXf (non-rigid)
+ * moves node boxes (transformed(): hull of the 8 corners, MRBox.h:336-345, corner order MRBox.h:289-303) and triangles. */
+typedef struct { int32_t face; float p[3]; float a, b; float distSq; int32_t edge; } OProj;
+
+static inline void xfApply( const float* x, const float* v, float* o ) /* AffineXf3f::operator(): A * v + b */
+{
+    for ( int r = 0; r < 3; ++r )
+        o[r] = ( x[3 * r] * v[0] + x[3 * r + 1] * v[1] + x[3 * r + 2] * v[2] ) + x[9 + r];
+}
+
+static inline float boxDistSqXf( const Node* nd, const float* treeXf, const float* pt )
+{
+    if ( !treeXf ) return boxDistSq( nd, pt );
+    Node t;
+    for ( int k = 0; k < 3; ++k ) { t.mn[k] = FLT_MAX; t.mx[k] = -FLT_MAX; } /* Box default: min = max(), max = lowest() */
+    for ( int c = 0; c < 8; ++c )
+    {
+        const float v[3] = { ( c & 1 ) ? nd->mx[0] : nd->mn[0], ( c & 2 ) ? nd->mx[1] : nd->mn[1], ( c & 4 ) ? nd->mx[2] : nd->mn[2] };
+        float q[3];
+        xfApply( treeXf, v, q );
+        for ( int k = 0; k < 3; ++k ) { if ( q[k] < t.mn[k] ) t.mn[k] = q[k]; if ( q[k] > t.mx[k] ) t.mx[k] = q[k]; }
+    }
+    return boxDistSq( &t, pt );
+}
+
+/* closestPointInTriangle<double> with its barycentric pair (MRClosestPointInTriangle.h:27-87) */
+static void closestPointBaryD( const double* p, const double* a, const double* b, const double* c, double* out, double* bary )
+{
+    const double ab[3] = { b[0] - a[0], b[1] - a[1], b[2] - a[2] };
+    const double ac[3] = { c[0] - a[0], c[1] - a[1], c[2] - a[2] };
+    const double ap[3] = { p[0] - a[0], p[1] - a[1], p[2] - a[2] };
+    const double d1 = dot3d( ab, ap ), d2 = dot3d( ac, ap );
+    if ( d1 <= 0 && d2 <= 0 ) { memcpy( out, a, 24 ); bary[0] = 0; bary[1] = 0; return; }
+    const double bp[3] = { p[0] - b[0], p[1] - b[1], p[2] - b[2] };
+    const double d3 = dot3d( ab, bp ), d4 = dot3d( ac, bp );
+    if ( d3 >= 0 && d4 <= d3 ) { memcpy( out, b, 24 ); bary[0] = 1; bary[1] = 0; return; }
+    const double cp[3] = { p[0] - c[0], p[1] - c[1], p[2] - c[2] };
+    const double d5 = dot3d( ab, cp ), d6 = dot3d( ac, cp );
+    if ( d6 >= 0 && d5 <= d6 ) { memcpy( out, c, 24 ); bary[0] = 0; bary[1] = 1; return; }
+    const double vc = d1 * d4 - d3 * d2;
+    if ( vc <= 0 && d1 >= 0 && d3 <= 0 )
+    {
+        const double v = d1 / ( d1 - d3 );
+        for ( int k = 0; k < 3; ++k ) out[k] = a[k] + v * ab[k];
+        bary[0] = v; bary[1] = 0; return;
+    }
+    const double vb = d5 * d2 - d1 * d6;
+    if ( vb <= 0 && d6 <= 0 && d2 >= 0 )
+    {
+        const double v = d2 / ( d2 - d6 );
+        for ( int k = 0; k < 3; ++k ) out[k] = a[k] + v * ac[k];
+        bary[0] = 0; bary[1] = v; return;
+    }
+    const double va = d3 * d6 - d5 * d4;
+    if ( va <= 0 )
+    {
+        if ( d4 < d3 ) { memcpy( out, b, 24 ); bary[0] = 1; bary[1] = 0; return; }
+        if ( d5 < d6 ) { memcpy( out, c, 24 ); bary[0] = 0; bary[1] = 1; return; }
+        const double v = ( d4 - d3 ) / ( ( d4 - d3 ) + ( d5 - d6 ) );
+        for ( int k = 0; k < 3; ++k ) out[k] = b[k] + v * ( c[k] - b[k] );
+        bary[0] = 1 - v; bary[1] = v; return;
+    }
+    const double denom = 1 / ( va + vb + vc );
+    const double v = vb * denom, w = vc * denom;
+    for ( int k = 0; k < 3; ++k ) out[k] = a[k] + v * ab[k] + w * ac[k];
+    bary[0] = v; bary[1] = w;
+}
+
+static OProj findProjectionFull( const OMesh* m, const float* pt, const float* treeXf, float upDistLimitSq, float loDistLimitSq )
+{
+    OProj res; memset( &res, 0, sizeof( res ) );
+    res.face = -1; res.edge = -1; res.distSq = upDistLimitSq;
+    if ( m->nNodes <= 0 ) return res;
+    struct { int32_t n; float d; } stack[64]; int sp = 0;
+    {
+        const float d = boxDistSqXf( &m->nodes[0], treeXf, pt );
+        if ( d < res.distSq ) { stack[sp].n = 0; stack[sp].d = d; ++sp; }
+    }
+    while ( sp > 0 )
+    {
+        --sp;
+        const int32_t n = stack[sp].n; const float sd = stack[sp].d;
+        const Node* nd = &m->nodes[n];
+        if ( sd >= res.distSq ) continue;
+        if ( nd->r < 0 )
+        {
+            float a[3], b[3], c[3];
+            triPoints( m, nd->l, a, b, c );
+            if ( treeXf )
+            {
+                float t[3];
+                xfApply( treeXf, a, t ); memcpy( a, t, 12 );
+                xfApply( treeXf, b, t ); memcpy( b, t, 12 );
+                xfApply( treeXf, c, t ); memcpy( c, t, 12 );
+            }
+            const double pd[3] = { pt[0], pt[1], pt[2] }, ad[3] = { a[0], a[1], a[2] }, bd[3] = { b[0], b[1], b[2] }, cd[3] = { c[0], c[1], c[2] };
+            double proj[3], bary[2];
+            closestPointBaryD( pd, ad, bd, cd, proj, bary );
+            const float pf[3] = { (float)proj[0], (float)proj[1], (float)proj[2] };
+            const float d[3] = { pf[0] - pt[0], pf[1] - pt[1], pf[2] - pt[2] };
+            const float cand = dot3f( d, d );
+            if ( cand < res.distSq )
+            {
+                res.face = nd->l; memcpy( res.p, pf, 12 ); res.a = (float)bary[0]; res.b = (float)bary[1]; res.distSq = cand;
+                if ( res.distSq <= loDistLimitSq ) break;
+            }
+            continue;
+        }
+        const float d1 = boxDistSqXf( &m->nodes[nd->l], treeXf, pt ), d2 = boxDistSqXf( &m->nodes[nd->r], treeXf, pt );
+        if ( d1 < d2 )
+        {
+            if ( d2 < res.distSq ) { stack[sp].n = nd->r; stack[sp].d = d2; ++sp; }
+            if ( d1 < res.distSq ) { stack[sp].n = nd->l; stack[sp].d = d1; ++sp; }
+        }
+        else
+        {
+            if ( d1 < res.distSq ) { stack[sp].n = nd->l; stack[sp].d = d1; ++sp; }
+            if ( d2 < res.distSq ) { stack[sp].n = nd->r; stack[sp].d = d2; ++sp; }
+        }
+    }
+    return res;
+}
+
 /* ---- exported C API (loaded by oracle/portlib.py through ctypes) -------------------------------------------------------- */
+
+/* pointXf12 / treeXf12 = row-major A then b, or NULL; out = n OProj records (edge is always -1: no topology here) */
+void orc_find_projections( void* h, const float* pts, size_t n, const float* pointXf12, const float* treeXf12, float up, float lo, void* out );
 
 void* orc_create( const float* pts, size_t nv, const int32_t* tris, size_t nf )
 {
@@ -566,4 +694,17 @@ void orc_chunk( size_t totalSize, size_t chunkSize, size_t overlap, size_t index
 {
     *offset = index * ( chunkSize - overlap );
     *size = chunkSize < totalSize - *offset ? chunkSize : totalSize - *offset;
+}
+
+
+void orc_find_projections( void* h, const float* pts, size_t n, const float* pointXf12, const float* treeXf12, float up, float lo, void* out )
+{
+    const OMesh* m = (const OMesh*)h;
+    OProj* o = (OProj*)out;
+    for ( size_t i = 0; i < n; ++i )
+    {
+        float q[3] = { pts[3 * i], pts[3 * i + 1], pts[3 * i + 2] };
+        if ( pointXf12 ) { float t[3]; xfApply( pointXf12, q, t ); memcpy( q, t, 12 ); }
+        o[i] = findProjectionFull( m, q, treeXf12, up, lo );
+    }
 }

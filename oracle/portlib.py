@@ -35,6 +35,7 @@ def lib():
         L.orc_calc_from_grid_with_distances.argtypes = [vp, vp, vp, C.c_float, C.c_float, C.c_int, C.c_float, C.c_float,
                                                         C.c_int, C.c_int, C.c_longlong, vp, vp]
         L.orc_find_projection_dist_sq.argtypes = [vp, vp, sz, C.c_float, C.c_float, vp]
+        L.orc_find_projections.argtypes = [vp, vp, sz, vp, vp, C.c_float, C.c_float, vp]
         L.orc_triangle_solid_angle.restype = C.c_float
         L.orc_triangle_solid_angle.argtypes = [vp, vp]
         L.orc_chunk_count.restype = sz
@@ -85,6 +86,8 @@ def split_by_chunks(total, chunk, overlap):
         out.append((o.value, s.value))
     return out
 
+
+PROJ_DTYPE = np.dtype([("face", "<i4"), ("point", "<f4", (3,)), ("a", "<f4"), ("b", "<f4"), ("dist_sq", "<f4"), ("edge", "<i4")])
 
 class PortMesh:
     kind = "port"
@@ -154,6 +157,16 @@ class PortMesh:
 
     def calc_grid_with_distances_layers(self, dims, xf12, z0, z1, **kw):
         return self.calc_from_grid_with_distances(dims, xf12, z0=z0, z1=z1, **kw)
+
+    def find_projections(self, pts, point_xf=None, tree_xf=None, up=FLT_MAX, lo=0.0):
+        """findProjections (MRPointsToMeshProjector.cpp:17-33): structured array face/point/a/b/dist_sq (edge = -1)"""
+        pts = np.ascontiguousarray(pts, np.float32).reshape(-1, 3)
+        out = np.zeros(len(pts), PROJ_DTYPE)
+        px = None if point_xf is None else np.ascontiguousarray(point_xf, np.float32)
+        tx = None if tree_xf is None else np.ascontiguousarray(tree_xf, np.float32)
+        lib().orc_find_projections(self.h, pts.ctypes.data, len(pts), None if px is None else px.ctypes.data,
+                                   None if tx is None else tx.ctypes.data, up, lo, out.ctypes.data)
+        return out
 
     def find_projection_dist_sq(self, pts, up=FLT_MAX, lo=0.0):
         pts = np.ascontiguousarray(pts, np.float32).reshape(-1, 3)

@@ -15,6 +15,7 @@
 #include "MRMesh/MRFastWindingNumber.h"
 #include "MRMesh/MRDistanceToMeshOptions.h"
 #include "MRMesh/MRMeshProject.h"
+#include "MRMesh/MRPointsToMeshProjector.h"
 #include "MRMesh/MRTorus.h"
 #include "MRMesh/MRMakeSphereMesh.h"
 #include "MRMesh/MRBitSet.h"
@@ -208,6 +209,40 @@ int mrref_find_projection_dist_sq( void* h, const float* pts, size_t n, float up
 
 /// marching cubes of a dense float volume by the reference's VolumeMesher (two calls: run -> counts, then fetch)
 static TriMesh g_lastMc;
+// IPointsToMeshProjector::findProjections of the reference's CPU class (MRPointsToMeshProjector.cpp:17-33):
+// out = n records of 8 x 4 bytes { int face; float point[3]; float baryA, baryB; float distSq; int edge }.
+// pointXf12 / treeXf12: row-major A then b, or null
+int mrref_find_projections( void* h, const float* pts, size_t n, const float* pointXf12, const float* treeXf12,
+                            float upDistLimitSq, float loDistLimitSq, void* out )
+{
+    auto& m = ( (RefMesh*)h )->mesh;
+    (void)m.getAABBTree();
+    auto toXf = []( const float* x )
+    {
+        AffineXf3f xf;
+        xf.A = Matrix3f( Vector3f( x[0], x[1], x[2] ), Vector3f( x[3], x[4], x[5] ), Vector3f( x[6], x[7], x[8] ) );
+        xf.b = Vector3f( x[9], x[10], x[11] );
+        return xf;
+    };
+    AffineXf3f pxf, txf;
+    if ( pointXf12 ) pxf = toXf( pointXf12 );
+    if ( treeXf12 ) txf = toXf( treeXf12 );
+    std::vector<Vector3f> points( n );
+    for ( size_t i = 0; i < n; ++i ) points[i] = Vector3f( pts[3 * i], pts[3 * i + 1], pts[3 * i + 2] );
+    std::vector<MeshProjectionResult> res;
+    PointsToMeshProjector proj;
+    proj.updateMeshData( &m );
+    proj.findProjections( res, points, pointXf12 ? &pxf : nullptr, treeXf12 ? &txf : nullptr, upDistLimitSq, loDistLimitSq );
+    struct Rec { int face; float p[3]; float a, b; float distSq; int edge; };
+    Rec* o = (Rec*)out;
+    for ( size_t i = 0; i < n; ++i )
+    {
+        const auto& r = res[i];
+        o[i] = Rec{ (int)r.proj.face, { r.proj.point.x, r.proj.point.y, r.proj.point.z }, r.mtp.bary.a, r.mtp.bary.b, r.distSq, (int)r.mtp.e };
+    }
+    return 0;
+}
+
 int mrref_marching_cubes( const float* vol, const int* dims, const float* voxelSize, const float* origin, float iso,
     int lessInside, size_t* nVerts, size_t* nTris )
 {

@@ -52,6 +52,8 @@ def lib():
         L.mrref_calc_grid_with_distances_layers.argtypes = [
             C.c_void_p, _i32p, _f32p, C.c_float, C.c_float, C.c_int, C.c_float, C.c_float, C.c_int, C.c_int, _f32p]
         L.mrref_find_projection_dist_sq.argtypes = [C.c_void_p, _f32p, C.c_size_t, C.c_float, C.c_float, _f32p]
+        L.mrref_find_projections.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_float, C.c_float,
+                                             C.c_void_p]
         L.mrref_marching_cubes.argtypes = [_f32p, _i32p, _f32p, _f32p, C.c_float, C.c_int, C.POINTER(C.c_size_t),
                                            C.POINTER(C.c_size_t)]
         L.mrref_marching_cubes_fetch.argtypes = [_f32p, _i32p]
@@ -63,6 +65,8 @@ NODE_DTYPE = np.dtype([("bmin", np.float32, 3), ("bmax", np.float32, 3), ("l", n
 DIPOLE_DTYPE = np.dtype([("pos", np.float32, 3), ("area", np.float32), ("dirArea", np.float32, 3), ("rr", np.float32)])
 FLT_MAX = float(np.finfo(np.float32).max)
 
+
+PROJ_DTYPE = np.dtype([("face", "<i4"), ("point", "<f4", (3,)), ("a", "<f4"), ("b", "<f4"), ("dist_sq", "<f4"), ("edge", "<i4")])
 
 class RefMesh:
     """The reference's MR::Mesh + MR::FastWindingNumber, driven from numpy."""
@@ -147,6 +151,16 @@ class RefMesh:
         assert lib().mrref_calc_grid_with_distances_layers(
             self.h, dims, np.asarray(xf12, np.float32), min_dist_sq, max_dist_sq, int(null_outside), threshold, beta,
             z0, z1, out) == 0
+        return out
+
+    def find_projections(self, pts, point_xf=None, tree_xf=None, up=FLT_MAX, lo=0.0):
+        """MR::PointsToMeshProjector::findProjections (the reference's CPU class): structured array incl. mtp.e"""
+        pts = np.ascontiguousarray(pts, np.float32).reshape(-1, 3)
+        out = np.zeros(len(pts), PROJ_DTYPE)
+        px = None if point_xf is None else np.ascontiguousarray(point_xf, np.float32)
+        tx = None if tree_xf is None else np.ascontiguousarray(tree_xf, np.float32)
+        lib().mrref_find_projections(self.h, pts.ctypes.data, len(pts), None if px is None else px.ctypes.data,
+                                     None if tx is None else tx.ctypes.data, up, lo, out.ctypes.data)
         return out
 
     def find_projection_dist_sq(self, pts, up=FLT_MAX, lo=0.0):

@@ -32,6 +32,7 @@ def test_struct_layouts_match_header():
     assert C.sizeof(mb.api.Config) == 32
     assert C.sizeof(mb.api.Stats) == 64
     assert C.sizeof(mb.api.McParams) == 48
+    assert mb.PROJECTION_DTYPE.itemsize == 32
     assert C.sizeof(mb.VolumeParams) == 48 and C.sizeof(mb.OffsetParams) == 32 and C.sizeof(mb.OffsetResult) == 56
     o = mb.DistOptions()
     assert (o.min_dist_sq, o.null_outside_min_max, o.winding_number_threshold, o.winding_number_beta) == (0.0, 1, 0.5, 2.0)

@@ -439,3 +439,46 @@ def test_general_affine_grid_transform():
     got = fwn.calc_from_grid_with_distances(dims, xf, mb.DistOptions(0.01, 0.25, True))
     rep = checker.compare_sdf(got, orc.calc_from_grid_with_distances(dims, xf, **band), orc.calc_from_grid(dims, xf))
     assert rep["ok"], rep
+
+
+# ---- IPointsToMeshProjector back-end -----------------------------------------------------------------------
+
+@pytest.mark.parametrize("name", ["torus", "noisy", "holes", "deleted"])
+def test_find_projections_identical_to_oracle(name):
+    """face, closest point, barycentrics and distSq of every query bit for bit (same visiting order as
+    findProjectionSubtree, closest point in double), with distance limits and with point / non-rigid tree transforms"""
+    pts, tris = _mesh(name)
+    orc = checker.best_oracle(pts, tris)
+    if getattr(orc, "kind", "") == "reference":
+        # the reference's Mesh may start a face's vertex loop at another vertex than the input triple did (getTriangulation);
+        # which vertex is `a` changes the last bit of a closest point on an edge, and with it the winner of a tie between
+        # the two faces of that edge.  The C++ adapter hands getTriangulation() to b2fwn_create; do the same here.
+        pts, tris = orc.points, orc.tris
+    fwn = mb.FastWindingNumber(pts, tris)
+    q = meshgen.query_points(20000, -2.5, 2.5, seed=11)
+    q[::7] = pts[(np.arange(len(q[::7])) * 13) % len(pts)]  # points ON the mesh: ties between the faces around a vertex
+    pxf = np.array([0.8, 0.6, 0, -0.6, 0.8, 0, 0, 0, 1, 0.1, -0.2, 0.3], np.float32)
+    txf = np.array([1.2, 0.1, 0, 0, 0.9, 0.2, 0.05, 0, 1.1, 0.3, 0.1, -0.2], np.float32)
+    for kw in (dict(), dict(up=0.09), dict(lo=0.01), dict(point_xf=pxf), dict(point_xf=pxf, tree_xf=txf), dict(tree_xf=txf, up=0.5, lo=0.001)):
+        want = orc.find_projections(q, **kw)
+        got = fwn.find_projections(q, kw.get("point_xf"), kw.get("tree_xf"), kw.get("up", mb.FLT_MAX), kw.get("lo", 0.0))
+        for f, g in (("face", "face"), ("point", "point"), ("a", "a"), ("b", "b"), ("dist_sq", "dist_sq")):
+            assert np.array_equal(got[g].view(np.uint32), want[f].view(np.uint32)), (name, sorted(kw), f)
+
+
+def test_find_projections_edge_cases():
+    pts, tris = _mesh("sphere")
+    fwn = mb.FastWindingNumber(pts, tris)
+    assert len(fwn.find_projections(np.zeros((0, 3), np.float32))) == 0
+    far = fwn.find_projections(np.array([[10, 0, 0]], np.float32), up_dist_limit_sq=1.0)
+    assert far["face"][0] == -1 and far["dist_sq"][0] == 1.0 and not far["point"].any()
+    empty = mb.FastWindingNumber(pts, np.full((4, 3), -1, np.int32))
+    r = empty.find_projections(np.array([[0.5, 0, 0]], np.float32))
+    assert r["face"][0] == -1 and r["dist_sq"][0] == mb.FLT_MAX
+    # device form
+    import torch
+    q = torch.from_numpy(meshgen.query_points(5000, -1.5, 1.5, seed=5)).cuda()
+    out = torch.zeros(5000 * 8, dtype=torch.float32, device="cuda")
+    fwn.find_projections_device(q.data_ptr(), 5000, out.data_ptr())
+    host = fwn.find_projections(q.cpu().numpy())
+    assert out.cpu().numpy().tobytes() == host.tobytes()

@@ -114,3 +114,21 @@ def test_port_against_golden_fixture():
         got = port.calc_from_grid_with_distances(dims, xf, min_dist_sq=float(o[0]), max_dist_sq=float(o[1]), null_outside=True)
         assert got.tobytes() == g[f"{name}_sdf_band"].tobytes()
         assert np.array_equal(port.calc_self_intersections(), g[f"{name}_selfint"])
+
+
+def test_projection_restatement_bit_exact_vs_reference():
+    """full MeshProjectionResult (face, point, barycentrics, distSq) of the C restatement against
+    MR::PointsToMeshProjector::findProjections, with limits and with point / non-rigid tree transforms"""
+    from oracle import reflib
+    if not reflib.available():
+        pytest.skip("oracle/_ref not built (no /root/reference here)")
+    pts, tris = meshgen.make_torus(2, 1, 48, 24)
+    q = meshgen.query_points(4000, -3.5, 3.5, seed=3)
+    m, r = portlib.PortMesh(pts, tris), reflib.RefMesh.from_arrays(pts, tris)
+    pxf = np.array([0.8, 0.6, 0, -0.6, 0.8, 0, 0, 0, 1, 0.1, -0.2, 0.3], np.float32)
+    txf = np.array([1.2, 0.1, 0, 0, 0.9, 0.2, 0.05, 0, 1.1, 0.3, 0.1, -0.2], np.float32)
+    for kw in (dict(), dict(up=0.25), dict(lo=0.05), dict(point_xf=pxf), dict(point_xf=pxf, tree_xf=txf), dict(tree_xf=txf, up=1.0)):
+        a, b = m.find_projections(q, **kw), r.find_projections(q, **kw)
+        for f in ("face", "point", "a", "b", "dist_sq"):
+            assert np.array_equal(a[f].view(np.uint32), b[f].view(np.uint32)), (kw.keys(), f)
+        assert np.array_equal(b["edge"] >= 0, b["face"] >= 0)
