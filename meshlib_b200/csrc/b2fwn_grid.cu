@@ -154,7 +154,7 @@ __device__ __forceinline__ void flushCounters( const unsigned ( &cnt )[5], unsig
 // MRMeshProject.cpp:78) -- the culled result is exactly what the walk would return.
 // The walk does not stop at the first leaf in range: it counts the node boxes in range (leaves weighted), which is the
 // length of the distance walk the brick's warp is going to do.  cost = 0 <=> culled; the counts feed the heavy-first order.
-constexpr unsigned COST_MAX = 2048u; // estimates stop here (one thread walks them): anything longer is heavy anyway
+constexpr unsigned COST_MAX = 4096u; // estimates stop here (one thread walks them): anything longer is heavy anyway
 __global__ void __launch_bounds__( 256 ) kBrickCull( const TravNode* __restrict__ nodes, const GridParams P, uint16_t* __restrict__ cost,
                                                      unsigned long long* __restrict__ totals )
 {
@@ -611,6 +611,7 @@ __global__ void __launch_bounds__( GRID_TB ) kGridFwn( const TravNode* __restric
 //  * the denormal guard of the reference (`d > 0`, MRDipole.h:24) can only matter when beta^2 rr < FLT_MIN; such nodes take
 //    a guarded copy of the loop body, all others carry no guard;
 //  * accepted terms are added under a predicate (one FFMA) instead of multiply + select + add.
+// (A second copy of the winding halves packed 32 B apart -- 4 nodes per line instead of 2 -- measured the same: c5_band 1151 ms.)
 // (Fetching node i+1 ahead of time measured SLOWER: c5_band 1419 ms against 1182 ms -- 8 more registers, 2 more loads.
 //  Block size 32 / 64 / 128 measured the same.)
 // The walk is a function of NV voxels per lane, used with NV = 4 by the regular bricks and with NV = 1 by the slices of

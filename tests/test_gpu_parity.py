@@ -482,3 +482,32 @@ def test_find_projections_edge_cases():
     fwn.find_projections_device(q.data_ptr(), 5000, out.data_ptr())
     host = fwn.find_projections(q.cpu().numpy())
     assert out.cpu().numpy().tobytes() == host.tobytes()
+
+
+def test_brick_order_does_not_change_results():
+    """heavy-first dispatch (walk-length estimates, listed bricks first) is scheduling only: the volume of a grid large
+    enough to switch it on (>= 65,536 bricks) is byte-identical to the one computed in plain linear order (B2FWN_LINEAR=1)"""
+    import hashlib
+    import subprocess
+    import sys
+    code = (
+        "import hashlib, numpy as np, meshlib_b200 as mb\n"
+        "from meshlib_b200 import meshgen\n"
+        "p, t = meshgen.make_uv_sphere(1, 300, 150)\n"
+        "p = meshgen.add_noise(p, 2e-3)\n"
+        "f = mb.FastWindingNumber(p, t)\n"
+        "dims = (256, 256, 136)\n"
+        "xf = mb.make_basis_xf((-1.1, -1.1, -1.1), (2.2 / 256, 2.2 / 256, 2.2 / 136))\n"
+        "h = hashlib.sha256()\n"
+        "for o in (mb.DistOptions(0.0, 0.002, False, 0.5, 2.0), mb.DistOptions()):\n"
+        "    h.update(f.calc_from_grid_with_distances(dims, xf, o).tobytes())\n"
+        "h.update(f.calc_from_grid((256, 256, 128), xf).tobytes())\n"
+        "print(h.hexdigest())\n")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    digests = []
+    for linear in ("0", "1"):
+        env = dict(os.environ, B2FWN_LINEAR=linear, PYTHONPATH=root)
+        r = subprocess.run([sys.executable, "-c", code], env=env, cwd=root, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        digests.append(r.stdout.strip().splitlines()[-1])
+    assert digests[0] == digests[1] and len(digests[0]) == 64
