@@ -699,7 +699,7 @@ __device__ __forceinline__ void fwnWalk( const TravNode* __restrict__ nodes, con
                 const float4 ta = __ldg( tp ), tb = __ldg( tp + 1 ), tc = __ldg( tp + 2 );
 #pragma unroll
                 for ( int v = 0; v < NV; ++v )
-                    if ( go[v] ) sum[v] = FA( sum[v], triangleSolidAngle( p[v], ta, tb, tc ) );
+                    if ( go[v] ) sum[v] = FA( sum[v], triangleSolidAngle( p[v], ta, tb, tc ) ); // (all NV angles + predicated adds measured slower)
             }
         }
         i = max( __reduce_min_sync( FULL, minOf( fR ) ), i + 1 );
@@ -891,6 +891,25 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
     uint32_t* heavyF = heavyD + cap;
     const unsigned nb256 = (unsigned)( ( numBricks + 255 ) / 256 );
     BrickOrder oD, oF;
+    // The winding-number estimates do not depend on the distance kernels: with distances (MODE 1) they run on the tree's
+    // high-priority side stream beside kBrickCull / kGridDist and are joined before kGridFwn5 -- their cost is latency (one
+    // thread walks up to COST_MAX nodes), not throughput, and per launch: the host-output calls pay it once per chunk.
+    const bool sideEst = order && MODE == 1 && t.sideStream;
+    auto fwnEstimates = [&]( cudaStream_t es )
+    {
+        const int gX = ( P.bricksX + GRP - 1 ) / GRP, gY = ( P.bricksY + GRP - 1 ) / GRP, gZ = ( P.bricksZ + GRP - 1 ) / GRP;
+        kGroupCostFwn<<<(unsigned)( ( (size_t)gX * gY * gZ + 255 ) / 256 ), 256, 0, es>>>( t.nodes, P, gX, gY, gZ, costF, totals + 2 );
+        kGroupHeavy<<<nb256, 256, 0, es>>>( t.nodes, costF, P, gX, gY, totals + 2, heavyF, counts + 1, clsF, cap );
+        if ( launches ) *launches += 2;
+        oF.heavy = heavyF; oF.count = counts + 1; oF.cls = clsF; oF.cap = cap;
+    };
+    if ( sideEst )
+    {
+        B2_CUDA( cudaEventRecord( t.evFork, st ) ); // after the scratch allocation and its memset
+        B2_CUDA( cudaStreamWaitEvent( t.sideStream, t.evFork, 0 ) );
+        fwnEstimates( t.sideStream );
+        B2_CUDA( cudaEventRecord( t.evJoin, t.sideStream ) );
+    }
     if ( band )
     {
         kBrickCull<<<nb256, 256, 0, st>>>( t.nodes, P, costD, totals );
@@ -902,14 +921,7 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
             oD.heavy = heavyD; oD.count = counts; oD.cls = clsD; oD.cap = cap;
         }
     }
-    if ( order )
-    {
-        const int gX = ( P.bricksX + GRP - 1 ) / GRP, gY = ( P.bricksY + GRP - 1 ) / GRP, gZ = ( P.bricksZ + GRP - 1 ) / GRP;
-        kGroupCostFwn<<<(unsigned)( ( (size_t)gX * gY * gZ + 255 ) / 256 ), 256, 0, st>>>( t.nodes, P, gX, gY, gZ, costF, totals + 2 );
-        kGroupHeavy<<<nb256, 256, 0, st>>>( t.nodes, costF, P, gX, gY, totals + 2, heavyF, counts + 1, clsF, cap );
-        if ( launches ) *launches += 2;
-        oF.heavy = heavyF; oF.count = counts + 1; oF.cls = clsF; oF.cap = cap;
-    }
+    if ( order && !sideEst ) fwnEstimates( st );
     const uint16_t* cullCost = band ? costD : nullptr;
     auto blocksFor = [&]( const BrickOrder& o ) { return (unsigned)( ( numBricks + o.cap + GRID_TB / 32 - 1 ) / ( GRID_TB / 32 ) ); };
     if ( wantStats )
@@ -938,6 +950,7 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
             if ( aa ) kGridDist<true, false><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, nullptr );
             else kGridDist<false, false><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, nullptr );
         }
+        if ( sideEst ) B2_CUDA( cudaStreamWaitEvent( st, t.evJoin, 0 ) );
         PeerOut po{};
         if ( peers && peers->n > 0 )
         {

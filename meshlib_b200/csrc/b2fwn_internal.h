@@ -69,6 +69,9 @@ struct DeviceTree
     TravNode* nodes = nullptr;   // numNodes
     LeafTri* leafTris = nullptr; // numLeaves, in pre-order leaf order
     LeafFilt* leafFilt = nullptr; // numLeaves, same order
+    // high-priority side stream of the grid launcher (walk-length estimates beside the distance kernels), forked / joined by events
+    cudaStream_t sideStream = nullptr;
+    cudaEvent_t evFork = nullptr, evJoin = nullptr;
 };
 
 struct GridXf

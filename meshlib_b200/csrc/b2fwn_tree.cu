@@ -416,6 +416,9 @@ void freeTree( DeviceTree& t )
 {
     cudaFree( t.points ); cudaFree( t.tris ); cudaFree( t.refNodes ); cudaFree( t.refDipoles );
     cudaFree( t.nodes ); cudaFree( t.leafTris ); cudaFree( t.leafFilt );
+    if ( t.sideStream ) cudaStreamDestroy( t.sideStream );
+    if ( t.evFork ) cudaEventDestroy( t.evFork );
+    if ( t.evJoin ) cudaEventDestroy( t.evJoin );
     t = DeviceTree{};
 }
 
@@ -424,6 +427,14 @@ int buildTree( DeviceTree& t, cudaStream_t st, uint64_t* launches )
     uint64_t nl = 0;
     const size_t F = t.numFaces;
     t.numLeaves = t.numNodes = 0; t.depth = 0;
+    if ( !t.sideStream )
+    {
+        int lo = 0, hi = 0;
+        B2_CUDA( cudaDeviceGetStreamPriorityRange( &lo, &hi ) ); // hi = greatest priority (numerically lowest)
+        B2_CUDA( cudaStreamCreateWithPriority( &t.sideStream, cudaStreamNonBlocking, hi ) );
+        B2_CUDA( cudaEventCreateWithFlags( &t.evFork, cudaEventDisableTiming ) );
+        B2_CUDA( cudaEventCreateWithFlags( &t.evJoin, cudaEventDisableTiming ) );
+    }
     if ( F == 0 ) return B2FWN_OK;
     if ( F > (size_t)0x3FFFFFFF ) { setError( "too many faces" ); return B2FWN_ERR_INVALID; }
 
