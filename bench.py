@@ -51,8 +51,8 @@ DEFAULT_WORKLOAD = "c5_band"
 # DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of ONE launch of the dominant kernel (kGridFwn5, whole grid on one
 # GPU) from an `ncu --set full` capture on B200; not measurable inside a timed run, so quoted from the committed capture
 NCU_TRAFFIC = {
-    "c5_band": (41.637380e9 + 34.415310e9, "profiles/r01/ncu_full_kGridFwn5_c5_band_v5.csv"),
-    "c3_band": (1.003856e9 + 0.503436e9, "profiles/r01/ncu_full_kGridDist_kGridFwn5_c3_band_v5.csv"),
+    "c5_band": (41.609227e9 + 34.414311e9, "profiles/r01/ncu_full_kGridFwn5_c5_band_v6.csv"),
+    "c3_band": (1.002902e9 + 0.504868e9, "profiles/r01/ncu_full_kGridDist_kGridFwn5_c3_band_v6.csv"),
 }
 
 

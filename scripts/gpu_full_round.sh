@@ -21,4 +21,8 @@ tail -3 gpurun_out/ncu_full_$WL.log
 ncu --set full --clock-control none --import-source on -k regex:kGridFwn5 -c 1 -f -o gpurun_out/prof_c5_band_fwn5 python bench.py --workload c5_band --steps 1 --warmup 0 --no-e2e --no-cpu > gpurun_out/ncu_full_c5_band.log 2>&1
 tail -2 gpurun_out/ncu_full_c5_band.log
 python scripts/diag_queries.py > gpurun_out/diag_queries.txt 2>&1; tail -2 gpurun_out/diag_queries.txt
+python scripts/diag_project.py > gpurun_out/diag_project.txt 2>&1; tail -2 gpurun_out/diag_project.txt
+python scripts/diag_e2e.py c5_band > gpurun_out/diag_e2e_c5.txt 2>&1; tail -3 gpurun_out/diag_e2e_c5.txt
+ncu --set full --clock-control none --import-source on -k regex:kFindProjections -c 1 -f -o gpurun_out/prof_project python scripts/diag_project.py > gpurun_out/ncu_full_project.log 2>&1
+tail -2 gpurun_out/ncu_full_project.log
 ls -la gpurun_out
