@@ -578,7 +578,7 @@ int b2fwn_calc_from_grid( b2fwn_handle h, const int32_t dims[3], const float xf[
 {
     if ( !h || !dims || !xf ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
     if ( dims[0] < 0 || dims[1] < 0 || dims[2] < 0 ) { setError( "invalid grid dimensions" ); return B2FWN_ERR_INVALID; }
-    if ( (size_t)dims[0] * dims[1] * dims[2] && !out ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    if ( (size_t)dims[0] * dims[1] * dims[2] != 0 && !out ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
     B2_CUDA( cudaSetDevice( h->device ) );
     const GridXf g = toXf( xf );
     return runChunked( h, dims, 0, dims[2], 0, 0, out, nullptr, nullptr, cb, user, [&]( int z0, int z1, float* d, cudaStream_t st )
@@ -592,7 +592,7 @@ int b2fwn_calc_from_grid_with_distances_layers( b2fwn_handle h, const int32_t di
     if ( !h || !dims || !xf || !opt ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
     if ( dims[0] < 0 || dims[1] < 0 || dims[2] < 0 ) { setError( "invalid grid dimensions" ); return B2FWN_ERR_INVALID; }
     if ( zBegin < 0 || zEnd > dims[2] || zBegin > zEnd ) { setError( "invalid layer range" ); return B2FWN_ERR_INVALID; }
-    if ( (size_t)dims[0] * dims[1] * ( zEnd - zBegin ) && !out ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    if ( (size_t)dims[0] * dims[1] * ( zEnd - zBegin ) != 0 && !out ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
     B2_CUDA( cudaSetDevice( h->device ) );
     const GridXf g = toXf( xf );
     const b2fwn_dist_options o = *opt;
@@ -667,7 +667,7 @@ int b2fwn_mesh_to_distance_volume( b2fwn_handle h, const b2fwn_volume_params* vo
     const int32_t* dims = vol->dims;
     int rc = B2FWN_ERR_INVALID;
     if ( dims[0] < 0 || dims[1] < 0 || dims[2] < 0 ) setError( "invalid grid dimensions" );
-    else if ( (size_t)dims[0] * dims[1] * dims[2] && !out ) setError( "null argument" );
+    else if ( (size_t)dims[0] * dims[1] * dims[2] != 0 && !out ) setError( "null argument" );
     else
         rc = runChunked( h, dims, 0, dims[2], 0, 0, out, nullptr, nullptr, cb, user, [&]( int z0, int z1, float* d, cudaStream_t st )
         {
