@@ -267,11 +267,31 @@ def run_ours(args, wl):
     p2p = world > 1 and args.gather == "p2p"
     peer_ptrs, my_ptr = [], None
     if p2p:
-        # peer-visible volumes: every rank maps the volumes of the others; the kernels store each result into all of them
-        my_ptr, token = fwn.shared_alloc(4 * total)
+        # peer-visible volumes: every rank maps the volumes of the others; the kernels store each result into all of them.
+        # Where CUDA IPC / peer access is not available (some container set-ups) every rank falls back to the NCCL gather.
+        ok, err, token = 1, "", b""
+        try:
+            my_ptr, token = fwn.shared_alloc(4 * total)
+        except mb.B2Error as e:
+            ok, err = 0, str(e)
         tokens = [None] * world
-        dist.all_gather_object(tokens, token)
-        peer_ptrs = [fwn.shared_open(tokens[r]) for r in range(world) if r != rank]
+        dist.all_gather_object(tokens, (ok, token))
+        if all(t[0] for t in tokens):
+            try:
+                peer_ptrs = [fwn.shared_open(tokens[r][1]) for r in range(world) if r != rank]
+            except mb.B2Error as e:
+                ok, err = 0, str(e)
+        flag = torch.tensor([ok], dtype=torch.int32, device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag[0]) == 0:
+            if rank == 0:
+                print(f"bench.py: peer-mapped volumes unavailable ({err or 'another rank failed'}); using --gather nccl", file=sys.stderr)
+            for q in peer_ptrs:
+                fwn.shared_close(q)
+            if my_ptr:
+                fwn.shared_free(my_ptr)
+            p2p, peer_ptrs, my_ptr = False, [], None
+    if p2p:
         volume = torch.as_tensor(mb.DeviceBuffer(my_ptr, total), device=dev)
     else:
         volume = torch.empty(total, dtype=torch.float32, device=dev)
