@@ -162,6 +162,21 @@ int b2fwn_calc_from_grid_with_distances_layers( b2fwn_handle h, const int32_t di
                                                 const b2fwn_dist_options* opt, int32_t z_begin, int32_t z_end, float* out,
                                                 b2fwn_progress cb, void* user );
 
+/* makeSignedByWindingNumber (source/MRVoxels/MRVDBConversions.cpp:491-568), the consumer of calcFromGrid[ByParts] behind the
+ * Smooth offset mode and doubleOffsetVdb: a dense volume of unsigned distances (dims voxels, x fastest; voxel (x,y,z) sits
+ * at grid_to_mesh_xf * (x,y,z)) gets the sign of the generalized winding number: volume[i] = -volume[i] where
+ * w(voxel i) > winding_number_threshold (MRVDBConversions.cpp:527-533).  The reference moves 4 B/voxel of winding numbers
+ * to the host and walks the grid again on the CPU; here the volume is updated in place by the winding-number kernel, the
+ * numbers never exist in memory.  NaN voxels stay as they are.  _device: d_volume is device memory of the handle's device
+ * and the layers [z_begin, z_end) are updated (d_volume points at layer z_begin); the host form streams the volume through
+ * the device in z-chunks (H2D, kernel, D2H overlapped). */
+int b2fwn_make_signed_by_winding_number_device( b2fwn_handle h, const int32_t dims[3], const float grid_to_mesh_xf[12],
+                                                float winding_number_beta, float winding_number_threshold,
+                                                int32_t z_begin, int32_t z_end, float* d_volume_at_z_begin );
+int b2fwn_make_signed_by_winding_number( b2fwn_handle h, const int32_t dims[3], const float grid_to_mesh_xf[12],
+                                         float winding_number_beta, float winding_number_threshold, float* volume,
+                                         b2fwn_progress cb, void* user );
+
 /* IFastWindingNumberByParts::calcFromGridByParts / calcFromGridWithDistancesByParts
  * (MRFastWindingNumber.h:96-106; GPU MRCudaFastWindingNumber.cpp:285-429).  Parts are whole z-layers, delivered
  * strictly in increasing z on the calling thread, consecutive parts overlapping by layer_overlap layers

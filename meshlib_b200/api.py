@@ -93,6 +93,7 @@ EXPORTS = [
     "b2fwn_calc_from_grid_with_distances_by_parts", "b2fwn_get_tree", "b2fwn_get_stats", "b2fwn_marching_cubes",
     "b2fwn_marching_cubes_fetch", "b2fwn_calc_from_grid_with_distances_layers", "b2fwn_measure_fp32_peak",
     "b2fwn_get_bounding_box", "b2fwn_mesh_to_distance_volume", "b2fwn_mc_offset_mesh",
+    "b2fwn_make_signed_by_winding_number", "b2fwn_make_signed_by_winding_number_device",
 ]
 
 
@@ -133,6 +134,8 @@ def load_library():
     L.b2fwn_shared_free.argtypes = [vp, vp]
     L.b2fwn_calc_from_grid_with_distances_layers.argtypes = [vp, i32p, f32p, C.POINTER(DistOptions), C.c_int32, C.c_int32,
                                                              vp, PROGRESS_CB, vp]
+    L.b2fwn_make_signed_by_winding_number_device.argtypes = [vp, i32p, f32p, C.c_float, C.c_float, C.c_int32, C.c_int32, vp]
+    L.b2fwn_make_signed_by_winding_number.argtypes = [vp, i32p, f32p, C.c_float, C.c_float, vp, PROGRESS_CB, vp]
     L.b2fwn_measure_fp32_peak.argtypes = [C.c_int32, C.POINTER(C.c_double)]
     L.b2fwn_calc_from_grid_by_parts.argtypes = [vp, i32p, f32p, C.c_float, C.c_int32, C.c_int32, PART_CB, vp,
                                                 PROGRESS_CB, vp]
@@ -254,6 +257,26 @@ class FastWindingNumber:
         _check(_lib.b2fwn_calc_from_grid_with_distances_layers(self._h, _dims(dims), _xf(grid_to_mesh_xf), C.byref(options),
                                                                z_begin, z_end, res.ctypes.data, _progress(cb), None))
         return res
+
+    # ---- makeSignedByWindingNumber (MRVDBConversions.cpp:491-568): sign of a dense unsigned distance volume ----
+    def make_signed_by_winding_number(self, volume, dims, grid_to_mesh_xf, winding_number_threshold=0.5,
+                                      winding_number_beta=2.0, cb=None):
+        """negates, in place, the values of the voxels whose winding number exceeds the threshold; `volume` is a
+        C-contiguous float32 host array of dims[0]*dims[1]*dims[2] values (x fastest), streamed through the device"""
+        n = int(dims[0]) * int(dims[1]) * int(dims[2])
+        if not (isinstance(volume, np.ndarray) and volume.dtype == np.float32 and volume.flags.c_contiguous
+                and volume.flags.writeable and volume.size == n):
+            raise ValueError("volume must be a writeable C-contiguous float32 array of dims[0]*dims[1]*dims[2] values")
+        _check(_lib.b2fwn_make_signed_by_winding_number(self._h, _dims(dims), _xf(grid_to_mesh_xf), winding_number_beta,
+                                                        winding_number_threshold, volume.ctypes.data, _progress(cb), None))
+        return volume
+
+    def make_signed_by_winding_number_device(self, d_volume_at_z_begin, dims, grid_to_mesh_xf, winding_number_threshold=0.5,
+                                             winding_number_beta=2.0, z_begin=0, z_end=None):
+        """the same on a volume resident in device memory (pointer to layer z_begin), layers [z_begin, z_end)"""
+        z_end = dims[2] if z_end is None else z_end
+        _check(_lib.b2fwn_make_signed_by_winding_number_device(self._h, _dims(dims), _xf(grid_to_mesh_xf), winding_number_beta,
+                                                               winding_number_threshold, z_begin, z_end, d_volume_at_z_begin))
 
     # ---- IFastWindingNumberByParts ----
     def _part_cb(self, res_func):

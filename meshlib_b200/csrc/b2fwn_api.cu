@@ -607,6 +607,46 @@ int b2fwn_calc_from_grid_with_distances( b2fwn_handle h, const int32_t dims[3], 
     return b2fwn_calc_from_grid_with_distances_layers( h, dims, xf, opt, 0, dims[2], out, cb, user );
 }
 
+// ---- makeSignedByWindingNumber: sign of a resident / streamed unsigned distance volume -----------------------------------
+
+int b2fwn_make_signed_by_winding_number_device( b2fwn_handle h, const int32_t dims[3], const float xf[12], float beta,
+                                                float threshold, int32_t zBegin, int32_t zEnd, float* dVolumeAtZBegin )
+{
+    if ( !h || !dims || !xf ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    if ( dims[0] < 0 || dims[1] < 0 || dims[2] < 0 || zBegin < 0 || zEnd > dims[2] || zBegin > zEnd )
+    {
+        setError( "invalid grid dimensions" );
+        return B2FWN_ERR_INVALID;
+    }
+    if ( (size_t)dims[0] * dims[1] * ( zEnd - zBegin ) != 0 && !dVolumeAtZBegin ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    KernelTimer tm( h );
+    if ( int e = launchSignGrid( h->tree, dims, toXf( xf ), beta, threshold, zBegin, zEnd, dVolumeAtZBegin, h->stream,
+                                 &h->stats.kernel_launches ) )
+        return e;
+    tm.stop();
+    B2_CUDA( cudaStreamSynchronize( h->stream ) );
+    return B2FWN_OK;
+}
+
+int b2fwn_make_signed_by_winding_number( b2fwn_handle h, const int32_t dims[3], const float xf[12], float beta, float threshold,
+                                         float* volume, b2fwn_progress cb, void* user )
+{
+    if ( !h || !dims || !xf ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    if ( dims[0] < 0 || dims[1] < 0 || dims[2] < 0 ) { setError( "invalid grid dimensions" ); return B2FWN_ERR_INVALID; }
+    if ( (size_t)dims[0] * dims[1] * dims[2] != 0 && !volume ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    const GridXf g = toXf( xf );
+    const size_t layer = (size_t)dims[0] * dims[1];
+    // chunk k: H2D on its compute stream, walk, D2H (runChunked) back to where it came from; the slot is free again by then
+    return runChunked( h, dims, 0, dims[2], 0, 0, volume, nullptr, nullptr, cb, user, [&]( int z0, int z1, float* d, cudaStream_t st )
+    {
+        B2_CUDA( cudaMemcpyAsync( d, volume + (size_t)z0 * layer, (size_t)( z1 - z0 ) * layer * sizeof( float ), cudaMemcpyHostToDevice, st ) );
+        // d holds the layers z0..z1 (its first float is voxel (0,0,z0)), like every slab the grid launchers write
+        return launchSignGrid( h->tree, dims, g, beta, threshold, z0, z1, d, st, &h->stats.kernel_launches );
+    } );
+}
+
 // ---- callers moved onto the device: meshToDistanceVolume, mcOffsetMesh --------------------------------------------------
 
 namespace

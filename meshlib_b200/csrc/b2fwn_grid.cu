@@ -824,11 +824,15 @@ void printStats( const char* what, const unsigned long long* h, double voxels, d
     fprintf( stderr, "\n" );
 }
 
-// MODE 0: winding numbers only; MODE 1: distance walk, then winding-number walk over the same slab
+// MODE 0: winding numbers only; MODE 1: distance walk, then winding-number walk over the same slab.
+// signOnly (MODE 1): the slab already holds (unsigned) distances -- no distance walk, the winding-number walk alone negates
+// the values of the voxels with w > threshold (NaN voxels are left as they are and are not walked)
 template <int MODE>
 int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, float beta, const b2fwn_dist_options* opt,
-                int zBegin, int zEnd, const ZChunks* zc, const PeerOut* peers, float* dOut, cudaStream_t st, uint64_t* launches )
+                int zBegin, int zEnd, const ZChunks* zc, const PeerOut* peers, float* dOut, cudaStream_t st, uint64_t* launches,
+                const bool signOnly = false )
 {
+    const bool distPass = MODE == 1 && !signOnly;
     if ( int e = checkDims( dims, zBegin, zEnd ) ) return e;
     if ( peers && peers->n > 0 && getenv( "B2FWN_STATS" ) ) { setError( "peer output is not available in stats mode" ); return B2FWN_ERR_INVALID; }
     if ( dims[0] == 0 || dims[1] == 0 || zEnd == zBegin ) return B2FWN_OK;
@@ -866,7 +870,7 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
     const bool aa = xf.A[1] == 0 && xf.A[2] == 0 && xf.A[3] == 0 && xf.A[5] == 0 && xf.A[6] == 0 && xf.A[7] == 0;
     static const bool wantStats = getenv( "B2FWN_STATS" ) != nullptr;
     static const bool heavyFirst = !( getenv( "B2FWN_LINEAR" ) && atoi( getenv( "B2FWN_LINEAR" ) ) ); // dev switch: plain linear order
-    const bool band = MODE == 1 && P.maxDistSq < FLT_MAX && P.numNodes > 0;
+    const bool band = distPass && P.maxDistSq < FLT_MAX && P.numNodes > 0;
     // small grids (c1: 16,384 bricks, 6.4 ms) lose more to the estimate kernels than a tail can cost them
     const bool order = heavyFirst && !wantStats && P.numNodes > 0 && numBricks >= ( 1u << 16 ) && numBricks <= 0xFFFFFFFFull;
 
@@ -894,7 +898,7 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
     // The winding-number estimates do not depend on the distance kernels: with distances (MODE 1) they run on the tree's
     // high-priority side stream beside kBrickCull / kGridDist and are joined before kGridFwn5 -- their cost is latency (one
     // thread walks up to COST_MAX nodes), not throughput, and per launch: the host-output calls pay it once per chunk.
-    const bool sideEst = order && MODE == 1 && t.sideStream;
+    const bool sideEst = order && distPass && t.sideStream;
     auto fwnEstimates = [&]( cudaStream_t es )
     {
         const int gX = ( P.bricksX + GRP - 1 ) / GRP, gY = ( P.bricksY + GRP - 1 ) / GRP, gZ = ( P.bricksZ + GRP - 1 ) / GRP;
@@ -929,7 +933,7 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
         unsigned long long* dStats = nullptr; unsigned long long h[2 * STAT_WORDS];
         B2_CUDA( cudaMalloc( &dStats, sizeof( h ) ) );
         B2_CUDA( cudaMemsetAsync( dStats, 0, sizeof( h ), st ) );
-        if ( MODE == 1 )
+        if ( distPass )
         {
             if ( aa ) kGridDist<true, true><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, dStats );
             else kGridDist<false, true><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, dStats );
@@ -940,12 +944,12 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
         B2_CUDA( cudaStreamSynchronize( st ) );
         cudaFree( dStats );
         const double nv = (double)dims[0] * dims[1] * P.nz, nb = (double)numBricks;
-        if ( MODE == 1 ) printStats( "dist", h, nv, nb );
+        if ( distPass ) printStats( "dist", h, nv, nb );
         printStats( "fwn ", h + STAT_WORDS, nv, nb );
     }
     else
     {
-        if ( MODE == 1 )
+        if ( distPass )
         {
             if ( aa ) kGridDist<true, false><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, nullptr );
             else kGridDist<false, false><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, nullptr );
@@ -963,7 +967,7 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
         else if ( aa ) kGridFwn5<MODE, true, false><<<blocksFor( oF ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, oF, po );
         else kGridFwn5<MODE, false, false><<<blocksFor( oF ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, oF, po );
     }
-    if ( launches ) *launches += ( MODE == 1 ? 2 : 1 );
+    if ( launches ) *launches += ( distPass ? 2 : 1 );
     static const bool debugOrder = getenv( "B2FWN_DEBUG" ) != nullptr;
     if ( debugOrder && scratch )
     {
@@ -991,6 +995,17 @@ int launchSdfGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf,
                    int zBegin, int zEnd, float* dOut, cudaStream_t st, uint64_t* launches, const ZChunks* zc, const PeerOut* peers )
 {
     return launchGrid<1>( t, dims, xf, opt.winding_number_beta, &opt, zBegin, zEnd, zc, peers, dOut, st, launches );
+}
+
+// In-place sign of a distance slab: value -> -value where the winding number of the voxel exceeds the threshold
+// (the per-voxel update of makeSignedByWindingNumber, source/MRVoxels/MRVDBConversions.cpp:517-533)
+int launchSignGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, float beta, float threshold, int zBegin, int zEnd,
+                    float* dVolumeAtZBegin, cudaStream_t st, uint64_t* launches )
+{
+    b2fwn_dist_options o{};
+    o.min_dist_sq = 0; o.max_dist_sq = FLT_MAX; o.null_outside_min_max = 0;
+    o.winding_number_threshold = threshold; o.winding_number_beta = beta;
+    return launchGrid<1>( t, dims, xf, beta, &o, zBegin, zEnd, nullptr, nullptr, dVolumeAtZBegin, st, launches, true );
 }
 
 } // namespace b2

@@ -116,6 +116,9 @@ struct PeerOut
 int launchSdfGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, const b2fwn_dist_options& opt,
                    int zBegin, int zEnd, float* dOut, cudaStream_t stream, uint64_t* launches, const ZChunks* zc = nullptr,
                    const PeerOut* peers = nullptr );
+// slab of (unsigned) distances -> negated in place where the voxel's winding number exceeds the threshold
+int launchSignGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, float beta, float threshold, int zBegin, int zEnd,
+                    float* dVolumeAtZBegin, cudaStream_t stream, uint64_t* launches );
 
 // closest point with face and barycentrics (b2fwn_project.cu) -----------------------------------------------------------
 int launchFindProjections( const DeviceTree& t, const float* dPts, size_t n, const float* pointXf12, const float* treeXf12,

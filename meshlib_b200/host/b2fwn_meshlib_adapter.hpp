@@ -118,6 +118,21 @@ public:
         return ctx.error.empty() ? status_( rc ) : unexpected( ctx.error );
     }
 
+    /// Beyond the interface: the dense loop of makeSignedByWindingNumber (source/MRVoxels/MRVDBConversions.cpp:
+    /// 517-568) in one call.  `volume` holds dims.x*dims.y*dims.z unsigned distances (x fastest, the VolumeIndexer order of
+    /// the reference loop); every voxel whose winding number exceeds windingNumberThreshold is negated in place.  The
+    /// winding numbers are never stored: no 4 B/voxel D2H + second pass over the grid as with calcFromGrid[ByParts].
+    Expected<void> makeSignedByWindingNumber( float* volume, const Vector3i& dims, const AffineXf3f& gridToMeshXf,
+                                              float windingNumberThreshold, float windingNumberBeta, const ProgressCallback& cb = {} )
+    {
+        if ( auto e = prepare_(); !e ) return e;
+        const int32_t d[3] = { dims.x, dims.y, dims.z };
+        float xf[12];
+        packXf_( gridToMeshXf, xf );
+        return status_( b2fwn_make_signed_by_winding_number( h_, d, xf, windingNumberBeta, windingNumberThreshold, volume,
+                                                              &progress_, (void*)&cb ) );
+    }
+
 private:
     struct PartCtx
     {

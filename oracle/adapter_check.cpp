@@ -124,6 +124,30 @@ int main()
     auto c = ours->calcFromGridWithDistances( da, dims, basis, opt, []( float ) { return false; } );
     check( !c.has_value() && c.error() == "Operation was canceled", "cancel.error_string" );
 
+    // makeSignedByWindingNumber: the reference's dense loop -- calcFromGrid, then negate every voxel with
+    // w > threshold (MRVDBConversions.cpp:527-533, 552-565) -- against the one in-place call of our class
+    {
+        auto b200 = std::dynamic_pointer_cast<B200::FastWindingNumber>( ours );
+        std::vector<float> ua( db.size() ), ub( db.size() );
+        for ( size_t i = 0; i < db.size(); ++i ) ua[i] = ub[i] = std::abs( db[i] );
+        const float thr = 0.4f, beta = 2.5f;
+        std::vector<float> w;
+        (void)ref.calcFromGrid( w, dims, basis, beta, {} );
+        for ( size_t i = 0; i < ub.size(); ++i )
+            if ( w[i] > thr ) ub[i] = -ub[i];
+        check( b200 && b200->makeSignedByWindingNumber( ua.data(), dims, basis, thr, beta ).has_value(), "makeSignedByWindingNumber.call" );
+        size_t mism = 0, inBand = 0, magDiff = 0, negatives = 0;
+        for ( size_t i = 0; i < ub.size(); ++i )
+        {
+            if ( std::abs( ua[i] ) != std::abs( ub[i] ) ) ++magDiff;
+            if ( ua[i] < 0 ) ++negatives;
+            if ( std::abs( w[i] - thr ) < 1e-3f ) { ++inBand; continue; }
+            if ( ( ua[i] < 0 ) != ( ub[i] < 0 ) ) ++mism;
+        }
+        std::printf( "makeSignedByWindingNumber.sign_mismatch_outside_band %zu in_band %zu magnitude_changed %zu negatives %zu\n", mism, inBand, magDiff, negatives );
+        check( mism == 0 && magDiff == 0 && negatives > 0, "makeSignedByWindingNumber.parity" );
+    }
+
     // IPointsToMeshProjector: our back-end against the reference's CPU class through the interface pointer,
     // the way findSignedDistances receives it (MRPointsToMeshProjector.cpp:35-62); rigid and non-rigid transform cases
     {

@@ -80,6 +80,18 @@ def ref_mesh_to_distance_volume(orc, origin, voxel_size, dims, **opts):
     return data, (float(data[ok].min()) if ok.any() else float(fmax)), (float(data[ok].max()) if ok.any() else float(-fmax))
 
 
+def ref_make_signed_by_winding_number(orc, volume, dims, xf, threshold=0.5, beta=2.0):
+    """MR::makeSignedByWindingNumber on a dense grid (source/MRVoxels/MRVDBConversions.cpp:491-568): winding numbers of all
+    voxels from the oracle's calcFromGrid (:552-556), then `val = -val` for every voxel with windVal > threshold (:527-533).
+    The OpenVDB plumbing around that loop (dense fill, accessors, prune) cannot be built here and has no arithmetic.
+    Returns (signed copy of the volume, winding numbers)."""
+    w = np.asarray(orc.calc_from_grid(dims, xf, beta=beta), np.float32)
+    out = np.array(volume, np.float32, copy=True).reshape(-1)
+    flip = w > np.float32(threshold)
+    out[flip] = -out[flip]
+    return out, w
+
+
 def ref_offset_grid(points, tris, offset, voxel_size):
     """grid of mcOffsetMesh: bbox.expanded(|offset|) -> calcOriginAndDimensions (source/MRVoxels/MROffset.cpp:163-165,
     MRCalcDims.h:18-27), in float32 like the reference"""
