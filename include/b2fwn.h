@@ -177,6 +177,19 @@ int b2fwn_make_signed_by_winding_number( b2fwn_handle h, const int32_t dims[3], 
                                          float winding_number_beta, float winding_number_threshold, float* volume,
                                          b2fwn_progress cb, void* user );
 
+/* SignDetectionMode::ProjectionNormal: signedDistanceToMesh (source/MRMesh/MRMeshDistance.cpp:13-59) for n points --
+ * the closest point of the mesh by the reference's own search order, then the sign of
+ * dot( closest - point, pseudonormal at the closest point ) (Mesh::isOutsideByProjNorm, source/MRMesh/MRMesh.cpp:165-168;
+ * pseudonormal of a face, an edge or a vertex by TriPoint::onEdge / inVertex, source/MRMesh/MRMeshMath.cpp:510-557).
+ * out[i] = signed distance, quiet NaN when null_outside_min_max and the squared distance is outside [min_dist_sq, max_dist_sq)
+ * (or the mesh has no face).  Without null_outside_min_max the limits are ignored, as in the reference (:19-24).
+ * winding_number_* of the options are not used.  Edge and vertex pseudonormals are built on the device from the
+ * triangulation at the first call (no half-edge topology is needed). */
+int b2fwn_signed_distances_by_projection_normal( b2fwn_handle h, const float* points_xyz, size_t n, const b2fwn_dist_options* opt,
+                                                 float* out, b2fwn_progress cb, void* user );
+int b2fwn_signed_distances_by_projection_normal_device( b2fwn_handle h, const float* d_points_xyz, size_t n,
+                                                        const b2fwn_dist_options* opt, float* d_out );
+
 /* IFastWindingNumberByParts::calcFromGridByParts / calcFromGridWithDistancesByParts
  * (MRFastWindingNumber.h:96-106; GPU MRCudaFastWindingNumber.cpp:285-429).  Parts are whole z-layers, delivered
  * strictly in increasing z on the calling thread, consecutive parts overlapping by layer_overlap layers
@@ -236,6 +249,13 @@ typedef struct b2fwn_volume_params
  * (FLT_MAX / -FLT_MAX when there is none, as MinMaxArg's initial state) */
 int b2fwn_mesh_to_distance_volume( b2fwn_handle h, const b2fwn_volume_params* vol, const b2fwn_dist_options* opt, float* out,
                                    float* out_min, float* out_max, b2fwn_progress cb, void* user );
+
+/* MR::meshToDistanceVolume with SignDetectionMode::ProjectionNormal (MRMeshToDistanceVolume.cpp:64-91 + signedDistanceToMesh):
+ * voxel centres origin + voxel_size * ( pos + 0.5 ) exactly as meshToDistanceFunctionVolume computes them (:83-84), generated
+ * on the device; same outputs as b2fwn_mesh_to_distance_volume */
+int b2fwn_mesh_to_distance_volume_by_projection_normal( b2fwn_handle h, const b2fwn_volume_params* vol,
+                                                        const b2fwn_dist_options* opt, float* out, float* out_min, float* out_max,
+                                                        b2fwn_progress cb, void* user );
 
 /* MR::mcOffsetMesh / generalOffsetMesh( Mode::Standard ) with SignDetectionMode::HoleWindingRule
  * (source/MRVoxels/MROffset.cpp:117-246, grid by calcOriginAndDimensions, source/MRVoxels/MRCalcDims.h:18-27):

@@ -94,6 +94,8 @@ EXPORTS = [
     "b2fwn_marching_cubes_fetch", "b2fwn_calc_from_grid_with_distances_layers", "b2fwn_measure_fp32_peak",
     "b2fwn_get_bounding_box", "b2fwn_mesh_to_distance_volume", "b2fwn_mc_offset_mesh",
     "b2fwn_make_signed_by_winding_number", "b2fwn_make_signed_by_winding_number_device",
+    "b2fwn_signed_distances_by_projection_normal", "b2fwn_signed_distances_by_projection_normal_device",
+    "b2fwn_mesh_to_distance_volume_by_projection_normal",
 ]
 
 
@@ -149,6 +151,10 @@ def load_library():
     L.b2fwn_mesh_to_distance_volume.argtypes = [vp, C.POINTER(VolumeParams), C.POINTER(DistOptions), vp, f32p, f32p,
                                                 PROGRESS_CB, vp]
     L.b2fwn_mc_offset_mesh.argtypes = [vp, C.POINTER(OffsetParams), C.POINTER(OffsetResult), PROGRESS_CB, vp]
+    L.b2fwn_signed_distances_by_projection_normal.argtypes = [vp, vp, C.c_size_t, C.POINTER(DistOptions), vp, PROGRESS_CB, vp]
+    L.b2fwn_signed_distances_by_projection_normal_device.argtypes = [vp, vp, C.c_size_t, C.POINTER(DistOptions), vp]
+    L.b2fwn_mesh_to_distance_volume_by_projection_normal.argtypes = [vp, C.POINTER(VolumeParams), C.POINTER(DistOptions), vp,
+                                                                     f32p, f32p, PROGRESS_CB, vp]
     _lib = L
     return L
 
@@ -417,6 +423,35 @@ class FastWindingNumber:
         lo, hi = C.c_float(), C.c_float()
         _check(_lib.b2fwn_mesh_to_distance_volume(self._h, C.byref(vp_), C.byref(options), res.ctypes.data, C.byref(lo),
                                                   C.byref(hi), _progress(cb), None))
+        return res, lo.value, hi.value
+
+    # ---- SignDetectionMode::ProjectionNormal (signedDistanceToMesh, source/MRMesh/MRMeshDistance.cpp:13-59) ----
+    def signed_distances_by_projection_normal(self, points, options=None, cb=None):
+        """distance to the closest point of the mesh for each point, negative where the pseudonormal at the closest point
+        says inside; NaN outside [min_dist_sq, max_dist_sq) when options.null_outside_min_max"""
+        options = options or DistOptions()
+        pts = np.ascontiguousarray(points, np.float32).reshape(-1, 3)
+        res = np.empty(len(pts), np.float32)
+        _check(_lib.b2fwn_signed_distances_by_projection_normal(self._h, pts.ctypes.data, len(pts), C.byref(options),
+                                                                res.ctypes.data, _progress(cb), None))
+        return res
+
+    def signed_distances_by_projection_normal_device(self, d_points_ptr, n, d_out_ptr, options=None):
+        options = options or DistOptions()
+        _check(_lib.b2fwn_signed_distances_by_projection_normal_device(self._h, d_points_ptr, n, C.byref(options), d_out_ptr))
+
+    def mesh_to_distance_volume_by_projection_normal(self, origin, voxel_size, dims, options=None, cb=None):
+        """MR::meshToDistanceVolume with SignDetectionMode::ProjectionNormal; returns (data, min, max)"""
+        options = options or DistOptions()
+        vp_ = VolumeParams()
+        vp_.origin[:] = [float(x) for x in origin]
+        vs = np.asarray(voxel_size, np.float32) * np.ones(3, np.float32)
+        vp_.voxel_size[:] = [float(x) for x in vs]
+        vp_.dims[:] = [int(d) for d in dims]
+        res = np.empty(int(dims[0]) * int(dims[1]) * int(dims[2]), np.float32)
+        lo, hi = C.c_float(), C.c_float()
+        _check(_lib.b2fwn_mesh_to_distance_volume_by_projection_normal(self._h, C.byref(vp_), C.byref(options), res.ctypes.data,
+                                                                       C.byref(lo), C.byref(hi), _progress(cb), None))
         return res, lo.value, hi.value
 
     def mc_offset_mesh(self, offset, voxel_size, close_holes=True, threshold=0.5, beta=2.0, cb=None, fetch=True):

@@ -726,6 +726,123 @@ int b2fwn_mesh_to_distance_volume( b2fwn_handle h, const b2fwn_volume_params* vo
     return B2FWN_OK;
 }
 
+// ---- SignDetectionMode::ProjectionNormal: signedDistanceToMesh per point / per voxel centre -------------------------------
+
+namespace
+{
+// one batch of m points already on the device: scratch slot 0 = [ points 3m (padded) | records 8m | distances m ]
+struct ProjNormalBatch
+{
+    float* dPts; b2fwn_projection* dProj; float* dDist;
+};
+int projNormalBatch( b2fwn_ctx* h, size_t m, ProjNormalBatch& b )
+{
+    const size_t inFloats = ( 3 * m + 3 ) / 4 * 4; // records start 16-B aligned
+    if ( int e = ensureScratch( h, 0, inFloats + 8 * m + m ) ) return e;
+    b.dPts = h->dScratch[0];
+    b.dProj = reinterpret_cast<b2fwn_projection*>( h->dScratch[0] + inFloats );
+    b.dDist = h->dScratch[0] + inFloats + 8 * m;
+    return B2FWN_OK;
+}
+} // namespace
+
+int b2fwn_signed_distances_by_projection_normal_device( b2fwn_handle h, const float* dPts, size_t n, const b2fwn_dist_options* opt,
+                                                        float* dOut )
+{
+    if ( !h || !opt || ( n && ( !dPts || !dOut ) ) ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    if ( n == 0 ) return B2FWN_OK;
+    b2fwn_projection* dProj = nullptr;
+    B2_CUDA( cudaMallocAsync( &dProj, n * sizeof( b2fwn_projection ), h->stream ) );
+    KernelTimer tm( h );
+    const int e = launchSignedDistProjNormal( h->tree, dPts, n, opt->min_dist_sq, opt->max_dist_sq, opt->null_outside_min_max, dProj, dOut,
+                                              h->stream, &h->stats.kernel_launches );
+    if ( !e ) tm.stop();
+    cudaFreeAsync( dProj, h->stream );
+    B2_CUDA( cudaStreamSynchronize( h->stream ) );
+    return e;
+}
+
+int b2fwn_signed_distances_by_projection_normal( b2fwn_handle h, const float* pts, size_t n, const b2fwn_dist_options* opt, float* out,
+                                                 b2fwn_progress cb, void* user )
+{
+    if ( !h || !opt || ( n && ( !pts || !out ) ) ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    if ( !report( cb, user, 0.f ) ) return canceled();
+    if ( n == 0 ) return B2FWN_OK;
+    const size_t chunk = std::min<size_t>( n, (size_t)4 << 20 );
+    ProjNormalBatch b{};
+    if ( int e = projNormalBatch( h, chunk, b ) ) return e;
+    double kernelMs = 0;
+    for ( size_t o = 0; o < n; o += chunk )
+    {
+        const size_t m = std::min( chunk, n - o );
+        B2_CUDA( cudaMemcpyAsync( b.dPts, pts + 3 * o, m * 3 * sizeof( float ), cudaMemcpyHostToDevice, h->stream ) );
+        cudaEventRecord( h->evA, h->stream );
+        if ( int e = launchSignedDistProjNormal( h->tree, b.dPts, m, opt->min_dist_sq, opt->max_dist_sq, opt->null_outside_min_max, b.dProj,
+                                                 b.dDist, h->stream, &h->stats.kernel_launches ) ) return e;
+        cudaEventRecord( h->evB, h->stream );
+        B2_CUDA( cudaMemcpyAsync( out + o, b.dDist, m * sizeof( float ), cudaMemcpyDeviceToHost, h->stream ) );
+        B2_CUDA( cudaStreamSynchronize( h->stream ) );
+        float ms = 0;
+        if ( cudaEventElapsedTime( &ms, h->evA, h->evB ) == cudaSuccess ) kernelMs += ms;
+        if ( !report( cb, user, float( o + m ) / float( n ) ) ) return canceled();
+    }
+    h->stats.last_kernel_ms = kernelMs;
+    return B2FWN_OK;
+}
+
+int b2fwn_mesh_to_distance_volume_by_projection_normal( b2fwn_handle h, const b2fwn_volume_params* vol, const b2fwn_dist_options* opt,
+                                                        float* out, float* outMin, float* outMax, b2fwn_progress cb, void* user )
+{
+    if ( !h || !vol || !opt ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    const int32_t* dims = vol->dims;
+    if ( dims[0] < 0 || dims[1] < 0 || dims[2] < 0 ) { setError( "invalid grid dimensions" ); return B2FWN_ERR_INVALID; }
+    const size_t layer = (size_t)dims[0] * dims[1], total = layer * dims[2];
+    if ( total != 0 && !out ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    if ( !report( cb, user, 0.f ) ) return canceled();
+    unsigned mm[2] = { 0xFFFFFFFFu, 0u };
+    if ( total != 0 )
+    {
+        // whole layers, about 8 Mi voxels per batch (44 B of scratch per voxel)
+        const int layers = (int)std::min<size_t>( std::max<size_t>( ( (size_t)8 << 20 ) / layer, 1 ), (size_t)dims[2] );
+        if ( layer * layers > 0xFFFFFFFFull ) { setError( "grid layer too large" ); return B2FWN_ERR_INVALID; }
+        ProjNormalBatch b{};
+        if ( int e = projNormalBatch( h, layer * layers, b ) ) return e;
+        unsigned* dMM = nullptr;
+        B2_CUDA( cudaMalloc( &dMM, sizeof( mm ) ) );
+        cudaMemcpyAsync( dMM, mm, sizeof( mm ), cudaMemcpyHostToDevice, h->stream );
+        double kernelMs = 0;
+        int rc = B2FWN_OK;
+        for ( int z0 = 0; z0 < dims[2] && rc == B2FWN_OK; z0 += layers )
+        {
+            const int z1 = std::min( dims[2], z0 + layers );
+            const size_t m = layer * ( z1 - z0 );
+            cudaEventRecord( h->evA, h->stream );
+            rc = launchVoxelCentres( vol->origin, vol->voxel_size, dims[0], dims[1], z0, z1, b.dPts, h->stream, &h->stats.kernel_launches );
+            if ( !rc ) rc = launchSignedDistProjNormal( h->tree, b.dPts, m, opt->min_dist_sq, opt->max_dist_sq, opt->null_outside_min_max, b.dProj,
+                                                        b.dDist, h->stream, &h->stats.kernel_launches );
+            if ( rc ) break;
+            kMinMax<<<(unsigned)std::min<size_t>( ( m + 255 ) / 256, 148 * 8 ), 256, 0, h->stream>>>( b.dDist, m, dMM );
+            ++h->stats.kernel_launches;
+            cudaEventRecord( h->evB, h->stream );
+            cudaMemcpyAsync( out + (size_t)z0 * layer, b.dDist, m * sizeof( float ), cudaMemcpyDeviceToHost, h->stream );
+            if ( cudaStreamSynchronize( h->stream ) != cudaSuccess ) { rc = cudaFail( cudaGetLastError(), "projection-normal volume batch" ); break; }
+            float ms = 0;
+            if ( cudaEventElapsedTime( &ms, h->evA, h->evB ) == cudaSuccess ) kernelMs += ms;
+            if ( !report( cb, user, float( z1 ) / float( dims[2] ) ) ) rc = canceled();
+        }
+        if ( rc == B2FWN_OK ) cudaMemcpy( mm, dMM, sizeof( mm ), cudaMemcpyDeviceToHost );
+        cudaFree( dMM );
+        if ( rc ) return rc;
+        h->stats.last_kernel_ms = kernelMs;
+    }
+    if ( outMin ) *outMin = mm[0] == 0xFFFFFFFFu ? FLT_MAX : fromOrd( mm[0] );
+    if ( outMax ) *outMax = mm[1] == 0u ? -FLT_MAX : fromOrd( mm[1] );
+    return B2FWN_OK;
+}
+
 int b2fwn_mc_offset_mesh( b2fwn_handle h, const b2fwn_offset_params* p, b2fwn_offset_result* res, b2fwn_progress cb, void* user )
 {
     if ( !h || !p || !res ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }

@@ -72,6 +72,10 @@ struct DeviceTree
     // high-priority side stream of the grid launcher (walk-length estimates beside the distance kernels), forked / joined by events
     cudaStream_t sideStream = nullptr;
     cudaEvent_t evFork = nullptr, evJoin = nullptr;
+    // pseudonormal tables of SignDetectionMode::ProjectionNormal, built on first use (b2fwn_normals.cu)
+    float* faceNormals = nullptr; // numFaces*3
+    float* vertNormals = nullptr; // numVerts*3
+    int32_t* faceAdj = nullptr;   // numFaces*3: face across the edge (v_k, v_k+1), -1 at a boundary
 };
 
 struct GridXf
@@ -123,6 +127,15 @@ int launchSignGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf
 // closest point with face and barycentrics (b2fwn_project.cu) -----------------------------------------------------------
 int launchFindProjections( const DeviceTree& t, const float* dPts, size_t n, const float* pointXf12, const float* treeXf12,
                            float upDistLimitSq, float loDistLimitSq, b2fwn_projection* dOut, cudaStream_t stream, uint64_t* launches );
+
+// signed distance by the pseudonormal at the closest point (b2fwn_normals.cu) ----------------------------------------------
+// dProj: n records of scratch; dPts / dOut: n points in, n signed distances (NaN = none) out
+int ensurePseudoNormals( DeviceTree& t, cudaStream_t stream, uint64_t* launches );
+int launchSignedDistProjNormal( DeviceTree& t, const float* dPts, size_t n, float minDistSq, float maxDistSq, int nullOutside,
+                                b2fwn_projection* dProj, float* dOut, cudaStream_t stream, uint64_t* launches );
+// voxel centres of the layers [z0, z1) of a volume, as meshToDistanceFunctionVolume computes them
+int launchVoxelCentres( const float origin[3], const float voxelSize[3], int dx, int dy, int z0, int z1, float* dPts, cudaStream_t stream,
+                        uint64_t* launches );
 
 // marching cubes (b2fwn_mc.cu) -----------------------------------------------------------------------------------
 struct McResult

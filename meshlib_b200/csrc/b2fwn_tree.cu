@@ -416,6 +416,7 @@ void freeTree( DeviceTree& t )
 {
     cudaFree( t.points ); cudaFree( t.tris ); cudaFree( t.refNodes ); cudaFree( t.refDipoles );
     cudaFree( t.nodes ); cudaFree( t.leafTris ); cudaFree( t.leafFilt );
+    cudaFree( t.faceNormals ); cudaFree( t.vertNormals ); cudaFree( t.faceAdj );
     if ( t.sideStream ) cudaStreamDestroy( t.sideStream );
     if ( t.evFork ) cudaEventDestroy( t.evFork );
     if ( t.evJoin ) cudaEventDestroy( t.evJoin );

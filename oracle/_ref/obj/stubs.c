@@ -38,19 +38,17 @@ void mrref_stub_17(void) __asm__("_ZN2MR25findSmallestCloseVerticesERKNS_4MeshEf
 void mrref_stub_17(void) { fprintf(stderr, "oracle/_ref: unlinked reference symbol called: _ZN2MR25findSmallestCloseVerticesERKNS_4MeshEfRKSt8functionIFbfEE\n"); abort(); }
 void mrref_stub_18(void) __asm__("_ZN2MR25findSmallestCloseVerticesERKNS_6VectorINS_7Vector3IfEENS_2IdINS_7VertTagEEEEEfPKNS_11TypedBitSetIS5_EERKSt8functionIFbfEE");
 void mrref_stub_18(void) { fprintf(stderr, "oracle/_ref: unlinked reference symbol called: _ZN2MR25findSmallestCloseVerticesERKNS_6VectorINS_7Vector3IfEENS_2IdINS_7VertTagEEEEEfPKNS_11TypedBitSetIS5_EERKSt8functionIFbfEE\n"); abort(); }
-void mrref_stub_19(void) __asm__("_ZN2MR7reverseERSt6vectorINS_2IdINS_7EdgeTagEEESaIS3_EE");
-void mrref_stub_19(void) { fprintf(stderr, "oracle/_ref: unlinked reference symbol called: _ZN2MR7reverseERSt6vectorINS_2IdINS_7EdgeTagEEESaIS3_EE\n"); abort(); }
-void mrref_stub_20(void) __asm__("_ZN2MR8makeCubeERKNS_7Vector3IfEES3_");
-void mrref_stub_20(void) { fprintf(stderr, "oracle/_ref: unlinked reference symbol called: _ZN2MR8makeCubeERKNS_7Vector3IfEES3_\n"); abort(); }
-void mrref_stub_21(void) __asm__("_ZN2MR9EdgePointC1ERKNS_12MeshTopologyENS_2IdINS_7VertTagEEE");
-void mrref_stub_21(void) { fprintf(stderr, "oracle/_ref: unlinked reference symbol called: _ZN2MR9EdgePointC1ERKNS_12MeshTopologyENS_2IdINS_7VertTagEEE\n"); abort(); }
-void mrref_stub_22(void) __asm__("_ZNK2MR12MeshTriPoint6onEdgeERKNS_12MeshTopologyE");
-void mrref_stub_22(void) { fprintf(stderr, "oracle/_ref: unlinked reference symbol called: _ZNK2MR12MeshTriPoint6onEdgeERKNS_12MeshTopologyE\n"); abort(); }
-void mrref_stub_23(void) __asm__("_ZNK2MR12MeshTriPoint8inVertexERKNS_12MeshTopologyE");
-void mrref_stub_23(void) { fprintf(stderr, "oracle/_ref: unlinked reference symbol called: _ZNK2MR12MeshTriPoint8inVertexERKNS_12MeshTopologyE\n"); abort(); }
-void mrref_stub_24(void) __asm__("_ZNK2MR14AABBTreePoints9heapBytesEv");
-void mrref_stub_24(void) { fprintf(stderr, "oracle/_ref: unlinked reference symbol called: _ZNK2MR14AABBTreePoints9heapBytesEv\n"); abort(); }
-void mrref_stub_25(void) __asm__("_ZNK2MR9FloatGridcvbEv");
-void mrref_stub_25(void) { fprintf(stderr, "oracle/_ref: unlinked reference symbol called: _ZNK2MR9FloatGridcvbEv\n"); abort(); }
-void mrref_stub_26(void) __asm__("_ZNK2MR9FloatGridptEv");
-void mrref_stub_26(void) { fprintf(stderr, "oracle/_ref: unlinked reference symbol called: _ZNK2MR9FloatGridptEv\n"); abort(); }
+void mrref_stub_19(void) __asm__("_ZN2MR4sameERKNS_12MeshTopologyERKNS_9EdgePointES5_");
+void mrref_stub_19(void) { fprintf(stderr, "oracle/_ref: unlinked reference symbol called: _ZN2MR4sameERKNS_12MeshTopologyERKNS_9EdgePointES5_\n"); abort(); }
+void mrref_stub_20(void) __asm__("_ZN2MR7reverseERSt6vectorINS_2IdINS_7EdgeTagEEESaIS3_EE");
+void mrref_stub_20(void) { fprintf(stderr, "oracle/_ref: unlinked reference symbol called: _ZN2MR7reverseERSt6vectorINS_2IdINS_7EdgeTagEEESaIS3_EE\n"); abort(); }
+void mrref_stub_21(void) __asm__("_ZN2MR8makeCubeERKNS_7Vector3IfEES3_");
+void mrref_stub_21(void) { fprintf(stderr, "oracle/_ref: unlinked reference symbol called: _ZN2MR8makeCubeERKNS_7Vector3IfEES3_\n"); abort(); }
+void mrref_stub_22(void) __asm__("_ZN2MR9EdgePointC1ERKNS_12MeshTopologyENS_2IdINS_7VertTagEEE");
+void mrref_stub_22(void) { fprintf(stderr, "oracle/_ref: unlinked reference symbol called: _ZN2MR9EdgePointC1ERKNS_12MeshTopologyENS_2IdINS_7VertTagEEE\n"); abort(); }
+void mrref_stub_23(void) __asm__("_ZNK2MR14AABBTreePoints9heapBytesEv");
+void mrref_stub_23(void) { fprintf(stderr, "oracle/_ref: unlinked reference symbol called: _ZNK2MR14AABBTreePoints9heapBytesEv\n"); abort(); }
+void mrref_stub_24(void) __asm__("_ZNK2MR9FloatGridcvbEv");
+void mrref_stub_24(void) { fprintf(stderr, "oracle/_ref: unlinked reference symbol called: _ZNK2MR9FloatGridcvbEv\n"); abort(); }
+void mrref_stub_25(void) __asm__("_ZNK2MR9FloatGridptEv");
+void mrref_stub_25(void) { fprintf(stderr, "oracle/_ref: unlinked reference symbol called: _ZNK2MR9FloatGridptEv\n"); abort(); }

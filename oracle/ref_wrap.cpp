@@ -23,7 +23,12 @@
 #include "MRMesh/MRTriMesh.h"
 #include "MRVoxels/MRMarchingCubes.h"
 #include "MRVoxels/MRVoxelsVolume.h"
+#include <tbb/blocked_range.h>
+#include <tbb/parallel_for.h>
+#include <cfloat>
+#include <cmath>
 #include <cstring>
+#include <limits>
 #include <thread>
 
 // MRTimer.cpp needs the (absent) spdlog submodule; the path only uses the RAII start/finish pair.
@@ -239,6 +244,86 @@ int mrref_find_projections( void* h, const float* pts, size_t n, const float* po
     {
         const auto& r = res[i];
         o[i] = Rec{ (int)r.proj.face, { r.proj.point.x, r.proj.point.y, r.proj.point.z }, r.mtp.bary.a, r.mtp.bary.b, r.distSq, (int)r.mtp.e };
+    }
+    return 0;
+}
+
+// signedDistanceToMesh, SignDetectionMode::ProjectionNormal (source/MRMesh/MRMeshDistance.cpp:13-38), through the reference's
+// own findProjection and Mesh::isOutsideByProjNorm; MRMeshDistance.cpp itself is not among the compiled TUs (its other sign
+// modes need the ray-intersection code), so the ten lines around those two calls are restated here.
+// outDist[i]: signed distance or NaN; outDot[i] (optional): dot( proj - pt, pseudonormal ), how far the decision is from a tie
+int mrref_signed_distance_proj_normal( void* h, const float* pts, size_t n, float minDistSqIn, float maxDistSqIn, int nullOutside,
+                                       float* outDist, float* outDot )
+{
+    auto& m = ( (RefMesh*)h )->mesh;
+    (void)m.getAABBTree();
+    const float nan = std::numeric_limits<float>::quiet_NaN();
+    tbb::parallel_for( tbb::blocked_range<size_t>( 0, n ), [&]( const tbb::blocked_range<size_t>& range )
+    {
+        for ( size_t i = range.begin(); i < range.end(); ++i )
+        {
+            const Vector3f p( pts[3 * i], pts[3 * i + 1], pts[3 * i + 2] );
+            float minDistSq = minDistSqIn, maxDistSq = maxDistSqIn;
+            if ( !nullOutside ) { minDistSq = 0; maxDistSq = FLT_MAX; } // :19-24
+            const auto proj = findProjection( p, m, maxDistSq, nullptr, minDistSq );
+            if ( outDot ) outDot[i] = nan;
+            if ( !proj ) { outDist[i] = nan; continue; } // :27-28
+            if ( nullOutside && ( proj.distSq < minDistSq || proj.distSq >= maxDistSq ) ) { outDist[i] = nan; continue; } // :30-31
+            float dist = std::sqrt( proj.distSq );
+            if ( !m.isOutsideByProjNorm( p, proj, nullptr ) ) dist = -dist; // :36-38
+            outDist[i] = dist;
+            if ( outDot ) outDot[i] = dot( proj.proj.point - p, m.pseudonormal( proj.mtp, nullptr ) );
+        }
+    } );
+    return 0;
+}
+
+// voxel centres of meshToDistanceFunctionVolume (source/MRVoxels/MRMeshToDistanceVolume.cpp:83-84), x fastest
+int mrref_voxel_centres( const float* origin, const float* voxelSize, const int* dims, float* out )
+{
+    const Vector3f o( origin[0], origin[1], origin[2] ), vs( voxelSize[0], voxelSize[1], voxelSize[2] );
+    size_t i = 0;
+    for ( int z = 0; z < dims[2]; ++z )
+        for ( int y = 0; y < dims[1]; ++y )
+            for ( int x = 0; x < dims[0]; ++x, ++i )
+            {
+                const auto coord = Vector3f( Vector3i( x, y, z ) ) + Vector3f::diagonal( 0.5f );
+                const auto c = o + mult( vs, coord );
+                out[3 * i] = c.x; out[3 * i + 1] = c.y; out[3 * i + 2] = c.z;
+            }
+    return 0;
+}
+
+// pseudonormals of all faces (leftNormal of edgeWithLeft), vertices, and of the three edges of every face
+// (source/MRMesh/MRMeshMath.cpp:510-547); edge k of face f = ( v_k, v_k+1 ) of getTriVerts( f )
+int mrref_pseudonormals( void* h, float* faceN, float* vertN, float* edgeN )
+{
+    auto& m = ( (RefMesh*)h )->mesh;
+    const auto& topo = m.topology;
+    for ( FaceId f{ 0 }; f < (int)topo.faceSize(); ++f )
+    {
+        Vector3f n, e[3];
+        if ( topo.hasFace( f ) )
+        {
+            const EdgeId e0 = topo.edgeWithLeft( f );
+            n = m.leftNormal( e0 );
+            // left ring of f starting at e0: e0 = (v0,v1), then (v1,v2), (v2,v0)
+            EdgeId ek = e0;
+            for ( int k = 0; k < 3; ++k )
+            {
+                e[k] = m.pseudonormal( ek.undirected(), nullptr );
+                ek = topo.prev( ek.sym() );
+            }
+        }
+        faceN[3 * (int)f] = n.x; faceN[3 * (int)f + 1] = n.y; faceN[3 * (int)f + 2] = n.z;
+        for ( int k = 0; k < 3; ++k )
+            for ( int c = 0; c < 3; ++c ) edgeN[9 * (int)f + 3 * k + c] = e[k][c];
+    }
+    for ( VertId v{ 0 }; v < (int)m.points.size(); ++v )
+    {
+        Vector3f n;
+        if ( topo.hasVert( v ) ) n = m.pseudonormal( v, nullptr );
+        vertN[3 * (int)v] = n.x; vertN[3 * (int)v + 1] = n.y; vertN[3 * (int)v + 2] = n.z;
     }
     return 0;
 }

@@ -54,6 +54,10 @@ def lib():
         L.mrref_find_projection_dist_sq.argtypes = [C.c_void_p, _f32p, C.c_size_t, C.c_float, C.c_float, _f32p]
         L.mrref_find_projections.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_float, C.c_float,
                                              C.c_void_p]
+        L.mrref_signed_distance_proj_normal.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_float, C.c_float, C.c_int,
+                                                        C.c_void_p, C.c_void_p]
+        L.mrref_voxel_centres.argtypes = [_f32p, _f32p, _i32p, C.c_void_p]
+        L.mrref_pseudonormals.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.mrref_marching_cubes.argtypes = [_f32p, _i32p, _f32p, _f32p, C.c_float, C.c_int, C.POINTER(C.c_size_t),
                                            C.POINTER(C.c_size_t)]
         L.mrref_marching_cubes_fetch.argtypes = [_f32p, _i32p]
@@ -163,6 +167,21 @@ class RefMesh:
                                      None if tx is None else tx.ctypes.data, up, lo, out.ctypes.data)
         return out
 
+    def signed_distance_proj_normal(self, pts, min_dist_sq=0.0, max_dist_sq=FLT_MAX, null_outside=True):
+        """MR::signedDistanceToMesh with SignDetectionMode::ProjectionNormal (source/MRMesh/MRMeshDistance.cpp:13-38) per point:
+        (signed distances with NaN, dot( proj - pt, pseudonormal ) = the margin of each sign decision)"""
+        pts = np.ascontiguousarray(pts, np.float32).reshape(-1, 3)
+        dist, dots = np.empty(len(pts), np.float32), np.empty(len(pts), np.float32)
+        lib().mrref_signed_distance_proj_normal(self.h, pts.ctypes.data, len(pts), min_dist_sq, max_dist_sq, int(null_outside),
+                                                dist.ctypes.data, dots.ctypes.data)
+        return dist, dots
+
+    def pseudonormals(self, n_faces, n_verts):
+        """(face normals (F,3), vertex pseudonormals (V,3), edge pseudonormals (F,3,3)) of the reference's topology"""
+        fn, vn, en = np.zeros((n_faces, 3), np.float32), np.zeros((n_verts, 3), np.float32), np.zeros((n_faces, 3, 3), np.float32)
+        lib().mrref_pseudonormals(self.h, fn.ctypes.data, vn.ctypes.data, en.ctypes.data)
+        return fn, vn, en
+
     def find_projection_dist_sq(self, pts, up=FLT_MAX, lo=0.0):
         pts = np.ascontiguousarray(pts, np.float32)
         out = np.empty(len(pts), np.float32)
@@ -188,3 +207,12 @@ def marching_cubes(volume, dims, voxel_size, origin, iso, less_inside=False):
 
 def hardware_threads():
     return lib().mrref_hardware_threads()
+
+
+def voxel_centres(origin, voxel_size, dims):
+    """voxel centres as meshToDistanceFunctionVolume computes them (source/MRVoxels/MRMeshToDistanceVolume.cpp:83-84), x fastest"""
+    d = np.ascontiguousarray(dims, np.int32)
+    out = np.empty((int(d[0]) * int(d[1]) * int(d[2]), 3), np.float32)
+    vs = np.ascontiguousarray(np.asarray(voxel_size, np.float32) * np.ones(3, np.float32))
+    lib().mrref_voxel_centres(np.ascontiguousarray(origin, np.float32), vs, d, out.ctypes.data)
+    return out

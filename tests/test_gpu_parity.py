@@ -597,3 +597,95 @@ def test_make_signed_by_winding_number_edge_cases():
     inside = float((host < 0).mean())
     assert abs(inside - 2 * np.pi ** 2 * 2 / (6.6 * 6.6 * 2.6)) < 0.02  # volume fraction of the (48 x 24 faceted) torus R 2, r 1
     fwn.close()
+
+
+# ---- SignDetectionMode::ProjectionNormal -------------------------------------------------------------------
+
+def _proj_normal_agrees(got, want, dots):
+    """NaN masks and magnitudes identical; signs identical wherever the reference's dot( proj - pt, pseudonormal ) is not
+    within rounding of zero (vertex pseudonormals are summed in face order here, in ring order there)"""
+    assert np.array_equal(np.isnan(got), np.isnan(want))
+    ok = ~np.isnan(want)
+    assert np.abs(got[ok]).tobytes() == np.abs(want[ok]).tobytes()
+    clear = ok & (np.abs(dots) > 1e-5 * np.abs(want))
+    assert clear.sum() > 0.99 * ok.sum()
+    assert np.array_equal(np.signbit(got[clear]), np.signbit(want[clear]))
+    return ok
+
+
+@pytest.mark.parametrize("name", ["torus", "holes", "deleted"])
+def test_signed_distances_by_projection_normal_match_reference(name):
+    import torch
+    pts, tris = _mesh(name)
+    orc = checker.best_oracle(pts, tris)
+    if orc.kind != "reference":
+        pytest.skip("needs the reference library (pseudonormals come from its half-edge topology)")
+    from oracle import reflib
+    rp, rt = orc.points, orc.tris
+    fwn = mb.FastWindingNumber(rp, rt)
+    q = meshgen.query_points(30000, float(rp.min()) - 0.6, float(rp.max()) + 0.6, seed=11)
+    _fn, rvn, _en = orc.pseudonormals(len(rt), len(rp))
+    q = np.concatenate([q, rp[::7] + np.float32(0.05) * rvn[::7], rp[::5] - np.float32(0.03) * rvn[::5]]).astype(np.float32)
+    for opt, kw in ((mb.DistOptions(0.0, mb.FLT_MAX, False), dict(null_outside=False)),
+                    (mb.DistOptions(0.3, 0.1, False), dict(null_outside=False)),  # limits are ignored without the NaN rule
+                    (mb.DistOptions(0.01, 0.49, True), dict(min_dist_sq=0.01, max_dist_sq=0.49, null_outside=True))):
+        want, dots = orc.signed_distance_proj_normal(q, **kw)
+        got = fwn.signed_distances_by_projection_normal(q, opt)
+        ok = _proj_normal_agrees(got, want, dots)
+        assert np.signbit(got[ok]).any() and not np.signbit(got[ok]).all()
+        d_q = torch.from_numpy(q).cuda()
+        d_out = torch.empty(len(q), dtype=torch.float32, device="cuda")
+        fwn.signed_distances_by_projection_normal_device(d_q.data_ptr(), len(q), d_out.data_ptr(), opt)
+        assert d_out.cpu().numpy().tobytes() == got.tobytes()
+    # the volume form: voxel centres as meshToDistanceFunctionVolume computes them
+    origin = (rp.min(0) - 0.4).astype(np.float32)
+    dims = (37, 41, 23)
+    voxel = ((rp.max(0) + 0.4 - origin) / np.asarray(dims, np.float32)).astype(np.float32)
+    centres = reflib.voxel_centres(origin, voxel, dims)
+    for opt, kw in ((mb.DistOptions(0.0, mb.FLT_MAX, False), dict(null_outside=False)),
+                    (mb.DistOptions(0.0, 0.09, True), dict(min_dist_sq=0.0, max_dist_sq=0.09, null_outside=True))):
+        want, dots = orc.signed_distance_proj_normal(centres, **kw)
+        prog = []
+        got, lo, hi = fwn.mesh_to_distance_volume_by_projection_normal(origin, voxel, dims, opt, cb=lambda v: prog.append(v) or True)
+        ok = _proj_normal_agrees(got, want, dots)
+        assert lo == got[ok].min() and hi == got[ok].max() and lo < 0 < hi
+        assert prog[0] == 0.0 and prog[-1] == 1.0
+    fwn.close()
+
+
+def test_projection_normal_edge_cases():
+    pts, tris = meshgen.make_torus(2, 1, 48, 24)
+    fwn = mb.FastWindingNumber(pts, tris)
+    assert len(fwn.signed_distances_by_projection_normal(np.zeros((0, 3), np.float32))) == 0
+    got, lo, hi = fwn.mesh_to_distance_volume_by_projection_normal((0, 0, 0), 0.1, (0, 4, 4))
+    assert len(got) == 0 and lo == mb.FLT_MAX and hi == -mb.FLT_MAX
+    # closed surface: the sign by the pseudonormal agrees with the winding number away from the surface
+    q = meshgen.query_points(20000, -3.4, 3.4, seed=5)
+    d = fwn.signed_distances_by_projection_normal(q, mb.DistOptions(0.0, mb.FLT_MAX, False))
+    w = fwn.calc_from_vector(q)
+    far = np.abs(d) > 1e-3
+    assert np.array_equal(d[far] < 0, w[far] > 0.5)
+    # more than one batch of 4 Mi points through the host form, against the device form in one launch
+    import torch
+    big = meshgen.query_points(5_000_000, -3.4, 3.4, seed=6)
+    opt = mb.DistOptions(0.0, 1.0, True)
+    host = fwn.signed_distances_by_projection_normal(big, opt)
+    d_q = torch.from_numpy(big).cuda()
+    d_out = torch.empty(len(big), dtype=torch.float32, device="cuda")
+    fwn.signed_distances_by_projection_normal_device(d_q.data_ptr(), len(big), d_out.data_ptr(), opt)
+    assert d_out.cpu().numpy().tobytes() == host.tobytes()
+    assert np.isnan(host).any() and not np.isnan(host).all()
+    # a volume of more than one batch of layers (8 Mi voxels per batch) against the point form on the same voxel centres
+    from oracle import normalslib
+    if normalslib.available():
+        origin, voxel, dims = (-3.3, -3.3, -1.3), (6.6 / 256, 6.6 / 256, 2.6 / 160), (256, 256, 160)
+        band = mb.DistOptions(0.0, 0.01, True)
+        vol, lo, hi = fwn.mesh_to_distance_volume_by_projection_normal(origin, voxel, dims, band)
+        ref_pts = fwn.signed_distances_by_projection_normal(normalslib.voxel_centres(origin, voxel, dims), band)
+        assert vol.tobytes() == ref_pts.tobytes()
+        assert lo == np.nanmin(vol) and hi == np.nanmax(vol) and -0.1 <= lo < 0 < hi <= 0.1
+    fwn.close()
+    # a mesh without faces has no projection anywhere
+    empty = mb.FastWindingNumber(np.zeros((0, 3), np.float32), np.zeros((0, 3), np.int32))
+    assert np.isnan(empty.signed_distances_by_projection_normal(q[:100])).all()
+    empty.close()

@@ -132,3 +132,58 @@ def test_projection_restatement_bit_exact_vs_reference():
         for f in ("face", "point", "a", "b", "dist_sq"):
             assert np.array_equal(a[f].view(np.uint32), b[f].view(np.uint32)), (kw.keys(), f)
         assert np.array_equal(b["edge"] >= 0, b["face"] >= 0)
+
+
+@needs_ref
+@pytest.mark.parametrize("name", ["torus", "noisy", "holes"])
+def test_projection_normal_arithmetic_of_the_device_header_vs_reference(name):
+    """SURVEY 8f N2 (ProjectionNormal): the header the device kernels are built from (b2fwn_normals_math.h), run on the host
+    like the kernels run it, against the reference's topology-based pseudonormals and signedDistanceToMesh: face and edge
+    pseudonormals bit for bit, vertex pseudonormals up to the ring's summation order, voxel centres bit for bit, and the
+    signed distances of query points identical wherever the reference's dot product is not within rounding of zero"""
+    from oracle import normalslib
+    if not normalslib.available():
+        pytest.skip("oracle/liboracle_normals.so not built")
+    if name == "torus":
+        pts, tris = meshgen.make_torus(2, 1, 96, 48)
+    else:
+        pts, tris = meshgen.make_uv_sphere(1, 80, 40)
+        pts = meshgen.add_noise(pts, 4e-3)
+        if name == "holes":
+            tris = tris[np.arange(len(tris)) % 9 != 4]
+    ref = reflib.RefMesh.from_arrays(pts, tris)
+    rp, rt = ref.points, ref.tris
+    fn, vn, adj = tabs = normalslib.tables(rp, rt)
+    rfn, rvn, ren = ref.pseudonormals(len(rt), len(rp))
+    assert fn.tobytes() == rfn.tobytes()
+    assert np.abs(vn - rvn).max() < 2e-6
+    assert (adj < 0).any() == (name == "holes")
+    other = np.where(adj >= 0, adj, np.arange(len(rt))[:, None])
+    s = fn[:, None, :] + fn[other]
+    length = np.sqrt((s[..., 0] * s[..., 0] + s[..., 1] * s[..., 1]) + s[..., 2] * s[..., 2], dtype=np.float32)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        en = np.where((adj >= 0)[..., None], (np.float32(1) / length)[..., None] * s, fn[:, None, :]).astype(np.float32)
+    assert en.tobytes() == ren.tobytes()
+    # signs: the reference's own projections (ours are bit-identical, N1) through the header's sign rule
+    q = meshgen.query_points(30000, float(rp.min()) - 0.6, float(rp.max()) + 0.6, seed=11)
+    q = np.concatenate([q, rp[::7] + np.float32(0.05) * rvn[::7], rp[::5] - np.float32(0.03) * rvn[::5]]).astype(np.float32)
+    for kw in (dict(null_outside=False), dict(min_dist_sq=0.01, max_dist_sq=0.49, null_outside=True)):
+        want, dots = ref.signed_distance_proj_normal(q, **kw)
+        lo, up = (kw["min_dist_sq"], kw["max_dist_sq"]) if kw["null_outside"] else (0.0, reflib.FLT_MAX)
+        rec = ref.find_projections(q, up=up, lo=lo)
+        got = normalslib.sign(rec, q, rt, tabs, **kw)
+        assert np.array_equal(np.isnan(got), np.isnan(want))
+        ok = ~np.isnan(want)
+        assert ok.any() and (kw["null_outside"] is False or (~ok).any())
+        assert np.abs(got[ok]).tobytes() == np.abs(want[ok]).tobytes()
+        clear = ok & (np.abs(dots) > 1e-6 * np.abs(want))
+        assert clear.sum() > 0.99 * ok.sum()
+        assert np.array_equal(np.signbit(got[clear]), np.signbit(want[clear]))
+        assert np.signbit(want[ok]).any() and not np.signbit(want[ok]).all()
+    # on-vertex and on-edge closest points must actually occur in the sample
+    a, b = rec["a"], rec["b"]
+    eps = 10 * np.finfo(np.float32).eps
+    assert ((a <= eps) & (b <= eps)).any() and ((b <= eps) & (a > eps) & (np.float32(1) - a - b > eps)).any()
+    # voxel centres of meshToDistanceFunctionVolume
+    args = ((-1.37, 0.21, 3.3), (0.013, 0.07, 0.11), (17, 9, 5))
+    assert normalslib.voxel_centres(*args).tobytes() == reflib.voxel_centres(*args).tobytes()
