@@ -207,6 +207,13 @@ int b2fwn_calc_from_grid_with_distances_by_parts( b2fwn_handle h, const int32_t 
  * dipoles = Dipole (32 B: pos xyz, area, dirArea xyz, rr; source/MRMesh/MRDipole.h:10-30). */
 int b2fwn_get_tree( b2fwn_handle h, void* out_nodes_32B, void* out_dipoles_32B, size_t capacity_nodes, size_t* n_nodes );
 
+/* Mesh edited in place (same triangulation, moved vertices): AABBTree::refit (source/MRMesh/MRAABBTree.cpp:62-94) with every
+ * vertex marked as changed, followed by calcDipoles (MRDipole.cpp:23-71), on the device.  The tree keeps its topology; boxes,
+ * dipoles, traversal nodes and leaf triangles are recomputed from points_xyz (n_verts must equal the handle's vertex
+ * count).  b2fwn_get_tree afterwards returns what the reference's refit + calcDipoles produce, bit for bit; the reference's
+ * CUDA class has no counterpart (it re-uploads and never invalidates).  b2fwn_stats.last_kernel_ms = refit time. */
+int b2fwn_update_points( b2fwn_handle h, const float* points_xyz, size_t n_verts );
+
 int b2fwn_get_stats( b2fwn_handle h, b2fwn_stats* out );
 
 /* diagnostics: measured FP32 FMA throughput (TFLOP/s) of the device = the roofline denominator bench.py reports

@@ -95,7 +95,7 @@ EXPORTS = [
     "b2fwn_get_bounding_box", "b2fwn_mesh_to_distance_volume", "b2fwn_mc_offset_mesh",
     "b2fwn_make_signed_by_winding_number", "b2fwn_make_signed_by_winding_number_device",
     "b2fwn_signed_distances_by_projection_normal", "b2fwn_signed_distances_by_projection_normal_device",
-    "b2fwn_mesh_to_distance_volume_by_projection_normal",
+    "b2fwn_mesh_to_distance_volume_by_projection_normal", "b2fwn_update_points",
 ]
 
 
@@ -144,6 +144,7 @@ def load_library():
     L.b2fwn_calc_from_grid_with_distances_by_parts.argtypes = [vp, i32p, f32p, C.POINTER(DistOptions), C.c_int32,
                                                                C.c_int32, PART_CB, vp, PROGRESS_CB, vp]
     L.b2fwn_get_tree.argtypes = [vp, vp, vp, C.c_size_t, C.POINTER(C.c_size_t)]
+    L.b2fwn_update_points.argtypes = [vp, vp, C.c_size_t]
     L.b2fwn_get_stats.argtypes = [vp, C.POINTER(Stats)]
     L.b2fwn_marching_cubes.argtypes = [vp, vp, C.c_int32, i32p, C.POINTER(McParams), u64p, u64p]
     L.b2fwn_marching_cubes_fetch.argtypes = [vp, vp, vp]
@@ -387,6 +388,11 @@ class FastWindingNumber:
 
     def shared_free(self, ptr):
         _check(_lib.b2fwn_shared_free(self._h, ptr))
+
+    def update_points(self, points):
+        """same triangulation, moved vertices: AABBTree::refit + calcDipoles on the device (source/MRMesh/MRAABBTree.cpp:62-94)"""
+        pts = np.ascontiguousarray(points, np.float32).reshape(-1, 3)
+        _check(_lib.b2fwn_update_points(self._h, pts.ctypes.data, len(pts)))
 
     # ---- parity / diagnostics ----
     def get_tree(self):

@@ -293,6 +293,22 @@ void b2fwn_destroy( b2fwn_handle h )
     delete h;
 }
 
+int b2fwn_update_points( b2fwn_handle h, const float* points, size_t nVerts )
+{
+    if ( !h || ( nVerts && !points ) ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    if ( nVerts != h->tree.numVerts ) { setError( "the number of vertices must not change (same triangulation, new coordinates)" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    B2_CUDA( cudaDeviceSynchronize() ); // nothing of an earlier call still reads the old coordinates
+    if ( nVerts ) B2_CUDA( cudaMemcpyAsync( h->tree.points, points, nVerts * 3 * sizeof( float ), cudaMemcpyHostToDevice, h->stream ) );
+    cudaEventRecord( h->evA, h->stream );
+    if ( int e = refitTree( h->tree, h->stream, &h->stats.kernel_launches ) ) return e;
+    cudaEventRecord( h->evB, h->stream );
+    B2_CUDA( cudaEventSynchronize( h->evB ) );
+    float ms = 0;
+    if ( cudaEventElapsedTime( &ms, h->evA, h->evB ) == cudaSuccess ) h->stats.last_kernel_ms = ms;
+    return B2FWN_OK;
+}
+
 int b2fwn_get_stats( b2fwn_handle h, b2fwn_stats* out )
 {
     if ( !h || !out ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }

@@ -76,6 +76,7 @@ struct DeviceTree
     float* faceNormals = nullptr; // numFaces*3
     float* vertNormals = nullptr; // numVerts*3
     int32_t* faceAdj = nullptr;   // numFaces*3: face across the edge (v_k, v_k+1), -1 at a boundary
+    uint8_t* nodeDepth = nullptr; // numNodes: depth of each node (bottom-up passes of build and refit)
 };
 
 struct GridXf
@@ -96,6 +97,9 @@ int cudaFail( cudaError_t e, const char* where );
 
 // tree build (b2fwn_tree.cu) -----------------------------------------------------------------------------------
 int buildTree( DeviceTree& t, cudaStream_t stream, uint64_t* launches );
+// new vertex coordinates in t.points, same triangulation: boxes, dipoles, traversal nodes and leaf triangles recomputed on the
+// unchanged tree topology (AABBTree::refit, MRAABBTree.cpp:62-94)
+int refitTree( DeviceTree& t, cudaStream_t stream, uint64_t* launches );
 void freeTree( DeviceTree& t );
 
 // traversal launchers (b2fwn_kernels.cu) ------------------------------------------------------------------------

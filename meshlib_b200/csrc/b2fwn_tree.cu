@@ -351,7 +351,7 @@ __global__ void kFinishDipoles( size_t nNodes, const RefNode* __restrict__ nodes
     }
     d.rr = rr;
     dip[i] = d;
-    const int link = nd.r < 0 ? -( leafSlotOfNode[i] + 1 ) : skip[i];
+    const int link = skip ? ( nd.r < 0 ? -( leafSlotOfNode[i] + 1 ) : skip[i] ) : __float_as_int( trav[i].q3.w ); // refit: links stay
     TravNode t;
     t.q0 = make_float4( nd.bmin[0], nd.bmin[1], nd.bmin[2], nd.bmax[0] );
     t.q1 = make_float4( nd.bmax[1], nd.bmax[2], __int_as_float( nd.r < 0 ? 0 : nd.r ), __int_as_float( link ) ); // .z = right child
@@ -367,8 +367,9 @@ __global__ void kLeafSlots( int nLeaves, const int32_t* __restrict__ leafNodeOfP
 {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if ( p >= nLeaves ) return;
-    leafSlotOfNode[leafNodeOfPos[p]] = p;
-    const size_t f = (size_t)keys[p].face;
+    size_t f;
+    if ( leafNodeOfPos ) { leafSlotOfNode[leafNodeOfPos[p]] = p; f = (size_t)keys[p].face; }
+    else f = (size_t)__float_as_int( out[p].a.w ); // refit: the same leaf order at new coordinates
     const int32_t ia = tris[3 * f], ib = tris[3 * f + 1], ic = tris[3 * f + 2];
     LeafTri t;
     t.a = make_float4( pts[3 * (size_t)ia], pts[3 * (size_t)ia + 1], pts[3 * (size_t)ia + 2], __int_as_float( (int)f ) );
@@ -408,6 +409,61 @@ __global__ void kLeafSlots( int nLeaves, const int32_t* __restrict__ leafNodeOfP
     out[p] = t;
 }
 
+// ---- refit (AABBTree::refit, MRAABBTree.cpp:62-94, with every vertex marked as changed) -----------------------------------
+
+// leaf nodes: computeFaceBox at the new coordinates; also the exact bounding box of the valid faces (as kFaceBoxes)
+__global__ void kRefitLeafNodes( size_t nNodes, RefNode* __restrict__ nodes, const float* __restrict__ pts, const int32_t* __restrict__ tris,
+                                 uint32_t* __restrict__ bbox6 )
+{
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    uint32_t bb[6] = { 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u, 0u };
+    if ( i < nNodes && nodes[i].r < 0 )
+    {
+        const size_t f = (size_t)nodes[i].l;
+#pragma unroll
+        for ( int d = 0; d < 3; ++d )
+        {
+            const float a = pts[3 * (size_t)tris[3 * f] + d];
+            const float b = pts[3 * (size_t)tris[3 * f + 1] + d];
+            const float c = pts[3 * (size_t)tris[3 * f + 2] + d];
+            float mn = FLT_MAX, mx = -FLT_MAX;
+            if ( a < mn ) mn = a; if ( a > mx ) mx = a;
+            if ( b < mn ) mn = b; if ( b > mx ) mx = b;
+            if ( c < mn ) mn = c; if ( c > mx ) mx = c;
+            nodes[i].bmin[d] = nextafterf( mn, -FLT_MAX );
+            nodes[i].bmax[d] = nextafterf( mx, FLT_MAX );
+            bb[d] = f2ord( mn ); bb[3 + d] = f2ord( mx );
+        }
+    }
+#pragma unroll
+    for ( int c = 0; c < 6; ++c )
+    {
+        const uint32_t r = c < 3 ? __reduce_min_sync( 0xFFFFFFFFu, bb[c] ) : __reduce_max_sync( 0xFFFFFFFFu, bb[c] );
+        if ( ( threadIdx.x & 31 ) == 0 )
+        {
+            if ( c < 3 ) atomicMin( bbox6 + c, r ); else atomicMax( bbox6 + c, r );
+        }
+    }
+}
+
+// inner nodes of one depth: box = left box, include( right box ) (MRAABBTree.cpp:90-91); deeper levels are complete already
+__global__ void kRefitInnerNodes( size_t nNodes, int level, const uint8_t* __restrict__ depth, RefNode* __restrict__ nodes )
+{
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if ( i >= nNodes || depth[i] != level ) return;
+    const int l = nodes[i].l, r = nodes[i].r;
+    if ( r < 0 ) return;
+#pragma unroll
+    for ( int d = 0; d < 3; ++d )
+    {
+        float mn = nodes[l].bmin[d], mx = nodes[l].bmax[d];
+        const float rmn = nodes[r].bmin[d], rmx = nodes[r].bmax[d];
+        if ( rmn < mn ) mn = rmn; // Box::include( Box ), MRBox.h
+        if ( rmx > mx ) mx = rmx;
+        nodes[i].bmin[d] = mn; nodes[i].bmax[d] = mx;
+    }
+}
+
 inline unsigned nblk( size_t n ) { return (unsigned)( ( n + TB - 1 ) / TB ); }
 
 } // anonymous namespace
@@ -416,7 +472,7 @@ void freeTree( DeviceTree& t )
 {
     cudaFree( t.points ); cudaFree( t.tris ); cudaFree( t.refNodes ); cudaFree( t.refDipoles );
     cudaFree( t.nodes ); cudaFree( t.leafTris ); cudaFree( t.leafFilt );
-    cudaFree( t.faceNormals ); cudaFree( t.vertNormals ); cudaFree( t.faceAdj );
+    cudaFree( t.faceNormals ); cudaFree( t.vertNormals ); cudaFree( t.faceAdj ); cudaFree( t.nodeDepth );
     if ( t.sideStream ) cudaStreamDestroy( t.sideStream );
     if ( t.evFork ) cudaEventDestroy( t.evFork );
     if ( t.evJoin ) cudaEventDestroy( t.evJoin );
@@ -541,7 +597,50 @@ int buildTree( DeviceTree& t, cudaStream_t st, uint64_t* launches )
     B2_CUDA( cudaStreamSynchronize( st ) );
 
     cudaFree( sortTmp ); cudaFree( dValid ); cudaFree( dLeaves ); cudaFree( dKeys ); cudaFree( dSegA ); cudaFree( dSegB );
-    cudaFree( dSegBox ); cudaFree( dSkip ); cudaFree( dDepth ); cudaFree( dLeafNodeOfPos ); cudaFree( dLeafSlotOfNode );
+    cudaFree( dSegBox ); cudaFree( dSkip ); cudaFree( dLeafNodeOfPos ); cudaFree( dLeafSlotOfNode );
+    t.nodeDepth = dDepth; // kept for refitTree
+    if ( launches ) *launches += nl;
+    return B2FWN_OK;
+}
+
+// The tree keeps its topology (which face sits in which leaf, the order of the nodes, the links); boxes are recomputed bottom
+// up from the new coordinates, then dipoles, traversal nodes and leaf triangles exactly as after a build.  The result is what
+// AABBTree::refit with all vertices changed + calcDipoles give on the reference's side, bit for bit.
+int refitTree( DeviceTree& t, cudaStream_t st, uint64_t* launches )
+{
+    // pseudonormals depend on the coordinates: rebuilt on next use
+    cudaFree( t.faceNormals ); cudaFree( t.vertNormals ); cudaFree( t.faceAdj );
+    t.faceNormals = t.vertNormals = nullptr; t.faceAdj = nullptr;
+    const size_t N = t.numNodes;
+    const int L = (int)t.numLeaves;
+    if ( N == 0 ) return B2FWN_OK;
+    if ( !t.nodeDepth ) { setError( "tree has no depth table" ); return B2FWN_ERR_INVALID; }
+    uint64_t nl = 0;
+    uint32_t* dBBox = nullptr;
+    B2_CUDA( cudaMalloc( &dBBox, 6 * sizeof( uint32_t ) ) );
+    kClearSegBoxes<<<1, 32, 0, st>>>( dBBox, 1 ); ++nl;
+    kRefitLeafNodes<<<nblk( N ), TB, 0, st>>>( N, t.refNodes, t.points, t.tris, dBBox ); ++nl;
+    for ( int lev = t.depth - 1; lev >= 0; --lev )
+    {
+        kRefitInnerNodes<<<nblk( N ), TB, 0, st>>>( N, lev, t.nodeDepth, t.refNodes ); ++nl;
+    }
+    kLeafSlots<<<nblk( L ), TB, 0, st>>>( L, nullptr, nullptr, nullptr, t.points, t.tris, t.leafTris, t.leafFilt ); ++nl;
+    kLeafDipoles<<<nblk( N ), TB, 0, st>>>( N, t.refNodes, t.points, t.tris, t.refDipoles ); ++nl;
+    for ( int lev = t.depth - 1; lev >= 0; --lev )
+    {
+        kInnerDipoles<<<nblk( N ), TB, 0, st>>>( N, lev, t.nodeDepth, t.refNodes, t.refDipoles ); ++nl;
+    }
+    kFinishDipoles<<<nblk( N ), TB, 0, st>>>( N, t.refNodes, t.refDipoles, nullptr, nullptr, t.nodes ); ++nl;
+    uint32_t hb[6];
+    B2_CUDA( cudaMemcpyAsync( hb, dBBox, sizeof( hb ), cudaMemcpyDeviceToHost, st ) );
+    B2_CUDA( cudaStreamSynchronize( st ) );
+    cudaFree( dBBox );
+    for ( int c = 0; c < 6; ++c )
+    {
+        const uint32_t u = ( hb[c] & 0x80000000u ) ? ( hb[c] & 0x7fffffffu ) : ~hb[c];
+        memcpy( &t.bbox[c], &u, 4 );
+    }
+    B2_CUDA( cudaGetLastError() );
     if ( launches ) *launches += nl;
     return B2FWN_OK;
 }

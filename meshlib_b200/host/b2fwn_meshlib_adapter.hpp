@@ -133,6 +133,16 @@ public:
                                                               &progress_, (void*)&cb ) );
     }
 
+    /// Beyond the interface: the mesh this object was made for had its vertices moved (same topology).
+    /// Counterpart of Mesh::updateCaches( changedVerts ) (source/MRMesh/MRMesh.cpp:565-578): the device tree is refitted like
+    /// AABBTree::refit (MRAABBTree.cpp:62-94), dipoles and leaf triangles are recomputed -- no re-upload of the triangulation,
+    /// no rebuild.  The reference's Cuda::FastWindingNumber never notices such a change.
+    Expected<void> updatePoints()
+    {
+        if ( !h_ ) return {}; // not uploaded yet: the first call will read the current coordinates
+        return status_( b2fwn_update_points( h_, reinterpret_cast<const float*>( mesh_.points.data() ), mesh_.points.size() ) );
+    }
+
 private:
     struct PartCtx
     {

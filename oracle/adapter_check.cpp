@@ -174,5 +174,23 @@ int main()
         }
         check( oursP->projectionsHeapBytes( 10 ) == 10 * ( 12 + 32 ), "projectionsHeapBytes" );
     }
+
+    // moved vertices: Mesh::updateCaches refits the reference's cached tree, updatePoints() refits ours; the
+    // two trees stay identical, so the winding numbers agree as tightly as after a build
+    {
+        auto b200 = std::dynamic_pointer_cast<B200::FastWindingNumber>( ours );
+        for ( auto& p : mesh.points )
+            p = Vector3f( 1.1f * p.x + 0.05f * std::sin( 3.f * p.y ), 0.9f * p.y, p.z + 0.1f * std::cos( 2.f * p.x ) );
+        mesh.updateCaches( mesh.topology.getValidVerts() );
+        check( b200 && b200->updatePoints().has_value(), "updatePoints.call" );
+        FastWindingNumber ref2( mesh );
+        std::vector<float> ua, ub;
+        check( ours->calcFromVector( ua, pts, 2.f ).has_value(), "updatePoints.calcFromVector.call" );
+        (void)ref2.calcFromVector( ub, pts, 2.f, {}, {} );
+        float maxD = 0;
+        for ( size_t i = 0; i < pts.size(); ++i ) maxD = std::max( maxD, std::abs( ua[i] - ub[i] ) );
+        std::printf( "updatePoints.max_abs_dw %g\n", maxD );
+        check( ua.size() == pts.size() && maxD < 1e-5f, "updatePoints.parity" );
+    }
     return g_fail ? 1 : 0;
 }

@@ -123,6 +123,19 @@ void mrref_get_nodes( void* h, void* out )
     std::memcpy( out, nodes.vec_.data(), nodes.size() * 32 );
 }
 
+/// moved vertices, same topology: Mesh::updateCaches (source/MRMesh/MRMesh.cpp:565-578) = AABBTree::refit on the cached tree
+/// (MRAABBTree.cpp:62-94) + dipoles recomputed on next use; every later call of this wrapper works on the refitted tree
+int mrref_update_points( void* h, const float* pts, size_t nVerts )
+{
+    auto& m = ( (RefMesh*)h )->mesh;
+    if ( nVerts != m.points.size() ) return 1;
+    (void)m.getAABBTree(); // the tree of the old coordinates must exist to be refitted
+    for ( size_t i = 0; i < nVerts; ++i ) m.points.vec_[i] = Vector3f( pts[3 * i], pts[3 * i + 1], pts[3 * i + 2] );
+    const VertBitSet changed = m.topology.getValidVerts();
+    m.updateCaches( changed );
+    return 0;
+}
+
 /// dipoles: 8 floats each = pos xyz, area, dirArea xyz, rr
 void mrref_get_dipoles( void* h, float* out )
 {

@@ -54,6 +54,7 @@ def lib():
         L.mrref_find_projection_dist_sq.argtypes = [C.c_void_p, _f32p, C.c_size_t, C.c_float, C.c_float, _f32p]
         L.mrref_find_projections.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_float, C.c_float,
                                              C.c_void_p]
+        L.mrref_update_points.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
         L.mrref_signed_distance_proj_normal.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_float, C.c_float, C.c_int,
                                                         C.c_void_p, C.c_void_p]
         L.mrref_voxel_centres.argtypes = [_f32p, _f32p, _i32p, C.c_void_p]
@@ -166,6 +167,11 @@ class RefMesh:
         lib().mrref_find_projections(self.h, pts.ctypes.data, len(pts), None if px is None else px.ctypes.data,
                                      None if tx is None else tx.ctypes.data, up, lo, out.ctypes.data)
         return out
+
+    def update_points(self, pts):
+        """Mesh::updateCaches after moving every vertex: the cached AABB tree is refitted (AABBTree::refit), not rebuilt"""
+        pts = np.ascontiguousarray(pts, np.float32).reshape(-1, 3)
+        assert lib().mrref_update_points(self.h, pts.ctypes.data, len(pts)) == 0
 
     def signed_distance_proj_normal(self, pts, min_dist_sq=0.0, max_dist_sq=FLT_MAX, null_outside=True):
         """MR::signedDistanceToMesh with SignDetectionMode::ProjectionNormal (source/MRMesh/MRMeshDistance.cpp:13-38) per point:

@@ -689,3 +689,53 @@ def test_projection_normal_edge_cases():
     empty = mb.FastWindingNumber(np.zeros((0, 3), np.float32), np.zeros((0, 3), np.int32))
     assert np.isnan(empty.signed_distances_by_projection_normal(q[:100])).all()
     empty.close()
+
+
+# ---- moved vertices, refit instead of rebuild -------------------------------------------------------------
+
+def test_update_points_matches_reference_refit():
+    """b2fwn_update_points against Mesh::updateCaches (AABBTree::refit on the cached tree + calcDipoles): identical nodes and
+    dipoles, and every query on the refitted tree under the same parity rules as after a build"""
+    pts, tris = _mesh("noisy")
+    orc = checker.best_oracle(pts, tris)
+    if orc.kind != "reference":
+        pytest.skip("needs the reference library (the C restatement has no refit)")
+    old, rt = orc.points, orc.tris
+    fwn = mb.FastWindingNumber(old, rt)
+    nodes0, dip0 = fwn.get_tree()
+    new = old.copy()
+    new[:, 0] = np.float32(1.15) * old[:, 0] + np.float32(0.08) * np.sin(np.float32(3) * old[:, 1])
+    new[:, 2] = old[:, 2] + np.float32(0.1) * np.cos(np.float32(2) * old[:, 0])
+    new = new.astype(np.float32)
+    orc.update_points(new)
+    fwn.update_points(new)
+    nodes, dip = fwn.get_tree()
+    assert nodes.tobytes() == orc.nodes().tobytes() and dip.tobytes() == orc.dipoles().tobytes()
+    assert np.array_equal(nodes["l"], nodes0["l"]) and np.array_equal(nodes["r"], nodes0["r"]) and nodes.tobytes() != nodes0.tobytes()
+    q = meshgen.query_points(30000, float(new.min()) - 0.5, float(new.max()) + 0.5, seed=17)
+    rep = checker.compare_w(fwn.calc_from_vector(q), orc.calc_from_vector(q), atol=2e-6)
+    assert rep["ok"], rep
+    dims = (40, 33, 26)
+    lo, hi = new.min(0) - 0.3, new.max(0) + 0.3
+    xf = mb.make_basis_xf(lo, (hi - lo) / np.asarray(dims, np.float32))
+    w = orc.calc_from_grid(dims, xf)
+    got = fwn.calc_from_grid_with_distances(dims, xf)
+    rep = checker.compare_sdf(got, orc.calc_from_grid_with_distances(dims, xf), w)
+    assert rep["ok"] and rep["dist_bit_exact_frac"] > 0.999, rep
+    a, b = fwn.find_projections(q[:8000]), orc.find_projections(q[:8000])
+    for f_ in ("face", "point", "a", "b", "dist_sq"):
+        assert np.array_equal(a[f_].view(np.uint32), b[f_].view(np.uint32)), f_
+    want, dots = orc.signed_distance_proj_normal(q[:8000], null_outside=False)
+    _proj_normal_agrees(fwn.signed_distances_by_projection_normal(q[:8000], mb.DistOptions(0.0, mb.FLT_MAX, False)), want, dots)
+    # a fresh build at the new coordinates has another tree but the same distances
+    fresh = mb.FastWindingNumber(new, rt)
+    assert fresh.get_tree()[0].tobytes() != nodes.tobytes()
+    assert np.abs(fresh.calc_from_grid_with_distances(dims, xf)).tobytes() == np.abs(got).tobytes()
+    fresh.close()
+    # moving the vertices back gives the tree of the build again
+    fwn.update_points(old)
+    nodes2, dip2 = fwn.get_tree()
+    assert nodes2.tobytes() == nodes0.tobytes() and dip2.tobytes() == dip0.tobytes()
+    with pytest.raises(mb.B2Error):
+        fwn.update_points(old[:-1])
+    fwn.close()
