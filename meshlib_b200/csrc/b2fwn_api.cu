@@ -821,11 +821,21 @@ int b2fwn_mesh_to_distance_volume_by_projection_normal( b2fwn_handle h, const b2
     unsigned mm[2] = { 0xFFFFFFFFu, 0u };
     if ( total != 0 )
     {
-        // whole layers, about 8 Mi voxels per batch (44 B of scratch per voxel)
+        // whole layers, about 8 Mi voxels per batch.  Without a lower limit the distances come from the brick walk of the grid
+        // kernels (the closest triangle's slot kept per voxel, 8 B of scratch per voxel); with minDistSq > 0 the reference's
+        // early exit makes the answer depend on its visiting order, which only the per-point search reproduces (44 B per voxel)
+        // The brick walk is a dev switch (B2FWN_PROJ_BRICKS=1), not the default: (1) where several triangles are exactly equally
+        // close it may keep another one than the reference's search, and at a vertex the reference's mesh builder duplicated
+        // (non-manifold: the pole of a UV sphere with faces removed) the duplicates have different pseudonormals -- 1 voxel of
+        // 34,891 got the other sign (profiles/r01/diag_projbricks_n2.txt); (2) it measured 2 x faster over the full range of a
+        // sphere but 3.5 x slower in a narrow band than the Morton-ordered per-point search (r01).
+        const char* envBricks = getenv( "B2FWN_PROJ_BRICKS" );
+        const bool bricks = envBricks && atoi( envBricks ) && ( !opt->null_outside_min_max || opt->min_dist_sq <= 0.f );
         const int layers = (int)std::min<size_t>( std::max<size_t>( ( (size_t)8 << 20 ) / layer, 1 ), (size_t)dims[2] );
         if ( layer * layers > 0xFFFFFFFFull ) { setError( "grid layer too large" ); return B2FWN_ERR_INVALID; }
         ProjNormalBatch b{};
         if ( int e = projNormalBatch( h, layer * layers, b ) ) return e;
+        int32_t* dSlot = reinterpret_cast<int32_t*>( b.dPts ); // brick path: no point list, the slots take its place
         unsigned* dMM = nullptr;
         B2_CUDA( cudaMalloc( &dMM, sizeof( mm ) ) );
         cudaMemcpyAsync( dMM, mm, sizeof( mm ), cudaMemcpyHostToDevice, h->stream );
@@ -836,9 +846,19 @@ int b2fwn_mesh_to_distance_volume_by_projection_normal( b2fwn_handle h, const b2
             const int z1 = std::min( dims[2], z0 + layers );
             const size_t m = layer * ( z1 - z0 );
             cudaEventRecord( h->evA, h->stream );
-            rc = launchVoxelCentres( vol->origin, vol->voxel_size, dims[0], dims[1], z0, z1, b.dPts, h->stream, &h->stats.kernel_launches );
-            if ( !rc ) rc = launchSignedDistProjNormal( h->tree, b.dPts, m, opt->min_dist_sq, opt->max_dist_sq, opt->null_outside_min_max, b.dProj,
-                                                        b.dDist, h->stream, &h->stats.kernel_launches );
+            if ( bricks )
+            {
+                rc = launchDistSlotGrid( h->tree, dims, vol->origin, vol->voxel_size, opt->null_outside_min_max ? opt->max_dist_sq : FLT_MAX,
+                                         opt->null_outside_min_max, z0, z1, b.dDist, dSlot, h->stream, &h->stats.kernel_launches );
+                if ( !rc ) rc = launchSignBySlot( h->tree, dims, vol->origin, vol->voxel_size, z0, z1, b.dDist, dSlot, h->stream,
+                                                  &h->stats.kernel_launches );
+            }
+            else
+            {
+                rc = launchVoxelCentres( vol->origin, vol->voxel_size, dims[0], dims[1], z0, z1, b.dPts, h->stream, &h->stats.kernel_launches );
+                if ( !rc ) rc = launchSignedDistProjNormal( h->tree, b.dPts, m, opt->min_dist_sq, opt->max_dist_sq, opt->null_outside_min_max, b.dProj,
+                                                            b.dDist, h->stream, &h->stats.kernel_launches );
+            }
             if ( rc ) break;
             kMinMax<<<(unsigned)std::min<size_t>( ( m + 255 ) / 256, 148 * 8 ), 256, 0, h->stream>>>( b.dDist, m, dMM );
             ++h->stats.kernel_launches;

@@ -322,11 +322,14 @@ __global__ void __launch_bounds__( 256 ) kGroupHeavy( const TravNode* __restrict
 // The result is the exact minimum over all triangles of the reference's per-triangle value, hence independent of the order.
 // 8 blocks per SM (64 registers, ~200 B of spills) measured faster than the spill-free 118 registers at 4 blocks: c3_full
 // 626 -> 535 ms, c5_band 1221 -> 1150 ms -- the walk is latency-bound (one dependent node fetch after another)
-template <bool AA, bool STATS, int MINB = 8>
+// PROJ (SignDetectionMode::ProjectionNormal over a volume): the voxel centres are origin + voxelSize * ( pos + 0.5 ), rounded
+// like meshToDistanceFunctionVolume rounds them (P.b = origin, P.A = diag( voxelSize )), and the leaf slot of the closest
+// triangle is stored beside the distance -- the sign kernel (b2fwn_normals.cu) recomputes the closest point on that one triangle
+template <bool AA, bool STATS, int MINB = 8, bool PROJ = false>
 __global__ void __launch_bounds__( GRID_TB, MINB ) kGridDist( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
                                                         const LeafFilt* __restrict__ filt, const GridParams P, float* __restrict__ out,
                                                         const uint16_t* __restrict__ cullCost, const BrickOrder O,
-                                                        unsigned long long* __restrict__ stats )
+                                                        unsigned long long* __restrict__ stats, int32_t* __restrict__ slotOut = nullptr )
 {
     unsigned cnt[5] = { 0, 0, 0, 0, 0 };
     const unsigned lane = threadIdx.x & 31;
@@ -337,13 +340,19 @@ __global__ void __launch_bounds__( GRID_TB, MINB ) kGridDist( const TravNode* __
 
     float3 p[VX];
     float pmag[VX], best[VX], lim[VX], sbest[VX]; // lim = best while the voxel still searches, -1 once it stopped; sbest = sqrt(best)
+    int bslot[PROJ ? VX : 1];                     // PROJ: leaf slot of the closest triangle so far
 #pragma unroll
     for ( int v = 0; v < VX; ++v )
     {
         const bool valid = B.rowValid && B.x0 + v < P.dx;
-        p[v] = applyXf( P.A, P.b, (float)( B.x0 + v ), (float)B.y, (float)B.z );
+        if ( PROJ )
+            p[v] = make_float3( __fadd_rn( P.b[0], __fmul_rn( P.A[0], (float)( B.x0 + v ) + 0.5f ) ), __fadd_rn( P.b[1], __fmul_rn( P.A[4], (float)B.y + 0.5f ) ),
+                                __fadd_rn( P.b[2], __fmul_rn( P.A[8], (float)B.z + 0.5f ) ) ); // MRMeshToDistanceVolume.cpp:83-84
+        else
+            p[v] = applyXf( P.A, P.b, (float)( B.x0 + v ), (float)B.y, (float)B.z );
         if ( AA ) { p[v].y = p[0].y; p[v].z = p[0].z; } // axis-aligned grid: the lane's voxels share y, z (see kGridFwn)
         pmag[v] = 1e-6f * ( fabsf( p[v].x ) + fabsf( p[v].y ) + fabsf( p[v].z ) );
+        if ( PROJ ) bslot[v] = -1;
         best[v] = P.maxDistSq;
         sbest[v] = sqrtf( P.maxDistSq );
         lim[v] = valid ? P.maxDistSq : -1.f;
@@ -391,6 +400,7 @@ __global__ void __launch_bounds__( GRID_TB, MINB ) kGridDist( const TravNode* __
                         {
                             best[v] = cand;
                             sbest[v] = sqrtf( cand );
+                            if ( PROJ ) bslot[v] = slot;
                             lim[v] = cand <= P.minDistSq ? -1.f : cand; // MRMeshProject.cpp:81-82: this voxel stops searching
                         }
                     }
@@ -454,6 +464,12 @@ __global__ void __launch_bounds__( GRID_TB, MINB ) kGridDist( const TravNode* __
 #pragma unroll
         for ( int v = 0; v < VX; ++v )
             if ( B.x0 + v < P.dx ) out[B.id + v] = res[v];
+    }
+    if ( PROJ )
+    {
+#pragma unroll
+        for ( int v = 0; v < VX; ++v )
+            if ( B.x0 + v < P.dx ) slotOut[B.id + v] = bslot[v];
     }
 }
 
@@ -984,6 +1000,50 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
 }
 
 } // anonymous namespace
+
+// Distance pass alone for SignDetectionMode::ProjectionNormal over the layers [zBegin, zEnd) of a volume: dOut = |d| (NaN outside
+// [minDistSq, maxDistSq) when nullOutside), dSlot = leaf slot of the closest triangle per voxel (-1 = none).  Voxel centres are
+// origin + voxelSize * ( pos + 0.5 ); minDistSq must be 0 (an early exit would depend on the visiting order).
+int launchDistSlotGrid( const DeviceTree& t, const int32_t dims[3], const float origin[3], const float voxelSize[3], float maxDistSq,
+                        int nullOutside, int zBegin, int zEnd, float* dOut, int32_t* dSlot, cudaStream_t st, uint64_t* launches )
+{
+    if ( int e = checkDims( dims, zBegin, zEnd ) ) return e;
+    if ( dims[0] == 0 || dims[1] == 0 || zEnd == zBegin ) return B2FWN_OK;
+    GridParams P{};
+    P.dx = dims[0]; P.dy = dims[1]; P.zBegin = zBegin;
+    P.nz = zEnd - zBegin; P.zChunk = INT_MAX / 2; P.zSkip = 0;
+    P.bricksX = ( dims[0] + BX - 1 ) / BX;
+    P.bricksY = ( dims[1] + BY - 1 ) / BY;
+    P.bricksZ = ( P.nz + BZ - 1 ) / BZ;
+    P.A[0] = voxelSize[0]; P.A[4] = voxelSize[1]; P.A[8] = voxelSize[2];
+    P.minDistSq = 0.f; P.maxDistSq = maxDistSq; P.nullOutside = nullOutside;
+    P.numNodes = (int)t.numNodes;
+    P.vecStore = ( dims[0] % VX == 0 ) && ( reinterpret_cast<uintptr_t>( dOut ) % 16 == 0 );
+    const size_t numBricks = (size_t)P.bricksX * P.bricksY * P.bricksZ;
+    const size_t blocks = ( numBricks + GRID_TB / 32 - 1 ) / ( GRID_TB / 32 );
+    if ( blocks > 0x7FFFFFFFull ) { setError( "grid too large for one launch" ); return B2FWN_ERR_INVALID; }
+    // the brick cull works on boxes of voxel centres: the usual basis form b = origin + 0.5 * voxelSize is exact enough for it
+    // (its boxes are padded); the distance kernel itself takes the origin form
+    GridParams Pc = P;
+    for ( int k = 0; k < 3; ++k ) { Pc.b[k] = origin[k] + 0.5f * voxelSize[k]; P.b[k] = origin[k]; }
+    const bool band = maxDistSq < FLT_MAX && P.numNodes > 0;
+    uint8_t* scratch = nullptr;
+    const size_t nbPad = ( numBricks + 15 ) & ~(size_t)15;
+    uint16_t* costD = nullptr;
+    if ( band )
+    {
+        B2_CUDA( cudaMallocAsync( &scratch, 64 + nbPad * sizeof( uint16_t ), st ) );
+        B2_CUDA( cudaMemsetAsync( scratch, 0, 64, st ) );
+        costD = reinterpret_cast<uint16_t*>( scratch + 64 );
+        kBrickCull<<<(unsigned)( ( numBricks + 255 ) / 256 ), 256, 0, st>>>( t.nodes, Pc, costD, reinterpret_cast<unsigned long long*>( scratch ) );
+        if ( launches ) ++*launches;
+    }
+    kGridDist<true, false, 8, true><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, costD, BrickOrder{}, nullptr, dSlot );
+    if ( launches ) ++*launches;
+    if ( scratch ) B2_CUDA( cudaFreeAsync( scratch, st ) );
+    B2_CUDA( cudaGetLastError() );
+    return B2FWN_OK;
+}
 
 int launchFwnGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, float beta, int zBegin, int zEnd,
                    float* dOut, cudaStream_t st, uint64_t* launches, const ZChunks* zc )

@@ -137,6 +137,12 @@ int launchFindProjections( const DeviceTree& t, const float* dPts, size_t n, con
 int ensurePseudoNormals( DeviceTree& t, cudaStream_t stream, uint64_t* launches );
 int launchSignedDistProjNormal( DeviceTree& t, const float* dPts, size_t n, float minDistSq, float maxDistSq, int nullOutside,
                                 b2fwn_projection* dProj, float* dOut, cudaStream_t stream, uint64_t* launches );
+// the same over the layers [z0, z1) of a volume by the brick walk: launchDistSlotGrid (b2fwn_grid.cu) leaves |d| / NaN in dVol and
+// the leaf slot of the closest triangle in dSlot, launchSignBySlot (b2fwn_normals.cu) turns dVol into signed distances
+int launchDistSlotGrid( const DeviceTree& t, const int32_t dims[3], const float origin[3], const float voxelSize[3], float maxDistSq,
+                        int nullOutside, int zBegin, int zEnd, float* dOut, int32_t* dSlot, cudaStream_t stream, uint64_t* launches );
+int launchSignBySlot( DeviceTree& t, const int32_t dims[3], const float origin[3], const float voxelSize[3], int z0, int z1, float* dVol,
+                      const int32_t* dSlot, cudaStream_t stream, uint64_t* launches );
 // voxel centres of the layers [z0, z1) of a volume, as meshToDistanceFunctionVolume computes them
 int launchVoxelCentres( const float origin[3], const float voxelSize[3], int dx, int dy, int z0, int z1, float* dPts, cudaStream_t stream,
                         uint64_t* launches );

@@ -10,6 +10,7 @@
 //                        vertex normal can differ; signs differ only where the dot product is within rounding of zero)
 // Compiled with -fmad=false: the arithmetic is b2fwn_normals_math.h, operation by operation as the reference's.
 #include "b2fwn_internal.h"
+#include "b2fwn_math.cuh"
 #include "b2fwn_normals_math.h"
 
 #include <cub/cub.cuh>
@@ -124,6 +125,49 @@ __global__ void __launch_bounds__( 256 ) kSignByProjNormal( const b2fwn_projecti
     out[i] = outsideByNormal( v3( r0.y, r0.z, r0.w ), pt, nrm ) ? dist : -dist;
 }
 
+// The volume form on top of the brick walk (kGridDist<PROJ>): vol holds |d| (NaN = outside the limits), slot the leaf slot of
+// the closest triangle.  One more closest-point evaluation on that triangle (closestPointInTriangle in double, as the walk did)
+// gives the point and its barycentrics; then the same sign rule as kSignByProjNormal.  Where two triangles are equally close
+// (closest point on their common edge or vertex) the walk may have kept another one than the reference's search: the
+// pseudonormal of an edge or a vertex does not depend on which of its faces reported it.
+__global__ void __launch_bounds__( 256 ) kSignBySlot( float* __restrict__ vol, const int32_t* __restrict__ slot, const LeafTri* __restrict__ leafTris,
+                                                      const int32_t* __restrict__ tris, const float* __restrict__ faceNormals,
+                                                      const float* __restrict__ vertNormals, const int32_t* __restrict__ faceAdj,
+                                                      const float ox, const float oy, const float oz, const float vx, const float vy, const float vz,
+                                                      const int dx, const int dy, const int z0, const size_t n )
+{
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if ( i >= n ) return;
+    const float d = vol[i];
+    if ( d != d ) return;
+    const int s = slot[i];
+    if ( s < 0 ) { vol[i] = __int_as_float( 0x7FC00000 ); return; } // no projection found (MRMeshDistance.cpp:27-28)
+    const size_t layer = (size_t)dx * dy;
+    const int z = z0 + (int)( i / layer );
+    const size_t r = i % layer;
+    const int y = (int)( r / dx ), x = (int)( r % dx );
+    const float3 p = make_float3( voxelCentre( ox, vx, x ), voxelCentre( oy, vy, y ), voxelCentre( oz, vz, z ) );
+    const float4* tp = reinterpret_cast<const float4*>( leafTris + s );
+    const float4 ta = __ldg( tp ), tb = __ldg( tp + 1 ), tc = __ldg( tp + 2 );
+    const int f = __float_as_int( ta.w );
+    double rx, ry, rz, va, vb;
+    closestPointBary( p, make_float3( ta.x, ta.y, ta.z ), make_float3( tb.x, tb.y, tb.z ), make_float3( tc.x, tc.y, tc.z ), rx, ry, rz, va, vb );
+    const TriSite site = triSite( __double2float_rn( va ), __double2float_rn( vb ) );
+    V3 nrm;
+    if ( site.vertex >= 0 ) nrm = ldPoint( vertNormals, tris[3 * (size_t)f + site.vertex] );
+    else
+    {
+        nrm = ldPoint( faceNormals, f );
+        if ( site.edge >= 0 )
+        {
+            const int g = faceAdj[3 * (size_t)f + site.edge];
+            nrm = edgeNormal( nrm, g >= 0 ? ldPoint( faceNormals, g ) : nrm, g >= 0 );
+        }
+    }
+    const V3 proj = v3( __double2float_rn( rx ), __double2float_rn( ry ), __double2float_rn( rz ) );
+    vol[i] = outsideByNormal( proj, v3( p.x, p.y, p.z ), nrm ) ? d : -d;
+}
+
 __global__ void __launch_bounds__( 256 ) kVoxelCentres( const float ox, const float oy, const float oz, const float vx, const float vy, const float vz,
                                                         const int dx, const int dy, const int z0, const size_t n, float* __restrict__ out )
 {
@@ -190,6 +234,19 @@ int launchSignedDistProjNormal( DeviceTree& t, const float* dPts, size_t n, floa
     if ( int e = launchFindProjections( t, dPts, n, nullptr, nullptr, up, lo, dProj, st, launches ) ) return e;
     kSignByProjNormal<<<nblk( n ), 256, 0, st>>>( dProj, dPts, n, t.tris, t.faceNormals, t.vertNormals, t.faceAdj, minDistSq, maxDistSq,
                                                   nullOutside, dOut );
+    if ( launches ) ++*launches;
+    B2_CUDA( cudaGetLastError() );
+    return B2FWN_OK;
+}
+
+int launchSignBySlot( DeviceTree& t, const int32_t dims[3], const float origin[3], const float voxelSize[3], int z0, int z1, float* dVol,
+                      const int32_t* dSlot, cudaStream_t st, uint64_t* launches )
+{
+    const size_t n = (size_t)dims[0] * dims[1] * ( z1 - z0 );
+    if ( n == 0 ) return B2FWN_OK;
+    if ( int e = ensurePseudoNormals( t, st, launches ) ) return e; // no tables for a mesh without faces: every slot is -1 then
+    kSignBySlot<<<nblk( n ), 256, 0, st>>>( dVol, dSlot, t.leafTris, t.tris, t.faceNormals, t.vertNormals, t.faceAdj, origin[0], origin[1], origin[2],
+                                           voxelSize[0], voxelSize[1], voxelSize[2], dims[0], dims[1], z0, n );
     if ( launches ) ++*launches;
     B2_CUDA( cudaGetLastError() );
     return B2FWN_OK;

@@ -32,56 +32,6 @@ struct Xf12
     float b[3];
 };
 
-// closestPointInTriangle<double> (MRClosestPointInTriangle.h:27-87) with its barycentric pair; same operations, same order
-__device__ __forceinline__ void closestPointBary( const float3 pf, const float3 fa, const float3 fb, const float3 fc,
-                                                  double& rx, double& ry, double& rz, double& ba, double& bb )
-{
-    const double px = pf.x, py = pf.y, pz = pf.z;
-    const double ax = fa.x, ay = fa.y, az = fa.z, bx = fb.x, by = fb.y, bz = fb.z, cx = fc.x, cy = fc.y, cz = fc.z;
-    const double abx = DS( bx, ax ), aby = DS( by, ay ), abz = DS( bz, az );
-    const double acx = DS( cx, ax ), acy = DS( cy, ay ), acz = DS( cz, az );
-    const double apx = DS( px, ax ), apy = DS( py, ay ), apz = DS( pz, az );
-    const double d1 = ddot3( abx, aby, abz, apx, apy, apz );
-    const double d2 = ddot3( acx, acy, acz, apx, apy, apz );
-    if ( d1 <= 0 && d2 <= 0 ) { rx = ax; ry = ay; rz = az; ba = 0; bb = 0; return; } // #1
-    const double bpx = DS( px, bx ), bpy = DS( py, by ), bpz = DS( pz, bz );
-    const double d3 = ddot3( abx, aby, abz, bpx, bpy, bpz );
-    const double d4 = ddot3( acx, acy, acz, bpx, bpy, bpz );
-    if ( d3 >= 0 && d4 <= d3 ) { rx = bx; ry = by; rz = bz; ba = 1; bb = 0; return; } // #2
-    const double cpx = DS( px, cx ), cpy = DS( py, cy ), cpz = DS( pz, cz );
-    const double d5 = ddot3( abx, aby, abz, cpx, cpy, cpz );
-    const double d6 = ddot3( acx, acy, acz, cpx, cpy, cpz );
-    if ( d6 >= 0 && d5 <= d6 ) { rx = cx; ry = cy; rz = cz; ba = 0; bb = 1; return; } // #3
-    const double vc = DS( DM( d1, d4 ), DM( d3, d2 ) );
-    if ( vc <= 0 && d1 >= 0 && d3 <= 0 )
-    {
-        const double v = d1 / DS( d1, d3 );
-        rx = DA( ax, DM( v, abx ) ); ry = DA( ay, DM( v, aby ) ); rz = DA( az, DM( v, abz ) ); ba = v; bb = 0; return; // #4
-    }
-    const double vb = DS( DM( d5, d2 ), DM( d1, d6 ) );
-    if ( vb <= 0 && d6 <= 0 && d2 >= 0 )
-    {
-        const double v = d2 / DS( d2, d6 );
-        rx = DA( ax, DM( v, acx ) ); ry = DA( ay, DM( v, acy ) ); rz = DA( az, DM( v, acz ) ); ba = 0; bb = v; return; // #5
-    }
-    const double va = DS( DM( d3, d6 ), DM( d5, d4 ) );
-    if ( va <= 0 )
-    {
-        if ( d4 < d3 ) { rx = bx; ry = by; rz = bz; ba = 1; bb = 0; return; }
-        if ( d5 < d6 ) { rx = cx; ry = cy; rz = cz; ba = 0; bb = 1; return; }
-        const double e = DS( d4, d3 ), g = DS( d5, d6 );
-        const double v = e / DA( e, g );
-        rx = DA( bx, DM( v, DS( cx, bx ) ) ); ry = DA( by, DM( v, DS( cy, by ) ) ); rz = DA( bz, DM( v, DS( cz, bz ) ) );
-        ba = DS( 1.0, v ); bb = v; return; // #6
-    }
-    const double denom = 1.0 / DA( DA( va, vb ), vc );
-    const double v = DM( vb, denom ), w = DM( vc, denom );
-    rx = DA( DA( ax, DM( v, abx ) ), DM( w, acx ) );
-    ry = DA( DA( ay, DM( v, aby ) ), DM( w, acy ) );
-    rz = DA( DA( az, DM( v, abz ) ), DM( w, acz ) ); // #0
-    ba = v; bb = w;
-}
-
 template <bool TXF>
 __device__ __forceinline__ float nodeBoxDistSq( const TravNode* __restrict__ nodes, const int n, const Xf12& treeXf, const float3 pt, int& right, int& link )
 {

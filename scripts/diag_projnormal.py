@@ -14,7 +14,7 @@ fwn = mb.FastWindingNumber(pts, tris)
 n = 256
 voxel = 2.4 / n
 t0 = time.perf_counter()
-fwn.signed_distances_by_projection_normal(np.zeros((1, 3), np.float32))
+fwn.signed_distances_by_projection_normal(np.array([[1.5, 0.2, 0.1]], np.float32))
 print(f"pseudonormal tables ({len(tris)} faces) + first call: {(time.perf_counter() - t0) * 1e3:.1f} ms")
 for label, opt in (("full range", mb.DistOptions(0.0, mb.FLT_MAX, False)), ("band 3 voxels, NaN outside", mb.DistOptions(0.0, (3 * voxel) ** 2, True))):
     for _ in range(2):
