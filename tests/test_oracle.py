@@ -187,3 +187,83 @@ def test_projection_normal_arithmetic_of_the_device_header_vs_reference(name):
     # voxel centres of meshToDistanceFunctionVolume
     args = ((-1.37, 0.21, 3.3), (0.013, 0.07, 0.11), (17, 9, 5))
     assert normalslib.voxel_centres(*args).tobytes() == reflib.voxel_centres(*args).tobytes()
+
+
+# ---- golden fixture of the SURVEY 8f rows (tests/golden/ref_golden_next.npz) ----------------------------------------------
+
+class _PortAndHeader:
+    """the CPU restatements: oracle/port.c for projections and winding numbers, the product's normals header run on the host
+    (oracle/normals_host.cpp) for the ProjectionNormal sign; no refit in the restatement"""
+
+    def __init__(self, pts, tris):
+        from oracle import normalslib
+        self.m, self.pts, self.tris = portlib.PortMesh(pts, tris), pts, tris
+        self.tabs = normalslib.tables(pts, tris) if normalslib.available() else None
+
+    def find_projections(self, q, up, lo):
+        return self.m.find_projections(q, up=up, lo=lo)
+
+    def signed_distance_pn(self, q, min_dist_sq, max_dist_sq, null_outside):
+        from oracle import normalslib
+        if self.tabs is None:
+            return None
+        lo, up = (min_dist_sq, max_dist_sq) if null_outside else (0.0, reflib.FLT_MAX)
+        rec = self.m.find_projections(q, up=up, lo=lo)
+        return normalslib.sign(rec, q, self.tris, self.tabs, min_dist_sq, max_dist_sq, null_outside)
+
+    def make_signed(self, unsigned, dims, xf, threshold, beta):
+        from oracle import checker
+        return checker.ref_make_signed_by_winding_number(self.m, unsigned, dims, xf, threshold, beta)[0]
+
+    def refit(self, new_points):
+        return None
+
+
+class _Reference:
+    def __init__(self, pts, tris):
+        self.m = reflib.RefMesh.from_arrays(pts, tris)
+        assert self.m.tris.tobytes() == np.ascontiguousarray(tris, np.int32).tobytes()  # fixture holds getTriangulation's order
+
+    def find_projections(self, q, up, lo):
+        return self.m.find_projections(q, up=up, lo=lo)
+
+    def signed_distance_pn(self, q, min_dist_sq, max_dist_sq, null_outside):
+        return self.m.signed_distance_proj_normal(q, min_dist_sq, max_dist_sq, null_outside)[0]
+
+    def make_signed(self, unsigned, dims, xf, threshold, beta):
+        from oracle import checker
+        return checker.ref_make_signed_by_winding_number(self.m, unsigned, dims, xf, threshold, beta)[0]
+
+    def refit(self, new_points):
+        self.m.update_points(new_points)
+        return self.m.nodes(), self.m.dipoles(), self.m.calc_from_vector(self.q)
+
+
+@pytest.mark.parametrize("name", ["torus", "noisy_sphere"])
+def test_restatements_against_golden_next_fixture(name):
+    """projection records, ProjectionNormal signed distances and the makeSignedByWindingNumber loop of the CPU restatements
+    against vectors generated from the unmodified reference (runs without /root/reference)"""
+    import golden_next_check as gc
+    g = gc.load()
+    ran = gc.check(_PortAndHeader, g, name)
+    assert f"{name}_proj" in ran and f"{name}_proj_limits" in ran and f"{name}_signed" in ran
+    from oracle import normalslib
+    assert (f"{name}_pn" in ran and f"{name}_pn_band" in ran) or not normalslib.available()
+    # face normals of the header bit for bit, vertex pseudonormals up to the ring order
+    if normalslib.available():
+        fn, vn, _adj = normalslib.tables(g[f"{name}_points"], g[f"{name}_tris"])
+        assert fn.tobytes() == g[f"{name}_face_normals"].tobytes()
+        assert np.abs(vn - g[f"{name}_vert_normals"]).max() < 2e-6
+
+
+@needs_ref
+@pytest.mark.parametrize("name", ["torus", "noisy_sphere"])
+def test_golden_next_fixture_is_what_the_reference_gives(name):
+    import golden_next_check as gc
+    g = gc.load()
+
+    def make(pts, tris):
+        r = _Reference(pts, tris)
+        r.q = g[f"{name}_q"]
+        return r
+    assert len(gc.check(make, g, name, w_atol=0.0)) == 6
