@@ -133,6 +133,20 @@ public:
                                                               &progress_, (void*)&cb ) );
     }
 
+    /// Beyond the interface: signedDistanceToMesh with SignDetectionMode::ProjectionNormal for a vector of points
+    /// (source/MRMesh/MRMeshDistance.cpp:13-59): res[i] = distance to the closest point of the mesh, negative where the
+    /// pseudonormal at that point says inside, NaN outside [minDistSq, maxDistSq) when options.nullOutsideMinMax.
+    /// options.signMode is not consulted; the winding-number fields are not used.
+    Expected<void> signedDistancesByProjectionNormal( std::vector<float>& res, const std::vector<Vector3f>& points,
+                                                      const DistanceToMeshOptions& options, const ProgressCallback& cb = {} )
+    {
+        if ( auto e = prepare_(); !e ) return e;
+        res.resize( points.size() );
+        const b2fwn_dist_options o = packOptions_( options );
+        return status_( b2fwn_signed_distances_by_projection_normal( h_, reinterpret_cast<const float*>( points.data() ), points.size(), &o,
+                                                                      res.data(), &progress_, (void*)&cb ) );
+    }
+
     /// Beyond the interface: the mesh this object was made for had its vertices moved (same topology).
     /// Counterpart of Mesh::updateCaches( changedVerts ) (source/MRMesh/MRMesh.cpp:565-578): the device tree is refitted like
     /// AABBTree::refit (MRAABBTree.cpp:62-94), dipoles and leaf triangles are recomputed -- no re-upload of the triangulation,
