@@ -542,6 +542,50 @@ void* orc_create( const float* pts, size_t nv, const int32_t* tris, size_t nf )
     return m;
 }
 
+/* Mesh::updateCaches with every vertex changed (MRMesh/MRMesh.cpp:565-578): AABBTree::refit (MRAABBTree.cpp:62-94) -- leaf boxes
+ * by computeFaceBox at the new coordinates, then inner boxes in decreasing node order, box = left box, include( right box ) --
+ * and the dipoles recomputed on the refitted tree (dipolesOwner_.reset(), calcDipoles on next use).  The topology stays. */
+int orc_update_points( void* h, const float* pts, size_t nv )
+{
+    OMesh* m = (OMesh*)h;
+    if ( nv != m->nv ) return 1;
+    memcpy( m->pts, pts, nv * 12 );
+    const int N = m->nNodes;
+    for ( int i = 0; i < N; ++i )
+    {
+        Node* nd = &m->nodes[i];
+        if ( nd->r >= 0 ) continue;
+        float p[3][3];
+        triPoints( m, nd->l, p[0], p[1], p[2] );
+        for ( int d = 0; d < 3; ++d )
+        {
+            float mn = FLT_MAX, mx = -FLT_MAX;
+            for ( int v = 0; v < 3; ++v )
+            {
+                if ( p[v][d] < mn ) mn = p[v][d];
+                if ( p[v][d] > mx ) mx = p[v][d];
+            }
+            nd->mn[d] = nextafterf( mn, -FLT_MAX );
+            nd->mx[d] = nextafterf( mx, FLT_MAX );
+        }
+    }
+    for ( int i = N - 1; i >= 0; --i )
+    {
+        Node* nd = &m->nodes[i];
+        if ( nd->r < 0 ) continue;
+        const Node *l = &m->nodes[nd->l], *r = &m->nodes[nd->r];
+        for ( int d = 0; d < 3; ++d )
+        {
+            nd->mn[d] = l->mn[d]; nd->mx[d] = l->mx[d];
+            if ( r->mn[d] < nd->mn[d] ) nd->mn[d] = r->mn[d]; /* Box::include( Box ), MRBox.h */
+            if ( r->mx[d] > nd->mx[d] ) nd->mx[d] = r->mx[d];
+        }
+    }
+    free( m->dip ); m->dip = NULL;
+    calcDipoles( m );
+    return 0;
+}
+
 void orc_destroy( void* h )
 {
     OMesh* m = (OMesh*)h;

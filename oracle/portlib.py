@@ -28,6 +28,7 @@ def lib():
         L.orc_num_nodes.restype = sz
         L.orc_num_nodes.argtypes = [vp]
         L.orc_get_nodes.argtypes = [vp, vp]
+        L.orc_update_points.argtypes = [vp, vp, sz]
         L.orc_get_dipoles.argtypes = [vp, vp]
         L.orc_calc_from_vector.argtypes = [vp, vp, sz, C.c_float, C.c_int32, vp, vp]
         L.orc_calc_self_intersections.argtypes = [vp, C.c_float, vp, vp]
@@ -112,6 +113,12 @@ class PortMesh:
 
     def counter_dict(self):
         return dict(zip(COUNTER_NAMES, (int(x) for x in self.counters)))
+
+    def update_points(self, pts):
+        """Mesh::updateCaches with every vertex moved: AABBTree::refit (MRAABBTree.cpp:62-94) + dipoles on the refitted tree"""
+        pts = np.ascontiguousarray(pts, np.float32).reshape(-1, 3)
+        assert lib().orc_update_points(self.h, pts.ctypes.data, len(pts)) == 0
+        self.points = pts
 
     def nodes(self):
         out = np.empty(lib().orc_num_nodes(self.h), NODE_DTYPE)

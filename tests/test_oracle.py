@@ -192,8 +192,8 @@ def test_projection_normal_arithmetic_of_the_device_header_vs_reference(name):
 # ---- golden fixture of the SURVEY 8f rows (tests/golden/ref_golden_next.npz) ----------------------------------------------
 
 class _PortAndHeader:
-    """the CPU restatements: oracle/port.c for projections and winding numbers, the product's normals header run on the host
-    (oracle/normals_host.cpp) for the ProjectionNormal sign; no refit in the restatement"""
+    """the CPU restatements: oracle/port.c for projections, winding numbers and the refit, the product's normals header run on
+    the host (oracle/normals_host.cpp) for the ProjectionNormal sign"""
 
     def __init__(self, pts, tris):
         from oracle import normalslib
@@ -216,7 +216,8 @@ class _PortAndHeader:
         return checker.ref_make_signed_by_winding_number(self.m, unsigned, dims, xf, threshold, beta)[0]
 
     def refit(self, new_points):
-        return None
+        self.m.update_points(new_points)
+        return self.m.nodes(), self.m.dipoles(), self.m.calc_from_vector(self.q)
 
 
 class _Reference:
@@ -245,8 +246,13 @@ def test_restatements_against_golden_next_fixture(name):
     against vectors generated from the unmodified reference (runs without /root/reference)"""
     import golden_next_check as gc
     g = gc.load()
-    ran = gc.check(_PortAndHeader, g, name)
-    assert f"{name}_proj" in ran and f"{name}_proj_limits" in ran and f"{name}_signed" in ran
+
+    def make(pts, tris):
+        m = _PortAndHeader(pts, tris)
+        m.q = g[f"{name}_q"]
+        return m
+    ran = gc.check(make, g, name, w_atol=0.0)
+    assert f"{name}_proj" in ran and f"{name}_proj_limits" in ran and f"{name}_signed" in ran and f"{name}_refit" in ran
     from oracle import normalslib
     assert (f"{name}_pn" in ran and f"{name}_pn_band" in ran) or not normalslib.available()
     # face normals of the header bit for bit, vertex pseudonormals up to the ring order
