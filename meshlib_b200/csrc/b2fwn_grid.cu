@@ -820,6 +820,71 @@ __global__ void __launch_bounds__( GRID_TB, MINB ) kGridFwn5( const TravNode* __
     }
 }
 
+// EXPERIMENT (B2FWN_FWN8=1, not the default, not yet measured): the same walk with 8 voxels per lane -- bricks of 16x4x4, so the
+// warp-uniform part of a node visit (two 16-B loads, the all-near test, one redux.min) is paid once per 256 voxels instead
+// of once per 128.  Per-voxel arithmetic is fwnWalk's, so every voxel gets the same bits as from kGridFwn5.  Plain linear
+// brick order (P.bricksX counts 16-wide bricks); no peer stores.  The distances of MODE 1 are re-read at the end instead of
+// being kept in registers across the walk.
+constexpr int VX8 = 8, BX8 = 16;
+template <int MODE, bool AA>
+__global__ void __launch_bounds__( GRID_TB, 8 ) kGridFwn8( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
+                                                     const GridParams P, float* __restrict__ out )
+{
+    const size_t brick = blockIdx.x * (size_t)( GRID_TB / 32 ) + ( threadIdx.x >> 5 );
+    if ( brick >= (size_t)P.bricksX * P.bricksY * P.bricksZ ) return;
+    const int lane = threadIdx.x & 31;
+    const int bx = (int)( brick % P.bricksX ), by = (int)( ( brick / P.bricksX ) % P.bricksY ), bz = (int)( brick / ( (size_t)P.bricksX * P.bricksY ) );
+    const int x0 = bx * BX8 + ( lane & 1 ) * VX8, y = by * BY + ( ( lane >> 1 ) & 3 ), z = globalZ( P, bz * BZ ) + ( lane >> 3 );
+    const bool rowValid = y < P.dy && bz * BZ + ( lane >> 3 ) < P.nz;
+    const size_t id = (size_t)x0 + (size_t)P.dx * ( (size_t)y + (size_t)P.dy * (size_t)( z - P.zBegin ) );
+    const bool vec = P.vecStore && x0 + VX8 <= P.dx;
+
+    float3 p[VX8];
+    float sum[VX8];
+    int fR[VX8];
+#pragma unroll
+    for ( int v = 0; v < VX8; ++v )
+    {
+        bool valid = rowValid && x0 + v < P.dx;
+        if ( MODE == 1 && valid ) { const float d = out[id + v]; valid = !( d != d ); }
+        p[v] = applyXf( P.A, P.b, (float)( x0 + v ), (float)y, (float)z );
+        if ( AA ) { p[v].y = p[0].y; p[v].z = p[0].z; }
+        sum[v] = 0.f;
+        fR[v] = valid ? 0 : INT_MAX;
+    }
+    const float3 pc = applyXf( P.A, P.b, (float)( bx * BX8 ) + 7.5f, (float)( by * BY ) + 1.5f, (float)globalZ( P, bz * BZ ) + 1.5f );
+    float rad = 0.f;
+#pragma unroll
+    for ( int v = 0; v < VX8; ++v )
+    {
+        const float ex = p[v].x - pc.x, ey = p[v].y - pc.y, ez = p[v].z - pc.z;
+        rad = fmaxf( rad, ex * ex + ey * ey + ez * ez );
+    }
+    rad = sqrtf( __uint_as_float( __reduce_max_sync( FULL, __float_as_uint( rad ) ) ) ) * 1.00001f;
+
+    fwnWalk<VX8>( nodes, tris, P.numNodes, P.betaSq, p, pc, rad, sum, fR );
+
+    if ( !rowValid ) return;
+    float res[VX8];
+#pragma unroll
+    for ( int v = 0; v < VX8; ++v )
+    {
+        const float d = ( MODE == 1 && x0 + v < P.dx ) ? out[id + v] : 0.f;
+        res[v] = fwnResult( MODE, sum[v], d, P.threshold );
+    }
+    if ( vec )
+    {
+        *reinterpret_cast<float4*>( out + id ) = make_float4( res[0], res[1], res[2], res[3] );
+        *reinterpret_cast<float4*>( out + id + 4 ) = make_float4( res[4], res[5], res[6], res[7] );
+    }
+    else
+    {
+#pragma unroll
+        for ( int v = 0; v < VX8; ++v )
+            if ( x0 + v < P.dx ) out[id + v] = res[v];
+    }
+}
+
 inline int checkDims( const int32_t dims[3], int zBegin, int zEnd )
 {
     if ( dims[0] < 0 || dims[1] < 0 || dims[2] < 0 || zBegin < 0 || zEnd > dims[2] || zBegin > zEnd )
@@ -972,7 +1037,17 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
         }
         if ( sideEst ) B2_CUDA( cudaStreamWaitEvent( st, t.evJoin, 0 ) );
         PeerOut po{};
-        if ( peers && peers->n > 0 )
+        static const bool fwn8 = getenv( "B2FWN_FWN8" ) && atoi( getenv( "B2FWN_FWN8" ) ); // experiment, see kGridFwn8
+        if ( fwn8 && !( peers && peers->n > 0 ) )
+        {
+            GridParams P8 = P;
+            P8.bricksX = ( dims[0] + BX8 - 1 ) / BX8;
+            const size_t nb8 = (size_t)P8.bricksX * P8.bricksY * P8.bricksZ;
+            const unsigned blocks8 = (unsigned)( ( nb8 + GRID_TB / 32 - 1 ) / ( GRID_TB / 32 ) );
+            if ( aa ) kGridFwn8<MODE, true><<<blocks8, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P8, dOut );
+            else kGridFwn8<MODE, false><<<blocks8, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P8, dOut );
+        }
+        else if ( peers && peers->n > 0 )
         {
             po = *peers;
             for ( int k = 0; k < po.n; ++k )
