@@ -146,29 +146,78 @@ def cpu_reference_setup(wl):
     return m, kind, cores, time.perf_counter() - t0
 
 
-def cpu_run_layers(m, wl, layers):
+def cpu_run_layers(m, wl, layers, keep=None):
+    """times the reference on the given z-layers; keep (a dict) receives {z: the reference's values of that layer}"""
     o = wl["opts"]
     t0 = time.perf_counter()
     for z in layers:
-        m.calc_grid_with_distances_layers(wl["dims"], wl["xf"], z, z + 1, min_dist_sq=o["min_dist_sq"], max_dist_sq=o["max_dist_sq"],
-                                          null_outside=o["null_outside"], threshold=o["threshold"], beta=o["beta"])
+        v = m.calc_grid_with_distances_layers(wl["dims"], wl["xf"], z, z + 1, min_dist_sq=o["min_dist_sq"], max_dist_sq=o["max_dist_sq"],
+                                              null_outside=o["null_outside"], threshold=o["threshold"], beta=o["beta"])
+        if keep is not None:
+            keep[z] = v
     return time.perf_counter() - t0
 
 
+PARITY_LAYERS = 16  # candidates: the GPU copies of these layers are kept for the parity block
+
+
 def choose_sample(m, wl, budget_s):
-    """evenly spaced z-layers worth about budget_s seconds of CPU work (probe: the middle layer)"""
+    """evenly spaced z-layers worth about budget_s seconds of CPU work (probe: the middle layer); always a subset of
+    sample_layers(dz, PARITY_LAYERS), whose GPU values the bench keeps"""
     dz = wl["dims"][2]
-    t1 = cpu_run_layers(m, wl, [dz // 2])
-    k = int(max(1, min(dz, 16, budget_s / max(t1, 1e-6))))
-    return sample_layers(dz, k), t1
+    cand = sample_layers(dz, min(dz, PARITY_LAYERS))
+    t1 = cpu_run_layers(m, wl, [cand[len(cand) // 2]])
+    k = int(max(1, min(len(cand), budget_s / max(t1, 1e-6))))
+    return [cand[int((i + 0.5) * len(cand) / k)] for i in range(k)], t1
 
 
-def cpu_baseline(wl, budget_s=15.0):
+def voxel_centres(wl, z, idx):
+    """float32 voxel centres xf(x, y, z) of the voxels idx (flat indices inside layer z)"""
+    dx = wl["dims"][0]
+    xf = np.asarray(wl["xf"], np.float32)
+    pos = np.stack([(idx % dx), (idx // dx), np.full(len(idx), z)], 1).astype(np.float32)
+    return (pos @ xf[:9].reshape(3, 3).T + xf[9:]).astype(np.float32)
+
+
+def parity_block(m, wl, ref_layers, gpu_layers):
+    """north_star's parity rules (oracle/checker.compare_sdf) on the sampled layers: the reference's values (computed for the
+    cpu_baseline anyway) against the same layers of the GPU volume.  Sign mismatches are excused only where the reference's
+    own winding number of that voxel lies within 1e-3 of the threshold."""
+    from oracle import checker
+    tot = {"layers": 0, "n": 0, "nan_mismatch": 0, "sign_mismatch": 0, "sign_mismatch_in_band": 0, "dist_mismatch": 0,
+           "dist_bit_exact": 0, "finite": 0, "max_rel_err": 0.0}
+    o = wl["opts"]
+    for z, want in ref_layers.items():
+        got = gpu_layers[z]
+        w_ref = None
+        both = ~np.isnan(got) & ~np.isnan(want)
+        diff = np.flatnonzero(both & (np.signbit(got) != np.signbit(want)))
+        if len(diff):
+            w_ref = np.full(want.shape, 10.0, np.float32)  # far from any threshold: only the differing voxels can be excused
+            w_ref[diff] = m.calc_from_vector(voxel_centres(wl, z, diff), beta=o["beta"])
+        rep = checker.compare_sdf(got, want, w_ref, threshold=o["threshold"])
+        tot["layers"] += 1
+        tot["n"] += rep["n"]
+        for k in ("nan_mismatch", "sign_mismatch", "dist_mismatch"):
+            tot[k] += rep[k]
+        tot["sign_mismatch_in_band"] += rep.get("sign_mismatch_in_band", 0)
+        tot["finite"] += int(both.sum())
+        tot["dist_bit_exact"] += int((np.abs(got[both]).view(np.uint32) == np.abs(want[both]).view(np.uint32)).sum())
+        tot["max_rel_err"] = max(tot["max_rel_err"], rep["max_rel_err"])
+    tot["dist_bit_exact_frac"] = tot.pop("dist_bit_exact") / max(tot["finite"], 1)
+    tot["ok"] = tot["nan_mismatch"] == 0 and tot["sign_mismatch"] == 0 and tot["dist_mismatch"] == 0
+    tot["rule"] = "NaN masks equal; sign equal outside |w_ref - threshold| < 1e-3; |d| within 1e-5 relative (oracle/checker.py)"
+    return tot
+
+
+def cpu_baseline(wl, budget_s=15.0, gpu_layers=None):
     m, kind, cores, setup_s = cpu_reference_setup(wl)
     layers, _ = choose_sample(m, wl, budget_s)
-    dt = cpu_run_layers(m, wl, layers)
+    keep = {} if gpu_layers is not None else None
+    dt = cpu_run_layers(m, wl, layers, keep)
     nvox = len(layers) * wl["dims"][0] * wl["dims"][1]
-    return {"value": nvox / dt, "unit": UNIT, "cores": cores, "kind": kind,
+    parity = parity_block(m, wl, keep, gpu_layers) if keep else None
+    return {"value": nvox / dt, "unit": UNIT, "cores": cores, "kind": kind, "parity": parity,
             "sample": f"{len(layers)} evenly spaced z-layers of {wl['dims'][0]}x{wl['dims'][1]} ({nvox} voxels, {dt:.2f} s); "
                       f"mesh+tree setup {setup_s:.1f} s excluded", "layers": layers}
 

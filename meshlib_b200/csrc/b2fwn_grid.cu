@@ -25,6 +25,7 @@
 // survivors get the reference's double closest point.
 #include "b2fwn_internal.h"
 #include "b2fwn_math.cuh"
+#include "b2fwn_brick_math.h"
 #include <cfloat>
 #include <climits>
 #include <cstdio>
@@ -102,11 +103,10 @@ __device__ __forceinline__ void brickFromIndex( const GridParams& P, const size_
 
 // warp slot -> brick.  The first `cap` slots belong to the heavy list, the rest walk the bricks in linear order and skip the
 // listed ones.  false: nothing to do for this warp.
-__device__ __forceinline__ bool brickOfWarp( const GridParams& P, const BrickOrder& O, Brick& B )
+__device__ __forceinline__ bool brickIndexOfWarp( const GridParams& P, const BrickOrder& O, size_t& brick )
 {
     const size_t slot = blockIdx.x * (size_t)( GRID_TB / 32 ) + ( threadIdx.x >> 5 );
     const size_t numBricks = (size_t)P.bricksX * P.bricksY * P.bricksZ;
-    size_t brick;
     if ( slot < O.cap )
     {
         if ( slot >= *O.count ) return false; // whole warp
@@ -118,6 +118,12 @@ __device__ __forceinline__ bool brickOfWarp( const GridParams& P, const BrickOrd
         if ( brick >= numBricks ) return false;
         if ( O.cap && O.cls[brick] ) return false;
     }
+    return true;
+}
+__device__ __forceinline__ bool brickOfWarp( const GridParams& P, const BrickOrder& O, Brick& B )
+{
+    size_t brick;
+    if ( !brickIndexOfWarp( P, O, brick ) ) return false;
     brickFromIndex( P, brick, B );
     return true;
 }
@@ -246,7 +252,9 @@ __device__ __forceinline__ float boxRadius( const GridParams& P, const float hx,
 
 // first level: one estimate per GROUP of 2 x 2 x 2 bricks (per brick the estimate cost 54 ms at c5, 5 % of the step); the
 // ball of a group contains the balls of its bricks, so a brick can only be heavy inside a heavy group
+// TX x TY x TZ = brick of the winding kernel the estimates are for (v5: 8 x 4 x 4, v6: 8 x 8 x 4)
 constexpr int GRP = 2;
+template <int TX, int TY, int TZ>
 __global__ void __launch_bounds__( 256 ) kGroupCostFwn( const TravNode* __restrict__ nodes, const GridParams P, const int gX, const int gY,
                                                         const int gZ, uint16_t* __restrict__ cost, unsigned long long* __restrict__ totals )
 {
@@ -256,8 +264,8 @@ __global__ void __launch_bounds__( 256 ) kGroupCostFwn( const TravNode* __restri
     if ( group < numGroups )
     {
         const int gx = (int)( group % gX ), gy = (int)( ( group / gX ) % gY ), gz = (int)( group / ( (size_t)gX * gY ) );
-        const float hx = 0.5f * ( GRP * BX - 1 ), hy = 0.5f * ( GRP * BY - 1 ), hz = 0.5f * ( GRP * BZ - 1 );
-        const float3 pc = applyXf( P.A, P.b, (float)( gx * GRP * BX ) + hx, (float)( gy * GRP * BY ) + hy, (float)globalZ( P, gz * GRP * BZ ) + hz );
+        const float hx = 0.5f * ( GRP * TX - 1 ), hy = 0.5f * ( GRP * TY - 1 ), hz = 0.5f * ( GRP * TZ - 1 );
+        const float3 pc = applyXf( P.A, P.b, (float)( gx * GRP * TX ) + hx, (float)( gy * GRP * TY ) + hy, (float)globalZ( P, gz * GRP * TZ ) + hz );
         c = fwnCostWalk( nodes, P.numNodes, P.betaSq, pc, boxRadius( P, hx, hy, hz ) );
         cost[group] = (uint16_t)c;
     }
@@ -288,6 +296,7 @@ __global__ void __launch_bounds__( 256 ) kBrickHeavy( const uint16_t* __restrict
     cls[brick] = h;
 }
 // second level: the bricks of a heavy group get their own estimate; those above the same threshold are listed
+template <int TX, int TY, int TZ>
 __global__ void __launch_bounds__( 256 ) kGroupHeavy( const TravNode* __restrict__ nodes, const uint16_t* __restrict__ cost, const GridParams P,
                                                       const int gX, const int gY, const unsigned long long* __restrict__ totals,
                                                       uint32_t* __restrict__ heavy, unsigned* __restrict__ count, uint8_t* __restrict__ cls,
@@ -302,8 +311,8 @@ __global__ void __launch_bounds__( 256 ) kGroupHeavy( const TravNode* __restrict
     uint8_t h = 0;
     if ( cost[group] > thr )
     {
-        const float hx = 0.5f * ( BX - 1 ), hy = 0.5f * ( BY - 1 ), hz = 0.5f * ( BZ - 1 );
-        const float3 pc = applyXf( P.A, P.b, (float)( bx * BX ) + hx, (float)( by * BY ) + hy, (float)globalZ( P, bz * BZ ) + hz );
+        const float hx = 0.5f * ( TX - 1 ), hy = 0.5f * ( TY - 1 ), hz = 0.5f * ( TZ - 1 );
+        const float3 pc = applyXf( P.A, P.b, (float)( bx * TX ) + hx, (float)( by * TY ) + hy, (float)globalZ( P, bz * TZ ) + hz );
         if ( fwnCostWalk( nodes, P.numNodes, P.betaSq, pc, boxRadius( P, hx, hy, hz ) ) > thr )
         {
             const unsigned k = atomicAdd( count, 1u );
@@ -820,68 +829,284 @@ __global__ void __launch_bounds__( GRID_TB, MINB ) kGridFwn5( const TravNode* __
     }
 }
 
-// EXPERIMENT (B2FWN_FWN8=1, not the default, not yet measured): the same walk with 8 voxels per lane -- bricks of 16x4x4, so the
-// warp-uniform part of a node visit (two 16-B loads, the all-near test, one redux.min) is paid once per 256 voxels instead
-// of once per 128.  Per-voxel arithmetic is fwnWalk's, so every voxel gets the same bits as from kGridFwn5.  Plain linear
-// brick order (P.bricksX counts 16-wide bricks); no peer stores.  The distances of MODE 1 are re-read at the end instead of
-// being kept in registers across the walk.
-constexpr int VX8 = 8, BX8 = 16;
-template <int MODE, bool AA>
-__global__ void __launch_bounds__( GRID_TB, 8 ) kGridFwn8( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
-                                                     const GridParams P, float* __restrict__ out )
+// ---- winding-number walk, v6 (axis-aligned grids: every MeshLib caller) ------------------------------------------------------
+// What v5 still paid per node, for every voxel: the exactly rounded far-field decision, the resume-index compare and select,
+// and the warp reduction that finds the next node.  A CPU replay of the walk on the bench workloads (c5_band, c3_band) shows
+// that most node visits need none of that: of ~200 visits per brick, ~85 are nodes EVERY voxel of the brick is near to
+// (all descend) and 60-80 are nodes EVERY voxel is far from (all accept the dipole); only the nodes whose beta-sphere cuts
+// the brick (28 of 193 visits at c5_band, 76 of 214 at c3_band) need per-voxel decisions.  So the walk has two modes:
+//  * UNIFORM: all voxels of the brick are awake at the same node.  One conservative brick-level test (b2fwn_brick_math.h,
+//    no square root) classifies the node: ALL_NEAR -> i+1, nothing else; ALL_FAR -> every voxel adds the dipole term, no
+//    decision, no resume index, no reduction, next node = skip link; MIXED -> a diverged section.
+//  * DIVERGED section = the subtree [i, skip(i)) of a MIXED node, walked like v5 with per-voxel resume indices and the
+//    reference's exactly rounded decisions.  At skip(i) every voxel is awake again: back to UNIFORM.
+//    (MIXED leaves are sections of length one: the leaf code lives in the diverged walk only.)
+// Bricks are 8 x 8 x 4 voxels, 8 consecutive x-voxels per lane: the per-node work that does not depend on the voxel (two 16-B
+// loads, the brick test, the y/z parts of dd and of the dot product -- the lane's voxels share y and z on an axis-aligned
+// grid) is paid once per 256 voxels; replay: 200 visits per 256-voxel brick against 193 per 128-voxel brick.
+// Arithmetic: Blackwell's packed FP32 (FADD2 / FMUL2 / FFMA2, two IEEE operations per issue slot) on voxel pairs.  ptxas 12.9
+// contracts mul.rn.f32x2 + add.rn.f32x2 into FFMA2 (also through the __fmul2_rn / __fadd2_rn intrinsics), which would change
+// the rounding of the DECISION, so the exactly rounded dx^2 is a scalar FMUL and only its two additions are packed.
+// The accepted TERM is the same sequence of operations in both modes (contracted dd, MUFU rsqrt, FFMA), so a voxel gets the
+// same bits whichever brick or mode it is computed in; terms are summed in pre-order of the accepted nodes, as in v5.
+constexpr int FX = 8;                       // voxels per lane
+constexpr int F6X = 8, F6Y = 8, F6Z = 4;    // brick of one warp: 1 x 8 x 4 lanes
+
+__device__ __forceinline__ float2 bc2( const float s ) { return make_float2( s, s ); }
+
+// what a lane needs of a node besides the voxel's own x: y/z parts of the squared distance and of dot(dp, dirArea)
+struct NodeLane
 {
-    const size_t brick = blockIdx.x * (size_t)( GRID_TB / 32 ) + ( threadIdx.x >> 5 );
-    if ( brick >= (size_t)P.bricksX * P.bricksY * P.bricksZ ) return;
-    const int lane = threadIdx.x & 31;
+    float dy2, dz2; // exactly rounded squares (decision)
+    float syz;      // dy^2 + dz^2, contracted (term)
+    float yz;       // dy * dirArea.y + dz * dirArea.z (term)
+};
+__device__ __forceinline__ NodeLane nodeLane( const float4 q2, const float4 q3, const float py, const float pz )
+{
+    const float dy = FS( q2.y, py ), dz = FS( q2.z, pz );
+    NodeLane L;
+    L.dy2 = FM( dy, dy );
+    L.dz2 = FM( dz, dz );
+    L.syz = fmaf( dy, dy, L.dz2 );
+    L.yz = fmaf( dy, q3.y, FM( dz, q3.z ) );
+    return L;
+}
+// term of a voxel pair: dot(dp, dirArea) and rsqrt(dd)^3, dd contracted
+__device__ __forceinline__ void termPair( const float2 dx, const NodeLane& L, const float q3x, float2& dot, float2& r3, float2& ddc )
+{
+    ddc = __ffma2_rn( dx, dx, bc2( L.syz ) );
+    const float2 r = make_float2( rsqrtApprox( ddc.x ), rsqrtApprox( ddc.y ) );
+    r3 = __fmul2_rn( __fmul2_rn( r, r ), r );
+    dot = __ffma2_rn( dx, bc2( q3x ), bc2( L.yz ) );
+}
+__device__ __forceinline__ float2 negate2( const float2 a ) { return make_float2( -a.x, -a.y ); }
+
+// ALL_FAR node: every voxel of the lane adds the dipole term
+__device__ __forceinline__ void fwn6AddAll( const float4 q2, const float4 q3, const float2 ( &px )[FX / 2], const float py, const float pz,
+                                            float2 ( &sum )[FX / 2] )
+{
+    const NodeLane L = nodeLane( q2, q3, py, pz );
+#pragma unroll
+    for ( int k = 0; k < FX / 2; ++k )
+    {
+        const float2 dx = __fadd2_rn( bc2( q2.x ), negate2( px[k] ) );
+        float2 dot, r3, ddc;
+        termPair( dx, L, q3.x, dot, r3, ddc );
+        sum[k] = __ffma2_rn( dot, r3, sum[k] );
+    }
+}
+
+// exactly rounded dd of a voxel pair: ( dx*dx + dy*dy ) + dz*dz, every operation rounded (MRDipole.h:21)
+__device__ __forceinline__ float2 exactDd( const float2 dx, const NodeLane& L )
+{
+    const float2 sq = make_float2( FM( dx.x, dx.x ), FM( dx.y, dx.y ) );
+    return __fadd2_rn( __fadd2_rn( sq, bc2( L.dy2 ) ), bc2( L.dz2 ) );
+}
+
+template <bool GUARD>
+__device__ __forceinline__ void fwn6Inner( const int i, const int link, const float thr, const float4 q2, const float4 q3,
+                                           const float2 ( &px )[FX / 2], const float py, const float pz, float2 ( &sum )[FX / 2], int ( &fR )[FX] )
+{
+    const NodeLane L = nodeLane( q2, q3, py, pz );
+#pragma unroll
+    for ( int k = 0; k < FX / 2; ++k )
+    {
+        const float2 dx = __fadd2_rn( bc2( q2.x ), negate2( px[k] ) );
+        const float2 dd = exactDd( dx, L );
+        float2 dot, r3, ddc;
+        termPair( dx, L, q3.x, dot, r3, ddc );
+        if ( i >= fR[2 * k] && !( dd.x <= thr ) )
+        {
+            if ( !GUARD || ( dd.x >= FLT_MIN && ddc.x >= FLT_MIN ) ) sum[k].x = fmaf( dot.x, r3.x, sum[k].x );
+            fR[2 * k] = link;
+        }
+        if ( i >= fR[2 * k + 1] && !( dd.y <= thr ) )
+        {
+            if ( !GUARD || ( dd.y >= FLT_MIN && ddc.y >= FLT_MIN ) ) sum[k].y = fmaf( dot.y, r3.y, sum[k].y );
+            fR[2 * k + 1] = link;
+        }
+    }
+}
+
+// diverged section: nodes [i, end) with per-voxel resume indices; returns end
+__device__ __forceinline__ int fwn6Section( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris, int i, const int end,
+                                            const float betaSq, const float2 ( &px )[FX / 2], const float py, const float pz,
+                                            float2 ( &sum )[FX / 2], int ( &fR )[FX] )
+{
+    while ( i < end )
+    {
+        const float4* np = reinterpret_cast<const float4*>( nodes + i );
+        const float4 q2 = __ldg( np + 2 ), q3 = __ldg( np + 3 );
+        const int link = __float_as_int( q3.w );
+        const float thr = FM( betaSq, q2.w );
+        if ( link >= 0 )
+        {
+            if ( thr >= 2.f * FLT_MIN ) fwn6Inner<false>( i, link, thr, q2, q3, px, py, pz, sum, fR );
+            else fwn6Inner<true>( i, link, thr, q2, q3, px, py, pz, sum, fR );
+        }
+        else
+        {
+            const NodeLane L = nodeLane( q2, q3, py, pz );
+            unsigned go = 0;
+#pragma unroll
+            for ( int k = 0; k < FX / 2; ++k )
+            {
+                const float2 dx = __fadd2_rn( bc2( q2.x ), negate2( px[k] ) );
+                const float2 dd = exactDd( dx, L );
+                float2 dot, r3, ddc;
+                termPair( dx, L, q3.x, dot, r3, ddc );
+                const bool a0 = i >= fR[2 * k], a1 = i >= fR[2 * k + 1];
+                const bool far0 = !( dd.x <= thr ), far1 = !( dd.y <= thr );
+                if ( a0 && far0 && dd.x >= FLT_MIN && ddc.x >= FLT_MIN ) sum[k].x = fmaf( dot.x, r3.x, sum[k].x );
+                if ( a1 && far1 && dd.y >= FLT_MIN && ddc.y >= FLT_MIN ) sum[k].y = fmaf( dot.y, r3.y, sum[k].y );
+                go |= ( a0 && !far0 ? 1u : 0u ) << ( 2 * k );
+                go |= ( a1 && !far1 ? 1u : 0u ) << ( 2 * k + 1 );
+                fR[2 * k] = a0 ? i + 1 : fR[2 * k];
+                fR[2 * k + 1] = a1 ? i + 1 : fR[2 * k + 1];
+            }
+            if ( __any_sync( FULL, go != 0 ) )
+            {
+                const float4* tp = reinterpret_cast<const float4*>( tris + ( -link - 1 ) );
+                const float4 ta = __ldg( tp ), tb = __ldg( tp + 1 ), tc = __ldg( tp + 2 );
+#pragma unroll
+                for ( int k = 0; k < FX / 2; ++k )
+                {
+                    if ( go & ( 1u << ( 2 * k ) ) ) sum[k].x = FA( sum[k].x, triangleSolidAngle( make_float3( px[k].x, py, pz ), ta, tb, tc ) );
+                    if ( go & ( 2u << ( 2 * k ) ) ) sum[k].y = FA( sum[k].y, triangleSolidAngle( make_float3( px[k].y, py, pz ), ta, tb, tc ) );
+                }
+            }
+        }
+        i = max( __reduce_min_sync( FULL, minOf( fR ) ), i + 1 );
+    }
+    return end;
+}
+
+template <int MODE, bool PEERS, int MINB = 7>
+__global__ void __launch_bounds__( GRID_TB, MINB ) kGridFwn6( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
+                                                        const GridParams P, float* __restrict__ out, const BrickOrder O, const PeerOut peers )
+{
+    const unsigned lane = threadIdx.x & 31;
+    size_t brick;
+    if ( !brickIndexOfWarp( P, O, brick ) ) return;
     const int bx = (int)( brick % P.bricksX ), by = (int)( ( brick / P.bricksX ) % P.bricksY ), bz = (int)( brick / ( (size_t)P.bricksX * P.bricksY ) );
-    const int x0 = bx * BX8 + ( lane & 1 ) * VX8, y = by * BY + ( ( lane >> 1 ) & 3 ), z = globalZ( P, bz * BZ ) + ( lane >> 3 );
-    const bool rowValid = y < P.dy && bz * BZ + ( lane >> 3 ) < P.nz;
+    const int x0 = bx * F6X, y = by * F6Y + (int)( lane & 7 ), lz = bz * F6Z + (int)( lane >> 3 );
+    const int z = globalZ( P, bz * F6Z ) + (int)( lane >> 3 ); // a brick never straddles two chunks
+    const bool rowValid = y < P.dy && lz < P.nz;
     const size_t id = (size_t)x0 + (size_t)P.dx * ( (size_t)y + (size_t)P.dy * (size_t)( z - P.zBegin ) );
-    const bool vec = P.vecStore && x0 + VX8 <= P.dx;
+    const int N = P.numNodes;
 
-    float3 p[VX8];
-    float sum[VX8];
-    int fR[VX8];
-#pragma unroll
-    for ( int v = 0; v < VX8; ++v )
+    // voxels that get a winding number: inside the grid and, MODE 1, not NaN (MRFastWindingNumber.cpp:72-74)
+    unsigned valid = 0;
+    if ( rowValid )
     {
-        bool valid = rowValid && x0 + v < P.dx;
-        if ( MODE == 1 && valid ) { const float d = out[id + v]; valid = !( d != d ); }
-        p[v] = applyXf( P.A, P.b, (float)( x0 + v ), (float)y, (float)z );
-        if ( AA ) { p[v].y = p[0].y; p[v].z = p[0].z; }
-        sum[v] = 0.f;
-        fR[v] = valid ? 0 : INT_MAX;
-    }
-    const float3 pc = applyXf( P.A, P.b, (float)( bx * BX8 ) + 7.5f, (float)( by * BY ) + 1.5f, (float)globalZ( P, bz * BZ ) + 1.5f );
-    float rad = 0.f;
 #pragma unroll
-    for ( int v = 0; v < VX8; ++v )
-    {
-        const float ex = p[v].x - pc.x, ey = p[v].y - pc.y, ez = p[v].z - pc.z;
-        rad = fmaxf( rad, ex * ex + ey * ey + ez * ez );
+        for ( int h = 0; h < 2; ++h )
+        {
+            if ( x0 + 4 * h >= P.dx ) continue;
+            if ( P.vecStore ) // dx % 4 == 0: the four voxels are inside the grid
+            {
+                unsigned m = 15u;
+                if ( MODE == 1 )
+                {
+                    const float4 d4 = *reinterpret_cast<const float4*>( out + id + 4 * h );
+                    m = ( d4.x == d4.x ? 1u : 0u ) | ( d4.y == d4.y ? 2u : 0u ) | ( d4.z == d4.z ? 4u : 0u ) | ( d4.w == d4.w ? 8u : 0u );
+                }
+                valid |= m << ( 4 * h );
+            }
+            else
+            {
+#pragma unroll
+                for ( int v = 4 * h; v < 4 * h + 4; ++v )
+                    if ( x0 + v < P.dx )
+                    {
+                        bool ok = true;
+                        if ( MODE == 1 ) { const float d = out[id + v]; ok = d == d; }
+                        valid |= ( ok ? 1u : 0u ) << v;
+                    }
+            }
+        }
     }
-    rad = sqrtf( __uint_as_float( __reduce_max_sync( FULL, __float_as_uint( rad ) ) ) ) * 1.00001f;
+    if ( !__any_sync( FULL, valid != 0 ) ) return; // nothing to compute, the distances (NaN) stay as they are
 
-    fwnWalk<VX8>( nodes, tris, P.numNodes, P.betaSq, p, pc, rad, sum, fR );
+    float2 px[FX / 2], sum[FX / 2];
+    float py, pz;
+    {
+        const float3 p0 = applyXf( P.A, P.b, (float)x0, (float)y, (float)z );
+        py = p0.y; pz = p0.z; // axis-aligned grid: y and z do not depend on x
+#pragma unroll
+        for ( int k = 0; k < FX / 2; ++k )
+        {
+            px[k] = make_float2( applyXf( P.A, P.b, (float)( x0 + 2 * k ), (float)y, (float)z ).x, applyXf( P.A, P.b, (float)( x0 + 2 * k + 1 ), (float)y, (float)z ).x );
+            sum[k] = make_float2( 0.f, 0.f );
+        }
+    }
+    // ball of the voxels that take part: centre of the brick, radius to the farthest such voxel
+    const float3 pc = applyXf( P.A, P.b, (float)x0 + 3.5f, (float)( by * F6Y ) + 3.5f, (float)globalZ( P, bz * F6Z ) + 1.5f );
+    float radSq = 0.f;
+    {
+        const float ey = py - pc.y, ez = pz - pc.z;
+        const float eyz = fmaf( ey, ey, ez * ez );
+#pragma unroll
+        for ( int v = 0; v < FX; ++v )
+        {
+            const float ex = ( ( v & 1 ) ? px[v / 2].y : px[v / 2].x ) - pc.x;
+            if ( valid & ( 1u << v ) ) radSq = fmaxf( radSq, fmaf( ex, ex, eyz ) );
+        }
+    }
+    radSq = __uint_as_float( __reduce_max_sync( FULL, __float_as_uint( radSq ) ) );
+    const BrickBall ball = makeBrickBall( pc.x, pc.y, pc.z, radSq );
+
+    int fR[FX];
+    int i = 0;
+    while ( i < N )
+    {
+        const float4* np = reinterpret_cast<const float4*>( nodes + i );
+        const float4 q2 = __ldg( np + 2 ), q3 = __ldg( np + 3 );
+        const int link = __float_as_int( q3.w );
+        const float thr = FM( P.betaSq, q2.w );
+        const float s = brickDistSq( ball, q2.x, q2.y, q2.z ), rhs = s * ball.r4;
+        if ( link >= 0 && brickAllNear( ball, s, rhs, thr ) ) { ++i; continue; }
+        const int next = skipOf( link, i );
+        if ( brickAllFar( ball, s, rhs, thr ) )
+        {
+            fwn6AddAll( q2, q3, px, py, pz, sum );
+            i = next;
+            continue;
+        }
+#pragma unroll
+        for ( int v = 0; v < FX; ++v ) fR[v] = ( valid & ( 1u << v ) ) ? i : INT_MAX;
+        i = fwn6Section( nodes, tris, i, next, P.betaSq, px, py, pz, sum, fR );
+    }
 
     if ( !rowValid ) return;
-    float res[VX8];
 #pragma unroll
-    for ( int v = 0; v < VX8; ++v )
+    for ( int h = 0; h < 2; ++h )
     {
-        const float d = ( MODE == 1 && x0 + v < P.dx ) ? out[id + v] : 0.f;
-        res[v] = fwnResult( MODE, sum[v], d, P.threshold );
-    }
-    if ( vec )
-    {
-        *reinterpret_cast<float4*>( out + id ) = make_float4( res[0], res[1], res[2], res[3] );
-        *reinterpret_cast<float4*>( out + id + 4 ) = make_float4( res[4], res[5], res[6], res[7] );
-    }
-    else
-    {
+        if ( x0 + 4 * h >= P.dx ) continue;
+        const float s4[4] = { sum[2 * h].x, sum[2 * h].y, sum[2 * h + 1].x, sum[2 * h + 1].y };
+        if ( P.vecStore )
+        {
+            float4 d4 = make_float4( 0.f, 0.f, 0.f, 0.f );
+            if ( MODE == 1 ) d4 = *reinterpret_cast<const float4*>( out + id + 4 * h );
+            const float4 r4 = make_float4( fwnResult( MODE, s4[0], d4.x, P.threshold ), fwnResult( MODE, s4[1], d4.y, P.threshold ),
+                                           fwnResult( MODE, s4[2], d4.z, P.threshold ), fwnResult( MODE, s4[3], d4.w, P.threshold ) );
+            *reinterpret_cast<float4*>( out + id + 4 * h ) = r4;
+            if ( PEERS )
+                for ( int k = 0; k < peers.n; ++k ) *reinterpret_cast<float4*>( peers.p[k] + id + 4 * h ) = r4;
+        }
+        else
+        {
 #pragma unroll
-        for ( int v = 0; v < VX8; ++v )
-            if ( x0 + v < P.dx ) out[id + v] = res[v];
+            for ( int v = 0; v < 4; ++v )
+                if ( x0 + 4 * h + v < P.dx )
+                {
+                    const float d = MODE == 1 ? out[id + 4 * h + v] : 0.f;
+                    const float r = fwnResult( MODE, s4[v], d, P.threshold );
+                    out[id + 4 * h + v] = r;
+                    if ( PEERS )
+                        for ( int k = 0; k < peers.n; ++k ) peers.p[k][id + 4 * h + v] = r;
+                }
+        }
     }
 }
 
@@ -951,13 +1176,26 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
     const bool aa = xf.A[1] == 0 && xf.A[2] == 0 && xf.A[3] == 0 && xf.A[5] == 0 && xf.A[6] == 0 && xf.A[7] == 0;
     static const bool wantStats = getenv( "B2FWN_STATS" ) != nullptr;
     static const bool heavyFirst = !( getenv( "B2FWN_LINEAR" ) && atoi( getenv( "B2FWN_LINEAR" ) ) ); // dev switch: plain linear order
+    static const bool forceV5 = getenv( "B2FWN_FWN5" ) && atoi( getenv( "B2FWN_FWN5" ) ); // dev switch: v5 winding walk on axis-aligned grids too
+    // winding walk: v6 (8 x 8 x 4 bricks) on axis-aligned grids, v5 (8 x 4 x 4) on general affine grids; the stats build counts v4's walk
+    const bool v6 = aa && !forceV5 && !wantStats;
+    GridParams PF = P; // brick layout of the winding kernel
+    if ( v6 )
+    {
+        PF.bricksX = ( dims[0] + F6X - 1 ) / F6X;
+        PF.bricksY = ( dims[1] + F6Y - 1 ) / F6Y;
+        PF.bricksZ = ( P.nz + F6Z - 1 ) / F6Z;
+    }
+    const size_t numBricksF = (size_t)PF.bricksX * PF.bricksY * PF.bricksZ;
     const bool band = distPass && P.maxDistSq < FLT_MAX && P.numNodes > 0;
     // small grids (c1: 16,384 bricks, 6.4 ms) lose more to the estimate kernels than a tail can cost them
     const bool order = heavyFirst && !wantStats && P.numNodes > 0 && numBricks >= ( 1u << 16 ) && numBricks <= 0xFFFFFFFFull;
 
     // scratch of this call: per-brick walk-length estimates (2 x u16), heavy lists (2 x cap u32), class bytes (2 x u8),
-    // totals (4 x u64) and list counters (2 x u32) in one stream-ordered allocation
+    // totals (4 x u64) and list counters (2 x u32) in one stream-ordered allocation (sized for the distance bricks; the
+    // winding kernel never has more)
     const unsigned cap = order ? (unsigned)std::min<size_t>( numBricks, 1u << 16 ) : 0;
+    const unsigned capF = order ? (unsigned)std::min<size_t>( numBricksF, cap ) : 0;
     const size_t nbPad = ( numBricks + 15 ) & ~(size_t)15;
     uint8_t* scratch = nullptr;
     const size_t scratchBytes = 64 + 2 * nbPad * sizeof( uint16_t ) + 2 * nbPad + 2 * (size_t)cap * sizeof( uint32_t );
@@ -982,11 +1220,20 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
     const bool sideEst = order && distPass && t.sideStream;
     auto fwnEstimates = [&]( cudaStream_t es )
     {
-        const int gX = ( P.bricksX + GRP - 1 ) / GRP, gY = ( P.bricksY + GRP - 1 ) / GRP, gZ = ( P.bricksZ + GRP - 1 ) / GRP;
-        kGroupCostFwn<<<(unsigned)( ( (size_t)gX * gY * gZ + 255 ) / 256 ), 256, 0, es>>>( t.nodes, P, gX, gY, gZ, costF, totals + 2 );
-        kGroupHeavy<<<nb256, 256, 0, es>>>( t.nodes, costF, P, gX, gY, totals + 2, heavyF, counts + 1, clsF, cap );
+        const int gX = ( PF.bricksX + GRP - 1 ) / GRP, gY = ( PF.bricksY + GRP - 1 ) / GRP, gZ = ( PF.bricksZ + GRP - 1 ) / GRP;
+        const unsigned gBlocks = (unsigned)( ( (size_t)gX * gY * gZ + 255 ) / 256 ), bBlocks = (unsigned)( ( numBricksF + 255 ) / 256 );
+        if ( v6 )
+        {
+            kGroupCostFwn<F6X, F6Y, F6Z><<<gBlocks, 256, 0, es>>>( t.nodes, PF, gX, gY, gZ, costF, totals + 2 );
+            kGroupHeavy<F6X, F6Y, F6Z><<<bBlocks, 256, 0, es>>>( t.nodes, costF, PF, gX, gY, totals + 2, heavyF, counts + 1, clsF, capF );
+        }
+        else
+        {
+            kGroupCostFwn<BX, BY, BZ><<<gBlocks, 256, 0, es>>>( t.nodes, PF, gX, gY, gZ, costF, totals + 2 );
+            kGroupHeavy<BX, BY, BZ><<<bBlocks, 256, 0, es>>>( t.nodes, costF, PF, gX, gY, totals + 2, heavyF, counts + 1, clsF, capF );
+        }
         if ( launches ) *launches += 2;
-        oF.heavy = heavyF; oF.count = counts + 1; oF.cls = clsF; oF.cap = cap;
+        oF.heavy = heavyF; oF.count = counts + 1; oF.cls = clsF; oF.cap = capF;
     };
     if ( sideEst )
     {
@@ -1009,6 +1256,7 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
     if ( order && !sideEst ) fwnEstimates( st );
     const uint16_t* cullCost = band ? costD : nullptr;
     auto blocksFor = [&]( const BrickOrder& o ) { return (unsigned)( ( numBricks + o.cap + GRID_TB / 32 - 1 ) / ( GRID_TB / 32 ) ); };
+    const unsigned blocksF = (unsigned)( ( numBricksF + oF.cap + GRID_TB / 32 - 1 ) / ( GRID_TB / 32 ) );
     if ( wantStats )
     {
         unsigned long long* dStats = nullptr; unsigned long long h[2 * STAT_WORDS];
@@ -1037,26 +1285,25 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
         }
         if ( sideEst ) B2_CUDA( cudaStreamWaitEvent( st, t.evJoin, 0 ) );
         PeerOut po{};
-        static const bool fwn8 = getenv( "B2FWN_FWN8" ) && atoi( getenv( "B2FWN_FWN8" ) ); // experiment, see kGridFwn8
-        if ( fwn8 && !( peers && peers->n > 0 ) )
-        {
-            GridParams P8 = P;
-            P8.bricksX = ( dims[0] + BX8 - 1 ) / BX8;
-            const size_t nb8 = (size_t)P8.bricksX * P8.bricksY * P8.bricksZ;
-            const unsigned blocks8 = (unsigned)( ( nb8 + GRID_TB / 32 - 1 ) / ( GRID_TB / 32 ) );
-            if ( aa ) kGridFwn8<MODE, true><<<blocks8, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P8, dOut );
-            else kGridFwn8<MODE, false><<<blocks8, GRID_TB, 0, st>>>( t.nodes, t.leafTris, P8, dOut );
-        }
-        else if ( peers && peers->n > 0 )
+        const bool toPeers = peers && peers->n > 0;
+        if ( toPeers )
         {
             po = *peers;
             for ( int k = 0; k < po.n; ++k )
-                if ( reinterpret_cast<uintptr_t>( po.p[k] ) % 16 != 0 ) P.vecStore = 0;
-            if ( aa ) kGridFwn5<MODE, true, true><<<blocksFor( oF ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, oF, po );
-            else kGridFwn5<MODE, false, true><<<blocksFor( oF ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, oF, po );
+                if ( reinterpret_cast<uintptr_t>( po.p[k] ) % 16 != 0 ) PF.vecStore = 0;
         }
-        else if ( aa ) kGridFwn5<MODE, true, false><<<blocksFor( oF ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, oF, po );
-        else kGridFwn5<MODE, false, false><<<blocksFor( oF ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, P, dOut, oF, po );
+        if ( v6 )
+        {
+            if ( toPeers ) kGridFwn6<MODE, true><<<blocksF, GRID_TB, 0, st>>>( t.nodes, t.leafTris, PF, dOut, oF, po );
+            else kGridFwn6<MODE, false><<<blocksF, GRID_TB, 0, st>>>( t.nodes, t.leafTris, PF, dOut, oF, po );
+        }
+        else if ( toPeers )
+        {
+            if ( aa ) kGridFwn5<MODE, true, true><<<blocksF, GRID_TB, 0, st>>>( t.nodes, t.leafTris, PF, dOut, oF, po );
+            else kGridFwn5<MODE, false, true><<<blocksF, GRID_TB, 0, st>>>( t.nodes, t.leafTris, PF, dOut, oF, po );
+        }
+        else if ( aa ) kGridFwn5<MODE, true, false><<<blocksF, GRID_TB, 0, st>>>( t.nodes, t.leafTris, PF, dOut, oF, po );
+        else kGridFwn5<MODE, false, false><<<blocksF, GRID_TB, 0, st>>>( t.nodes, t.leafTris, PF, dOut, oF, po );
     }
     if ( launches ) *launches += ( distPass ? 2 : 1 );
     static const bool debugOrder = getenv( "B2FWN_DEBUG" ) != nullptr;
