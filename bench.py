@@ -413,6 +413,10 @@ def run_ours(args, wl):
     if world > 1:
         dev_ms = wall_ms  # gathers overlap the kernels: the step is the bracketed region (device synchronised on both sides)
     checksum = float(torch.nan_to_num(volume[:: max(1, total // (1 << 22))]).double().abs().sum())
+    # parity block: the GPU's values of the candidate sample layers, compared below with the reference's values of the same layers
+    gpu_layers = None
+    if rank == 0 and not args.no_cpu:
+        gpu_layers = {z: volume[z * layer:(z + 1) * layer].cpu().numpy() for z in sample_layers(dims[2], min(dims[2], PARITY_LAYERS))}
     if world > 1:  # every rank must hold the same, complete volume
         c = torch.tensor([checksum, -checksum], dtype=torch.float64, device=dev)
         dist.all_reduce(c, op=dist.ReduceOp.MAX)
@@ -449,9 +453,14 @@ def run_ours(args, wl):
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e_ms = float(t[0])
+        # the host-output call must deliver what the device-resident call left in HBM (same kernels, chunked): bit for bit
+        e2e_same = None
+        if gpu_layers is not None:
+            e2e_same = all(np.array_equal(host_np[(z - z0) * layer:(z - z0 + 1) * layer].view(np.uint32), g.view(np.uint32))
+                           for z, g in gpu_layers.items() if z0 <= z < z1)
         e2e = {"value": total / (e_ms * 1e-3), "unit": UNIT, "ms_per_step": e_ms, "steps": e_steps,
                "h2d_bytes_per_step": int(wl["points"].nbytes + wl["tris"].nbytes + 12 * 4 + 20),
-               "d2h_bytes_per_step": int(4 * nslab),
+               "d2h_bytes_per_step": int(4 * nslab), "equals_resident_volume_on_sample_layers": e2e_same,
                "includes": "b2fwn_create (mesh H2D + device tree/dipole build) + grid call into pinned host memory, per rank; host wall clock"}
 
     if rank != 0:
@@ -499,7 +508,8 @@ def run_ours(args, wl):
     out["roofline"]["hbm"]["achieved"] = (4.0 * nslab0 + st0.num_nodes * 64 + st0.num_leaves * 64) / (k_ms * 1e-3) / 1e9
     out["roofline"]["hbm"]["frac"] = out["roofline"]["hbm"]["achieved"] / hbm_peak
     if world == 1 and not args.no_cpu:
-        cb = cpu_baseline(wl, args.cpu_budget)
+        cb = cpu_baseline(wl, args.cpu_budget, gpu_layers)
+        out["parity"] = cb.pop("parity")
         fpv, per_voxel, n = algorithmic_flops(wl, cb["layers"])
         layers_for_gpu_ref = cb["layers"]
         del cb["layers"]

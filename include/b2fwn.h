@@ -15,6 +15,10 @@
  *    (reference: source/MRMesh/MRExpected.h:42-51).
  *  - "host" calls take host pointers and copy; "_device" calls take device pointers of the handle's GPU
  *    and only enqueue + synchronise the handle's stream.
+ *  - host OUTPUT of the grid calls may be pageable (std::vector<float>, numpy) or pinned.  Pinned memory (cudaMallocHost /
+ *    cudaHostRegister) receives each chunk by one asynchronous copy behind the next chunk's kernels.  Pageable memory is
+ *    filled through a pinned staging ring (256 MiB per device, allocated at the first such call, kept for the life of the
+ *    process) and 4 copier threads per device (B2FWN_COPY_THREADS), also behind the next chunk's kernels: both overlap.
  *  - grid linearisation id = x + dx*(y + dy*z) (source/MRMesh/MRVolumeIndexer.h:132-140); the query point of
  *    voxel (x,y,z) is A*(x,y,z)+b with xf = {A row-major (9), b (3)} (source/MRMesh/MRAffineXf.h:46).
  *  - there is no CPU fallback: without a CUDA device b2fwn_create fails.
@@ -43,10 +47,19 @@ typedef int ( *b2fwn_progress )( float progress, void* user );
  * return 0 to continue, non-zero to abort (GridByPartsFunc, source/MRMesh/MRFastWindingNumber.h:88) */
 typedef int ( *b2fwn_part_cb )( const float* data, const int32_t dims[3], int32_t z_offset, void* user );
 
+/* Devices of a handle.  n_devices <= 1: the single device `device` (the reference always uses device 0,
+ * MRCudaFastWindingNumber.cpp:48).  n_devices > 1: devices[0 .. n_devices) of ONE process; the tree is built on devices[0] and
+ * copied to the others (peer copies over NVLink), and the host-output grid calls (b2fwn_calc_from_grid,
+ * b2fwn_calc_from_grid_with_distances[_layers], the by-parts calls, b2fwn_make_signed_by_winding_number,
+ * b2fwn_mesh_to_distance_volume) deal their z-chunks round-robin over all of them, every device copying its chunks straight
+ * into the caller's buffer: no gather.  All other calls (point vectors, *_device forms, marching cubes) run on devices[0]. */
+#define B2FWN_MAX_DEVICES 16
 typedef struct b2fwn_config
 {
-    int32_t device;        /* CUDA device ordinal; reference always uses 0 (MRCudaFastWindingNumber.cpp:48) */
-    int32_t reserved[7];
+    int32_t device;
+    int32_t n_devices;
+    int32_t devices[B2FWN_MAX_DEVICES];
+    int32_t reserved[6];
 } b2fwn_config;
 
 /* mirrors MR::DistanceToMeshOptions (source/MRMesh/MRDistanceToMeshOptions.h:10-33) */
@@ -193,7 +206,10 @@ int b2fwn_signed_distances_by_projection_normal_device( b2fwn_handle h, const fl
 /* IFastWindingNumberByParts::calcFromGridByParts / calcFromGridWithDistancesByParts
  * (MRFastWindingNumber.h:96-106; GPU MRCudaFastWindingNumber.cpp:285-429).  Parts are whole z-layers, delivered
  * strictly in increasing z on the calling thread, consecutive parts overlapping by layer_overlap layers
- * (chunk maths: source/MRMesh/MRChunkIterator.cpp:25-49).  max_layers_per_part <= 0 chooses by free memory. */
+ * (chunk maths: source/MRMesh/MRChunkIterator.cpp:25-49).  max_layers_per_part <= 0: one eighth of a device's share of the
+ * grid (32 Mi .. 256 Mi voxels); in either case never more than fits twice into the safe share of the free device memory,
+ * 80 % of (free - 128 MB) as getCudaSafeMemoryLimit (source/MRCuda/MRCudaBasic.cpp:75-107).
+ * The part callback receives library-owned pinned memory that is valid during the callback only. */
 int b2fwn_calc_from_grid_by_parts( b2fwn_handle h, const int32_t dims[3], const float xf[12], float beta,
                                    int32_t layer_overlap, int32_t max_layers_per_part, b2fwn_part_cb part, void* part_user,
                                    b2fwn_progress cb, void* user );
@@ -201,6 +217,22 @@ int b2fwn_calc_from_grid_with_distances_by_parts( b2fwn_handle h, const int32_t 
                                                   const b2fwn_dist_options* opt, int32_t layer_overlap,
                                                   int32_t max_layers_per_part, b2fwn_part_cb part, void* part_user,
                                                   b2fwn_progress cb, void* user );
+
+/* The same with caller-owned part memory (what the C++ adapter uses: GridByPartsFunc takes a std::vector<float>&& it owns,
+ * MRFastWindingNumber.h:88): `buffer` is asked on the calling thread, in increasing z and a few parts ahead of `part`, where the
+ * part with the given dims / z_offset shall be delivered (dims[0]*dims[1]*dims[2] floats; NULL aborts the call); the part is
+ * copied there while the next parts are computed, then `part` is called with that pointer.  buffer == NULL: as above. */
+typedef float* ( *b2fwn_part_buffer_cb )( const int32_t dims[3], int32_t z_offset, void* user );
+int b2fwn_calc_from_grid_by_parts_into( b2fwn_handle h, const int32_t dims[3], const float xf[12], float beta,
+                                        int32_t layer_overlap, int32_t max_layers_per_part, b2fwn_part_buffer_cb buffer,
+                                        b2fwn_part_cb part, void* part_user, b2fwn_progress cb, void* user );
+int b2fwn_calc_from_grid_with_distances_by_parts_into( b2fwn_handle h, const int32_t dims[3], const float xf[12],
+                                                       const b2fwn_dist_options* opt, int32_t layer_overlap,
+                                                       int32_t max_layers_per_part, b2fwn_part_buffer_cb buffer,
+                                                       b2fwn_part_cb part, void* part_user, b2fwn_progress cb, void* user );
+
+/* getCudaSafeMemoryLimit (source/MRCuda/MRCudaBasic.cpp:75-90) of a device: 80 % of (free - 128 MB), in bytes; 0 on failure */
+size_t b2fwn_safe_memory_limit( int32_t device );
 
 /* debug / parity: download the device-built tree in the reference's layouts:
  * nodes = AABBTreeNode (32 B: box.min xyz, box.max xyz, l, r; source/MRMesh/MRAABBTreeNode.h:29-45),

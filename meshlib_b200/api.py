@@ -19,6 +19,7 @@ _lib = None
 
 PROGRESS_CB = C.CFUNCTYPE(C.c_int, C.c_float, C.c_void_p)
 PART_CB = C.CFUNCTYPE(C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_int32), C.c_int32, C.c_void_p)
+PART_BUFFER_CB = C.CFUNCTYPE(C.c_void_p, C.POINTER(C.c_int32), C.c_int32, C.c_void_p)
 
 
 class B2Error(RuntimeError):
@@ -29,8 +30,12 @@ class B2Error(RuntimeError):
         self.code = code
 
 
+MAX_DEVICES = 16
+
+
 class Config(C.Structure):
-    _fields_ = [("device", C.c_int32), ("reserved", C.c_int32 * 7)]
+    """b2fwn_config: one device, or n_devices > 1 devices of this process (the host-output grid calls use them all)"""
+    _fields_ = [("device", C.c_int32), ("n_devices", C.c_int32), ("devices", C.c_int32 * MAX_DEVICES), ("reserved", C.c_int32 * 6)]
 
 
 class DistOptions(C.Structure):
@@ -96,6 +101,7 @@ EXPORTS = [
     "b2fwn_make_signed_by_winding_number", "b2fwn_make_signed_by_winding_number_device",
     "b2fwn_signed_distances_by_projection_normal", "b2fwn_signed_distances_by_projection_normal_device",
     "b2fwn_mesh_to_distance_volume_by_projection_normal", "b2fwn_update_points",
+    "b2fwn_calc_from_grid_by_parts_into", "b2fwn_calc_from_grid_with_distances_by_parts_into", "b2fwn_safe_memory_limit",
 ]
 
 
@@ -143,6 +149,12 @@ def load_library():
                                                 PROGRESS_CB, vp]
     L.b2fwn_calc_from_grid_with_distances_by_parts.argtypes = [vp, i32p, f32p, C.POINTER(DistOptions), C.c_int32,
                                                                C.c_int32, PART_CB, vp, PROGRESS_CB, vp]
+    L.b2fwn_calc_from_grid_by_parts_into.argtypes = [vp, i32p, f32p, C.c_float, C.c_int32, C.c_int32, PART_BUFFER_CB, PART_CB, vp,
+                                                     PROGRESS_CB, vp]
+    L.b2fwn_calc_from_grid_with_distances_by_parts_into.argtypes = [vp, i32p, f32p, C.POINTER(DistOptions), C.c_int32, C.c_int32,
+                                                                    PART_BUFFER_CB, PART_CB, vp, PROGRESS_CB, vp]
+    L.b2fwn_safe_memory_limit.argtypes = [C.c_int32]
+    L.b2fwn_safe_memory_limit.restype = C.c_size_t
     L.b2fwn_get_tree.argtypes = [vp, vp, vp, C.c_size_t, C.POINTER(C.c_size_t)]
     L.b2fwn_update_points.argtypes = [vp, vp, C.c_size_t]
     L.b2fwn_get_stats.argtypes = [vp, C.POINTER(Stats)]
@@ -207,12 +219,18 @@ class FastWindingNumber:
     The mesh is uploaded and the AABB tree + dipoles are built on the device in the constructor (the reference does it
     lazily at the first call, MRCudaFastWindingNumber.cpp:46-85)."""
 
-    def __init__(self, points, tris, device=0):
+    def __init__(self, points, tris, device=0, devices=None):
+        """devices: list of CUDA ordinals of THIS process for the host-output grid calls (b2fwn_config.n_devices > 1)"""
         self._h = None
         L = load_library()
         self.points = np.ascontiguousarray(points, np.float32).reshape(-1, 3)
         self.tris = np.ascontiguousarray(tris, np.int32).reshape(-1, 3)
         cfg = Config(device=device)
+        if devices is not None and len(devices) > 1:
+            cfg.device, cfg.n_devices = int(devices[0]), len(devices)
+            for i, d in enumerate(devices):
+                cfg.devices[i] = int(d)
+            device = int(devices[0])
         h = C.c_void_p()
         _check(L.b2fwn_create(self.points.ctypes.data, len(self.points), self.tris.ctypes.data, len(self.tris),
                               C.byref(cfg), C.byref(h)))
@@ -309,6 +327,38 @@ class FastWindingNumber:
         _check(_lib.b2fwn_calc_from_grid_with_distances_by_parts(
             self._h, _dims(dims), _xf(grid_to_mesh_xf), C.byref(options), layer_overlap, max_layers_per_part,
             self._part_cb(res_func), None, _progress(cb), None))
+
+    def calc_from_grid_with_distances_by_parts_into(self, res_func, dims, grid_to_mesh_xf, options=None, layer_overlap=0, cb=None,
+                                                    max_layers_per_part=0, distances=True, beta=2.0):
+        """by-parts with caller-owned part memory (b2fwn_*_by_parts_into): every part lands in a fresh pageable numpy array that
+        is handed to res_func(arr, dims, z_offset) -- what the C++ adapter does with std::vector<float>"""
+        bufs = {}
+
+        def buffer(dims_p, z_offset, _u):
+            try:
+                a = np.empty(dims_p[0] * dims_p[1] * dims_p[2], np.float32)
+            except MemoryError:
+                return None
+            bufs[z_offset] = a
+            return a.ctypes.data
+
+        def part(_data, dims_p, z_offset, _u):
+            a = bufs.pop(z_offset)
+            try:
+                ok = res_func(a, (dims_p[0], dims_p[1], dims_p[2]), z_offset)
+            except Exception:
+                return 1
+            return 0 if (ok is None or ok) else 1
+
+        bcb, pcb = PART_BUFFER_CB(buffer), PART_CB(part)
+        if distances:
+            options = options or DistOptions()
+            _check(_lib.b2fwn_calc_from_grid_with_distances_by_parts_into(
+                self._h, _dims(dims), _xf(grid_to_mesh_xf), C.byref(options), layer_overlap, max_layers_per_part, bcb, pcb, None,
+                _progress(cb), None))
+        else:
+            _check(_lib.b2fwn_calc_from_grid_by_parts_into(self._h, _dims(dims), _xf(grid_to_mesh_xf), beta, layer_overlap,
+                                                           max_layers_per_part, bcb, pcb, None, _progress(cb), None))
 
     # ---- device-pointer forms (multi-GPU slabs, benches) ----
     def calc_from_vector_device(self, d_points_ptr, n, d_out_ptr, beta=2.0, skip_face=-1):

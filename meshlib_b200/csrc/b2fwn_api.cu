@@ -1,7 +1,7 @@
 // b2fwn_api.cu -- the C ABI of include/b2fwn.h: handle, memory, streams, chunking / by-parts pipelines.
 // Host-side orchestration only; all arithmetic lives in b2fwn_tree.cu / b2fwn_kernels.cu / b2fwn_mc.cu.
 // There is deliberately no CPU implementation behind any entry point.
-#include "b2fwn_internal.h"
+#include "b2fwn_ctx.h"
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
@@ -27,49 +27,10 @@ int cudaFail( cudaError_t e, const char* where )
 
 using namespace b2;
 
-struct b2fwn_ctx
-{
-    int device = 0;
-    cudaStream_t stream = nullptr;     // compute
-    cudaStream_t stream2 = nullptr;    // compute of every second chunk of the host-output calls (overlaps the tail of the previous one)
-    cudaStream_t copyStream = nullptr; // D2H of finished parts
-    cudaEvent_t evA = nullptr, evB = nullptr;
-    DeviceTree tree;
-    b2fwn_stats stats{};
-    McResult mc;
-    // scratch for the host-pointer entry points
-    float* dScratch[2] = { nullptr, nullptr };
-    size_t scratchFloats[2] = { 0, 0 };
-    float* hPinned[2] = { nullptr, nullptr };
-    size_t pinnedFloats[2] = { 0, 0 };
-    cudaEvent_t partDone[2] = { nullptr, nullptr };
-    cudaEvent_t computeDone[2] = { nullptr, nullptr };
-};
-
 namespace
 {
 
 const char* kCanceled = "Operation was canceled"; // source/MRMesh/MRExpected.h:42-51
-
-int ensureScratch( b2fwn_ctx* h, int slot, size_t floats )
-{
-    if ( h->scratchFloats[slot] >= floats ) return B2FWN_OK;
-    if ( h->dScratch[slot] ) cudaFree( h->dScratch[slot] );
-    h->dScratch[slot] = nullptr; h->scratchFloats[slot] = 0;
-    B2_CUDA( cudaMalloc( &h->dScratch[slot], floats * sizeof( float ) ) );
-    h->scratchFloats[slot] = floats;
-    return B2FWN_OK;
-}
-
-int ensurePinned( b2fwn_ctx* h, int slot, size_t floats )
-{
-    if ( h->pinnedFloats[slot] >= floats ) return B2FWN_OK;
-    if ( h->hPinned[slot] ) cudaFreeHost( h->hPinned[slot] );
-    h->hPinned[slot] = nullptr; h->pinnedFloats[slot] = 0;
-    B2_CUDA( cudaMallocHost( &h->hPinned[slot], floats * sizeof( float ) ) );
-    h->pinnedFloats[slot] = floats;
-    return B2FWN_OK;
-}
 
 bool report( b2fwn_progress cb, void* user, float v )
 {
@@ -106,100 +67,21 @@ struct KernelTimer
     }
 };
 
-// layers per chunk for the host-pointer grid calls: whole layers, one eighth of the grid but between 32 Mi and 256 Mi voxels
-// (128 MiB .. 1 GiB) per chunk, so that the D2H of chunk k overlaps the kernels of chunk k+1, the copy left over after the
-// last kernel is short, cancellation is polled many times per second -- and the per-launch costs (walk-length estimates,
-// kernel tails, stream-ordered scratch) are paid tens of times per grid, not hundreds (8-layer chunks of 2048^2 made the
-// host-output call 1.5x slower than the kernels themselves, r01)
-int defaultLayersPerPart( const int32_t dims[3], int overlap )
+// the common shape of the host-output grid calls: whole range or a z-range into a contiguous host buffer
+int runToHost( b2fwn_ctx* h, const int32_t dims[3], int zBegin, int zEnd, float* hostOut, b2fwn_progress cb, void* user, const ChunkLaunch& launch )
 {
-    const size_t layer = (size_t)dims[0] * dims[1];
-    if ( layer == 0 ) return std::max( dims[2], 1 );
-    const size_t total = layer * (size_t)std::max( dims[2], 1 );
-    const size_t voxels = std::min<size_t>( std::max<size_t>( total / 8, (size_t)32 << 20 ), (size_t)256 << 20 );
-    size_t layers = voxels / layer;
-    layers = std::max<size_t>( layers, (size_t)overlap + 1 );
-    layers = std::max<size_t>( layers, 2 );
-    return (int)std::min<size_t>( layers, (size_t)std::max( dims[2], 1 ) );
+    ChunkedCall c;
+    c.dims = dims; c.zBegin = zBegin; c.zEnd = zEnd; c.hostOut = hostOut; c.progress = cb; c.progressUser = user;
+    return runChunked( h, c, launch );
 }
 
-// Generic z-chunked pipeline.  launch(zBegin, zEnd, dOut) enqueues the kernel on h->stream.
-// If part != nullptr the chunks (with overlap) are handed to the consumer from pinned staging buffers, in z order, on
-// the calling thread, while the next chunk is computed (the reference's cudaPipeline, source/MRCuda/MRCudaPipeline.hpp:9-48).
-// Otherwise chunks are copied straight into hostOut.
-template <typename Launch>
-int runChunked( b2fwn_ctx* h, const int32_t dims[3], int zBegin, int zEnd, int overlap, int layersPerPart, float* hostOut,
-                b2fwn_part_cb part, void* partUser, b2fwn_progress cb, void* user, Launch launch )
+int runByParts( b2fwn_ctx* h, const int32_t dims[3], int overlap, int maxLayers, b2fwn_part_buffer_cb buffer, b2fwn_part_cb part, void* partUser,
+                b2fwn_progress cb, void* user, const ChunkLaunch& launch )
 {
-    if ( zBegin < 0 || zEnd > dims[2] || zBegin > zEnd ) { setError( "invalid layer range" ); return B2FWN_ERR_INVALID; }
-    const int nz = zEnd - zBegin;
-    const size_t layer = (size_t)dims[0] * dims[1];
-    if ( nz == 0 || layer == 0 ) return B2FWN_OK;
-    if ( overlap < 0 ) { setError( "negative layer overlap" ); return B2FWN_ERR_INVALID; }
-    if ( layersPerPart <= 0 ) layersPerPart = defaultLayersPerPart( dims, overlap );
-    layersPerPart = std::min( layersPerPart, nz );
-    if ( layersPerPart <= overlap ) { setError( "part must be larger than the overlap" ); return B2FWN_ERR_INVALID; }
-    // splitByChunks (source/MRMesh/MRChunkIterator.cpp:25-49): offset_k = k*(chunk-overlap), last chunk shorter
-    const int step = layersPerPart - overlap;
-    const int count = nz <= overlap ? 1 : ( nz - overlap + step - 1 ) / step;
-    if ( !report( cb, user, 0.f ) ) return canceled();
-    for ( int s = 0; s < 2; ++s )
-    {
-        if ( int e = ensureScratch( h, s, (size_t)layersPerPart * layer ) ) return e;
-        if ( part ) if ( int e = ensurePinned( h, s, (size_t)layersPerPart * layer ) ) return e;
-    }
-    auto finishPart = [&]( int k ) -> int
-    {
-        const int s = k & 1;
-        B2_CUDA( cudaEventSynchronize( h->partDone[s] ) );
-        if ( part )
-        {
-            const int z0 = k * step, z1 = std::min( nz, z0 + layersPerPart );
-            const int32_t pd[3] = { dims[0], dims[1], z1 - z0 };
-            if ( part( h->hPinned[s], pd, zBegin + z0, partUser ) != 0 )
-            {
-                setError( "by-parts consumer failed" );
-                return B2FWN_ERR_CANCELED;
-            }
-        }
-        return B2FWN_OK;
-    };
-    // Chunks alternate between two compute streams: the kernels of chunk k+1 are enqueued while chunk k still runs and move
-    // in as its last (longest) walks drain -- a chunk is a small launch, its tail and its walk-length estimates would
-    // otherwise be paid in full every time (c3_band: 4 chunks took 62 ms against 34 ms for the grid in one launch).
-    cudaStream_t cs[2] = { h->stream, h->stream2 };
-    cudaEventRecord( h->evA, h->stream );
-    B2_CUDA( cudaStreamWaitEvent( h->stream2, h->evA, 0 ) ); // nothing of this call starts before the call
-    for ( int k = 0; k < count; ++k )
-    {
-        const int s = k & 1;
-        const int z0 = k * step, z1 = std::min( nz, z0 + layersPerPart );
-        // slot s is free again: the copy of chunk k-2 finished (finishPart(k-2) waited for it on the host)
-        if ( int e = launch( zBegin + z0, zBegin + z1, h->dScratch[s], cs[s] ) ) { cudaDeviceSynchronize(); return e; }
-        B2_CUDA( cudaEventRecord( h->computeDone[s], cs[s] ) );
-        B2_CUDA( cudaStreamWaitEvent( h->copyStream, h->computeDone[s], 0 ) );
-        float* dst = part ? h->hPinned[s] : hostOut + (size_t)z0 * layer;
-        B2_CUDA( cudaMemcpyAsync( dst, h->dScratch[s], (size_t)( z1 - z0 ) * layer * sizeof( float ), cudaMemcpyDeviceToHost, h->copyStream ) );
-        B2_CUDA( cudaEventRecord( h->partDone[s], h->copyStream ) );
-        if ( k > 0 )
-        {
-            if ( int e = finishPart( k - 1 ) ) { cudaDeviceSynchronize(); return e; }
-            if ( !report( cb, user, float( k ) / float( count ) ) ) { cudaDeviceSynchronize(); return canceled(); }
-        }
-    }
-    // kernel time of the call: from its first launch to the end of its last kernel (both streams)
-    B2_CUDA( cudaStreamWaitEvent( h->stream, h->computeDone[0], 0 ) );
-    if ( count > 1 ) B2_CUDA( cudaStreamWaitEvent( h->stream, h->computeDone[1], 0 ) );
-    cudaEventRecord( h->evB, h->stream );
-    if ( int e = finishPart( count - 1 ) ) return e;
-    B2_CUDA( cudaStreamSynchronize( h->stream ) );
-    B2_CUDA( cudaStreamSynchronize( h->stream2 ) );
-    {
-        float ms = 0;
-        if ( cudaEventElapsedTime( &ms, h->evA, h->evB ) == cudaSuccess ) h->stats.last_kernel_ms = ms;
-    }
-    if ( !report( cb, user, 1.f ) ) return canceled();
-    return B2FWN_OK;
+    ChunkedCall c;
+    c.dims = dims; c.zBegin = 0; c.zEnd = dims[2]; c.overlap = overlap; c.layersPerPart = maxLayers;
+    c.part = part; c.partBuffer = buffer; c.partUser = partUser; c.progress = cb; c.progressUser = user;
+    return runChunked( h, c, launch );
 }
 
 } // anonymous namespace
@@ -217,61 +99,10 @@ int b2fwn_device_count( void )
     return n;
 }
 
-int b2fwn_create( const float* points, size_t nVerts, const int32_t* tris, size_t nFaces, const b2fwn_config* cfg,
-                  b2fwn_handle* out )
+namespace
 {
-    if ( !out || ( nVerts && !points ) || ( nFaces && !tris ) ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
-    *out = nullptr;
-    const int dev = cfg ? cfg->device : 0;
-    B2_CUDA( cudaSetDevice( dev ) );
-    b2fwn_ctx* h = new b2fwn_ctx;
-    h->device = dev;
-    auto fail = [&]( int e ) { b2fwn_destroy( h ); return e; };
-#define B2_TRY( expr ) do { cudaError_t _e = ( expr ); if ( _e != cudaSuccess ) return fail( cudaFail( _e, #expr ) ); } while ( 0 )
-    B2_TRY( cudaStreamCreateWithFlags( &h->stream, cudaStreamNonBlocking ) );
-    B2_TRY( cudaStreamCreateWithFlags( &h->stream2, cudaStreamNonBlocking ) );
-    {
-        // the grid launchers take their per-launch scratch from the stream-ordered pool: keep it cached across synchronisations
-        // (the default releases it at every one, and a host-output call synchronises per chunk)
-        cudaMemPool_t pool = nullptr;
-        unsigned long long keep = ~0ull;
-        if ( cudaDeviceGetDefaultMemPool( &pool, h->device ) == cudaSuccess )
-            cudaMemPoolSetAttribute( pool, cudaMemPoolAttrReleaseThreshold, &keep );
-    }
-    B2_TRY( cudaStreamCreateWithFlags( &h->copyStream, cudaStreamNonBlocking ) );
-    B2_TRY( cudaEventCreate( &h->evA ) );
-    B2_TRY( cudaEventCreate( &h->evB ) );
-    for ( int s = 0; s < 2; ++s )
-    {
-        B2_TRY( cudaEventCreateWithFlags( &h->partDone[s], cudaEventDisableTiming ) );
-        B2_TRY( cudaEventCreateWithFlags( &h->computeDone[s], cudaEventDisableTiming ) );
-    }
-    h->tree.numVerts = nVerts; h->tree.numFaces = nFaces;
-    if ( nVerts )
-    {
-        B2_TRY( cudaMalloc( &h->tree.points, nVerts * 3 * sizeof( float ) ) );
-        B2_TRY( cudaMemcpyAsync( h->tree.points, points, nVerts * 3 * sizeof( float ), cudaMemcpyHostToDevice, h->stream ) );
-    }
-    if ( nFaces )
-    {
-        B2_TRY( cudaMalloc( &h->tree.tris, nFaces * 3 * sizeof( int32_t ) ) );
-        B2_TRY( cudaMemcpyAsync( h->tree.tris, tris, nFaces * 3 * sizeof( int32_t ), cudaMemcpyHostToDevice, h->stream ) );
-    }
-#undef B2_TRY
-    cudaEventRecord( h->evA, h->stream );
-    if ( int e = buildTree( h->tree, h->stream, &h->stats.kernel_launches ) ) return fail( e );
-    cudaEventRecord( h->evB, h->stream );
-    cudaEventSynchronize( h->evB );
-    float ms = 0;
-    cudaEventElapsedTime( &ms, h->evA, h->evB );
-    h->stats.tree_build_ms = ms;
-    h->stats.num_nodes = h->tree.numNodes;
-    h->stats.num_leaves = h->tree.numLeaves;
-    *out = h;
-    return B2FWN_OK;
-}
 
-void b2fwn_destroy( b2fwn_handle h )
+void destroyCtx( b2fwn_ctx* h )
 {
     if ( !h ) return;
     cudaSetDevice( h->device );
@@ -285,12 +116,165 @@ void b2fwn_destroy( b2fwn_handle h )
         if ( h->partDone[s] ) cudaEventDestroy( h->partDone[s] );
         if ( h->computeDone[s] ) cudaEventDestroy( h->computeDone[s] );
     }
+    if ( h->dMinMax ) cudaFree( h->dMinMax );
     if ( h->evA ) cudaEventDestroy( h->evA );
     if ( h->evB ) cudaEventDestroy( h->evB );
     if ( h->stream ) cudaStreamDestroy( h->stream );
     if ( h->stream2 ) cudaStreamDestroy( h->stream2 );
     if ( h->copyStream ) cudaStreamDestroy( h->copyStream );
     delete h;
+}
+
+// streams, events and the private stream-ordered pool of one device context; on failure the half-made context is destroyed
+int newCtx( int dev, b2fwn_ctx** out )
+{
+    *out = nullptr;
+    B2_CUDA( cudaSetDevice( dev ) );
+    b2fwn_ctx* h = new b2fwn_ctx;
+    h->device = dev;
+#define B2_TRY( expr ) do { cudaError_t _e = ( expr ); if ( _e != cudaSuccess ) { const int rc = cudaFail( _e, #expr ); destroyCtx( h ); return rc; } } while ( 0 )
+    B2_TRY( cudaStreamCreateWithFlags( &h->stream, cudaStreamNonBlocking ) );
+    B2_TRY( cudaStreamCreateWithFlags( &h->stream2, cudaStreamNonBlocking ) );
+    B2_TRY( cudaStreamCreateWithFlags( &h->copyStream, cudaStreamNonBlocking ) );
+    B2_TRY( cudaEventCreate( &h->evA ) );
+    B2_TRY( cudaEventCreate( &h->evB ) );
+    for ( int s = 0; s < 2; ++s )
+    {
+        B2_TRY( cudaEventCreateWithFlags( &h->partDone[s], cudaEventDisableTiming ) );
+        B2_TRY( cudaEventCreateWithFlags( &h->computeDone[s], cudaEventDisableTiming ) );
+    }
+#undef B2_TRY
+    if ( int e = initTreeAux( h->tree, dev ) ) { destroyCtx( h ); return e; }
+    *out = h;
+    return B2FWN_OK;
+}
+
+// the traversal arrays of the primary's tree onto every replica: binary-tree broadcast over peer copies (NVLink where peer access
+// exists, staged by the driver otherwise); the parity-dump arrays (refNodes, refDipoles) stay on the primary
+int broadcastTree( b2fwn_ctx* h )
+{
+    if ( h->replicas.empty() ) return B2FWN_OK;
+    std::vector<b2fwn_ctx*> all{ h };
+    all.insert( all.end(), h->replicas.begin(), h->replicas.end() );
+    const DeviceTree& T = h->tree;
+    for ( size_t i = 1; i < all.size(); ++i )
+    {
+        b2fwn_ctx* r = all[i];
+        DeviceTree& t = r->tree;
+        B2_CUDA( cudaSetDevice( r->device ) );
+        if ( t.numVerts != T.numVerts || t.numFaces != T.numFaces || t.numNodes != T.numNodes || t.numLeaves != T.numLeaves )
+        {
+            cudaFree( t.points ); cudaFree( t.tris ); cudaFree( t.nodes ); cudaFree( t.leafTris ); cudaFree( t.leafFilt );
+            t.points = nullptr; t.tris = nullptr; t.nodes = nullptr; t.leafTris = nullptr; t.leafFilt = nullptr;
+            if ( T.numVerts ) B2_CUDA( cudaMalloc( &t.points, T.numVerts * 3 * sizeof( float ) ) );
+            if ( T.numFaces ) B2_CUDA( cudaMalloc( &t.tris, T.numFaces * 3 * sizeof( int32_t ) ) );
+            if ( T.numNodes ) B2_CUDA( cudaMalloc( &t.nodes, T.numNodes * sizeof( TravNode ) ) );
+            if ( T.numLeaves ) B2_CUDA( cudaMalloc( &t.leafTris, T.numLeaves * sizeof( LeafTri ) ) );
+            if ( T.numLeaves ) B2_CUDA( cudaMalloc( &t.leafFilt, T.numLeaves * sizeof( LeafFilt ) ) );
+        }
+        // pseudonormal tables depend on the coordinates: rebuilt on next use
+        cudaFree( t.faceNormals ); cudaFree( t.vertNormals ); cudaFree( t.faceAdj );
+        t.faceNormals = t.vertNormals = nullptr; t.faceAdj = nullptr;
+        t.numVerts = T.numVerts; t.numFaces = T.numFaces; t.numNodes = T.numNodes; t.numLeaves = T.numLeaves; t.depth = T.depth;
+        memcpy( t.bbox, T.bbox, sizeof( t.bbox ) );
+        for ( b2fwn_ctx* o : all )
+            if ( o != r )
+            {
+                int can = 0;
+                if ( cudaDeviceCanAccessPeer( &can, r->device, o->device ) == cudaSuccess && can )
+                {
+                    const cudaError_t e = cudaDeviceEnablePeerAccess( o->device, 0 );
+                    if ( e != cudaSuccess ) (void)cudaGetLastError(); // already enabled, or not available: the copies still work
+                }
+            }
+        r->stats.num_nodes = T.numNodes; r->stats.num_leaves = T.numLeaves;
+    }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    B2_CUDA( cudaEventRecord( h->evA, h->stream ) );
+    for ( size_t have = 1; have < all.size(); have *= 2 )
+        for ( size_t i = 0; i < have && i + have < all.size(); ++i )
+        {
+            b2fwn_ctx *src = all[i], *dst = all[i + have];
+            const DeviceTree &S = src->tree, &D = dst->tree;
+            B2_CUDA( cudaSetDevice( dst->device ) );
+            B2_CUDA( cudaStreamWaitEvent( dst->stream, src->evA, 0 ) );
+            auto copy = [&]( void* d, const void* s, size_t bytes ) -> cudaError_t
+            { return bytes ? cudaMemcpyPeerAsync( d, dst->device, s, src->device, bytes, dst->stream ) : cudaSuccess; };
+            B2_CUDA( copy( D.points, S.points, T.numVerts * 3 * sizeof( float ) ) );
+            B2_CUDA( copy( D.tris, S.tris, T.numFaces * 3 * sizeof( int32_t ) ) );
+            B2_CUDA( copy( D.nodes, S.nodes, T.numNodes * sizeof( TravNode ) ) );
+            B2_CUDA( copy( D.leafTris, S.leafTris, T.numLeaves * sizeof( LeafTri ) ) );
+            B2_CUDA( copy( D.leafFilt, S.leafFilt, T.numLeaves * sizeof( LeafFilt ) ) );
+            B2_CUDA( cudaEventRecord( dst->evA, dst->stream ) );
+        }
+    for ( b2fwn_ctx* r : h->replicas )
+    {
+        B2_CUDA( cudaSetDevice( r->device ) );
+        B2_CUDA( cudaStreamSynchronize( r->stream ) );
+    }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    return B2FWN_OK;
+}
+
+} // namespace
+
+int b2fwn_create( const float* points, size_t nVerts, const int32_t* tris, size_t nFaces, const b2fwn_config* cfg,
+                  b2fwn_handle* out )
+{
+    if ( !out || ( nVerts && !points ) || ( nFaces && !tris ) ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    *out = nullptr;
+    std::vector<int> devices{ cfg ? cfg->device : 0 };
+    if ( cfg && cfg->n_devices > 1 )
+    {
+        if ( cfg->n_devices > B2FWN_MAX_DEVICES ) { setError( "too many devices" ); return B2FWN_ERR_INVALID; }
+        devices.assign( cfg->devices, cfg->devices + cfg->n_devices );
+        for ( size_t i = 0; i < devices.size(); ++i )
+            for ( size_t j = 0; j < i; ++j )
+                if ( devices[i] == devices[j] ) { setError( "device listed twice" ); return B2FWN_ERR_INVALID; }
+    }
+    b2fwn_ctx* h = nullptr;
+    if ( int e = newCtx( devices[0], &h ) ) return e;
+    auto fail = [&]( int e ) { b2fwn_destroy( h ); return e; };
+#define B2_TRY( expr ) do { cudaError_t _e = ( expr ); if ( _e != cudaSuccess ) return fail( cudaFail( _e, #expr ) ); } while ( 0 )
+    h->tree.numVerts = nVerts; h->tree.numFaces = nFaces;
+    if ( nVerts )
+    {
+        B2_TRY( cudaMalloc( &h->tree.points, nVerts * 3 * sizeof( float ) ) );
+        B2_TRY( cudaMemcpyAsync( h->tree.points, points, nVerts * 3 * sizeof( float ), cudaMemcpyHostToDevice, h->stream ) );
+    }
+    if ( nFaces )
+    {
+        B2_TRY( cudaMalloc( &h->tree.tris, nFaces * 3 * sizeof( int32_t ) ) );
+        B2_TRY( cudaMemcpyAsync( h->tree.tris, tris, nFaces * 3 * sizeof( int32_t ), cudaMemcpyHostToDevice, h->stream ) );
+    }
+#undef B2_TRY
+    // the other devices' contexts come up on the host while the primary builds
+    cudaEventRecord( h->evA, h->stream );
+    if ( int e = buildTree( h->tree, h->stream, &h->stats.kernel_launches ) ) return fail( e );
+    cudaEventRecord( h->evB, h->stream );
+    cudaEventSynchronize( h->evB );
+    float ms = 0;
+    cudaEventElapsedTime( &ms, h->evA, h->evB );
+    h->stats.tree_build_ms = ms;
+    h->stats.num_nodes = h->tree.numNodes;
+    h->stats.num_leaves = h->tree.numLeaves;
+    for ( size_t i = 1; i < devices.size(); ++i )
+    {
+        b2fwn_ctx* r = nullptr;
+        if ( int e = newCtx( devices[i], &r ) ) return fail( e );
+        h->replicas.push_back( r );
+    }
+    if ( int e = broadcastTree( h ) ) return fail( e );
+    cudaSetDevice( h->device );
+    *out = h;
+    return B2FWN_OK;
+}
+
+void b2fwn_destroy( b2fwn_handle h )
+{
+    if ( !h ) return;
+    for ( b2fwn_ctx* r : h->replicas ) destroyCtx( r );
+    destroyCtx( h );
 }
 
 int b2fwn_update_points( b2fwn_handle h, const float* points, size_t nVerts )
@@ -306,13 +290,16 @@ int b2fwn_update_points( b2fwn_handle h, const float* points, size_t nVerts )
     B2_CUDA( cudaEventSynchronize( h->evB ) );
     float ms = 0;
     if ( cudaEventElapsedTime( &ms, h->evA, h->evB ) == cudaSuccess ) h->stats.last_kernel_ms = ms;
-    return B2FWN_OK;
+    return broadcastTree( h );
 }
+
+size_t b2fwn_safe_memory_limit( int32_t device ) { return safeMemoryLimit( device ); }
 
 int b2fwn_get_stats( b2fwn_handle h, b2fwn_stats* out )
 {
     if ( !h || !out ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
     *out = h->stats;
+    for ( const b2fwn_ctx* r : h->replicas ) out->kernel_launches += r->stats.kernel_launches;
     return B2FWN_OK;
 }
 
@@ -347,41 +334,40 @@ int b2fwn_calc_from_vector( b2fwn_handle h, const float* pts, size_t n, float be
     B2_CUDA( cudaSetDevice( h->device ) );
     if ( !report( cb, user, 0.f ) ) return canceled();
     if ( n == 0 ) return B2FWN_OK;
-    // chunks of 4 Mi points: H2D of chunk k+1 and D2H of chunk k-1 overlap the kernel of chunk k
+    // chunks of 4 Mi points in two device slots: the D2H of chunk k runs on the copy stream while chunk k+1 is uploaded and
+    // walked.  With pageable host memory (std::vector of the adapter) both copies are staged by the driver and block the
+    // calling thread, so only pinned memory overlaps fully; the walk itself is 6.6 ms per 10 M points (C2) either way.
     const size_t chunk = (size_t)4 << 20;
     const size_t count = ( n + chunk - 1 ) / chunk;
     for ( int s = 0; s < 2; ++s )
         if ( int e = ensureScratch( h, s, std::min( n, chunk ) * 4 ) ) return e; // 3 floats in + 1 out per point
-    double kernelMs = 0;
+    B2_CUDA( cudaEventRecord( h->evA, h->stream ) );
     for ( size_t k = 0; k < count; ++k )
     {
         const int s = (int)( k & 1 );
         const size_t o = k * chunk, m = std::min( chunk, n - o );
         float* dIn = h->dScratch[s];
         float* dOut = h->dScratch[s] + 3 * std::min( n, chunk );
-        if ( k >= 2 ) B2_CUDA( cudaEventSynchronize( h->partDone[s] ) );
+        if ( k >= 2 ) B2_CUDA( cudaStreamWaitEvent( h->stream, h->partDone[s], 0 ) ); // the slot's previous result has left
         B2_CUDA( cudaMemcpyAsync( dIn, pts + 3 * o, m * 3 * sizeof( float ), cudaMemcpyHostToDevice, h->stream ) );
-        cudaEventRecord( h->evA, h->stream );
         if ( int e = launchFwnVector( h->tree, dIn, m, beta, skipFace, dOut, h->stream, &h->stats.kernel_launches ) ) return e;
-        cudaEventRecord( h->evB, h->stream );
         B2_CUDA( cudaEventRecord( h->computeDone[s], h->stream ) );
         B2_CUDA( cudaStreamWaitEvent( h->copyStream, h->computeDone[s], 0 ) );
         B2_CUDA( cudaMemcpyAsync( out + o, dOut, m * sizeof( float ), cudaMemcpyDeviceToHost, h->copyStream ) );
         B2_CUDA( cudaEventRecord( h->partDone[s], h->copyStream ) );
         if ( cb )
         {
-            B2_CUDA( cudaEventSynchronize( h->evB ) );
+            B2_CUDA( cudaEventSynchronize( h->computeDone[s] ) );
             if ( !report( cb, user, float( k + 1 ) / float( count ) ) ) { cudaDeviceSynchronize(); return canceled(); }
         }
-        if ( cudaEventSynchronize( h->evB ) == cudaSuccess )
-        {
-            float ms = 0;
-            if ( cudaEventElapsedTime( &ms, h->evA, h->evB ) == cudaSuccess ) kernelMs += ms;
-        }
     }
+    B2_CUDA( cudaEventRecord( h->evB, h->stream ) );
     B2_CUDA( cudaStreamSynchronize( h->stream ) );
     B2_CUDA( cudaStreamSynchronize( h->copyStream ) );
-    h->stats.last_kernel_ms = kernelMs;
+    {
+        float ms = 0; // first upload to last kernel: includes the H2D copies between the kernels
+        if ( cudaEventElapsedTime( &ms, h->evA, h->evB ) == cudaSuccess ) h->stats.last_kernel_ms = ms;
+    }
     return B2FWN_OK;
 }
 
@@ -567,26 +553,43 @@ int b2fwn_shared_free( b2fwn_handle h, void* dPtr )
     return B2FWN_OK;
 }
 
+int b2fwn_calc_from_grid_by_parts_into( b2fwn_handle h, const int32_t dims[3], const float xf[12], float beta, int32_t overlap,
+                                        int32_t maxLayers, b2fwn_part_buffer_cb buffer, b2fwn_part_cb part, void* partUser,
+                                        b2fwn_progress cb, void* user )
+{
+    if ( !h || !dims || !xf || !part ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    if ( dims[0] < 0 || dims[1] < 0 || dims[2] < 0 ) { setError( "invalid grid dimensions" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    const GridXf g = toXf( xf );
+    return runByParts( h, dims, overlap, maxLayers, buffer, part, partUser, cb, user, [&]( b2fwn_ctx* dev, int z0, int z1, float* d, cudaStream_t st )
+        { return launchFwnGrid( dev->tree, dims, g, beta, z0, z1, d, st, &dev->stats.kernel_launches ); } );
+}
+
 int b2fwn_calc_from_grid_by_parts( b2fwn_handle h, const int32_t dims[3], const float xf[12], float beta, int32_t overlap,
                                    int32_t maxLayers, b2fwn_part_cb part, void* partUser, b2fwn_progress cb, void* user )
 {
-    if ( !h || !dims || !xf || !part ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    return b2fwn_calc_from_grid_by_parts_into( h, dims, xf, beta, overlap, maxLayers, nullptr, part, partUser, cb, user );
+}
+
+int b2fwn_calc_from_grid_with_distances_by_parts_into( b2fwn_handle h, const int32_t dims[3], const float xf[12],
+                                                       const b2fwn_dist_options* opt, int32_t overlap, int32_t maxLayers,
+                                                       b2fwn_part_buffer_cb buffer, b2fwn_part_cb part, void* partUser,
+                                                       b2fwn_progress cb, void* user )
+{
+    if ( !h || !dims || !xf || !opt || !part ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    if ( dims[0] < 0 || dims[1] < 0 || dims[2] < 0 ) { setError( "invalid grid dimensions" ); return B2FWN_ERR_INVALID; }
     B2_CUDA( cudaSetDevice( h->device ) );
     const GridXf g = toXf( xf );
-    return runChunked( h, dims, 0, dims[2], overlap, maxLayers, nullptr, part, partUser, cb, user, [&]( int z0, int z1, float* d, cudaStream_t st )
-        { return launchFwnGrid( h->tree, dims, g, beta, z0, z1, d, st, &h->stats.kernel_launches ); } );
+    const b2fwn_dist_options o = *opt;
+    return runByParts( h, dims, overlap, maxLayers, buffer, part, partUser, cb, user, [&]( b2fwn_ctx* dev, int z0, int z1, float* d, cudaStream_t st )
+        { return launchSdfGrid( dev->tree, dims, g, o, z0, z1, d, st, &dev->stats.kernel_launches ); } );
 }
 
 int b2fwn_calc_from_grid_with_distances_by_parts( b2fwn_handle h, const int32_t dims[3], const float xf[12],
                                                   const b2fwn_dist_options* opt, int32_t overlap, int32_t maxLayers,
                                                   b2fwn_part_cb part, void* partUser, b2fwn_progress cb, void* user )
 {
-    if ( !h || !dims || !xf || !opt || !part ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
-    B2_CUDA( cudaSetDevice( h->device ) );
-    const GridXf g = toXf( xf );
-    const b2fwn_dist_options o = *opt;
-    return runChunked( h, dims, 0, dims[2], overlap, maxLayers, nullptr, part, partUser, cb, user, [&]( int z0, int z1, float* d, cudaStream_t st )
-        { return launchSdfGrid( h->tree, dims, g, o, z0, z1, d, st, &h->stats.kernel_launches ); } );
+    return b2fwn_calc_from_grid_with_distances_by_parts_into( h, dims, xf, opt, overlap, maxLayers, nullptr, part, partUser, cb, user );
 }
 
 int b2fwn_calc_from_grid( b2fwn_handle h, const int32_t dims[3], const float xf[12], float beta, float* out,
@@ -597,8 +600,8 @@ int b2fwn_calc_from_grid( b2fwn_handle h, const int32_t dims[3], const float xf[
     if ( (size_t)dims[0] * dims[1] * dims[2] != 0 && !out ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
     B2_CUDA( cudaSetDevice( h->device ) );
     const GridXf g = toXf( xf );
-    return runChunked( h, dims, 0, dims[2], 0, 0, out, nullptr, nullptr, cb, user, [&]( int z0, int z1, float* d, cudaStream_t st )
-        { return launchFwnGrid( h->tree, dims, g, beta, z0, z1, d, st, &h->stats.kernel_launches ); } );
+    return runToHost( h, dims, 0, dims[2], out, cb, user, [&]( b2fwn_ctx* dev, int z0, int z1, float* d, cudaStream_t st )
+        { return launchFwnGrid( dev->tree, dims, g, beta, z0, z1, d, st, &dev->stats.kernel_launches ); } );
 }
 
 int b2fwn_calc_from_grid_with_distances_layers( b2fwn_handle h, const int32_t dims[3], const float xf[12],
@@ -612,8 +615,8 @@ int b2fwn_calc_from_grid_with_distances_layers( b2fwn_handle h, const int32_t di
     B2_CUDA( cudaSetDevice( h->device ) );
     const GridXf g = toXf( xf );
     const b2fwn_dist_options o = *opt;
-    return runChunked( h, dims, zBegin, zEnd, 0, 0, out, nullptr, nullptr, cb, user, [&]( int z0, int z1, float* d, cudaStream_t st )
-        { return launchSdfGrid( h->tree, dims, g, o, z0, z1, d, st, &h->stats.kernel_launches ); } );
+    return runToHost( h, dims, zBegin, zEnd, out, cb, user, [&]( b2fwn_ctx* dev, int z0, int z1, float* d, cudaStream_t st )
+        { return launchSdfGrid( dev->tree, dims, g, o, z0, z1, d, st, &dev->stats.kernel_launches ); } );
 }
 
 int b2fwn_calc_from_grid_with_distances( b2fwn_handle h, const int32_t dims[3], const float xf[12],
@@ -655,11 +658,11 @@ int b2fwn_make_signed_by_winding_number( b2fwn_handle h, const int32_t dims[3], 
     const GridXf g = toXf( xf );
     const size_t layer = (size_t)dims[0] * dims[1];
     // chunk k: H2D on its compute stream, walk, D2H (runChunked) back to where it came from; the slot is free again by then
-    return runChunked( h, dims, 0, dims[2], 0, 0, volume, nullptr, nullptr, cb, user, [&]( int z0, int z1, float* d, cudaStream_t st )
+    return runToHost( h, dims, 0, dims[2], volume, cb, user, [&]( b2fwn_ctx* dev, int z0, int z1, float* d, cudaStream_t st )
     {
         B2_CUDA( cudaMemcpyAsync( d, volume + (size_t)z0 * layer, (size_t)( z1 - z0 ) * layer * sizeof( float ), cudaMemcpyHostToDevice, st ) );
         // d holds the layers z0..z1 (its first float is voxel (0,0,z0)), like every slab the grid launchers write
-        return launchSignGrid( h->tree, dims, g, beta, threshold, z0, z1, d, st, &h->stats.kernel_launches );
+        return launchSignGrid( dev->tree, dims, g, beta, threshold, z0, z1, d, st, &dev->stats.kernel_launches );
     } );
 }
 
@@ -714,10 +717,17 @@ int b2fwn_mesh_to_distance_volume( b2fwn_handle h, const b2fwn_volume_params* vo
         volatile float half = 0.5f * vol->voxel_size[c];
         xf[9 + c] = vol->origin[c] + half;
     }
-    unsigned* dMM = nullptr;
-    B2_CUDA( cudaMalloc( &dMM, 2 * sizeof( unsigned ) ) );
+    // running min / max per device (8 B each, part of the handle), combined on the host afterwards
+    std::vector<b2fwn_ctx*> devs{ h };
+    devs.insert( devs.end(), h->replicas.begin(), h->replicas.end() );
     const unsigned init[2] = { 0xFFFFFFFFu, 0u };
-    cudaMemcpyAsync( dMM, init, sizeof( init ), cudaMemcpyHostToDevice, h->stream );
+    for ( b2fwn_ctx* d : devs )
+    {
+        B2_CUDA( cudaSetDevice( d->device ) );
+        if ( !d->dMinMax ) B2_CUDA( cudaMalloc( &d->dMinMax, sizeof( init ) ) );
+        B2_CUDA( cudaMemcpy( d->dMinMax, init, sizeof( init ), cudaMemcpyHostToDevice ) );
+    }
+    B2_CUDA( cudaSetDevice( h->device ) );
     const GridXf g = toXf( xf );
     const b2fwn_dist_options o = *opt;
     const int32_t* dims = vol->dims;
@@ -725,18 +735,24 @@ int b2fwn_mesh_to_distance_volume( b2fwn_handle h, const b2fwn_volume_params* vo
     if ( dims[0] < 0 || dims[1] < 0 || dims[2] < 0 ) setError( "invalid grid dimensions" );
     else if ( (size_t)dims[0] * dims[1] * dims[2] != 0 && !out ) setError( "null argument" );
     else
-        rc = runChunked( h, dims, 0, dims[2], 0, 0, out, nullptr, nullptr, cb, user, [&]( int z0, int z1, float* d, cudaStream_t st )
+        rc = runToHost( h, dims, 0, dims[2], out, cb, user, [&]( b2fwn_ctx* dev, int z0, int z1, float* d, cudaStream_t st )
         {
-            if ( int e = launchSdfGrid( h->tree, dims, g, o, z0, z1, d, st, &h->stats.kernel_launches ) ) return e;
+            if ( int e = launchSdfGrid( dev->tree, dims, g, o, z0, z1, d, st, &dev->stats.kernel_launches ) ) return e;
             const size_t n = (size_t)dims[0] * dims[1] * ( z1 - z0 );
-            kMinMax<<<(unsigned)std::min<size_t>( ( n + 255 ) / 256, 148 * 8 ), 256, 0, st>>>( d, n, dMM );
-            ++h->stats.kernel_launches;
+            kMinMax<<<(unsigned)std::min<size_t>( ( n + 255 ) / 256, 148 * 8 ), 256, 0, st>>>( d, n, dev->dMinMax );
+            ++dev->stats.kernel_launches;
             return B2FWN_OK;
         } );
-    unsigned mm[2] = { 0xFFFFFFFFu, 0u };
-    if ( rc == B2FWN_OK ) cudaMemcpy( mm, dMM, sizeof( mm ), cudaMemcpyDeviceToHost );
-    cudaFree( dMM );
     if ( rc ) return rc;
+    unsigned mm[2] = { 0xFFFFFFFFu, 0u };
+    for ( b2fwn_ctx* d : devs )
+    {
+        unsigned one[2];
+        B2_CUDA( cudaSetDevice( d->device ) );
+        B2_CUDA( cudaMemcpy( one, d->dMinMax, sizeof( one ), cudaMemcpyDeviceToHost ) );
+        mm[0] = std::min( mm[0], one[0] ); mm[1] = std::max( mm[1], one[1] );
+    }
+    B2_CUDA( cudaSetDevice( h->device ) );
     if ( outMin ) *outMin = mm[0] == 0xFFFFFFFFu ? FLT_MAX : fromOrd( mm[0] );
     if ( outMax ) *outMax = mm[1] == 0u ? -FLT_MAX : fromOrd( mm[1] );
     return B2FWN_OK;
@@ -769,7 +785,7 @@ int b2fwn_signed_distances_by_projection_normal_device( b2fwn_handle h, const fl
     B2_CUDA( cudaSetDevice( h->device ) );
     if ( n == 0 ) return B2FWN_OK;
     b2fwn_projection* dProj = nullptr;
-    B2_CUDA( cudaMallocAsync( &dProj, n * sizeof( b2fwn_projection ), h->stream ) );
+    B2_CUDA( cudaMallocFromPoolAsync( &dProj, n * sizeof( b2fwn_projection ), h->tree.pool, h->stream ) );
     KernelTimer tm( h );
     const int e = launchSignedDistProjNormal( h->tree, dPts, n, opt->min_dist_sq, opt->max_dist_sq, opt->null_outside_min_max, dProj, dOut,
                                               h->stream, &h->stats.kernel_launches );

@@ -1201,7 +1201,7 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
     const size_t scratchBytes = 64 + 2 * nbPad * sizeof( uint16_t ) + 2 * nbPad + 2 * (size_t)cap * sizeof( uint32_t );
     if ( band || order )
     {
-        B2_CUDA( cudaMallocAsync( &scratch, scratchBytes, st ) );
+        B2_CUDA( cudaMallocFromPoolAsync( &scratch, scratchBytes, t.pool, st ) );
         B2_CUDA( cudaMemsetAsync( scratch, 0, 64, st ) );
     }
     unsigned long long* totals = reinterpret_cast<unsigned long long*>( scratch ); // [0,1] distance, [2,3] winding number
@@ -1354,7 +1354,7 @@ int launchDistSlotGrid( const DeviceTree& t, const int32_t dims[3], const float 
     uint16_t* costD = nullptr;
     if ( band )
     {
-        B2_CUDA( cudaMallocAsync( &scratch, 64 + nbPad * sizeof( uint16_t ), st ) );
+        B2_CUDA( cudaMallocFromPoolAsync( &scratch, 64 + nbPad * sizeof( uint16_t ), t.pool, st ) );
         B2_CUDA( cudaMemsetAsync( scratch, 0, 64, st ) );
         costD = reinterpret_cast<uint16_t*>( scratch + 64 );
         kBrickCull<<<(unsigned)( ( numBricks + 255 ) / 256 ), 256, 0, st>>>( t.nodes, Pc, costD, reinterpret_cast<unsigned long long*>( scratch ) );

@@ -72,6 +72,9 @@ struct DeviceTree
     // high-priority side stream of the grid launcher (walk-length estimates beside the distance kernels), forked / joined by events
     cudaStream_t sideStream = nullptr;
     cudaEvent_t evFork = nullptr, evJoin = nullptr;
+    // private stream-ordered pool of the per-launch scratch (cached across synchronisations; the device's default pool and its
+    // release threshold, which belong to the host application, are left alone)
+    cudaMemPool_t pool = nullptr;
     // pseudonormal tables of SignDetectionMode::ProjectionNormal, built on first use (b2fwn_normals.cu)
     float* faceNormals = nullptr; // numFaces*3
     float* vertNormals = nullptr; // numVerts*3
@@ -96,6 +99,8 @@ int cudaFail( cudaError_t e, const char* where );
     } while ( 0 )
 
 // tree build (b2fwn_tree.cu) -----------------------------------------------------------------------------------
+// side stream, fork / join events and the private memory pool of a tree on `device` (idempotent)
+int initTreeAux( DeviceTree& t, int device );
 int buildTree( DeviceTree& t, cudaStream_t stream, uint64_t* launches );
 // new vertex coordinates in t.points, same triangulation: boxes, dipoles, traversal nodes and leaf triangles recomputed on the
 // unchanged tree topology (AABBTree::refit, MRAABBTree.cpp:62-94)

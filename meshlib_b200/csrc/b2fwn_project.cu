@@ -198,7 +198,7 @@ int launchFindProjections( const DeviceTree& t, const float* dPts, size_t n, con
         cub::DeviceRadixSort::SortPairs( nullptr, tempBytes, (const uint32_t*)nullptr, (uint32_t*)nullptr, (const uint32_t*)nullptr, (uint32_t*)nullptr,
                                          (int)n, 0, 30, st );
         const size_t words = ( n + 3 ) & ~(size_t)3;
-        B2_CUDA( cudaMallocAsync( &scratch, 4 * words * sizeof( uint32_t ) + tempBytes, st ) );
+        B2_CUDA( cudaMallocFromPoolAsync( &scratch, 4 * words * sizeof( uint32_t ) + tempBytes, t.pool, st ) );
         uint32_t *keysIn = scratch, *keysOut = scratch + words, *idxIn = scratch + 2 * words, *idxOut = scratch + 3 * words;
         float3 lo, scale;
         {

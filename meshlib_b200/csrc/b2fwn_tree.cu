@@ -468,6 +468,30 @@ inline unsigned nblk( size_t n ) { return (unsigned)( ( n + TB - 1 ) / TB ); }
 
 } // anonymous namespace
 
+int initTreeAux( DeviceTree& t, int device )
+{
+    if ( !t.sideStream )
+    {
+        int lo = 0, hi = 0;
+        B2_CUDA( cudaDeviceGetStreamPriorityRange( &lo, &hi ) ); // hi = greatest priority (numerically lowest)
+        B2_CUDA( cudaStreamCreateWithPriority( &t.sideStream, cudaStreamNonBlocking, hi ) );
+        B2_CUDA( cudaEventCreateWithFlags( &t.evFork, cudaEventDisableTiming ) );
+        B2_CUDA( cudaEventCreateWithFlags( &t.evJoin, cudaEventDisableTiming ) );
+    }
+    if ( !t.pool )
+    {
+        cudaMemPoolProps props{};
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = device;
+        B2_CUDA( cudaMemPoolCreate( &t.pool, &props ) );
+        unsigned long long keep = ~0ull; // a host-output call synchronises per chunk: keep the scratch cached in between
+        B2_CUDA( cudaMemPoolSetAttribute( t.pool, cudaMemPoolAttrReleaseThreshold, &keep ) );
+    }
+    return B2FWN_OK;
+}
+
 void freeTree( DeviceTree& t )
 {
     cudaFree( t.points ); cudaFree( t.tris ); cudaFree( t.refNodes ); cudaFree( t.refDipoles );
@@ -476,6 +500,7 @@ void freeTree( DeviceTree& t )
     if ( t.sideStream ) cudaStreamDestroy( t.sideStream );
     if ( t.evFork ) cudaEventDestroy( t.evFork );
     if ( t.evJoin ) cudaEventDestroy( t.evJoin );
+    if ( t.pool ) cudaMemPoolDestroy( t.pool );
     t = DeviceTree{};
 }
 
@@ -484,13 +509,11 @@ int buildTree( DeviceTree& t, cudaStream_t st, uint64_t* launches )
     uint64_t nl = 0;
     const size_t F = t.numFaces;
     t.numLeaves = t.numNodes = 0; t.depth = 0;
-    if ( !t.sideStream )
+    if ( !t.sideStream || !t.pool )
     {
-        int lo = 0, hi = 0;
-        B2_CUDA( cudaDeviceGetStreamPriorityRange( &lo, &hi ) ); // hi = greatest priority (numerically lowest)
-        B2_CUDA( cudaStreamCreateWithPriority( &t.sideStream, cudaStreamNonBlocking, hi ) );
-        B2_CUDA( cudaEventCreateWithFlags( &t.evFork, cudaEventDisableTiming ) );
-        B2_CUDA( cudaEventCreateWithFlags( &t.evJoin, cudaEventDisableTiming ) );
+        int dev = 0;
+        B2_CUDA( cudaGetDevice( &dev ) );
+        if ( int e = initTreeAux( t, dev ) ) return e;
     }
     if ( F == 0 ) return B2FWN_OK;
     if ( F > (size_t)0x3FFFFFFF ) { setError( "too many faces" ); return B2FWN_ERR_INVALID; }

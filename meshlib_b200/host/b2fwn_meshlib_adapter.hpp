@@ -28,7 +28,9 @@
 
 #include <cfloat>
 #include <cstring>
+#include <deque>
 #include <memory>
+#include <new>
 #include <string>
 #include <vector>
 
@@ -41,7 +43,14 @@ class FastWindingNumber final : public IFastWindingNumber, public IFastWindingNu
 {
 public:
     /// stores a reference: the mesh must outlive this object (as MR::FastWindingNumber, MRFastWindingNumber.h:54-56)
-    explicit FastWindingNumber( const Mesh& mesh, int device = 0 ) : mesh_( mesh ), device_( device ) {}
+    explicit FastWindingNumber( const Mesh& mesh, int device = 0 ) : mesh_( mesh ), devices_{ device } {}
+    /// several GPUs of this process (b2fwn_config.n_devices): the grid calls below deal their z-chunks over all of them and
+    /// every GPU copies its chunks straight into `res` / the parts; the reference class is tied to device 0
+    /// (MRCudaFastWindingNumber.cpp:48)
+    FastWindingNumber( const Mesh& mesh, std::vector<int> devices ) : mesh_( mesh ), devices_( std::move( devices ) )
+    {
+        if ( devices_.empty() ) devices_.push_back( 0 );
+    }
     ~FastWindingNumber() override { b2fwn_destroy( h_ ); }
     FastWindingNumber( const FastWindingNumber& ) = delete;
     FastWindingNumber& operator=( const FastWindingNumber& ) = delete;
@@ -100,8 +109,8 @@ public:
         const int32_t d[3] = { dims.x, dims.y, dims.z };
         float xf[12];
         packXf_( gridToMeshXf, xf );
-        PartCtx ctx{ &resFunc, {} };
-        const int rc = b2fwn_calc_from_grid_by_parts( h_, d, xf, beta, layerOverlap, 0, &part_, &ctx, &progress_, (void*)&cb );
+        PartCtx ctx{ &resFunc, {}, {} };
+        const int rc = b2fwn_calc_from_grid_by_parts_into( h_, d, xf, beta, layerOverlap, 0, &partBuffer_, &part_, &ctx, &progress_, (void*)&cb );
         return ctx.error.empty() ? status_( rc ) : unexpected( ctx.error );
     }
 
@@ -113,8 +122,8 @@ public:
         float xf[12];
         packXf_( gridToMeshXf, xf );
         const b2fwn_dist_options o = packOptions_( options );
-        PartCtx ctx{ &resFunc, {} };
-        const int rc = b2fwn_calc_from_grid_with_distances_by_parts( h_, d, xf, &o, layerOverlap, 0, &part_, &ctx, &progress_, (void*)&cb );
+        PartCtx ctx{ &resFunc, {}, {} };
+        const int rc = b2fwn_calc_from_grid_with_distances_by_parts_into( h_, d, xf, &o, layerOverlap, 0, &partBuffer_, &part_, &ctx, &progress_, (void*)&cb );
         return ctx.error.empty() ? status_( rc ) : unexpected( ctx.error );
     }
 
@@ -162,6 +171,7 @@ private:
     {
         GridByPartsFunc* func;
         std::string error;
+        std::deque<std::pair<int, std::vector<float>>> pending; // parts being filled by the library, by zOffset
     };
 
     // lazy one-time upload + device tree/dipole build (replaces prepareData_, MRCudaFastWindingNumber.cpp:46-85:
@@ -172,7 +182,13 @@ private:
         const auto tris = mesh_.topology.getTriangulation(); // invalid faces come out with invalid (-1) vertex ids
         static_assert( sizeof( ThreeVertIds ) == 3 * sizeof( int32_t ) );
         b2fwn_config cfg{};
-        cfg.device = device_;
+        cfg.device = devices_[0];
+        if ( devices_.size() > 1 )
+        {
+            if ( devices_.size() > B2FWN_MAX_DEVICES ) return unexpected( std::string( "too many devices" ) );
+            cfg.n_devices = int32_t( devices_.size() );
+            for ( size_t i = 0; i < devices_.size(); ++i ) cfg.devices[i] = devices_[i];
+        }
         return status_( b2fwn_create( reinterpret_cast<const float*>( mesh_.points.data() ), mesh_.points.size(),
                                       reinterpret_cast<const int32_t*>( tris.data() ), tris.size(), &cfg, &h_ ) );
     }
@@ -189,11 +205,29 @@ private:
         return ( !cb || cb( v ) ) ? 1 : 0;
     }
 
-    static int part_( const float* data, const int32_t dims[3], int32_t zOffset, void* user )
+    // the consumer receives an owned vector it may keep or discard (MRCudaFastWindingNumber.cpp:340-354): the library asks for
+    // the storage a few parts ahead and fills it (overlapped copies) while later parts are computed; no second copy here
+    static float* partBuffer_( const int32_t dims[3], int32_t zOffset, void* user )
     {
         auto& ctx = *static_cast<PartCtx*>( user );
-        // the consumer receives an owned vector it may keep or discard (MRCudaFastWindingNumber.cpp:340-354)
-        std::vector<float> chunk( data, data + size_t( dims[0] ) * dims[1] * dims[2] );
+        try
+        {
+            ctx.pending.emplace_back( zOffset, std::vector<float>( size_t( dims[0] ) * dims[1] * dims[2] ) );
+        }
+        catch ( const std::bad_alloc& )
+        {
+            ctx.error = "not enough host memory for a part of the grid";
+            return nullptr;
+        }
+        return ctx.pending.back().second.data();
+    }
+
+    static int part_( const float*, const int32_t dims[3], int32_t zOffset, void* user )
+    {
+        auto& ctx = *static_cast<PartCtx*>( user );
+        if ( ctx.pending.empty() || ctx.pending.front().first != zOffset ) { ctx.error = "by-parts protocol error"; return 1; }
+        std::vector<float> chunk = std::move( ctx.pending.front().second );
+        ctx.pending.pop_front();
         auto r = ( *ctx.func )( std::move( chunk ), Vector3i( dims[0], dims[1], dims[2] ), zOffset );
         if ( r ) return 0;
         ctx.error = r.error();
@@ -221,7 +255,7 @@ private:
     }
 
     const Mesh& mesh_;
-    int device_ = 0;
+    std::vector<int> devices_;
     b2fwn_handle h_ = nullptr;
 };
 

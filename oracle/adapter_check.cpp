@@ -13,9 +13,13 @@
 #include "MRMesh/MRTriMesh.h"
 #include "MRVoxels/MRMarchingCubes.h"
 #include "MRVoxels/MRVoxelsVolume.h"
+#include <chrono>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
+#include <cstring>
 #include <memory>
+#include <sstream>
 
 using namespace MR;
 
@@ -26,8 +30,85 @@ static void check( bool ok, const char* what )
     if ( !ok ) ++g_fail;
 }
 
-int main()
+// --bench pts.bin tris.bin nx ny nz ox oy oz voxel maxDistSq nullOutside devices(csv) [byparts]
+// End to end through the C++ adapter the way a MeshLib caller sees it: a Mesh (built here by the reference's own
+// Mesh::fromTriangles, not timed), then ONE calcFromGridWithDistances into a std::vector<float> (pageable), wall clock.  The
+// first call includes prepare_ (upload + device tree build); the second reuses the handle.  `res` is pre-sized and touched
+// before the timed call (the resize inside the adapter is then a no-op): value-initialising 34 GB on one thread is the
+// caller's cost with the reference class as well and would hide everything else.
+static double nowMs()
 {
+    return std::chrono::duration<double, std::milli>( std::chrono::steady_clock::now().time_since_epoch() ).count();
+}
+template <typename T>
+static std::vector<T> readAll( const char* path )
+{
+    std::vector<T> v;
+    FILE* f = std::fopen( path, "rb" );
+    if ( !f ) return v;
+    std::fseek( f, 0, SEEK_END );
+    const long n = std::ftell( f );
+    std::fseek( f, 0, SEEK_SET );
+    v.resize( size_t( n ) / sizeof( T ) );
+    if ( std::fread( v.data(), sizeof( T ), v.size(), f ) != v.size() ) v.clear();
+    std::fclose( f );
+    return v;
+}
+static int benchMain( int argc, char** argv )
+{
+    if ( argc < 14 ) { std::printf( "usage: --bench pts.bin tris.bin nx ny nz ox oy oz voxel maxDistSq nullOutside devices [byparts]\n" ); return 2; }
+    auto pts = readAll<Vector3f>( argv[2] );
+    auto tr = readAll<ThreeVertIds>( argv[3] );
+    if ( pts.empty() || tr.empty() ) { std::printf( "cannot read the mesh files\n" ); return 2; }
+    const Vector3i dims( std::atoi( argv[4] ), std::atoi( argv[5] ), std::atoi( argv[6] ) );
+    const Vector3f origin( (float)std::atof( argv[7] ), (float)std::atof( argv[8] ), (float)std::atof( argv[9] ) );
+    const float voxel = (float)std::atof( argv[10] );
+    DistanceToMeshOptions opt;
+    opt.maxDistSq = (float)std::atof( argv[11] );
+    opt.nullOutsideMinMax = std::atoi( argv[12] ) != 0;
+    std::vector<int> devices;
+    { std::stringstream ss( argv[13] ); std::string t; while ( std::getline( ss, t, ',' ) ) devices.push_back( std::atoi( t.c_str() ) ); }
+    const bool byParts = argc > 14 && !std::strcmp( argv[14], "byparts" );
+    double t0 = nowMs();
+    Triangulation tris;
+    tris.vec_ = std::move( tr );
+    VertCoords coords;
+    coords.vec_ = std::move( pts );
+    Mesh mesh = Mesh::fromTriangles( std::move( coords ), tris );
+    std::printf( "bench.mesh_build_ms %.1f faces %zu\n", nowMs() - t0, (size_t)mesh.topology.numValidFaces() );
+    const AffineXf3f basis{ Matrix3f::scale( voxel ), origin + Vector3f::diagonal( 0.5f * voxel ) };
+    const size_t total = size_t( dims.x ) * dims.y * dims.z;
+    std::vector<float> res( total, 1.f ); // sized and touched by the caller
+    for ( int rep = 0; rep < 3; ++rep )
+    {
+        // rep 0: fresh object (prepare_ inside the call); rep 1: same object again; rep 2: fresh object, by-parts consumer copies into res
+        static std::unique_ptr<B200::FastWindingNumber> fwn;
+        if ( rep != 1 ) fwn = std::make_unique<B200::FastWindingNumber>( mesh, devices );
+        t0 = nowMs();
+        Expected<void> r;
+        if ( rep == 2 )
+        {
+            if ( !byParts ) break;
+            r = fwn->calcFromGridWithDistancesByParts( [&]( std::vector<float>&& data, const Vector3i& d, int z ) -> Expected<void>
+            {
+                std::memcpy( res.data() + size_t( z ) * d.x * d.y, data.data(), data.size() * sizeof( float ) );
+                return {};
+            }, dims, basis, opt, 0, {} );
+        }
+        else r = fwn->calcFromGridWithDistances( res, dims, basis, opt, {} );
+        const double ms = nowMs() - t0;
+        if ( !r ) { std::printf( "bench.call FAIL (%s)\n", r.error().c_str() ); return 1; }
+        double sum = 0;
+        for ( size_t i = 0; i < total; i += 4099 ) if ( res[i] == res[i] ) sum += std::abs( res[i] );
+        std::printf( "bench.%s_ms %.1f voxels_per_s %.4g checksum %.6f\n", rep == 0 ? "first_call_with_prepare" : rep == 1 ? "second_call" : "by_parts_with_prepare",
+                     ms, double( total ) / ( ms * 1e-3 ), sum );
+    }
+    return 0;
+}
+
+int main( int argc, char** argv )
+{
+    if ( argc > 1 && !std::strcmp( argv[1], "--bench" ) ) return benchMain( argc, argv );
     Mesh mesh = makeTorus( 2.f, 1.f, 64, 32 );
     // the reference-facing handle type used by every caller (params.fwn): std::shared_ptr<IFastWindingNumber>
     std::shared_ptr<IFastWindingNumber> ours = std::make_shared<B200::FastWindingNumber>( mesh );
@@ -75,6 +156,22 @@ int main()
     }
     std::printf( "calcFromGridWithDistances.sign_mismatch_outside_band %zu in_band %zu max_rel_dist_err %g\n", signMism, band, maxRel );
     check( da.size() == db.size() && signMism == 0 && maxRel <= 1e-5f, "calcFromGridWithDistances.parity" );
+
+    // several GPUs of one process (b2fwn_config.n_devices): chunks dealt over the devices, every device copies into `res`
+    // itself; the volume must be the single-device one bit for bit (same kernels, same per-voxel arithmetic)
+    if ( b2fwn_device_count() >= 2 )
+    {
+        setenv( "B2FWN_MIN_CHUNK_VOXELS", "8000", 1 ); // test switch of the library: small chunks, so that both devices get several
+        B200::FastWindingNumber multi( mesh, std::vector<int>{ 0, 1 } );
+        std::vector<float> dm;
+        const Vector3i big( 40, 40, 96 ); // enough layers for several chunks per device
+        std::vector<float> d1;
+        check( multi.calcFromGridWithDistances( dm, big, basis, opt, {} ).has_value(), "multiDevice.call" );
+        check( ours->calcFromGridWithDistances( d1, big, basis, opt, {} ).has_value(), "multiDevice.single.call" );
+        check( dm.size() == d1.size() && std::memcmp( dm.data(), d1.data(), dm.size() * sizeof( float ) ) == 0, "multiDevice.bit_identical" );
+        unsetenv( "B2FWN_MIN_CHUNK_VOXELS" );
+    }
+    else std::printf( "multiDevice skipped (one device)\n" );
 
     // mcOffsetMesh's by-parts branch: our chunks -> the reference's MarchingCubesByParts
     const float offset = 0.1f;

@@ -29,7 +29,7 @@ def test_header_symbols_exported():
 
 def test_struct_layouts_match_header():
     assert C.sizeof(mb.DistOptions) == 20
-    assert C.sizeof(mb.api.Config) == 32
+    assert C.sizeof(mb.api.Config) == 96
     assert C.sizeof(mb.api.Stats) == 64
     assert C.sizeof(mb.api.McParams) == 48
     assert mb.PROJECTION_DTYPE.itemsize == 32
@@ -37,6 +37,21 @@ def test_struct_layouts_match_header():
     o = mb.DistOptions()
     assert (o.min_dist_sq, o.null_outside_min_max, o.winding_number_threshold, o.winding_number_beta) == (0.0, 1, 0.5, 2.0)
     assert o.max_dist_sq == np.finfo(np.float32).max
+
+
+def test_struct_sizes_against_the_c_compiler(tmp_path):
+    # the header compiled as plain C: its sizeof values are what the ctypes mirrors must have
+    import subprocess
+    src = tmp_path / "sz.c"
+    src.write_text('#include <stdio.h>\n#include "b2fwn.h"\nint main(void){printf("%zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(b2fwn_config),'
+                   'sizeof(b2fwn_dist_options), sizeof(b2fwn_stats), sizeof(b2fwn_projection), sizeof(b2fwn_mc_params),'
+                   'sizeof(b2fwn_volume_params), sizeof(b2fwn_offset_params), sizeof(b2fwn_offset_result));return 0;}\n')
+    exe = tmp_path / "sz"
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", f"-I{ROOT}/include", str(src), "-o", str(exe)], check=True)
+    got = [int(x) for x in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.split()]
+    want = [C.sizeof(mb.api.Config), C.sizeof(mb.DistOptions), C.sizeof(mb.api.Stats), mb.PROJECTION_DTYPE.itemsize, C.sizeof(mb.api.McParams),
+            C.sizeof(mb.VolumeParams), C.sizeof(mb.OffsetParams), C.sizeof(mb.OffsetResult)]
+    assert got == want
 
 
 def test_no_cpu_fallback_without_device():
