@@ -8,8 +8,8 @@ A "step" is one pass of the hot path over the whole voxel grid of the workload.
   value  : voxels/s, result resident in HBM (the _device form of the C ABI), device time by CUDA events on the
            launching stream (b2fwn_stats.last_kernel_ms), max over ranks.
   e2e    : voxels/s through the reference-facing call with HOST buffers: mesh arrays on the host -> b2fwn_create
-           (H2D + device tree/dipole build) -> b2fwn_calc_from_grid_with_distances into a pinned host volume
-           (chunked D2H inside the timed region).
+           (H2D + device tree/dipole build) -> b2fwn_calc_from_grid_with_distances into a PAGEABLE host volume (chunked,
+           staged D2H inside the timed region) -> b2fwn_destroy; one process drives all N GPUs (multi-device handle).
   --impl reference : the reference's own CPU/TBB implementation (oracle/_ref when it was built, else the C
            restatement) on a bounded sample of the same workload, all host threads.
 N > 1 (torchrun): the grid is sharded by z (interleaved chunks of a few layers per rank, meshlib_b200/slabs.py), mesh and
@@ -406,6 +406,11 @@ def run_ours(args, wl):
     wall_ms = 1e3 * (time.perf_counter() - t0)
     clocks = sampler.stop() if rank == 0 else None
     launches = fwn.stats().kernel_launches - launches0
+    per_rank_kernel_ms = None
+    if world > 1:  # the slowest rank must be visible
+        g = [torch.zeros(1, dtype=torch.float64, device=dev) for _ in range(world)]
+        dist.all_gather(g, torch.tensor([k_sum / args.steps], dtype=torch.float64, device=dev))
+        per_rank_kernel_ms = [float(x[0]) for x in g]
     t = torch.tensor([k_sum + g_sum, k_sum, g_sum, wall_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -424,6 +429,10 @@ def run_ours(args, wl):
             raise SystemExit(f"volumes differ between ranks: checksum range [{-float(c[1])}, {float(c[0])}]")
 
     # ---- e2e: host mesh -> create (H2D + device tree build) -> host volume, all inside the timed region --------------
+    # ONE process drives all N GPUs through the library's own multi-device handle (b2fwn_config.n_devices): what a MeshLib caller
+    # gets from MR::B200::FastWindingNumber( mesh, devices ).  Under torchrun the other ranks release their GPUs and wait.
+    # The output buffer is PAGEABLE host memory that the caller has sized and touched (a std::vector<float> after resize);
+    # the same call into pinned memory is reported beside it.
     e2e = None
     if not args.no_e2e:
         del volume, slab
@@ -433,35 +442,48 @@ def run_ours(args, wl):
                 fwn.shared_close(q)
             barrier()
             fwn.shared_free(my_ptr)
-        torch.cuda.empty_cache()
-        nslab = (z1 - z0) * layer
-        host = torch.empty(nslab, dtype=torch.float32, pin_memory=True)
-        host_np = host.numpy()
-        sub_xf = np.array(xf, np.float32)
-        # the slab as its own grid: b' = A*(0,0,z0) + b would round differently; use the by-layers host call instead
-        e_steps = max(1, min(args.steps, 3))
         fwn.close()
+        torch.cuda.empty_cache()
         barrier()
-        t0 = time.perf_counter()
-        for _ in range(e_steps):
-            f2 = mb.FastWindingNumber(wl["points"], wl["tris"], device=local)
-            f2.calc_from_grid_with_distances_layers(dims, sub_xf, z0, z1, opts, out=host_np)
-            f2.close()
+        if rank == 0:
+            devices = list(range(world))
+            e_steps = max(1, min(args.steps, 3))
+
+            def run(out, steps):
+                t0 = time.perf_counter()
+                for _ in range(steps):
+                    f2 = mb.FastWindingNumber(wl["points"], wl["tris"], devices=devices)
+                    f2.calc_from_grid_with_distances(dims, xf, opts, out=out)
+                    st = f2.stats()
+                    f2.close()
+                return 1e3 * (time.perf_counter() - t0) / steps, st
+
+            host_np = np.empty(total, np.float32)
+            host_np.fill(0)  # touched, like the vector a caller resized
+            run(host_np, 1)  # warm-up: contexts on the other devices, staging rings
+            e_ms, st2 = run(host_np, e_steps)
+            # the host-output call must deliver what the device-resident call left in HBM (same kernels, chunked): bit for bit
+            e2e_same = None
+            if gpu_layers is not None:
+                e2e_same = all(np.array_equal(host_np[z * layer:(z + 1) * layer].view(np.uint32), g.view(np.uint32)) for z, g in gpu_layers.items())
+            e2e_checksum = float(np.nan_to_num(host_np[:: max(1, total // (1 << 22))]).astype(np.float64).__abs__().sum())
+            del host_np
+            pinned_ms = None
+            if not args.no_pinned:
+                host = torch.empty(total, dtype=torch.float32, pin_memory=True)
+                run(host.numpy(), 1)
+                pinned_ms, _ = run(host.numpy(), e_steps)
+                del host
+            e2e = {"value": total / (e_ms * 1e-3), "unit": UNIT, "ms_per_step": e_ms, "steps": e_steps,
+                   "h2d_bytes_per_step": int(wl["points"].nbytes + wl["tris"].nbytes + 12 * 4 + 20),
+                   "d2h_bytes_per_step": int(4 * total), "equals_resident_volume_on_sample_layers": e2e_same, "checksum": e2e_checksum,
+                   "host_buffer": "pageable (numpy, sized and touched by the caller): pinned staging ring + copier threads inside the library",
+                   "pinned_buffer": None if pinned_ms is None else {"value": total / (pinned_ms * 1e-3), "ms_per_step": pinned_ms},
+                   "kernel_ms_of_the_call": st2.last_kernel_ms, "tree_build_ms": st2.tree_build_ms,
+                   "includes": f"one process, {world} GPU(s): b2fwn_create (mesh H2D + device tree/dipole build on GPU 0"
+                               + (", peer copies of the tree to the others" if world > 1 else "")
+                               + ") + b2fwn_calc_from_grid_with_distances into the host buffer + b2fwn_destroy; host wall clock"}
         barrier()
-        e_ms = 1e3 * (time.perf_counter() - t0) / e_steps
-        t = torch.tensor([e_ms], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e_ms = float(t[0])
-        # the host-output call must deliver what the device-resident call left in HBM (same kernels, chunked): bit for bit
-        e2e_same = None
-        if gpu_layers is not None:
-            e2e_same = all(np.array_equal(host_np[(z - z0) * layer:(z - z0 + 1) * layer].view(np.uint32), g.view(np.uint32))
-                           for z, g in gpu_layers.items() if z0 <= z < z1)
-        e2e = {"value": total / (e_ms * 1e-3), "unit": UNIT, "ms_per_step": e_ms, "steps": e_steps,
-               "h2d_bytes_per_step": int(wl["points"].nbytes + wl["tris"].nbytes + 12 * 4 + 20),
-               "d2h_bytes_per_step": int(4 * nslab), "equals_resident_volume_on_sample_layers": e2e_same,
-               "includes": "b2fwn_create (mesh H2D + device tree/dipole build) + grid call into pinned host memory, per rank; host wall clock"}
 
     if rank != 0:
         if world > 1:
@@ -489,7 +511,7 @@ def run_ours(args, wl):
                        (st0.num_nodes * 64 + st0.num_leaves * 64) / 1e6, 4 * total / 1e6),
                    "timing": ("CUDA events on the launching stream" if world == 1 else
                               "host clock around the K steps, device synchronised and ranks barriered on both sides") + ", max over ranks"},
-        "kernel_ms_per_step": k_ms, "gather_exposed_ms_per_step": g_ms, "wall_ms_per_step": wall_ms,
+        "kernel_ms_per_step": k_ms, "kernel_ms_per_rank": per_rank_kernel_ms, "gather_exposed_ms_per_step": g_ms, "wall_ms_per_step": wall_ms,
         "tree_build_ms": st0.tree_build_ms, "num_faces": int(st0.num_leaves), "num_nodes": int(st0.num_nodes),
         "clocks": clocks, "gpu_launches": int(launches), "checksum": checksum,
     }
@@ -540,6 +562,7 @@ def main():
     ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"], help="N > 1: fused peer stores, or NCCL all-gather")
     ap.add_argument("--stages", type=int, default=4, help="N > 1: compute/gather pipeline stages over z")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-pinned", action="store_true", help="skip the pinned-buffer variant of the e2e leg")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     args = ap.parse_args()

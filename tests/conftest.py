@@ -3,6 +3,10 @@ import sys
 
 import pytest
 
+# test switch of the library (b2fwn_pipeline.cu): 16-KiB staging pieces, so that even the small test grids travel through the
+# pinned ring in several pieces per chunk; bench.py runs with the default 32-MiB pieces
+os.environ.setdefault("B2FWN_PIECE_FLOATS", "4096")
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)

@@ -1,0 +1,199 @@
+"""GPU tests of the host side of the grid calls (meshlib_b200/csrc/b2fwn_pipeline.cu): pageable / pinned / device outputs,
+caller-owned by-parts buffers, several devices of one process, cancellation, the memory budget.  The numbers themselves are
+pinned against the oracle in test_gpu_parity.py; here every variant must deliver the SAME bits as the device-resident call."""
+import os
+
+import numpy as np
+import pytest
+
+import meshlib_b200 as mb
+from meshlib_b200 import meshgen
+from oracle import checker
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def torus():
+    pts, tris = meshgen.make_torus(2, 1, 96, 48)
+    fwn = mb.FastWindingNumber(pts, tris)
+    yield pts, tris, fwn
+    fwn.close()
+
+
+@pytest.fixture()
+def small_chunks(monkeypatch):
+    # test switch of the library: chunks of ~20k voxels instead of >= 32 Mi, so that small grids run many chunks
+    monkeypatch.setenv("B2FWN_MIN_CHUNK_VOXELS", "20000")
+
+
+def _device_volume(fwn, dims, xf, opts):
+    import torch
+    n = dims[0] * dims[1] * dims[2]
+    d = torch.empty(n, dtype=torch.float32, device="cuda")
+    fwn.calc_from_grid_with_distances_device(dims, xf, d.data_ptr(), opts)
+    return d.cpu().numpy()
+
+
+@pytest.mark.parametrize("band", [False, True])
+def test_pageable_pinned_and_device_outputs_are_identical(torus, small_chunks, band):
+    import torch
+    _p, _t, fwn = torus
+    dims = (64, 60, 44)  # x % 4 == 0: vector stores; 168,960 voxels -> 9 chunks, several staging pieces per chunk
+    xf = mb.make_basis_xf((-3.3, -3.3, -1.3), (0.103, 0.11, 0.06))
+    opts = mb.DistOptions(0.0, 0.09, False) if band else mb.DistOptions()
+    want = _device_volume(fwn, dims, xf, opts)
+    pageable = np.full(want.size, np.float32(7e33))
+    fwn.calc_from_grid_with_distances(dims, xf, opts, out=pageable)
+    assert pageable.tobytes() == want.tobytes()
+    pinned = torch.full((want.size,), 7e33, dtype=torch.float32).pin_memory()
+    fwn.calc_from_grid_with_distances(dims, xf, opts, out=pinned.numpy())
+    assert pinned.numpy().tobytes() == want.tobytes()
+    # a z-range into the middle of a pageable buffer, and winding numbers alone
+    part = np.empty(dims[0] * dims[1] * 17, np.float32)
+    fwn.calc_from_grid_with_distances_layers(dims, xf, 9, 26, opts, out=part)
+    layer = dims[0] * dims[1]
+    assert part.tobytes() == want[9 * layer:26 * layer].tobytes()
+    import torch as _t2
+    dw = _t2.empty(want.size, dtype=_t2.float32, device="cuda")
+    fwn.calc_from_grid_device(dims, xf, dw.data_ptr())
+    assert fwn.calc_from_grid(dims, xf).tobytes() == dw.cpu().numpy().tobytes()
+
+
+def test_ragged_grid_through_the_staging_ring(torus, small_chunks):
+    _p, _t, fwn = torus
+    dims = (37, 29, 23)
+    xf = mb.make_basis_xf((-3.2, -3.2, -1.2), (0.17, 0.22, 0.1))
+    want = _device_volume(fwn, dims, xf, mb.DistOptions())
+    got = fwn.calc_from_grid_with_distances(dims, xf)
+    assert got.tobytes() == want.tobytes()
+
+
+def test_by_parts_into_caller_owned_buffers(torus, small_chunks):
+    _p, _t, fwn = torus
+    dims = (40, 36, 31)
+    xf = mb.make_basis_xf((-3.2, -3.2, -1.3), (0.16, 0.18, 0.085))
+    full = _device_volume(fwn, dims, xf, mb.DistOptions())
+    layer = dims[0] * dims[1]
+    for overlap, per_part in ((0, 0), (1, 4), (2, 7), (1, 31)):
+        seen, vol = [], np.full(full.size, np.float32(7e33))
+
+        def part(arr, d, z0):
+            assert arr.size == layer * d[2] and arr.flags.owndata  # the consumer owns the memory it receives
+            seen.append(z0)
+            vol[z0 * layer:(z0 + d[2]) * layer] = arr
+            return True
+
+        fwn.calc_from_grid_with_distances_by_parts_into(part, dims, xf, layer_overlap=overlap, max_layers_per_part=per_part)
+        assert seen == sorted(seen) and len(set(seen)) == len(seen) and seen[0] == 0
+        assert vol.tobytes() == full.tobytes()
+    # winding numbers alone, consumer failure
+    w = fwn.calc_from_grid(dims, xf)
+    got = np.empty_like(w)
+
+    def part_w(arr, d, z0):
+        got[z0 * layer:(z0 + d[2]) * layer] = arr
+
+    fwn.calc_from_grid_with_distances_by_parts_into(part_w, dims, xf, layer_overlap=1, max_layers_per_part=5, distances=False)
+    assert got.tobytes() == w.tobytes()
+    with pytest.raises(mb.B2Error):
+        fwn.calc_from_grid_with_distances_by_parts_into(lambda *a: False, dims, xf, max_layers_per_part=4)
+    # the handle is still usable after an aborted call
+    assert fwn.calc_from_grid_with_distances(dims, xf).tobytes() == full.tobytes()
+
+
+def test_cancellation_midway_and_reuse(torus, small_chunks):
+    _p, _t, fwn = torus
+    dims = (48, 48, 40)
+    xf = mb.make_basis_xf((-3.2, -3.2, -1.3), (0.135, 0.135, 0.066))
+    seen = []
+    with pytest.raises(mb.B2Error) as e:
+        fwn.calc_from_grid_with_distances(dims, xf, cb=lambda v: seen.append(v) or v < 0.3)
+    assert str(e.value) == "Operation was canceled" and e.value.code == 2
+    assert seen[0] == 0.0 and 0.3 <= seen[-1] < 1.0
+    want = _device_volume(fwn, dims, xf, mb.DistOptions())
+    assert fwn.calc_from_grid_with_distances(dims, xf).tobytes() == want.tobytes()
+
+
+def test_min_dist_with_null_outside_false_option_shape(torus, small_chunks):
+    """mcOffsetMesh( closeHoles ) asks for minDistSq > 0 with nullOutsideMinMax = false (MROffset.cpp:176-183).  The reference stops
+    a voxel's search as soon as a candidate is within minDist (MRMeshProject.cpp:60-63), so what such a voxel reports depends on the
+    visiting order: the contract is |d| <= minDist on both sides there, and bit-identical distances everywhere else -- in the
+    full-grid call, in a z-slab and in the chunked host call."""
+    pts, tris, fwn = torus
+    orc = checker.best_oracle(pts, tris)
+    dims = (48, 44, 36)
+    xf = mb.make_basis_xf((-3.3, -3.3, -1.3), (0.1375, 0.15, 0.0722))
+    min_d, max_d = 0.22, 0.5
+    o = dict(min_dist_sq=min_d * min_d, max_dist_sq=max_d * max_d, null_outside=False)
+    want = orc.calc_from_grid_with_distances(dims, xf, **o)
+    opts = mb.DistOptions(o["min_dist_sq"], o["max_dist_sq"], False)
+    full = _device_volume(fwn, dims, xf, opts)
+    host = fwn.calc_from_grid_with_distances(dims, xf, opts)
+    layer = dims[0] * dims[1]
+    slab = fwn.calc_from_grid_with_distances_layers(dims, xf, 10, 22, opts)
+    lim = np.float32(np.sqrt(np.float32(o["min_dist_sq"]))) * np.float32(1 + 1e-6)
+    for got in (full, host):
+        near = np.abs(want) <= lim
+        assert near.sum() > 1000 and (~near).sum() > 1000
+        assert (np.abs(got[near]) <= lim).all()
+        assert np.array_equal(np.abs(got[~near]).view(np.uint32), np.abs(want[~near]).view(np.uint32))
+    near = np.abs(want[10 * layer:22 * layer]) <= lim
+    assert np.array_equal(slab[~near].view(np.uint32), full[10 * layer:22 * layer][~near].view(np.uint32))
+    assert (np.abs(slab[near]) <= lim).all()
+    w = orc.calc_from_grid(dims, xf)
+    rep = checker.compare_sdf(np.where(np.abs(want) <= lim, want, full), want, w)
+    assert rep["sign_mismatch"] == 0 and rep["nan_mismatch"] == 0, rep
+    signs_near = np.signbit(full) == np.signbit(want)
+    assert signs_near[(np.abs(w - 0.5) >= 1e-3)].all()
+
+
+def test_safe_memory_limit_and_budgeted_parts(torus):
+    _p, _t, fwn = torus
+    lim = mb.load_library().b2fwn_safe_memory_limit(0)
+    import torch
+    free, total = torch.cuda.mem_get_info(0)
+    assert 0 < lim < free and lim > 0.5 * free  # 80 % of (free - 128 MB), MRCudaBasic.cpp:75-90
+    # a caller asking for parts of "as many layers as possible" gets whole layers within the budget
+    dims = (32, 32, 24)
+    xf = mb.make_basis_xf((-3.2, -3.2, -1.3), (0.2, 0.2, 0.11))
+    parts = []
+    fwn.calc_from_grid_with_distances_by_parts(lambda a, d, z: parts.append((z, d[2])) or True, dims, xf, max_layers_per_part=1 << 20)
+    assert parts == [(0, 24)]
+
+
+def test_several_devices_of_one_process(small_chunks):
+    L = mb.load_library()
+    if L.b2fwn_device_count() < 2:
+        pytest.skip("one CUDA device")
+    pts, tris = meshgen.make_torus(2, 1, 96, 48)
+    n = min(L.b2fwn_device_count(), 4)
+    one = mb.FastWindingNumber(pts, tris)
+    many = mb.FastWindingNumber(pts, tris, devices=list(range(n)))
+    dims = (64, 60, 70)
+    xf = mb.make_basis_xf((-3.3, -3.3, -1.3), (0.103, 0.11, 0.038))
+    for opts in (mb.DistOptions(), mb.DistOptions(0.0, 0.09, False)):
+        want = one.calc_from_grid_with_distances(dims, xf, opts)
+        assert many.calc_from_grid_with_distances(dims, xf, opts).tobytes() == want.tobytes()
+    layer = dims[0] * dims[1]
+    vol = np.empty(layer * dims[2], np.float32)
+    seen = []
+
+    def part(arr, d, z0):
+        seen.append(z0)
+        vol[z0 * layer:(z0 + d[2]) * layer] = arr
+
+    many.calc_from_grid_with_distances_by_parts_into(part, dims, xf, layer_overlap=1, max_layers_per_part=6)
+    assert seen == sorted(seen) and vol.tobytes() == one.calc_from_grid_with_distances(dims, xf).tobytes()
+    assert many.calc_from_grid(dims, xf).tobytes() == one.calc_from_grid(dims, xf).tobytes()
+    got, lo, hi = many.mesh_to_distance_volume((-3.3, -3.3, -1.3), (0.103, 0.11, 0.038), dims)
+    w1, lo1, hi1 = one.mesh_to_distance_volume((-3.3, -3.3, -1.3), (0.103, 0.11, 0.038), dims)
+    assert got.tobytes() == w1.tobytes() and (lo, hi) == (lo1, hi1)
+    # moved vertices reach every replica
+    moved = (pts * np.float32(1.05)).astype(np.float32)
+    one.update_points(moved)
+    many.update_points(moved)
+    assert many.calc_from_grid_with_distances(dims, xf).tobytes() == one.calc_from_grid_with_distances(dims, xf).tobytes()
+    assert many.stats().kernel_launches > one.stats().kernel_launches / 2
+    one.close()
+    many.close()
