@@ -48,6 +48,13 @@ WORKLOADS = {
 }
 DEFAULT_WORKLOAD = "c5_band"
 
+# C3 as BASELINE.json states it: generalOffsetMesh (Standard mode, HoleWindingRule sign) of the 2 M-face noisy sphere at ~512^3 voxels
+# INCLUDING marching cubes: b2fwn_mc_offset_mesh (distance band + marching cubes, both in HBM).  Diagnostic workload, not the headline.
+OFFSET_WORKLOADS = {
+    "c3_offset": dict(mesh=("noisy_sphere", 1414, 707, 1e-3), voxel=2.04 / 508.0, offset=0.02, close_holes=True),
+    "c5_offset": dict(mesh=("noisy_sphere", 3162, 1581, 1e-3), voxel=2.04 / 2040.0, offset=0.005, close_holes=True),
+}
+
 # DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of ONE launch of the dominant kernel (kGridFwn5, whole grid on one
 # GPU) from an `ncu --set full` capture on B200; not measurable inside a timed run, so quoted from the committed capture
 NCU_TRAFFIC = {
@@ -282,6 +289,81 @@ def run_reference_arm(args, wl):
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# offset workloads: distance band + marching cubes (north_star subsystem 4), single GPU
+# ---------------------------------------------------------------------------------------------------------------------
+
+def run_offset(args, name):
+    import torch
+    import meshlib_b200 as mb
+    w = OFFSET_WORKLOADS[name]
+    spec = w["mesh"]
+    pts, tris = meshgen.make_uv_sphere(1, spec[1], spec[2])
+    pts = meshgen.add_noise(pts, spec[3], seed=42)
+    torch.cuda.set_device(0)
+    fwn = mb.FastWindingNumber(pts, tris)
+    for _ in range(args.warmup):
+        fwn.mc_offset_mesh(w["offset"], w["voxel"], close_holes=w["close_holes"], fetch=False)
+    sampler = ClockSampler(0)
+    sampler.start()
+    l0 = fwn.stats().kernel_launches
+    sdf = mc = 0.0
+    for _ in range(args.steps):
+        _v, _t, info = fwn.mc_offset_mesh(w["offset"], w["voxel"], close_holes=w["close_holes"], fetch=False)
+        sdf += info["sdf_ms"]
+        mc += info["mc_ms"]
+    clocks = sampler.stop()
+    launches = fwn.stats().kernel_launches - l0
+    sdf, mc = sdf / args.steps, mc / args.steps
+    dims = info["dims"]
+    total = dims[0] * dims[1] * dims[2]
+    # e2e: host mesh -> create -> offset -> TriMesh on the host (pageable numpy), create + fetch + destroy inside
+    fwn.close()
+    e_steps = max(1, min(args.steps, 3))
+    t0 = time.perf_counter()
+    for _ in range(e_steps):
+        f2 = mb.FastWindingNumber(pts, tris)
+        v, t, info2 = f2.mc_offset_mesh(w["offset"], w["voxel"], close_holes=w["close_holes"], fetch=True)
+        f2.close()
+    e_ms = 1e3 * (time.perf_counter() - t0) / e_steps
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak, hbm_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json)") if "hbm_gbs" in peaks else (6650.0, "fallback")
+    out_bytes = 12 * info["n_verts"] + 12 * info["n_tris"]
+    mc_bytes = 10.5 * total + out_bytes  # value read twice, code written + read, segment totals; + the compacted output
+    desc = (f"{name}: mcOffsetMesh of {len(tris)} faces, voxel {w['voxel']:.6g}, offset {w['offset']}, grid {dims[0]}x{dims[1]}x{dims[2]}, "
+            f"HoleWindingRule, closeHoles={w['close_holes']}, incl. marching cubes")
+    out = {"metric": METRIC, "value": total / ((sdf + mc) * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": sdf + mc, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": desc, "timing": "CUDA events on the launching stream (b2fwn_offset_result.sdf_ms + mc_ms)",
+                      "l2": "volume %.0f MB per step, larger than L2" % (4 * total / 1e6)},
+           "sdf_ms": sdf, "mc_ms": mc, "n_verts": int(info["n_verts"]), "n_tris": int(info["n_tris"]), "clocks": clocks, "gpu_launches": int(launches),
+           "e2e": {"value": total / (e_ms * 1e-3), "unit": UNIT, "ms_per_step": e_ms, "steps": e_steps,
+                   "h2d_bytes_per_step": int(pts.nbytes + tris.nbytes), "d2h_bytes_per_step": int(out_bytes),
+                   "includes": "b2fwn_create + b2fwn_mc_offset_mesh + b2fwn_marching_cubes_fetch into pageable numpy arrays + b2fwn_destroy; host wall clock"},
+           "roofline": {"bound": "hbm", "kernel": "kMcClassify + scans + kMcEmit (marching cubes stage)", "achieved": mc_bytes / (mc * 1e-3) / 1e9,
+                        "peak": hbm_peak, "peak_source": hbm_src, "unit": "GB/s", "frac": mc_bytes / (mc * 1e-3) / 1e9 / hbm_peak,
+                        "algorithmic_bytes": mc_bytes, "traffic": None}}
+    if not args.no_cpu:
+        from oracle import checker
+        orc = checker.best_oracle(pts, tris)
+        t0 = time.perf_counter()
+        wv, wt, _sdf, worigin, wdims = checker.ref_mc_offset_mesh(orc, pts, orc.tris if hasattr(orc, "tris") else tris, w["offset"], w["voxel"],
+                                                                 close_holes=w["close_holes"])
+        c_s = time.perf_counter() - t0
+        from oracle import reflib
+        out["cpu_baseline"] = {"value": total / c_s, "unit": UNIT, "cores": reflib.hardware_threads() if reflib.available() else 1,
+                               "kind": getattr(orc, "kind", "port"), "sample": f"the whole pipeline once: reference SDF band + reference marching cubes, {c_s:.1f} s"}
+        same_tris = (len(t) == len(wt)) and bool(np.array_equal(t, wt)) if hasattr(orc, "tris") and np.array_equal(orc.tris, tris) else None
+        out["parity"] = {"dims_equal": tuple(wdims) == tuple(info2["dims"]), "origin_equal": bool(np.array_equal(worigin, info2["origin"])),
+                         "n_verts": [int(len(v)), int(len(wv))], "n_tris": [int(len(t)), int(len(wt))], "triangles_identical": same_tris,
+                         "max_vertex_diff": float(np.abs(v - wv).max()) if len(v) == len(wv) else None}
+    print(json.dumps(out))
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -556,7 +638,7 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS) + sorted(OFFSET_WORKLOADS))
     ap.add_argument("--grid", type=int, default=None, help="override the grid size (diagnostics only; not the headline)")
     ap.add_argument("--z-chunk", type=int, default=8, help="N > 1: layers per interleaved chunk (multiple of 4)")
     ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"], help="N > 1: fused peer stores, or NCCL all-gather")
@@ -566,6 +648,10 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     args = ap.parse_args()
+    if args.workload in OFFSET_WORKLOADS:
+        if args.impl == "reference" or args.gpus != 1:
+            raise SystemExit("offset workloads are single-GPU diagnostics of our arm")
+        return run_offset(args, args.workload)
     wl = build_workload(args.workload, args.grid)
     if args.impl == "reference":
         run_reference_arm(args, wl)

@@ -17,8 +17,8 @@
  *    and only enqueue + synchronise the handle's stream.
  *  - host OUTPUT of the grid calls may be pageable (std::vector<float>, numpy) or pinned.  Pinned memory (cudaMallocHost /
  *    cudaHostRegister) receives each chunk by one asynchronous copy behind the next chunk's kernels.  Pageable memory is
- *    filled through a pinned staging ring (256 MiB per device, allocated at the first such call, kept for the life of the
- *    process) and 4 copier threads per device (B2FWN_COPY_THREADS), also behind the next chunk's kernels: both overlap.
+ *    filled through a pinned staging ring (384 MiB per device, allocated at the first such call, kept for the life of the
+ *    process) and up to 8 copier threads per device (B2FWN_COPY_THREADS), also behind the next chunk's kernels: both overlap.
  *  - grid linearisation id = x + dx*(y + dy*z) (source/MRMesh/MRVolumeIndexer.h:132-140); the query point of
  *    voxel (x,y,z) is A*(x,y,z)+b with xf = {A row-major (9), b (3)} (source/MRMesh/MRAffineXf.h:46).
  *  - there is no CPU fallback: without a CUDA device b2fwn_create fails.

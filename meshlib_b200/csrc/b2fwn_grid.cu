@@ -931,8 +931,10 @@ __device__ __forceinline__ void fwn6Inner( const int i, const int link, const fl
 // diverged section: nodes [i, end) with per-voxel resume indices; returns end
 __device__ __forceinline__ int fwn6Section( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris, int i, const int end,
                                             const float betaSq, const float2 ( &px )[FX / 2], const float py, const float pz,
-                                            float2 ( &sum )[FX / 2], int ( &fR )[FX] )
+                                            float2 ( &sum )[FX / 2], int ( &fR )[FX], const float pxLane, unsigned char* __restrict__ smList,
+                                            float* __restrict__ smRes )
 {
+    const unsigned lane = threadIdx.x & 31;
     while ( i < end )
     {
         const float4* np = reinterpret_cast<const float4*>( nodes + i );
@@ -966,14 +968,42 @@ __device__ __forceinline__ int fwn6Section( const TravNode* __restrict__ nodes, 
             }
             if ( __any_sync( FULL, go != 0 ) )
             {
+                // The voxels that are near this triangle are few and scattered over lanes and voxel slots (ncu, c5_band: the exact
+                // solid angle ran with 12 of 32 lanes active, slot by slot, and took 31 % of the kernel's time).  They are
+                // compacted: every (lane, slot) pair becomes one work item in a per-warp list, the warp evaluates 32 items at a
+                // time with all lanes busy and hands the results back through shared memory.  Each voxel still adds its own term
+                // at the same place of its sum: the bits do not change.
                 const float4* tp = reinterpret_cast<const float4*>( tris + ( -link - 1 ) );
                 const float4 ta = __ldg( tp ), tb = __ldg( tp + 1 ), tc = __ldg( tp + 2 );
+                const int cnt = __popc( go );
+                int incl = cnt;
+#pragma unroll
+                for ( int d = 1; d < 32; d <<= 1 )
+                {
+                    const int t = __shfl_up_sync( FULL, incl, d );
+                    if ( lane >= (unsigned)d ) incl += t;
+                }
+                const int total = __shfl_sync( FULL, incl, 31 );
+                int pos = incl - cnt;
+                for ( unsigned g = go; g; g &= g - 1 ) smList[pos++] = (unsigned char)( lane * FX + ( __ffs( g ) - 1 ) );
+                __syncwarp();
+                for ( int t0 = 0; t0 < total; t0 += 32 )
+                {
+                    const int t = t0 + (int)lane;
+                    const unsigned code = t < total ? smList[t] : 0u;
+                    const int L = (int)( code >> 3 ), v = (int)( code & 7u );
+                    const float qx = __shfl_sync( FULL, pxLane, v ); // lane v holds the x of voxel slot v (the same for every lane)
+                    const float qy = __shfl_sync( FULL, py, L ), qz = __shfl_sync( FULL, pz, L );
+                    if ( t < total ) smRes[( v << 5 ) + L] = triangleSolidAngle( make_float3( qx, qy, qz ), ta, tb, tc );
+                }
+                __syncwarp();
 #pragma unroll
                 for ( int k = 0; k < FX / 2; ++k )
                 {
-                    if ( go & ( 1u << ( 2 * k ) ) ) sum[k].x = FA( sum[k].x, triangleSolidAngle( make_float3( px[k].x, py, pz ), ta, tb, tc ) );
-                    if ( go & ( 2u << ( 2 * k ) ) ) sum[k].y = FA( sum[k].y, triangleSolidAngle( make_float3( px[k].y, py, pz ), ta, tb, tc ) );
+                    if ( go & ( 1u << ( 2 * k ) ) ) sum[k].x = FA( sum[k].x, smRes[( ( 2 * k ) << 5 ) + lane] );
+                    if ( go & ( 2u << ( 2 * k ) ) ) sum[k].y = FA( sum[k].y, smRes[( ( 2 * k + 1 ) << 5 ) + lane] );
                 }
+                __syncwarp();
             }
         }
         i = max( __reduce_min_sync( FULL, minOf( fR ) ), i + 1 );
@@ -985,6 +1015,9 @@ template <int MODE, bool PEERS, int MINB = 7>
 __global__ void __launch_bounds__( GRID_TB, MINB ) kGridFwn6( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
                                                         const GridParams P, float* __restrict__ out, const BrickOrder O, const PeerOut peers )
 {
+    // work items of a leaf's exact solid angles and their results (fwn6Section), per warp
+    __shared__ unsigned char sList[GRID_TB / 32][32 * FX];
+    __shared__ float sRes[GRID_TB / 32][32 * FX];
     const unsigned lane = threadIdx.x & 31;
     size_t brick;
     if ( !brickIndexOfWarp( P, O, brick ) ) return;
@@ -1040,6 +1073,8 @@ __global__ void __launch_bounds__( GRID_TB, MINB ) kGridFwn6( const TravNode* __
             sum[k] = make_float2( 0.f, 0.f );
         }
     }
+    // x of voxel slot (lane & 7), the same bits as px[] (same function, same arguments): lane v serves slot v in fwn6Section
+    const float pxLane = applyXf( P.A, P.b, (float)( x0 + (int)( lane & 7 ) ), (float)y, (float)z ).x;
     // ball of the voxels that take part: centre of the brick, radius to the farthest such voxel
     const float3 pc = applyXf( P.A, P.b, (float)x0 + 3.5f, (float)( by * F6Y ) + 3.5f, (float)globalZ( P, bz * F6Z ) + 1.5f );
     float radSq = 0.f;
@@ -1075,7 +1110,7 @@ __global__ void __launch_bounds__( GRID_TB, MINB ) kGridFwn6( const TravNode* __
         }
 #pragma unroll
         for ( int v = 0; v < FX; ++v ) fR[v] = ( valid & ( 1u << v ) ) ? i : INT_MAX;
-        i = fwn6Section( nodes, tris, i, next, P.betaSq, px, py, pz, sum, fR );
+        i = fwn6Section( nodes, tris, i, next, P.betaSq, px, py, pz, sum, fR, pxLane, sList[threadIdx.x >> 5], sRes[threadIdx.x >> 5] );
     }
 
     if ( !rowValid ) return;

@@ -110,7 +110,7 @@ struct CopyJob
 
 struct HostRing
 {
-    static constexpr int R = 8;                           // staging slots
+    static constexpr int R = 12;                          // staging slots
     size_t PIECE = (size_t)8 << 20;                       // floats per slot: 32 MiB (B2FWN_PIECE_FLOATS: test switch)
     int device = 0;
     float* slot[R] = {};
@@ -132,7 +132,9 @@ struct HostRing
             if ( e == cudaSuccess ) e = cudaEventCreateWithFlags( &ev[s], cudaEventDisableTiming );
             if ( e != cudaSuccess ) { error = cudaGetErrorString( e ); (void)cudaGetLastError(); return; }
         }
-        int threads = 4;
+        // measured on the 16-thread host of a B200 box (c5_band, 34 GB into pageable memory): 2 threads 1577 ms, 4 threads 1345 ms,
+        // 8 threads 1133 ms against 1116 ms into pinned memory (profiles/r02)
+        int threads = (int)std::max( 2u, std::min( 8u, std::thread::hardware_concurrency() / 2 ) );
         if ( const char* t = getenv( "B2FWN_COPY_THREADS" ) ) threads = std::max( 1, std::min( atoi( t ), R ) );
         for ( int t = 0; t < threads; ++t ) std::thread( [this] { threadMain(); } ).detach();
         ok = true;
@@ -181,7 +183,7 @@ struct HostRing
     }
 };
 
-// one ring per device for the life of the process (256 MiB of pinned memory, allocated at the first pageable host-output call
+// one ring per device for the life of the process (384 MiB of pinned memory, allocated at the first pageable host-output call
 // on that device; never freed: its threads outlive every handle)
 HostRing* ringOf( int device, std::string& err )
 {
@@ -203,11 +205,13 @@ bool isPinned( const void* p )
 
 struct Geometry
 {
-    int nz, step, layersPerPart, count;
-    size_t layer;
-    int z0( int k ) const { return k * step; }
-    int z1( int k ) const { return std::min( nz, k * step + layersPerPart ); }
-    size_t floats( int k ) const { return (size_t)( z1( k ) - z0( k ) ) * layer; }
+    int nz = 0, count = 0, maxLayers = 0;
+    size_t layer = 0;
+    std::vector<int> begin, end; // layers [begin[k], end[k]) of the call's range
+    int z0( int k ) const { return begin[k]; }
+    int z1( int k ) const { return end[k]; }
+    size_t floats( int k ) const { return (size_t)( end[k] - begin[k] ) * layer; }
+    void add( int b, int e ) { begin.push_back( b ); end.push_back( e ); maxLayers = std::max( maxLayers, e - b ); count = (int)begin.size(); }
 };
 
 // layers per chunk when the caller leaves the choice to us: whole layers, one eighth of a device's share of the grid but
@@ -259,7 +263,7 @@ void driveDevice( b2fwn_ctx* dev, const int d, const int nd, const ChunkedCall& 
     if ( n == 0 ) return;
     if ( cudaBad( cudaSetDevice( dev->device ), "cudaSetDevice" ) ) return;
     const bool libraryParts = c.part && !c.partBuffer;
-    const size_t chunkFloats = (size_t)g.layersPerPart * g.layer;
+    const size_t chunkFloats = (size_t)g.maxLayers * g.layer;
     for ( int s = 0; s < 2 && s < n; ++s )
     {
         int e = ensureScratch( dev, s, chunkFloats );
@@ -377,11 +381,17 @@ int runChunked( b2fwn_ctx* h, const ChunkedCall& c, const ChunkLaunch& launch )
     if ( c.overlap < 0 ) { setError( "negative layer overlap" ); return B2FWN_ERR_INVALID; }
     std::vector<b2fwn_ctx*> devs{ h };
     devs.insert( devs.end(), h->replicas.begin(), h->replicas.end() );
-    g.layersPerPart = chooseLayersPerPart( devs, dims, g.nz, c.overlap, c.layersPerPart );
-    if ( g.layersPerPart <= c.overlap ) { setError( "part must be larger than the overlap" ); return B2FWN_ERR_INVALID; }
-    // splitByChunks (source/MRMesh/MRChunkIterator.cpp:25-49): offset_k = k*(chunk-overlap), last chunk shorter
-    g.step = g.layersPerPart - c.overlap;
-    g.count = g.nz <= c.overlap ? 1 : ( g.nz - c.overlap + g.step - 1 ) / g.step;
+    // (r02: chunk sizes that fall geometrically -- half of the rest per round, short tail -- were tried for the contiguous host
+    // output and lost: 1778 ms against 1133 ms at c5_band into pageable memory.  The driver thread feeds the copies of a chunk
+    // before it can launch the chunk after the next, so a 17-GB first chunk left the GPU idle behind its copy.)
+    {
+        const int layersPerPart = chooseLayersPerPart( devs, dims, g.nz, c.overlap, c.layersPerPart );
+        if ( layersPerPart <= c.overlap ) { setError( "part must be larger than the overlap" ); return B2FWN_ERR_INVALID; }
+        // splitByChunks (source/MRMesh/MRChunkIterator.cpp:25-49): offset_k = k*(chunk-overlap), last chunk shorter
+        const int step = layersPerPart - c.overlap;
+        const int count = g.nz <= c.overlap ? 1 : ( g.nz - c.overlap + step - 1 ) / step;
+        for ( int k = 0; k < count; ++k ) g.add( k * step, std::min( g.nz, k * step + layersPerPart ) );
+    }
     auto report = [&]( float v ) { return !c.progress || c.progress( v, c.progressUser ) != 0; };
     if ( !report( 0.f ) ) { setError( kCanceled ); return B2FWN_ERR_CANCELED; }
 

@@ -79,6 +79,15 @@ static int benchMain( int argc, char** argv )
     const AffineXf3f basis{ Matrix3f::scale( voxel ), origin + Vector3f::diagonal( 0.5f * voxel ) };
     const size_t total = size_t( dims.x ) * dims.y * dims.z;
     std::vector<float> res( total, 1.f ); // sized and touched by the caller
+    {
+        // process warm-up on a tiny mesh: CUDA context, the library's staging ring (what a long-running MeshLib process has paid once)
+        Mesh tiny = makeTorus( 2.f, 1.f, 16, 8 );
+        B200::FastWindingNumber warm( tiny, devices );
+        std::vector<float> w;
+        t0 = nowMs();
+        (void)warm.calcFromGridWithDistances( w, Vector3i( 16, 16, 16 ), AffineXf3f{ Matrix3f::scale( 0.4f ), Vector3f::diagonal( -3.f ) }, DistanceToMeshOptions{}, {} );
+        std::printf( "bench.process_warmup_ms %.1f\n", nowMs() - t0 );
+    }
     for ( int rep = 0; rep < 3; ++rep )
     {
         // rep 0: fresh object (prepare_ inside the call); rep 1: same object again; rep 2: fresh object, by-parts consumer copies into res
