@@ -318,6 +318,29 @@ typedef struct b2fwn_offset_result
 } b2fwn_offset_result;
 int b2fwn_mc_offset_mesh( b2fwn_handle h, const b2fwn_offset_params* p, b2fwn_offset_result* res, b2fwn_progress cb, void* user );
 
+/* ---- after marching cubes: the half-edge tables of the result (first slice) ---------------------------- */
+
+/* MeshTopology::HalfEdgeRecord (source/MRMesh/MRMeshTopology.h:581-594): sym(e) = e ^ 1; next / prev = counter-clockwise /
+ * clockwise neighbour among the half-edges with the same origin; -1 = invalid id */
+typedef struct b2fwn_half_edge
+{
+    int32_t next, prev, org, left;
+} b2fwn_half_edge;
+
+/* Replaces Mesh::fromTriMesh -> MeshBuilder::fromTriangles (source/MRMesh/MRMeshBuilder.cpp:371-540; the last step of mcOffsetMesh,
+ * source/MRVoxels/MROffset.cpp:222-225) for an oriented manifold triangulation: half-edge records, one half-edge per vertex and
+ * per face, built on the device by one radix sort over the face corners.  tris_abc = NULL: the triangles of the handle's last
+ * marching-cubes result, still in HBM (n_tris / n_verts are then ignored); otherwise n_tris triples on the host
+ * (tris_on_device = 0) or on the handle's device.  Half-edges are numbered by sorted (min vertex, max vertex): 2u = min -> max,
+ * 2u + 1 = max -> min (the reference's numbering depends on its thread count and is no contract); faces and vertices keep their
+ * ids, edge_per_face[f] starts at the first corner of f.  The three arrays in the layout of MeshTopology::write
+ * (MRMeshTopology.cpp:2461-2477) load with MeshTopology::read, which also validates them.
+ * Returns B2FWN_ERR_INVALID ("... not an oriented manifold ...") for meshes the direct construction does not cover (an edge with
+ * three faces, two faces on the same side of an edge, a vertex with two fans): the caller keeps the CPU builder for those. */
+int b2fwn_build_topology( b2fwn_handle h, const int32_t* tris_abc, size_t n_tris, int32_t tris_on_device, size_t n_verts,
+                          uint64_t* n_half_edges, uint64_t* n_verts_out, uint64_t* n_faces_out );
+int b2fwn_build_topology_fetch( b2fwn_handle h, b2fwn_half_edge* out_edges, int32_t* out_edge_per_vertex, int32_t* out_edge_per_face );
+
 #ifdef __cplusplus
 }
 #endif

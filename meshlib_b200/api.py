@@ -102,6 +102,7 @@ EXPORTS = [
     "b2fwn_signed_distances_by_projection_normal", "b2fwn_signed_distances_by_projection_normal_device",
     "b2fwn_mesh_to_distance_volume_by_projection_normal", "b2fwn_update_points",
     "b2fwn_calc_from_grid_by_parts_into", "b2fwn_calc_from_grid_with_distances_by_parts_into", "b2fwn_safe_memory_limit",
+    "b2fwn_build_topology", "b2fwn_build_topology_fetch",
 ]
 
 
@@ -153,6 +154,8 @@ def load_library():
                                                      PROGRESS_CB, vp]
     L.b2fwn_calc_from_grid_with_distances_by_parts_into.argtypes = [vp, i32p, f32p, C.POINTER(DistOptions), C.c_int32, C.c_int32,
                                                                     PART_BUFFER_CB, PART_CB, vp, PROGRESS_CB, vp]
+    L.b2fwn_build_topology.argtypes = [vp, vp, C.c_size_t, C.c_int32, C.c_size_t, u64p, u64p, u64p]
+    L.b2fwn_build_topology_fetch.argtypes = [vp, vp, vp, vp]
     L.b2fwn_safe_memory_limit.argtypes = [C.c_int32]
     L.b2fwn_safe_memory_limit.restype = C.c_size_t
     L.b2fwn_get_tree.argtypes = [vp, vp, vp, C.c_size_t, C.POINTER(C.c_size_t)]
@@ -524,6 +527,25 @@ class FastWindingNumber:
         tris = np.empty((r.n_tris, 3), np.int32)
         _check(_lib.b2fwn_marching_cubes_fetch(self._h, verts.ctypes.data, tris.ctypes.data))
         return verts, tris, info
+
+    # ---- half-edge tables (Mesh::fromTriMesh on the device) ----
+    def build_topology(self, tris=None, n_verts=0, on_device=False, n_tris=0):
+        """MeshTopology tables of a triangulation: tris=None -> the handle's last marching-cubes result (still on the device); a
+        host (F,3) int32 array; or a device pointer with n_tris.  Returns (half_edges (2E,4) int32 {next, prev, org, left},
+        edge_per_vertex (V,), edge_per_face (F,)); raises B2Error for non-manifold input"""
+        nh, nv, nf = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        if tris is None:
+            _check(_lib.b2fwn_build_topology(self._h, None, 0, 0, 0, C.byref(nh), C.byref(nv), C.byref(nf)))
+        elif on_device:
+            _check(_lib.b2fwn_build_topology(self._h, tris, n_tris, 1, n_verts, C.byref(nh), C.byref(nv), C.byref(nf)))
+        else:
+            t = np.ascontiguousarray(tris, np.int32).reshape(-1, 3)
+            _check(_lib.b2fwn_build_topology(self._h, t.ctypes.data, len(t), 0, n_verts, C.byref(nh), C.byref(nv), C.byref(nf)))
+        he = np.empty((nh.value, 4), np.int32)
+        epv = np.empty(nv.value, np.int32)
+        epf = np.empty(nf.value, np.int32)
+        _check(_lib.b2fwn_build_topology_fetch(self._h, he.ctypes.data, epv.ctypes.data, epf.ctypes.data))
+        return he, epv, epf
 
     # ---- marching cubes ----
     def marching_cubes(self, volume, dims, origin, voxel_size, iso, less_inside=False, on_device=False):

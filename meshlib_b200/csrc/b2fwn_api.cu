@@ -6,6 +6,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cstring>
+#include <thread>
 #include <vector>
 
 namespace b2
@@ -86,19 +87,6 @@ int runByParts( b2fwn_ctx* h, const int32_t dims[3], int overlap, int maxLayers,
 
 } // anonymous namespace
 
-#pragma GCC visibility push( default )
-extern "C"
-{
-
-const char* b2fwn_last_error( void ) { return g_lastError.c_str(); }
-
-int b2fwn_device_count( void )
-{
-    int n = 0;
-    if ( cudaGetDeviceCount( &n ) != cudaSuccess ) { (void)cudaGetLastError(); return 0; }
-    return n;
-}
-
 namespace
 {
 
@@ -109,6 +97,7 @@ void destroyCtx( b2fwn_ctx* h )
     cudaDeviceSynchronize();
     freeTree( h->tree );
     freeMc( h->mc );
+    freeTopology( h->topo );
     for ( int s = 0; s < 2; ++s )
     {
         if ( h->dScratch[s] ) cudaFree( h->dScratch[s] );
@@ -149,74 +138,69 @@ int newCtx( int dev, b2fwn_ctx** out )
     return B2FWN_OK;
 }
 
-// the traversal arrays of the primary's tree onto every replica: binary-tree broadcast over peer copies (NVLink where peer access
-// exists, staged by the driver otherwise); the parity-dump arrays (refNodes, refDipoles) stay on the primary
-int broadcastTree( b2fwn_ctx* h )
+// one device's share of b2fwn_create: context, mesh upload, tree + dipole build
+int createOne( int dev, const float* points, size_t nVerts, const int32_t* tris, size_t nFaces, b2fwn_ctx** out )
 {
-    if ( h->replicas.empty() ) return B2FWN_OK;
-    std::vector<b2fwn_ctx*> all{ h };
-    all.insert( all.end(), h->replicas.begin(), h->replicas.end() );
-    const DeviceTree& T = h->tree;
-    for ( size_t i = 1; i < all.size(); ++i )
+    b2fwn_ctx* h = nullptr;
+    if ( int e = newCtx( dev, &h ) ) return e;
+#define B2_TRY( expr ) do { cudaError_t _e = ( expr ); if ( _e != cudaSuccess ) { const int rc = cudaFail( _e, #expr ); destroyCtx( h ); return rc; } } while ( 0 )
+    h->tree.numVerts = nVerts; h->tree.numFaces = nFaces;
+    if ( nVerts )
     {
-        b2fwn_ctx* r = all[i];
-        DeviceTree& t = r->tree;
-        B2_CUDA( cudaSetDevice( r->device ) );
-        if ( t.numVerts != T.numVerts || t.numFaces != T.numFaces || t.numNodes != T.numNodes || t.numLeaves != T.numLeaves )
-        {
-            cudaFree( t.points ); cudaFree( t.tris ); cudaFree( t.nodes ); cudaFree( t.leafTris ); cudaFree( t.leafFilt );
-            t.points = nullptr; t.tris = nullptr; t.nodes = nullptr; t.leafTris = nullptr; t.leafFilt = nullptr;
-            if ( T.numVerts ) B2_CUDA( cudaMalloc( &t.points, T.numVerts * 3 * sizeof( float ) ) );
-            if ( T.numFaces ) B2_CUDA( cudaMalloc( &t.tris, T.numFaces * 3 * sizeof( int32_t ) ) );
-            if ( T.numNodes ) B2_CUDA( cudaMalloc( &t.nodes, T.numNodes * sizeof( TravNode ) ) );
-            if ( T.numLeaves ) B2_CUDA( cudaMalloc( &t.leafTris, T.numLeaves * sizeof( LeafTri ) ) );
-            if ( T.numLeaves ) B2_CUDA( cudaMalloc( &t.leafFilt, T.numLeaves * sizeof( LeafFilt ) ) );
-        }
-        // pseudonormal tables depend on the coordinates: rebuilt on next use
-        cudaFree( t.faceNormals ); cudaFree( t.vertNormals ); cudaFree( t.faceAdj );
-        t.faceNormals = t.vertNormals = nullptr; t.faceAdj = nullptr;
-        t.numVerts = T.numVerts; t.numFaces = T.numFaces; t.numNodes = T.numNodes; t.numLeaves = T.numLeaves; t.depth = T.depth;
-        memcpy( t.bbox, T.bbox, sizeof( t.bbox ) );
-        for ( b2fwn_ctx* o : all )
-            if ( o != r )
-            {
-                int can = 0;
-                if ( cudaDeviceCanAccessPeer( &can, r->device, o->device ) == cudaSuccess && can )
-                {
-                    const cudaError_t e = cudaDeviceEnablePeerAccess( o->device, 0 );
-                    if ( e != cudaSuccess ) (void)cudaGetLastError(); // already enabled, or not available: the copies still work
-                }
-            }
-        r->stats.num_nodes = T.numNodes; r->stats.num_leaves = T.numLeaves;
+        B2_TRY( cudaMalloc( &h->tree.points, nVerts * 3 * sizeof( float ) ) );
+        B2_TRY( cudaMemcpyAsync( h->tree.points, points, nVerts * 3 * sizeof( float ), cudaMemcpyHostToDevice, h->stream ) );
     }
-    B2_CUDA( cudaSetDevice( h->device ) );
-    B2_CUDA( cudaEventRecord( h->evA, h->stream ) );
-    for ( size_t have = 1; have < all.size(); have *= 2 )
-        for ( size_t i = 0; i < have && i + have < all.size(); ++i )
-        {
-            b2fwn_ctx *src = all[i], *dst = all[i + have];
-            const DeviceTree &S = src->tree, &D = dst->tree;
-            B2_CUDA( cudaSetDevice( dst->device ) );
-            B2_CUDA( cudaStreamWaitEvent( dst->stream, src->evA, 0 ) );
-            auto copy = [&]( void* d, const void* s, size_t bytes ) -> cudaError_t
-            { return bytes ? cudaMemcpyPeerAsync( d, dst->device, s, src->device, bytes, dst->stream ) : cudaSuccess; };
-            B2_CUDA( copy( D.points, S.points, T.numVerts * 3 * sizeof( float ) ) );
-            B2_CUDA( copy( D.tris, S.tris, T.numFaces * 3 * sizeof( int32_t ) ) );
-            B2_CUDA( copy( D.nodes, S.nodes, T.numNodes * sizeof( TravNode ) ) );
-            B2_CUDA( copy( D.leafTris, S.leafTris, T.numLeaves * sizeof( LeafTri ) ) );
-            B2_CUDA( copy( D.leafFilt, S.leafFilt, T.numLeaves * sizeof( LeafFilt ) ) );
-            B2_CUDA( cudaEventRecord( dst->evA, dst->stream ) );
-        }
-    for ( b2fwn_ctx* r : h->replicas )
+    if ( nFaces )
     {
-        B2_CUDA( cudaSetDevice( r->device ) );
-        B2_CUDA( cudaStreamSynchronize( r->stream ) );
+        B2_TRY( cudaMalloc( &h->tree.tris, nFaces * 3 * sizeof( int32_t ) ) );
+        B2_TRY( cudaMemcpyAsync( h->tree.tris, tris, nFaces * 3 * sizeof( int32_t ), cudaMemcpyHostToDevice, h->stream ) );
     }
-    B2_CUDA( cudaSetDevice( h->device ) );
+#undef B2_TRY
+    cudaEventRecord( h->evA, h->stream );
+    if ( int e = buildTree( h->tree, h->stream, &h->stats.kernel_launches ) ) { destroyCtx( h ); return e; }
+    cudaEventRecord( h->evB, h->stream );
+    cudaEventSynchronize( h->evB );
+    float ms = 0;
+    cudaEventElapsedTime( &ms, h->evA, h->evB );
+    h->stats.tree_build_ms = ms;
+    h->stats.num_nodes = h->tree.numNodes;
+    h->stats.num_leaves = h->tree.numLeaves;
+    *out = h;
+    return B2FWN_OK;
+}
+
+// runs fn( ctx ) for the primary on the calling thread and for every replica on a thread of its own; first error wins
+template <typename Fn>
+int onAllDevices( b2fwn_ctx* h, Fn fn )
+{
+    std::vector<int> rc( h->replicas.size(), B2FWN_OK );
+    std::vector<std::string> err( h->replicas.size() );
+    std::vector<std::thread> th;
+    for ( size_t i = 0; i < h->replicas.size(); ++i )
+        th.emplace_back( [&, i] { rc[i] = fn( h->replicas[i] ); if ( rc[i] ) err[i] = b2fwn_last_error(); } );
+    const int rc0 = fn( h );
+    for ( auto& t : th ) t.join();
+    cudaSetDevice( h->device );
+    if ( rc0 ) return rc0;
+    for ( size_t i = 0; i < rc.size(); ++i )
+        if ( rc[i] ) { setError( err[i] ); return rc[i]; }
     return B2FWN_OK;
 }
 
 } // namespace
+
+#pragma GCC visibility push( default )
+extern "C"
+{
+
+const char* b2fwn_last_error( void ) { return g_lastError.c_str(); }
+
+int b2fwn_device_count( void )
+{
+    int n = 0;
+    if ( cudaGetDeviceCount( &n ) != cudaSuccess ) { (void)cudaGetLastError(); return 0; }
+    return n;
+}
 
 int b2fwn_create( const float* points, size_t nVerts, const int32_t* tris, size_t nFaces, const b2fwn_config* cfg,
                   b2fwn_handle* out )
@@ -232,39 +216,27 @@ int b2fwn_create( const float* points, size_t nVerts, const int32_t* tris, size_
             for ( size_t j = 0; j < i; ++j )
                 if ( devices[i] == devices[j] ) { setError( "device listed twice" ); return B2FWN_ERR_INVALID; }
     }
-    b2fwn_ctx* h = nullptr;
-    if ( int e = newCtx( devices[0], &h ) ) return e;
-    auto fail = [&]( int e ) { b2fwn_destroy( h ); return e; };
-#define B2_TRY( expr ) do { cudaError_t _e = ( expr ); if ( _e != cudaSuccess ) return fail( cudaFail( _e, #expr ) ); } while ( 0 )
-    h->tree.numVerts = nVerts; h->tree.numFaces = nFaces;
-    if ( nVerts )
-    {
-        B2_TRY( cudaMalloc( &h->tree.points, nVerts * 3 * sizeof( float ) ) );
-        B2_TRY( cudaMemcpyAsync( h->tree.points, points, nVerts * 3 * sizeof( float ), cudaMemcpyHostToDevice, h->stream ) );
-    }
-    if ( nFaces )
-    {
-        B2_TRY( cudaMalloc( &h->tree.tris, nFaces * 3 * sizeof( int32_t ) ) );
-        B2_TRY( cudaMemcpyAsync( h->tree.tris, tris, nFaces * 3 * sizeof( int32_t ), cudaMemcpyHostToDevice, h->stream ) );
-    }
-#undef B2_TRY
-    // the other devices' contexts come up on the host while the primary builds
-    cudaEventRecord( h->evA, h->stream );
-    if ( int e = buildTree( h->tree, h->stream, &h->stats.kernel_launches ) ) return fail( e );
-    cudaEventRecord( h->evB, h->stream );
-    cudaEventSynchronize( h->evB );
-    float ms = 0;
-    cudaEventElapsedTime( &ms, h->evA, h->evB );
-    h->stats.tree_build_ms = ms;
-    h->stats.num_nodes = h->tree.numNodes;
-    h->stats.num_leaves = h->tree.numLeaves;
+    // Every device builds its own copy of the tree, all at once (one host thread per device): the build is deterministic, so the
+    // copies are identical, and the wall time is that of one build.  (r02: building once and copying the arrays to the other
+    // devices over NVLink needs peer access between the devices, and with peer access enabled every later cudaMalloc / cudaFree of
+    // the process is mapped into the peers as well -- create + destroy of a 2-device handle cost 450 ms more than of one device.)
+    std::vector<b2fwn_ctx*> made( devices.size(), nullptr );
+    std::vector<int> rc( devices.size(), B2FWN_OK );
+    std::vector<std::string> err( devices.size() );
+    std::vector<std::thread> th;
     for ( size_t i = 1; i < devices.size(); ++i )
-    {
-        b2fwn_ctx* r = nullptr;
-        if ( int e = newCtx( devices[i], &r ) ) return fail( e );
-        h->replicas.push_back( r );
-    }
-    if ( int e = broadcastTree( h ) ) return fail( e );
+        th.emplace_back( [&, i] { rc[i] = createOne( devices[i], points, nVerts, tris, nFaces, &made[i] ); if ( rc[i] ) err[i] = b2fwn_last_error(); } );
+    rc[0] = createOne( devices[0], points, nVerts, tris, nFaces, &made[0] );
+    for ( auto& t : th ) t.join();
+    for ( size_t i = 0; i < devices.size(); ++i )
+        if ( rc[i] )
+        {
+            if ( i ) setError( err[i] );
+            for ( b2fwn_ctx* c : made ) destroyCtx( c );
+            return rc[i];
+        }
+    b2fwn_ctx* h = made[0];
+    h->replicas.assign( made.begin() + 1, made.end() );
     cudaSetDevice( h->device );
     *out = h;
     return B2FWN_OK;
@@ -281,16 +253,19 @@ int b2fwn_update_points( b2fwn_handle h, const float* points, size_t nVerts )
 {
     if ( !h || ( nVerts && !points ) ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
     if ( nVerts != h->tree.numVerts ) { setError( "the number of vertices must not change (same triangulation, new coordinates)" ); return B2FWN_ERR_INVALID; }
-    B2_CUDA( cudaSetDevice( h->device ) );
-    B2_CUDA( cudaDeviceSynchronize() ); // nothing of an earlier call still reads the old coordinates
-    if ( nVerts ) B2_CUDA( cudaMemcpyAsync( h->tree.points, points, nVerts * 3 * sizeof( float ), cudaMemcpyHostToDevice, h->stream ) );
-    cudaEventRecord( h->evA, h->stream );
-    if ( int e = refitTree( h->tree, h->stream, &h->stats.kernel_launches ) ) return e;
-    cudaEventRecord( h->evB, h->stream );
-    B2_CUDA( cudaEventSynchronize( h->evB ) );
-    float ms = 0;
-    if ( cudaEventElapsedTime( &ms, h->evA, h->evB ) == cudaSuccess ) h->stats.last_kernel_ms = ms;
-    return broadcastTree( h );
+    return onAllDevices( h, [&]( b2fwn_ctx* d ) -> int
+    {
+        B2_CUDA( cudaSetDevice( d->device ) );
+        B2_CUDA( cudaDeviceSynchronize() ); // nothing of an earlier call still reads the old coordinates
+        if ( nVerts ) B2_CUDA( cudaMemcpyAsync( d->tree.points, points, nVerts * 3 * sizeof( float ), cudaMemcpyHostToDevice, d->stream ) );
+        cudaEventRecord( d->evA, d->stream );
+        if ( int e = refitTree( d->tree, d->stream, &d->stats.kernel_launches ) ) return e;
+        cudaEventRecord( d->evB, d->stream );
+        B2_CUDA( cudaEventSynchronize( d->evB ) );
+        float ms = 0;
+        if ( cudaEventElapsedTime( &ms, d->evA, d->evB ) == cudaSuccess ) d->stats.last_kernel_ms = ms;
+        return B2FWN_OK;
+    } );
 }
 
 size_t b2fwn_safe_memory_limit( int32_t device ) { return safeMemoryLimit( device ); }
@@ -962,7 +937,7 @@ int b2fwn_mc_offset_mesh( b2fwn_handle h, const b2fwn_offset_params* p, b2fwn_of
     mp.iso = p->offset;
     mp.less_inside = 1;
     cudaEventRecord( h->evA, h->stream );
-    rc = marchingCubesDevice( dVol, dims, mp, h->mc, h->stream, &h->stats.kernel_launches );
+    rc = marchingCubesDevice( dVol, dims, mp, h->mc, h->stream, &h->stats.kernel_launches, h->tree.pool );
     cudaEventRecord( h->evB, h->stream );
     cudaEventSynchronize( h->evB );
     cudaEventElapsedTime( &ms, h->evA, h->evB );
@@ -1048,7 +1023,7 @@ int b2fwn_marching_cubes( b2fwn_handle h, const float* volume, int32_t onDevice,
         dVol = dTmp;
     }
     KernelTimer tm( h );
-    const int rc = marchingCubesDevice( dVol, dims, *p, h->mc, h->stream, &h->stats.kernel_launches );
+    const int rc = marchingCubesDevice( dVol, dims, *p, h->mc, h->stream, &h->stats.kernel_launches, h->tree.pool );
     tm.stop();
     cudaStreamSynchronize( h->stream );
     if ( dTmp ) cudaFree( dTmp );
@@ -1065,6 +1040,50 @@ int b2fwn_marching_cubes_fetch( b2fwn_handle h, float* outVerts, int32_t* outTri
         B2_CUDA( cudaMemcpy( outVerts, h->mc.dVerts, h->mc.nVerts * 3 * sizeof( float ), cudaMemcpyDeviceToHost ) );
     if ( h->mc.nTris && outTris )
         B2_CUDA( cudaMemcpy( outTris, h->mc.dTris, h->mc.nTris * 3 * sizeof( int32_t ), cudaMemcpyDeviceToHost ) );
+    return B2FWN_OK;
+}
+
+// ---- half-edge tables of a triangle mesh ---------------------------------------------------------------------------------
+
+int b2fwn_build_topology( b2fwn_handle h, const int32_t* tris, size_t nTris, int32_t onDevice, size_t nVerts, uint64_t* nHalfEdges,
+                          uint64_t* nVertsOut, uint64_t* nFacesOut )
+{
+    if ( !h || !nHalfEdges ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    *nHalfEdges = 0;
+    const int32_t* dTris = tris;
+    int32_t* dTmp = nullptr;
+    if ( !tris )
+    {
+        dTris = h->mc.dTris; nTris = h->mc.nTris; nVerts = h->mc.nVerts; // the marching-cubes result of this handle
+    }
+    else if ( !onDevice && nTris )
+    {
+        B2_CUDA( cudaMalloc( &dTmp, nTris * 3 * sizeof( int32_t ) ) );
+        const cudaError_t e = cudaMemcpyAsync( dTmp, tris, nTris * 3 * sizeof( int32_t ), cudaMemcpyHostToDevice, h->stream );
+        if ( e != cudaSuccess ) { cudaFree( dTmp ); return cudaFail( e, "H2D triangles" ); }
+        dTris = dTmp;
+    }
+    KernelTimer tm( h );
+    const int rc = buildTopologyDevice( dTris, nTris, nVerts, h->topo, h->stream, &h->stats.kernel_launches );
+    tm.stop();
+    cudaStreamSynchronize( h->stream );
+    if ( dTmp ) cudaFree( dTmp );
+    if ( rc ) return rc;
+    *nHalfEdges = h->topo.nHalfEdges;
+    if ( nVertsOut ) *nVertsOut = h->topo.nVerts;
+    if ( nFacesOut ) *nFacesOut = h->topo.nFaces;
+    return B2FWN_OK;
+}
+
+int b2fwn_build_topology_fetch( b2fwn_handle h, b2fwn_half_edge* outEdges, int32_t* outEdgePerVertex, int32_t* outEdgePerFace )
+{
+    if ( !h ) { setError( "null handle" ); return B2FWN_ERR_INVALID; }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    const TopoResult& t = h->topo;
+    if ( t.nHalfEdges && outEdges ) B2_CUDA( cudaMemcpy( outEdges, t.dEdges, t.nHalfEdges * sizeof( b2fwn_half_edge ), cudaMemcpyDeviceToHost ) );
+    if ( t.nVerts && t.dEdgePerVertex && outEdgePerVertex ) B2_CUDA( cudaMemcpy( outEdgePerVertex, t.dEdgePerVertex, t.nVerts * 4, cudaMemcpyDeviceToHost ) );
+    if ( t.nFaces && t.dEdgePerFace && outEdgePerFace ) B2_CUDA( cudaMemcpy( outEdgePerFace, t.dEdgePerFace, t.nFaces * 4, cudaMemcpyDeviceToHost ) );
     return B2FWN_OK;
 }
 

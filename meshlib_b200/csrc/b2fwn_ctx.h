@@ -15,6 +15,7 @@ struct b2fwn_ctx
     b2::DeviceTree tree;
     b2fwn_stats stats{};
     b2::McResult mc;
+    b2::TopoResult topo;
     // scratch for the host-pointer entry points
     float* dScratch[2] = { nullptr, nullptr };
     size_t scratchFloats[2] = { 0, 0 };

@@ -160,7 +160,18 @@ struct McResult
     uint64_t nVerts = 0, nTris = 0;
 };
 int marchingCubesDevice( const float* dVolume, const int32_t dims[3], const b2fwn_mc_params& p, McResult& out,
-                         cudaStream_t stream, uint64_t* launches );
+                         cudaStream_t stream, uint64_t* launches, cudaMemPool_t pool = nullptr );
 void freeMc( McResult& r );
+
+// half-edge tables of a triangle mesh (b2fwn_topology.cu) ----------------------------------------------------------------
+struct TopoResult
+{
+    b2fwn_half_edge* dEdges = nullptr; // nHalfEdges records {next, prev, org, left}
+    int32_t* dEdgePerVertex = nullptr; // nVerts, -1 = vertex without faces
+    int32_t* dEdgePerFace = nullptr;   // nFaces
+    size_t nHalfEdges = 0, nVerts = 0, nFaces = 0;
+};
+int buildTopologyDevice( const int32_t* dTris, size_t nFaces, size_t nVerts, TopoResult& out, cudaStream_t stream, uint64_t* launches );
+void freeTopology( TopoResult& r );
 
 } // namespace b2

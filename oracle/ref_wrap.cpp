@@ -23,6 +23,11 @@
 #include "MRMesh/MRTriMesh.h"
 #include "MRVoxels/MRMarchingCubes.h"
 #include "MRVoxels/MRVoxelsVolume.h"
+#include "MRMesh/MRMeshBuilder.h"
+#include "MRMesh/MRMeshTopology.h"
+#include "MRMesh/MRRegionBoundary.h"
+#include "MRMesh/MRIOParsing.h"
+#include <sstream>
 #include <tbb/blocked_range.h>
 #include <tbb/parallel_for.h>
 #include <cfloat>
@@ -30,6 +35,7 @@
 #include <cstring>
 #include <limits>
 #include <thread>
+#include <chrono>
 
 // MRTimer.cpp needs the (absent) spdlog submodule; the path only uses the RAII start/finish pair.
 namespace MR
@@ -38,6 +44,20 @@ void Timer::restart( std::string ) {}
 void Timer::start( std::string ) {}
 void Timer::start( const char* ) {}
 void Timer::finish() {}
+}
+
+// MRIOParsing.cpp pulls in the text parsers (fast_float, boost); MeshTopology::read only needs this one function of it
+// (source/MRMesh/MRIOParsing.cpp:103-110, restated)
+namespace MR
+{
+std::streamoff getStreamSize( std::istream& in )
+{
+    const auto posStart = in.tellg();
+    in.seekg( 0, std::ios::end );
+    const auto posEnd = in.tellg();
+    in.seekg( posStart );
+    return posEnd - posStart;
+}
 }
 
 using namespace MR;
@@ -369,6 +389,53 @@ void mrref_marching_cubes_fetch( float* outVerts, int* outTris )
         for ( int k = 0; k < 3; ++k )
             outTris[3 * t + k] = (int)g_lastMc.tris.vec_[t][k];
     g_lastMc = {};
+}
+
+// ---- half-edge tables ---------------------------------------------------------------------------------------
+// Loads tables built elsewhere through the reference's own deserialiser: the stream layout of MeshTopology::write
+// (MRMeshTopology.cpp:2461-2477) into MeshTopology::read (:2479-2534), which runs computeValidsFromEdges and checkValidity.
+// Returns 0 and the triangulation the reference reads back from them (getTriangulation), the number of undirected edges and of
+// boundary loops; 1 when the reference rejects the tables.
+int mrref_topology_from_tables( const void* halfEdges16B, uint32_t nHalfEdges, const int* edgePerVertex, uint32_t nVerts,
+    const int* edgePerFace, uint32_t nFaces, int* outTris, int* outUndirectedEdges, int* outBoundaryLoops, int* outValidVerts )
+{
+    std::stringstream ss( std::ios::in | std::ios::out | std::ios::binary );
+    ss.write( (const char*)&nHalfEdges, 4 );
+    ss.write( (const char*)halfEdges16B, size_t( nHalfEdges ) * 16 );
+    ss.write( (const char*)&nVerts, 4 );
+    ss.write( (const char*)edgePerVertex, size_t( nVerts ) * 4 );
+    ss.write( (const char*)&nFaces, 4 );
+    ss.write( (const char*)edgePerFace, size_t( nFaces ) * 4 );
+    MeshTopology topo;
+    if ( !topo.read( ss ) )
+        return 1;
+    const auto t = topo.getTriangulation();
+    for ( size_t f = 0; f < nFaces && f < t.size(); ++f )
+        for ( int k = 0; k < 3; ++k )
+            outTris[3 * f + k] = (int)t.vec_[f][k];
+    *outUndirectedEdges = (int)topo.computeNotLoneUndirectedEdges();
+    *outBoundaryLoops = (int)findRightBoundary( topo ).size();
+    *outValidVerts = topo.numValidVerts();
+    return 0;
+}
+
+// the reference's own builder on the same triangles (Mesh::fromTriMesh's core, MRMeshBuilder.cpp:518-540): the counts the tables
+// above must agree with, and the wall time of the CPU step they replace
+int mrref_builder_stats( const int* tris, size_t nFaces, int* outValidFaces, int* outUndirectedEdges, int* outBoundaryLoops, int* outValidVerts,
+    double* outSeconds )
+{
+    Triangulation t;
+    t.vec_.resize( nFaces );
+    for ( size_t f = 0; f < nFaces; ++f )
+        t.vec_[f] = ThreeVertIds{ VertId( tris[3 * f] ), VertId( tris[3 * f + 1] ), VertId( tris[3 * f + 2] ) };
+    const auto t0 = std::chrono::steady_clock::now();
+    const MeshTopology topo = MeshBuilder::fromTriangles( t );
+    *outSeconds = std::chrono::duration<double>( std::chrono::steady_clock::now() - t0 ).count();
+    *outValidFaces = topo.numValidFaces();
+    *outUndirectedEdges = (int)topo.computeNotLoneUndirectedEdges();
+    *outBoundaryLoops = (int)findRightBoundary( topo ).size();
+    *outValidVerts = topo.numValidVerts();
+    return 0;
 }
 
 } // extern "C"

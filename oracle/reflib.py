@@ -62,6 +62,10 @@ def lib():
         L.mrref_marching_cubes.argtypes = [_f32p, _i32p, _f32p, _f32p, C.c_float, C.c_int, C.POINTER(C.c_size_t),
                                            C.POINTER(C.c_size_t)]
         L.mrref_marching_cubes_fetch.argtypes = [_f32p, _i32p]
+        ip = C.POINTER(C.c_int)
+        L.mrref_topology_from_tables.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p,
+                                                 ip, ip, ip]
+        L.mrref_builder_stats.argtypes = [C.c_void_p, C.c_size_t, ip, ip, ip, ip, C.POINTER(C.c_double)]
         _lib = L
     return _lib
 
@@ -209,6 +213,29 @@ def marching_cubes(volume, dims, voxel_size, origin, iso, less_inside=False):
     tris = np.empty((nt.value, 3), np.int32)
     lib().mrref_marching_cubes_fetch(verts, tris)
     return verts, tris
+
+
+def topology_from_tables(half_edges, edge_per_vertex, edge_per_face):
+    """half-edge tables {next, prev, org, left} through the reference's MeshTopology::read (which validates them with
+    checkValidity); returns None when the reference rejects them, else (tris read back, undirected edges, boundary loops, valid verts)"""
+    he = np.ascontiguousarray(half_edges, np.int32).reshape(-1, 4)
+    epv = np.ascontiguousarray(edge_per_vertex, np.int32)
+    epf = np.ascontiguousarray(edge_per_face, np.int32)
+    tris = np.full((len(epf), 3), -1, np.int32)
+    ue, bl, vv = C.c_int(), C.c_int(), C.c_int()
+    rc = lib().mrref_topology_from_tables(he.ctypes.data, len(he), epv.ctypes.data, len(epv), epf.ctypes.data, len(epf), tris.ctypes.data,
+                                          C.byref(ue), C.byref(bl), C.byref(vv))
+    if rc != 0:
+        return None
+    return tris, ue.value, bl.value, vv.value
+
+
+def builder_stats(tris):
+    """MeshBuilder::fromTriangles of the reference on the same triangles: (valid faces, undirected edges, boundary loops, valid verts, s)"""
+    t = np.ascontiguousarray(tris, np.int32).reshape(-1, 3)
+    vf, ue, bl, vv, sec = C.c_int(), C.c_int(), C.c_int(), C.c_int(), C.c_double()
+    lib().mrref_builder_stats(t.ctypes.data, len(t), C.byref(vf), C.byref(ue), C.byref(bl), C.byref(vv), C.byref(sec))
+    return vf.value, ue.value, bl.value, vv.value, sec.value
 
 
 def hardware_threads():

@@ -197,3 +197,79 @@ def test_several_devices_of_one_process(small_chunks):
     assert many.stats().kernel_launches > one.stats().kernel_launches / 2
     one.close()
     many.close()
+
+
+# ---- half-edge tables on the device (first slice) -----------------------------------------------------------
+def _check_tables(tris, n_verts, he, epv, epf):
+    """structure checks that need no reference, then the reference's own MeshTopology::read + checkValidity where it is present"""
+    tris = np.asarray(tris, np.int32)
+    assert he.shape[0] % 2 == 0 and epf.shape == (len(tris),) and epv.shape == (n_verts,)
+    nxt, prv, org, left = he[:, 0], he[:, 1], he[:, 2], he[:, 3]
+    e = np.arange(len(he))
+    assert (nxt >= 0).all() and (prv >= 0).all() and np.array_equal(prv[nxt], e) and np.array_equal(nxt[prv], e)
+    assert np.array_equal(org[nxt], org)  # next stays in the ring of the origin
+    # the three half-edges of every face: e0, prev(sym(e0)), prev(sym(e1))
+    e0 = epf
+    e1 = prv[e0 ^ 1]
+    e2 = prv[e1 ^ 1]
+    assert np.array_equal(prv[e2 ^ 1], e0)
+    f = np.arange(len(tris))
+    assert np.array_equal(left[e0], f) and np.array_equal(left[e1], f) and np.array_equal(left[e2], f)
+    assert np.array_equal(np.stack([org[e0], org[e1], org[e2]], 1), tris)
+    used = np.zeros(n_verts, bool)
+    used[tris.ravel()] = True
+    assert np.array_equal(epv >= 0, used) and np.array_equal(org[epv[used]], np.flatnonzero(used))
+    from oracle import reflib
+    if reflib.available():
+        got = reflib.topology_from_tables(he, epv, epf)
+        assert got is not None, "the reference's MeshTopology::read rejected the tables"
+        rtris, n_ue, n_loops, n_vv = got
+        assert np.array_equal(rtris, tris) and n_ue == len(he) // 2 and n_vv == int(used.sum())
+        vf, ue, bl, vv, _s = reflib.builder_stats(tris)
+        assert (vf, ue, bl, vv) == (len(tris), n_ue, n_loops, n_vv)  # the reference's own builder agrees on every count
+        return n_loops
+    return None
+
+
+def test_half_edge_tables_of_closed_and_open_meshes(torus):
+    pts, tris, fwn = torus
+    he, epv, epf = fwn.build_topology(tris, len(pts))
+    assert len(he) == 3 * len(tris)  # closed manifold: E = 3F / 2
+    loops = _check_tables(tris, len(pts), he, epv, epf)
+    assert loops in (None, 0)
+    # an open mesh: a sphere with two runs of faces removed has two boundary loops; unused vertices stay invalid
+    p2, t2 = meshgen.make_uv_sphere(1, 48, 24)
+    t2 = np.delete(t2, np.r_[300:340, 1500:1530], axis=0)
+    he, epv, epf = fwn.build_topology(t2, len(p2) + 5)
+    loops = _check_tables(t2, len(p2) + 5, he, epv, epf)
+    assert loops in (None, 2)
+    assert (epv[len(p2):] == -1).all()
+    # holes that touch in a vertex leave it with two fans and two gaps: which gap follows which fan is geometry, not topology --
+    # refused like every other vertex that is not a disc or a half-disc
+    with pytest.raises(mb.B2Error):
+        fwn.build_topology(meshgen.make_uv_sphere(1, 48, 24)[1][np.arange(2304) % 11 != 3], len(p2))
+    # non-manifold and degenerate input is refused, not mis-built: the caller keeps the CPU builder for it
+    bad = np.concatenate([tris, tris[:1]])  # the same face twice: an edge with two faces on one side
+    with pytest.raises(mb.B2Error) as e:
+        fwn.build_topology(bad, len(pts))
+    assert "manifold" in str(e.value)
+    flipped = tris.copy()
+    flipped[7] = flipped[7][::-1]  # inconsistent orientation
+    with pytest.raises(mb.B2Error):
+        fwn.build_topology(flipped, len(pts))
+    with pytest.raises(mb.B2Error):
+        fwn.build_topology(np.array([[0, 0, 1]], np.int32), 3)
+    two_fans = np.array([[0, 1, 2], [0, 2, 3], [0, 3, 1], [1, 3, 2], [0, 5, 4], [0, 6, 5], [0, 4, 6], [4, 5, 6]], np.int32)  # two tetrahedra sharing vertex 0
+    with pytest.raises(mb.B2Error) as e:
+        fwn.build_topology(two_fans, 7)
+    assert "fan" in str(e.value)
+    assert fwn.build_topology(np.zeros((0, 3), np.int32), 4)[0].shape == (0, 4)
+
+
+def test_offset_mesh_to_half_edges_without_leaving_the_device(torus):
+    """mcOffsetMesh's last step (Mesh::fromTriMesh, MROffset.cpp:222-225): marching cubes result -> MeshTopology tables, both in HBM"""
+    _p, _t, fwn = torus
+    v, t, info = fwn.mc_offset_mesh(0.15, 0.11)
+    he, epv, epf = fwn.build_topology()
+    assert len(epf) == len(t) and len(epv) == len(v)
+    _check_tables(t, len(v), he, epv, epf)
