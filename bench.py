@@ -292,6 +292,132 @@ def run_reference_arm(args, wl):
 
 
 # ---------------------------------------------------------------------------------------------------------------------
+# query workloads: winding numbers of point vectors (C2) and of face centres (C4); the metric's second half, single GPU
+# ---------------------------------------------------------------------------------------------------------------------
+QUERY_WORKLOADS = {
+    # C2: calcFromVector, 10 M random points in [-1.5, 1.5]^3 against the 1 M-triangle UV sphere
+    "c2": dict(kind="vector", mesh=("uv_sphere", 1000, 500), n=10_000_000),
+    # C4: calcSelfIntersections of two interpenetrating tori, 5.12 M triangles (one query per face)
+    "c4": dict(kind="faces", mesh=("two_tori", 1600, 800)),
+}
+
+
+def run_queries(args, name):
+    import torch
+    import meshlib_b200 as mb
+    w = QUERY_WORKLOADS[name]
+    if w["mesh"][0] == "uv_sphere":
+        pts, tris = meshgen.make_uv_sphere(1, w["mesh"][1], w["mesh"][2])
+    else:
+        pts, tris = meshgen.two_tori(2.0, 0.7, w["mesh"][1], w["mesh"][2])
+    torch.cuda.set_device(0)
+    fwn = mb.FastWindingNumber(pts, tris)
+    vector = w["kind"] == "vector"
+    if vector:
+        q = meshgen.query_points(w["n"])
+        n = len(q)
+        dq = torch.from_numpy(q).cuda()
+        dout = torch.empty(n, dtype=torch.float32, device="cuda")
+        step = lambda: fwn.calc_from_vector_device(dq.data_ptr(), n, dout.data_ptr())
+    else:
+        n = len(tris)
+        dbits = torch.zeros((n + 63) // 64, dtype=torch.int64, device="cuda")
+        dout = torch.empty(n, dtype=torch.float32, device="cuda")
+        step = lambda: fwn.calc_self_intersections_device(dbits.data_ptr(), dout.data_ptr())
+    for _ in range(args.warmup):
+        step()
+    sampler = ClockSampler(0)
+    sampler.start()
+    l0 = fwn.stats().kernel_launches
+    ms = 0.0
+    for _ in range(args.steps):
+        step()
+        ms += fwn.stats().last_kernel_ms
+    clocks = sampler.stop()
+    launches = fwn.stats().kernel_launches - l0
+    ms /= args.steps
+    got_w = dout.cpu().numpy()
+    got_bits = None if vector else dbits.cpu().numpy().view(np.uint64)
+    st = fwn.stats()
+    fwn.close()
+    # e2e: host mesh + host queries -> create -> call with host buffers (pageable) -> destroy
+    e_steps = max(1, min(args.steps, 3))
+    t0 = time.perf_counter()
+    for _ in range(e_steps):
+        f2 = mb.FastWindingNumber(pts, tris)
+        res = f2.calc_from_vector(q) if vector else f2.calc_self_intersections()
+        f2.close()
+    e_ms = 1e3 * (time.perf_counter() - t0) / e_steps
+    fp32_peak = mb.measure_fp32_peak(0)
+    desc = (f"{name}: calcFromVector, {n} random points vs {len(tris)} triangles (UV sphere)" if vector else
+            f"{name}: calcSelfIntersections, {len(tris)} triangles (two interpenetrating tori), one query per face")
+    out = {"metric": "winding_number_queries_per_sec", "value": n / (ms * 1e-3), "unit": "queries/s", "n_gpus": 1, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+           "data": "synthetic",
+           "config": {"workload": desc, "timing": "CUDA events on the launching stream (incl. the Morton sort of the queries)",
+                      "l2": "tree+triangles %.0f MB, queries %.0f MB per step" % ((st.num_nodes * 64 + st.num_leaves * 48) / 1e6, (12 if vector else 0) * n / 1e6 + 4 * n / 1e6)},
+           "clocks": clocks, "gpu_launches": int(launches), "tree_build_ms": st.tree_build_ms,
+           "e2e": {"value": n / (e_ms * 1e-3), "unit": "queries/s", "ms_per_step": e_ms, "steps": e_steps,
+                   "h2d_bytes_per_step": int(pts.nbytes + tris.nbytes + (q.nbytes if vector else 0)),
+                   "d2h_bytes_per_step": int(4 * n if vector else 8 * ((n + 63) // 64)),
+                   "includes": "b2fwn_create (H2D + device tree build) + the host-buffer call (pageable numpy) + b2fwn_destroy; host wall clock"},
+           "roofline": {"bound": "fp32", "achieved": None, "peak": fp32_peak, "unit": "TFLOP/s", "frac": None, "traffic": None,
+                        "peak_source": "FFMA micro-benchmark run on this GPU just now (b2fwn_measure_fp32_peak)"}}
+    if not args.no_cpu:
+        from oracle import checker, portlib, reflib
+        orc = checker.best_oracle(pts, tris)
+        # bounded sample of the same queries on all host threads
+        if vector:
+            k = 200_000
+            orc.calc_from_vector(q[:k])
+            t0 = time.perf_counter()
+            want = orc.calc_from_vector(q[:k])
+            t1 = time.perf_counter() - t0
+            k2 = int(min(n, max(k, k * args.cpu_budget / max(t1, 1e-6))))
+            idx = np.arange(0, n, max(1, n // k2))[:k2]
+            t0 = time.perf_counter()
+            want = orc.calc_from_vector(q[idx])
+            c_s = time.perf_counter() - t0
+            rep = checker.compare_w(got_w[idx], want, atol=2e-6)
+            out["parity"] = {"n": int(len(idx)), "max_abs_dw": rep["max_abs_diff"], "bit_exact_frac": rep["bit_exact_frac"], "ok": rep["ok"],
+                             "rule": "|w - w_ref| <= 2e-6 on the sampled queries"}
+            sample, nq = f"{len(idx)} of the {n} queries (every {max(1, n // k2)}th), {c_s:.2f} s", len(idx)
+        else:
+            t0 = time.perf_counter()
+            want = orc.calc_self_intersections()
+            c_s = time.perf_counter() - t0
+            rep = checker.compare_bits(got_bits, want, got_w, len(tris))
+            out["parity"] = {"n": int(len(tris)), "mismatch_outside_bands": rep["mismatch"], "mismatch_in_bands": rep["mismatch_in_band"],
+                             "set_bits": rep["set"], "ok": rep["ok"], "rule": "bit f equal wherever w is not within 1e-3 of 0 or 1"}
+            sample, nq = f"all {len(tris)} faces once, {c_s:.2f} s", len(tris)
+        out["cpu_baseline"] = {"value": nq / c_s, "unit": "queries/s", "cores": reflib.hardware_threads() if reflib.available() else 1,
+                               "kind": getattr(orc, "kind", "port"), "sample": sample}
+        # reference-algorithm operation counts on a sample (C restatement with counters): 8 Vf + 10 Af + 80 Lf per query
+        m = portlib.PortMesh(pts, tris)
+        m.reset_counters()
+        ks = 50_000
+        if vector:
+            m.calc_from_vector(q[:: max(1, n // ks)][:ks])
+            cnt_n = len(q[:: max(1, n // ks)][:ks])
+        else:
+            P, T = m_points(pts), tris[:: max(1, len(tris) // ks)][:ks]
+            centres = ((P[T[:, 0]] + P[T[:, 1]] + P[T[:, 2]]) * np.float32(1 / 3.0)).astype(np.float32)
+            m.calc_from_vector(centres)
+            cnt_n = len(centres)
+        c = m.counter_dict()
+        fpq = (8 * c["fwn_visits"] + 10 * c["fwn_accepts"] + 80 * c["fwn_leaves"]) / max(cnt_n, 1)
+        ach = fpq * n / (ms * 1e-3) / 1e12
+        out["roofline"].update({"achieved": ach, "frac": ach / fp32_peak, "flops_per_query": fpq,
+                                "ops_per_query": {k2_: v / cnt_n for k2_, v in c.items() if k2_.startswith("fwn")},
+                                "ops_sample": f"{cnt_n} queries, reference algorithm counters (face-centre sample without the skipped face for c4)"})
+    print(json.dumps(out))
+
+
+def m_points(pts):
+    return np.asarray(pts, np.float32)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
 # offset workloads: distance band + marching cubes (north_star subsystem 4), single GPU
 # ---------------------------------------------------------------------------------------------------------------------
 
@@ -428,10 +554,17 @@ def run_ours(args, wl):
         volume = torch.empty(total, dtype=torch.float32, device=dev)
     slab = volume[z0 * layer:z1 * layer]
 
-    def barrier():
+    host_group = dist.new_group(backend="gloo") if world > 1 else None
+
+    def barrier(host_only=False):
         torch.cuda.synchronize()
         if world > 1:
-            dist.barrier()
+            if host_only:
+                # the ranks that wait must not occupy their GPU: an NCCL barrier spins in a kernel, and rank 0 drives ALL GPUs in
+                # the e2e leg (two processes on one GPU are time-sliced: r02 measured 1322 ms instead of ~750 ms at N = 2)
+                dist.barrier(group=host_group)
+            else:
+                dist.barrier()
             torch.cuda.synchronize()
 
 
@@ -527,6 +660,7 @@ def run_ours(args, wl):
         fwn.close()
         torch.cuda.empty_cache()
         barrier()
+        barrier(host_only=True)
         if rank == 0:
             devices = list(range(world))
             e_steps = max(1, min(args.steps, 3))
@@ -562,10 +696,10 @@ def run_ours(args, wl):
                    "host_buffer": "pageable (numpy, sized and touched by the caller): pinned staging ring + copier threads inside the library",
                    "pinned_buffer": None if pinned_ms is None else {"value": total / (pinned_ms * 1e-3), "ms_per_step": pinned_ms},
                    "kernel_ms_of_the_call": st2.last_kernel_ms, "tree_build_ms": st2.tree_build_ms,
-                   "includes": f"one process, {world} GPU(s): b2fwn_create (mesh H2D + device tree/dipole build on GPU 0"
-                               + (", peer copies of the tree to the others" if world > 1 else "")
+                   "includes": f"one process, {world} GPU(s): b2fwn_create (mesh H2D + device tree/dipole build"
+                               + (", on every GPU at once" if world > 1 else "")
                                + ") + b2fwn_calc_from_grid_with_distances into the host buffer + b2fwn_destroy; host wall clock"}
-        barrier()
+        barrier(host_only=True)
 
     if rank != 0:
         if world > 1:
@@ -638,7 +772,7 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS) + sorted(OFFSET_WORKLOADS))
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS) + sorted(OFFSET_WORKLOADS) + sorted(QUERY_WORKLOADS))
     ap.add_argument("--grid", type=int, default=None, help="override the grid size (diagnostics only; not the headline)")
     ap.add_argument("--z-chunk", type=int, default=8, help="N > 1: layers per interleaved chunk (multiple of 4)")
     ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"], help="N > 1: fused peer stores, or NCCL all-gather")
@@ -648,6 +782,10 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     args = ap.parse_args()
+    if args.workload in QUERY_WORKLOADS:
+        if args.impl == "reference" or args.gpus != 1:
+            raise SystemExit("query workloads are single-GPU diagnostics of our arm")
+        return run_queries(args, args.workload)
     if args.workload in OFFSET_WORKLOADS:
         if args.impl == "reference" or args.gpus != 1:
             raise SystemExit("offset workloads are single-GPU diagnostics of our arm")

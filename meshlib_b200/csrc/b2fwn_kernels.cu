@@ -10,8 +10,10 @@
 // one-thread-per-query kernels for point vectors and face centroids.
 #include "b2fwn_internal.h"
 #include "b2fwn_math.cuh"
+#include <cub/device/device_radix_sort.cuh>
 #include <cfloat>
 #include <climits>
+#include <cstdlib>
 
 namespace b2
 {
@@ -46,29 +48,59 @@ __device__ __forceinline__ float fwnSingle( const TravNode* __restrict__ nodes, 
     return FM( INV_4PI, res );
 }
 
+// order[t] = index of the query thread t handles (Morton order of the points, so that the lanes of a warp walk nearly the same
+// nodes); nullptr = input order
 __global__ void __launch_bounds__( 128 ) kFwnVector( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris, int numNodes,
-    const float* __restrict__ pts, size_t n, float betaSq, int skipFace, float* __restrict__ out )
+    const float* __restrict__ pts, size_t n, float betaSq, int skipFace, float* __restrict__ out, const uint32_t* __restrict__ order )
+{
+    const size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if ( t >= n ) return;
+    const size_t i = order ? order[t] : t;
+    const float3 q = make_float3( pts[3 * i], pts[3 * i + 1], pts[3 * i + 2] );
+    out[i] = numNodes > 0 ? fwnSingle( nodes, tris, numNodes, q, betaSq, skipFace ) : 0.f;
+}
+
+__device__ __forceinline__ uint32_t spread10( uint32_t v ) // 10 bits -> every third bit
+{
+    v = ( v | ( v << 16 ) ) & 0x030000FFu;
+    v = ( v | ( v << 8 ) ) & 0x0300F00Fu;
+    v = ( v | ( v << 4 ) ) & 0x030C30C3u;
+    v = ( v | ( v << 2 ) ) & 0x09249249u;
+    return v;
+}
+
+// 30-bit Morton code of every point inside the box of the mesh grown by half its size (points beyond are clamped: they are far
+// from every node and walk the same few top nodes anyway)
+__global__ void __launch_bounds__( 256 ) kMortonKeys( const float* __restrict__ pts, size_t n, float3 lo, float3 inv, uint32_t* __restrict__ keys,
+                                                      uint32_t* __restrict__ vals )
 {
     const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if ( i >= n ) return;
-    const float3 q = make_float3( pts[3 * i], pts[3 * i + 1], pts[3 * i + 2] );
-    out[i] = numNodes > 0 ? fwnSingle( nodes, tris, numNodes, q, betaSq, skipFace ) : 0.f;
+    const float fx = fminf( fmaxf( ( pts[3 * i] - lo.x ) * inv.x, 0.f ), 1023.f );
+    const float fy = fminf( fmaxf( ( pts[3 * i + 1] - lo.y ) * inv.y, 0.f ), 1023.f );
+    const float fz = fminf( fmaxf( ( pts[3 * i + 2] - lo.z ) * inv.z, 0.f ), 1023.f );
+    // NaN coordinates: fmaxf( NaN, 0 ) = 0 -- any cell will do, the walk itself is order-independent
+    keys[i] = spread10( (uint32_t)fx ) | ( spread10( (uint32_t)fy ) << 1 ) | ( spread10( (uint32_t)fz ) << 2 );
+    vals[i] = (uint32_t)i;
 }
 
 // calcSelfIntersections (MRFastWindingNumber.cpp:40-52): query = triCenter(f) = (1/3.0f)*(a+b+c), skipFace = f,
 // bit set iff w < 0 || w > 1; thresholding on the device (the reference GPU does it on the host after D2H,
 // MRCudaFastWindingNumber.cpp:163-169)
 __global__ void __launch_bounds__( 128 ) kFwnFaces( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris, int numNodes,
-    const float* __restrict__ pts, const int32_t* __restrict__ faces, size_t nFaces, float betaSq,
+    const float* __restrict__ pts, const int32_t* __restrict__ faces, size_t nLeaves, float betaSq,
     float* __restrict__ outW, uint32_t* __restrict__ outBits32 )
 {
-    const size_t f = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    // thread t takes the face of leaf slot t: leaves are stored in the tree's pre-order, so the faces of a warp are neighbours in
+    // space and their walks share most nodes (in face-id order a warp's walks have nothing to do with each other unless the
+    // mesh happens to be numbered coherently).  Deleted faces are no leaves: their bits and values stay zero (cleared before).
+    const size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if ( t >= nLeaves ) return;
+    const size_t f = (size_t)__float_as_int( __ldg( reinterpret_cast<const float4*>( tris + t ) ).w );
     bool flag = false;
-    if ( f < nFaces )
     {
         const int32_t ia = faces[3 * f], ib = faces[3 * f + 1], ic = faces[3 * f + 2];
         float w = 0.f;
-        if ( ia >= 0 && ib >= 0 && ic >= 0 && numNodes > 0 )
         {
             const float third = 1 / 3.0f;
             float3 q;
@@ -80,9 +112,7 @@ __global__ void __launch_bounds__( 128 ) kFwnFaces( const TravNode* __restrict__
         }
         if ( outW ) outW[f] = w;
     }
-    const unsigned bal = __ballot_sync( FULL, flag );
-    if ( ( threadIdx.x & 31 ) == 0 && f < nFaces && outBits32 )
-        outBits32[f >> 5] = bal;
+    if ( flag && outBits32 ) atomicOr( outBits32 + ( f >> 5 ), 1u << ( f & 31 ) );
 }
 
 } // anonymous namespace
@@ -92,9 +122,31 @@ int launchFwnVector( const DeviceTree& t, const float* dPts, size_t n, float bet
 {
     if ( n == 0 ) return B2FWN_OK;
     const size_t blocks = ( n + 127 ) / 128;
+    // Morton order for vectors large enough to pay for the sort (r02, C2: 10 M random points against 1 M triangles)
+    static const bool noSort = getenv( "B2FWN_NO_QUERY_SORT" ) != nullptr; // dev switch
+    uint32_t* order = nullptr;
+    uint8_t* scratch = nullptr;
+    if ( !noSort && n >= ( 1u << 15 ) && n < 0xFFFFFFFFull && t.numLeaves > 0 && t.pool )
+    {
+        size_t tmpBytes = 0;
+        cub::DeviceRadixSort::SortPairs( nullptr, tmpBytes, (uint32_t*)nullptr, (uint32_t*)nullptr, (uint32_t*)nullptr, (uint32_t*)nullptr, (int)n, 0, 30, st );
+        const size_t nPad = ( n + 63 ) & ~(size_t)63;
+        B2_CUDA( cudaMallocFromPoolAsync( &scratch, 4 * nPad * sizeof( uint32_t ) + tmpBytes, t.pool, st ) );
+        uint32_t* keys = reinterpret_cast<uint32_t*>( scratch );
+        uint32_t *keys2 = keys + nPad, *vals = keys2 + nPad, *vals2 = vals + nPad;
+        float3 lo, inv;
+        const float ext[3] = { t.bbox[3] - t.bbox[0], t.bbox[4] - t.bbox[1], t.bbox[5] - t.bbox[2] };
+        lo = make_float3( t.bbox[0] - 0.5f * ext[0], t.bbox[1] - 0.5f * ext[1], t.bbox[2] - 0.5f * ext[2] );
+        inv = make_float3( ext[0] > 0 ? 1024.f / ( 2 * ext[0] ) : 0.f, ext[1] > 0 ? 1024.f / ( 2 * ext[1] ) : 0.f, ext[2] > 0 ? 1024.f / ( 2 * ext[2] ) : 0.f );
+        kMortonKeys<<<(unsigned)( ( n + 255 ) / 256 ), 256, 0, st>>>( dPts, n, lo, inv, keys, vals );
+        B2_CUDA( cub::DeviceRadixSort::SortPairs( vals2 + nPad, tmpBytes, keys, keys2, vals, vals2, (int)n, 0, 30, st ) );
+        order = vals2;
+        if ( launches ) *launches += 5; // keys + 4 radix passes
+    }
     kFwnVector<<<(unsigned)blocks, 128, 0, st>>>( t.nodes, t.leafTris, (int)t.numNodes, dPts, n, beta * beta,
-                                                  skipFace < 0 ? -1 : skipFace, dOut );
+                                                  skipFace < 0 ? -1 : skipFace, dOut, order );
     if ( launches ) ++*launches;
+    if ( scratch ) B2_CUDA( cudaFreeAsync( scratch, st ) );
     B2_CUDA( cudaGetLastError() );
     return B2FWN_OK;
 }
@@ -104,9 +156,11 @@ int launchFwnFaces( const DeviceTree& t, float beta, float* dOutW, uint64_t* dBi
     const size_t n = t.numFaces;
     if ( n == 0 ) return B2FWN_OK;
     if ( dBits ) B2_CUDA( cudaMemsetAsync( dBits, 0, ( ( n + 63 ) / 64 ) * sizeof( uint64_t ), st ) );
-    const size_t blocks = ( n + 127 ) / 128;
-    kFwnFaces<<<(unsigned)blocks, 128, 0, st>>>( t.nodes, t.leafTris, (int)t.numNodes, t.points, t.tris, n, beta * beta, dOutW,
-                                                 reinterpret_cast<uint32_t*>( dBits ) );
+    if ( dOutW ) B2_CUDA( cudaMemsetAsync( dOutW, 0, n * sizeof( float ), st ) );
+    const size_t L = t.numLeaves;
+    if ( L == 0 ) return B2FWN_OK;
+    kFwnFaces<<<(unsigned)( ( L + 127 ) / 128 ), 128, 0, st>>>( t.nodes, t.leafTris, (int)t.numNodes, t.points, t.tris, L, beta * beta, dOutW,
+                                                              reinterpret_cast<uint32_t*>( dBits ) );
     if ( launches ) ++*launches;
     B2_CUDA( cudaGetLastError() );
     return B2FWN_OK;

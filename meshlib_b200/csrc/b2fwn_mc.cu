@@ -340,6 +340,9 @@ int marchingCubesDevice( const float* dVolume, const int32_t dims[3], const b2fw
     uint8_t* dCode = nullptr; uint32_t *dSegV = nullptr, *dSegT = nullptr; void* dTmp = nullptr;
     // scratch from the handle's stream-ordered pool: cached between calls, no device-wide synchronisation per allocation
     // (r02: of 6.9 ms for marching cubes at 512^3 the two kernels took 2.6 ms, cudaMalloc / cudaFree most of the rest)
+    // -- for volumes whose scratch fits the part of the pool that stays cached (1 GiB); larger ones pay cudaMalloc once per call
+    // either way (c5_offset, 2050^3: 225 ms with plain allocations, 307 ms through a pool that is trimmed after every call)
+    if ( g.total + 2 * ( S + 1 ) * sizeof( uint32_t ) > ( (size_t)1 << 30 ) - ( (size_t)64 << 20 ) ) pool = nullptr;
     auto alloc = [&]( void** ptr, size_t bytes ) { return pool ? cudaMallocFromPoolAsync( ptr, bytes, pool, st ) : cudaMalloc( ptr, bytes ); };
     auto cleanup = [&]()
     {

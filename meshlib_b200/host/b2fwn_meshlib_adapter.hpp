@@ -24,6 +24,7 @@
 #include "MRMesh/MRDistanceToMeshOptions.h"
 #include "MRMesh/MRPointsToMeshProjector.h"
 #include "MRMesh/MRMeshProject.h"
+#include "MRMesh/MRTriMesh.h"
 #include "b2fwn.h"
 
 #include <cfloat>
@@ -31,6 +32,7 @@
 #include <deque>
 #include <memory>
 #include <new>
+#include <sstream>
 #include <string>
 #include <vector>
 
@@ -164,6 +166,59 @@ public:
     {
         if ( !h_ ) return {}; // not uploaded yet: the first call will read the current coordinates
         return status_( b2fwn_update_points( h_, reinterpret_cast<const float*>( mesh_.points.data() ), mesh_.points.size() ) );
+    }
+
+    /// Beyond the interface (SURVEY 8a a19 + 8f N4): mcOffsetMesh / generalOffsetMesh( Mode::Standard ) with
+    /// SignDetectionMode::HoleWindingRule (source/MRVoxels/MROffset.cpp:117-246) with every stage on the device: the distance band
+    /// on the grid of calcOriginAndDimensions, marching cubes at iso = offset, and the half-edge tables of the result
+    /// (Mesh::fromTriMesh, MROffset.cpp:222-225).  The host only receives the finished arrays: points, and the tables in the
+    /// layout of MeshTopology::write, loaded (and validated) by MeshTopology::read.  A marching-cubes result that is not an
+    /// oriented manifold goes through the reference's own Mesh::fromTriMesh instead.
+    Expected<Mesh> offsetMesh( float offset, float voxelSize, bool closeHolesInHoleWindingNumber = true, float windingNumberThreshold = 0.5f,
+                               float windingNumberBeta = 2.f, const ProgressCallback& cb = {} )
+    {
+        if ( auto e = prepare_(); !e ) return unexpected( e.error() );
+        b2fwn_offset_params p{};
+        p.voxel_size = voxelSize; p.offset = offset; p.close_holes = closeHolesInHoleWindingNumber ? 1 : 0;
+        p.winding_number_threshold = windingNumberThreshold; p.winding_number_beta = windingNumberBeta;
+        b2fwn_offset_result r{};
+        if ( auto e = status_( b2fwn_mc_offset_mesh( h_, &p, &r, &progress_, (void*)&cb ) ); !e ) return unexpected( e.error() );
+        Mesh res;
+        res.points.resize( r.n_verts );
+        uint64_t nHalf = 0, nV = 0, nF = 0;
+        if ( b2fwn_build_topology( h_, nullptr, 0, 0, 0, &nHalf, &nV, &nF ) != B2FWN_OK )
+        {
+            TriMesh tm;
+            tm.points.resize( r.n_verts );
+            tm.tris.resize( r.n_tris );
+            static_assert( sizeof( ThreeVertIds ) == 3 * sizeof( int32_t ) );
+            if ( auto e = status_( b2fwn_marching_cubes_fetch( h_, reinterpret_cast<float*>( tm.points.data() ), reinterpret_cast<int32_t*>( tm.tris.data() ) ) ); !e )
+                return unexpected( e.error() );
+            return Mesh::fromTriMesh( std::move( tm ) );
+        }
+        if ( auto e = status_( b2fwn_marching_cubes_fetch( h_, reinterpret_cast<float*>( res.points.data() ), nullptr ) ); !e ) return unexpected( e.error() );
+        // the stream layout of MeshTopology::write (MRMeshTopology.cpp:2461-2477)
+        std::string buf( 12 + nHalf * sizeof( b2fwn_half_edge ) + ( nV + nF ) * sizeof( int32_t ), '\0' );
+        char* q = buf.data();
+        const uint32_t cnt[3] = { uint32_t( nHalf ), uint32_t( nV ), uint32_t( nF ) };
+        std::memcpy( q, &cnt[0], 4 );
+        auto* edges = reinterpret_cast<b2fwn_half_edge*>( q + 4 );
+        char* qv = q + 4 + nHalf * sizeof( b2fwn_half_edge );
+        std::memcpy( qv, &cnt[1], 4 );
+        char* qf = qv + 4 + nV * sizeof( int32_t );
+        std::memcpy( qf, &cnt[2], 4 );
+        // q + 4 is 4-byte aligned only: fetch into aligned vectors, then copy
+        {
+            std::vector<b2fwn_half_edge> he( nHalf );
+            std::vector<int32_t> epv( nV ), epf( nF );
+            if ( auto e = status_( b2fwn_build_topology_fetch( h_, he.data(), epv.data(), epf.data() ) ); !e ) return unexpected( e.error() );
+            std::memcpy( edges, he.data(), nHalf * sizeof( b2fwn_half_edge ) );
+            std::memcpy( qv + 4, epv.data(), nV * sizeof( int32_t ) );
+            std::memcpy( qf + 4, epf.data(), nF * sizeof( int32_t ) );
+        }
+        std::istringstream in( std::move( buf ), std::ios::binary );
+        if ( auto e = res.topology.read( in ); !e ) return unexpected( e.error() );
+        return res;
     }
 
 private:

@@ -226,6 +226,32 @@ int main( int argc, char** argv )
         check( triA->points.size() == triB->points.size() && triA->tris.size() == triB->tris.size() && triA->tris.size() > 0, "offsetMesh.counts" );
     }
 
+    // the whole offset pipeline on the device, half-edge tables included (SURVEY 8a a19 + 8f N4): the Mesh must be valid for the
+    // reference (MeshTopology::read ran checkValidity) and equal the TriMesh above in every count
+    {
+        auto b200 = std::dynamic_pointer_cast<B200::FastWindingNumber>( ours );
+        auto m = b200->offsetMesh( offset, voxel, false );
+        check( m.has_value(), "offsetMesh.device_pipeline.call" );
+        if ( m )
+        {
+            // its own grid (calcOriginAndDimensions of the mesh box), so not the TriMesh above: an offset surface of a torus is a closed
+            // orientable surface of genus 1 -- V - E + F = 0, no boundary -- and the reference must accept the tables
+            const int V = m->topology.numValidVerts(), F = m->topology.numValidFaces();
+            const int E = (int)m->topology.computeNotLoneUndirectedEdges();
+            std::printf( "offsetMesh.device_pipeline verts %d faces %d edges %d\n", V, F, E );
+            check( F > 1000 && (int)m->points.size() == V && m->topology.checkValidity(), "offsetMesh.device_pipeline.valid_mesh" );
+            check( V - E + F == 0 && 2 * E == 3 * F, "offsetMesh.device_pipeline.closed_genus_1" );
+            float maxDev = 0; // every vertex of the offset surface lies at distance |offset| from the torus (to a voxel's interpolation error)
+            for ( const auto& p : m->points )
+            {
+                const float rho = std::sqrt( p.x * p.x + p.y * p.y ) - 2.f;
+                maxDev = std::max( maxDev, std::abs( std::sqrt( rho * rho + p.z * p.z ) - ( 1.f + offset ) ) );
+            }
+            std::printf( "offsetMesh.device_pipeline.max_radial_deviation %g\n", maxDev );
+            check( maxDev < 0.02f, "offsetMesh.device_pipeline.geometry" );
+        }
+    }
+
     // cancellation travels as the reference's error string
     auto c = ours->calcFromGridWithDistances( da, dims, basis, opt, []( float ) { return false; } );
     check( !c.has_value() && c.error() == "Operation was canceled", "cancel.error_string" );
