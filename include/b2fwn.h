@@ -274,6 +274,10 @@ int b2fwn_marching_cubes_fetch( b2fwn_handle h, float* out_verts_xyz, int32_t* o
  * it (source/MRMesh/MRMesh.cpp:213-226); B2FWN_ERR_INVALID for a mesh without valid faces */
 int b2fwn_get_bounding_box( b2fwn_handle h, float out_min_max[6] );
 
+/* MR::suggestVoxelSize (source/MRVoxels/MROffset.cpp:25-31): cbrt( volume of the mesh's bounding box / approx_num_voxels ), from the
+ * box the device build already holds */
+int b2fwn_suggest_voxel_size( b2fwn_handle h, float approx_num_voxels, float* out_voxel_size );
+
 /* mirrors MR::DistanceVolumeParams (source/MRVoxels/MRDistanceVolumeParams.h:9-22) */
 typedef struct b2fwn_volume_params
 {

@@ -102,7 +102,7 @@ EXPORTS = [
     "b2fwn_signed_distances_by_projection_normal", "b2fwn_signed_distances_by_projection_normal_device",
     "b2fwn_mesh_to_distance_volume_by_projection_normal", "b2fwn_update_points",
     "b2fwn_calc_from_grid_by_parts_into", "b2fwn_calc_from_grid_with_distances_by_parts_into", "b2fwn_safe_memory_limit",
-    "b2fwn_build_topology", "b2fwn_build_topology_fetch",
+    "b2fwn_build_topology", "b2fwn_build_topology_fetch", "b2fwn_suggest_voxel_size",
 ]
 
 
@@ -156,6 +156,7 @@ def load_library():
                                                                     PART_BUFFER_CB, PART_CB, vp, PROGRESS_CB, vp]
     L.b2fwn_build_topology.argtypes = [vp, vp, C.c_size_t, C.c_int32, C.c_size_t, u64p, u64p, u64p]
     L.b2fwn_build_topology_fetch.argtypes = [vp, vp, vp, vp]
+    L.b2fwn_suggest_voxel_size.argtypes = [vp, C.c_float, f32p]
     L.b2fwn_safe_memory_limit.argtypes = [C.c_int32]
     L.b2fwn_safe_memory_limit.restype = C.c_size_t
     L.b2fwn_get_tree.argtypes = [vp, vp, vp, C.c_size_t, C.POINTER(C.c_size_t)]
@@ -463,6 +464,12 @@ class FastWindingNumber:
         return s
 
     # ---- callers of the interface, on the device ----
+    def suggest_voxel_size(self, approx_num_voxels):
+        """MR::suggestVoxelSize (source/MRVoxels/MROffset.cpp:25-31)"""
+        v = C.c_float()
+        _check(_lib.b2fwn_suggest_voxel_size(self._h, float(approx_num_voxels), C.byref(v)))
+        return v.value
+
     def bounding_box(self):
         bb = (C.c_float * 6)()
         _check(_lib.b2fwn_get_bounding_box(self._h, bb))

@@ -428,6 +428,7 @@ int b2fwn_calc_from_grid_device( b2fwn_handle h, const int32_t dims[3], const fl
                                  int32_t zEnd, float* dOut )
 {
     if ( !h || !dims || !xf ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    if ( !dOut && dims[0] > 0 && dims[1] > 0 && zEnd > zBegin ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
     B2_CUDA( cudaSetDevice( h->device ) );
     KernelTimer tm( h );
     if ( int e = launchFwnGrid( h->tree, dims, toXf( xf ), beta, zBegin, zEnd, dOut, h->stream, &h->stats.kernel_launches ) ) return e;
@@ -440,6 +441,7 @@ int b2fwn_calc_from_grid_with_distances_device( b2fwn_handle h, const int32_t di
                                                 const b2fwn_dist_options* opt, int32_t zBegin, int32_t zEnd, float* dOut )
 {
     if ( !h || !dims || !xf || !opt ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    if ( !dOut && dims[0] > 0 && dims[1] > 0 && zEnd > zBegin ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
     B2_CUDA( cudaSetDevice( h->device ) );
     KernelTimer tm( h );
     if ( int e = launchSdfGrid( h->tree, dims, toXf( xf ), *opt, zBegin, zEnd, dOut, h->stream, &h->stats.kernel_launches ) ) return e;
@@ -671,6 +673,22 @@ float fromOrd( unsigned o )
     return f;
 }
 } // namespace
+
+int b2fwn_suggest_voxel_size( b2fwn_handle h, float approxNumVoxels, float* out )
+{
+    if ( !h || !out ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    if ( h->tree.numLeaves == 0 ) { setError( "mesh has no valid faces" ); return B2FWN_ERR_INVALID; }
+    // Box::volume (MRBox.h:112-119): product of the float extents, left to right; then std::cbrt of the float quotient (MROffset.cpp:28-30)
+    volatile float vol = 1.f;
+    for ( int c = 0; c < 3; ++c )
+    {
+        volatile float ext = h->tree.bbox[3 + c] - h->tree.bbox[c];
+        vol = vol * ext;
+    }
+    volatile float q = vol / approxNumVoxels;
+    *out = cbrtf( q );
+    return B2FWN_OK;
+}
 
 int b2fwn_get_bounding_box( b2fwn_handle h, float out[6] )
 {

@@ -159,6 +159,29 @@ __device__ __forceinline__ void blockVoxelPos( const McGrid& g, int* sPos, int& 
     while ( y >= g.dy ) { y -= g.dy; ++z; }
 }
 
+// The +x corners of a voxel are the own-x corners of the next voxel: inside a row the lane to the right has them already
+__device__ __forceinline__ void loadCellShared( const float* __restrict__ vol, const McGrid& g, size_t i, int x, int y, int z, bool inGrid, Cell& c )
+{
+    const unsigned lane = threadIdx.x & 31;
+    c.hasX = x + 1 < g.dx; c.hasY = y + 1 < g.dy; c.hasZ = z + 1 < g.dz;
+    const size_t sy = (size_t)g.dx, sz = g.layer;
+    const bool hy = inGrid && c.hasY, hz = inGrid && c.hasZ;
+    c.v[0] = inGrid ? __ldg( vol + i ) : 0.f;
+    c.v[2] = hy ? __ldg( vol + i + sy ) : 0.f;
+    c.v[4] = hz ? __ldg( vol + i + sz ) : 0.f;
+    c.v[6] = ( hy && hz ) ? __ldg( vol + i + sy + sz ) : 0.f;
+    // lane + 1 holds voxel i + 1 = (x + 1, y, z) whenever x + 1 is still inside the row; its has-flags in y and z are ours
+    const float n0 = __shfl_down_sync( FULL, c.v[0], 1 ), n2 = __shfl_down_sync( FULL, c.v[2], 1 );
+    const float n4 = __shfl_down_sync( FULL, c.v[4], 1 ), n6 = __shfl_down_sync( FULL, c.v[6], 1 );
+    const bool fromLane = lane < 31;
+    const bool hx = inGrid && c.hasX;
+    c.v[1] = !hx ? 0.f : fromLane ? n0 : __ldg( vol + i + 1 );
+    c.v[3] = !( hx && c.hasY ) ? 0.f : fromLane ? n2 : __ldg( vol + i + 1 + sy );
+    c.v[5] = !( hx && c.hasZ ) ? 0.f : fromLane ? n4 : __ldg( vol + i + 1 + sz );
+    c.v[7] = !( hx && c.hasY && c.hasZ ) ? 0.f : fromLane ? n6 : __ldg( vol + i + 1 + sy + sz );
+    // loadCell leaves v[3], v[5], v[6], v[7] at 0 unless the cell is complete; nothing reads them in that case
+}
+
 __global__ void __launch_bounds__( MC_TB ) kMcClassify( const float* __restrict__ vol, const McGrid g, uint8_t* __restrict__ code,
                                                         uint32_t* __restrict__ segV, uint32_t* __restrict__ segT )
 {
@@ -167,13 +190,34 @@ __global__ void __launch_bounds__( MC_TB ) kMcClassify( const float* __restrict_
     unsigned vm = 0, nt = 0;
     int x, y, z;
     blockVoxelPos( g, sPos, x, y, z );
-    if ( i < g.total )
+    const bool inGrid = i < g.total;
+    Cell c;
+    loadCellShared( vol, g, i, x, y, z, inGrid, c );
+    if ( inGrid )
     {
-        Cell c;
-        loadCell( vol, g, i, x, y, z, c );
-        vm = vertexMask( c, g.iso );
-        const int cfg = cellCase( c, g.iso );
-        nt = cfg < 0 ? 0 : cTriCount[cfg];
+        const bool full = c.hasX && c.hasY && c.hasZ;
+        unsigned low = 0, inv = 0;
+#pragma unroll
+        for ( int k = 0; k < 8; ++k )
+        {
+            if ( lowerThan( c.v[k], g.iso ) ) low |= 1u << k;
+            if ( invalidVal( c.v[k], g.iso ) ) inv |= 1u << k;
+        }
+        if ( full && inv == 0 )
+        {
+            // the common cell: eight valid corners.  Case bits = corner bits with 2 <-> 3 and 6 <-> 7 swapped (cCornerBit); an edge
+            // owns a vertex iff its ends lie on different sides (hasSepPoint without NaN)
+            const unsigned cfg = ( low & 0x33u ) | ( ( low & 0x44u ) << 1 ) | ( ( low & 0x88u ) >> 1 );
+            nt = cTriCount[cfg]; // 0 for 0x00 and 0xFF
+            const unsigned l0 = low & 1u;
+            vm = ( ( ( low >> 1 ) & 1u ) ^ l0 ) | ( ( ( ( low >> 2 ) & 1u ) ^ l0 ) << 1 ) | ( ( ( ( low >> 4 ) & 1u ) ^ l0 ) << 2 );
+        }
+        else if ( !( full && inv == 0xFFu ) ) // a complete cell of NaNs yields nothing (cellCase :inv == 0xFF, vertexMask: v0 invalid)
+        {
+            vm = vertexMask( c, g.iso );
+            const int cfg = cellCase( c, g.iso );
+            nt = cfg < 0 ? 0 : cTriCount[cfg];
+        }
         code[i] = (uint8_t)( vm | ( nt << 3 ) );
     }
     const unsigned sv = __reduce_add_sync( FULL, __popc( vm ) );

@@ -76,11 +76,16 @@ __device__ __forceinline__ float ord2f( uint32_t u )
     return __uint_as_float( ( u & 0x80000000u ) ? ( u & 0x7fffffffu ) : ~u );
 }
 
-__global__ void kValidFlags( const int32_t* __restrict__ tris, size_t nFaces, uint8_t* __restrict__ flags )
+// a face is valid when none of its ids is negative (MeshTopology::getTriangulation marks deleted faces that way); an id beyond
+// the vertex array is a malformed triangulation: counted, so that the build fails with an error instead of reading out of bounds
+__global__ void kValidFlags( const int32_t* __restrict__ tris, size_t nFaces, size_t nVerts, uint8_t* __restrict__ flags, int* __restrict__ outOfRange )
 {
     size_t f = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if ( f >= nFaces ) return;
-    flags[f] = ( tris[3 * f] >= 0 && tris[3 * f + 1] >= 0 && tris[3 * f + 2] >= 0 ) ? 1 : 0;
+    const int a = tris[3 * f], b = tris[3 * f + 1], c = tris[3 * f + 2];
+    const bool valid = a >= 0 && b >= 0 && c >= 0;
+    if ( valid && ( (size_t)a >= nVerts || (size_t)b >= nVerts || (size_t)c >= nVerts ) ) { atomicAdd( outOfRange, 1 ); flags[f] = 0; return; }
+    flags[f] = valid ? 1 : 0;
 }
 
 // computeFaceBox (MRAABBTree.cpp:15-29) + Box::insignificantlyExpanded (MRBox.h:260-270)
@@ -518,28 +523,46 @@ int buildTree( DeviceTree& t, cudaStream_t st, uint64_t* launches )
     if ( F == 0 ) return B2FWN_OK;
     if ( F > (size_t)0x3FFFFFFF ) { setError( "too many faces" ); return B2FWN_ERR_INVALID; }
 
+    // every temporary of the build is released on every way out (an out-of-memory failure half way through a 10 M-face build
+    // would otherwise leak gigabytes: b2fwn_destroy only knows the arrays the tree keeps)
+    struct Temps
+    {
+        std::vector<void*> p;
+        ~Temps() { for ( void* q : p ) cudaFree( q ); }
+        cudaError_t alloc( void** ptr, size_t bytes )
+        {
+            const cudaError_t e = cudaMalloc( ptr, bytes );
+            if ( e == cudaSuccess ) p.push_back( *ptr );
+            return e;
+        }
+        void release( void* q ) { for ( auto& x : p ) if ( x == q ) { cudaFree( q ); x = nullptr; } }
+        void keep( void* q ) { for ( auto& x : p ) if ( x == q ) x = nullptr; }
+    } temps;
+#define T_ALLOC( ptr, bytes ) B2_CUDA( temps.alloc( (void**)&( ptr ), ( bytes ) ) )
     // 1. valid faces in increasing id order (MRAABBTree.cpp:35-46)
     uint8_t* dFlags = nullptr; int32_t* dValid = nullptr; int* dNum = nullptr;
-    B2_CUDA( cudaMalloc( &dFlags, F ) );
-    B2_CUDA( cudaMalloc( &dValid, F * sizeof( int32_t ) ) );
-    B2_CUDA( cudaMalloc( &dNum, sizeof( int ) ) );
-    kValidFlags<<<nblk( F ), TB, 0, st>>>( t.tris, F, dFlags ); ++nl;
+    T_ALLOC( dFlags, F );
+    T_ALLOC( dValid, F * sizeof( int32_t ) );
+    T_ALLOC( dNum, 2 * sizeof( int ) );
+    B2_CUDA( cudaMemsetAsync( dNum, 0, 2 * sizeof( int ), st ) );
+    kValidFlags<<<nblk( F ), TB, 0, st>>>( t.tris, F, t.numVerts, dFlags, dNum + 1 ); ++nl;
     {
         size_t tmpBytes = 0;
         thrust::counting_iterator<int32_t> ids( 0 );
         cub::DeviceSelect::Flagged( nullptr, tmpBytes, ids, dFlags, dValid, dNum, (int)F, st );
-        void* tmp = nullptr;
-        B2_CUDA( cudaMalloc( &tmp, tmpBytes ) );
-        cub::DeviceSelect::Flagged( tmp, tmpBytes, ids, dFlags, dValid, dNum, (int)F, st );
-        int num = 0;
-        B2_CUDA( cudaMemcpyAsync( &num, dNum, sizeof( int ), cudaMemcpyDeviceToHost, st ) );
+        void* selTmp = nullptr;
+        T_ALLOC( selTmp, tmpBytes );
+        cub::DeviceSelect::Flagged( selTmp, tmpBytes, ids, dFlags, dValid, dNum, (int)F, st );
+        int num[2] = { 0, 0 };
+        B2_CUDA( cudaMemcpyAsync( num, dNum, sizeof( num ), cudaMemcpyDeviceToHost, st ) );
         B2_CUDA( cudaStreamSynchronize( st ) );
-        cudaFree( tmp );
-        t.numLeaves = (size_t)num;
+        temps.release( selTmp );
+        if ( num[1] > 0 ) { setError( "triangulation refers to vertex ids beyond the vertex array" ); return B2FWN_ERR_INVALID; }
+        t.numLeaves = (size_t)num[0];
     }
-    cudaFree( dFlags ); cudaFree( dNum );
+    temps.release( dFlags ); temps.release( dNum );
     const int L = (int)t.numLeaves;
-    if ( L == 0 ) { cudaFree( dValid ); return B2FWN_OK; }
+    if ( L == 0 ) return B2FWN_OK;
     t.numNodes = 2 * (size_t)L - 1;
     const size_t N = t.numNodes;
     int levels = 0; // number of splitting levels = ceil(log2 L)
@@ -550,15 +573,15 @@ int buildTree( DeviceTree& t, cudaStream_t st, uint64_t* launches )
     uint32_t* dSegBox = nullptr; int32_t *dSkip = nullptr, *dLeafNodeOfPos = nullptr, *dLeafSlotOfNode = nullptr;
     uint8_t* dDepth = nullptr;
     const size_t maxSegs = (size_t)1 << levels;
-    B2_CUDA( cudaMalloc( &dLeaves, (size_t)L * sizeof( LeafBox ) ) );
-    B2_CUDA( cudaMalloc( &dKeys, (size_t)L * sizeof( LevelKey ) ) );
-    B2_CUDA( cudaMalloc( &dSegA, 2 * maxSegs * sizeof( Seg ) ) );
-    B2_CUDA( cudaMalloc( &dSegB, 2 * maxSegs * sizeof( Seg ) ) );
-    B2_CUDA( cudaMalloc( &dSegBox, maxSegs * 6 * sizeof( uint32_t ) ) );
-    B2_CUDA( cudaMalloc( &dSkip, N * sizeof( int32_t ) ) );
-    B2_CUDA( cudaMalloc( &dDepth, N ) );
-    B2_CUDA( cudaMalloc( &dLeafNodeOfPos, (size_t)L * sizeof( int32_t ) ) );
-    B2_CUDA( cudaMalloc( &dLeafSlotOfNode, N * sizeof( int32_t ) ) );
+    T_ALLOC( dLeaves, (size_t)L * sizeof( LeafBox ) );
+    T_ALLOC( dKeys, (size_t)L * sizeof( LevelKey ) );
+    T_ALLOC( dSegA, 2 * maxSegs * sizeof( Seg ) );
+    T_ALLOC( dSegB, 2 * maxSegs * sizeof( Seg ) );
+    T_ALLOC( dSegBox, maxSegs * 6 * sizeof( uint32_t ) );
+    T_ALLOC( dSkip, N * sizeof( int32_t ) );
+    T_ALLOC( dDepth, N );
+    T_ALLOC( dLeafNodeOfPos, (size_t)L * sizeof( int32_t ) );
+    T_ALLOC( dLeafSlotOfNode, N * sizeof( int32_t ) );
     B2_CUDA( cudaMalloc( &t.refNodes, N * sizeof( RefNode ) ) );
     B2_CUDA( cudaMalloc( &t.refDipoles, N * sizeof( RefDipole ) ) );
     B2_CUDA( cudaMalloc( &t.nodes, N * sizeof( TravNode ) ) );
@@ -566,7 +589,7 @@ int buildTree( DeviceTree& t, cudaStream_t st, uint64_t* launches )
     B2_CUDA( cudaMalloc( &t.leafFilt, (size_t)L * sizeof( LeafFilt ) ) );
 
     uint32_t* dBBox = nullptr;
-    B2_CUDA( cudaMalloc( &dBBox, 6 * sizeof( uint32_t ) ) );
+    T_ALLOC( dBBox, 6 * sizeof( uint32_t ) );
     kClearSegBoxes<<<1, 32, 0, st>>>( dBBox, 1 ); ++nl;
     kFaceBoxes<<<nblk( L ), TB, 0, st>>>( t.points, t.tris, dValid, L, dLeaves, dBBox ); ++nl;
     {
@@ -578,7 +601,7 @@ int buildTree( DeviceTree& t, cudaStream_t st, uint64_t* launches )
             const uint32_t u = ( hb[c] & 0x80000000u ) ? ( hb[c] & 0x7fffffffu ) : ~hb[c];
             memcpy( &t.bbox[c], &u, 4 );
         }
-        cudaFree( dBBox );
+        temps.release( dBBox );
     }
     kInitPerm<<<nblk( L ), TB, 0, st>>>( L, dKeys, dLeaves ); ++nl;
     const Seg root = { 0, L, 0, 0 };
@@ -586,7 +609,7 @@ int buildTree( DeviceTree& t, cudaStream_t st, uint64_t* launches )
 
     size_t sortTmpBytes = 0; void* sortTmp = nullptr;
     cub::DeviceMergeSort::SortKeys( nullptr, sortTmpBytes, dKeys, L, LevelKeyLess(), st );
-    B2_CUDA( cudaMalloc( &sortTmp, sortTmpBytes ) );
+    T_ALLOC( sortTmp, sortTmpBytes );
 
     // 2. breadth-first build, one segmented sort per level
     for ( int lev = 0; lev <= levels; ++lev )
@@ -619,9 +642,9 @@ int buildTree( DeviceTree& t, cudaStream_t st, uint64_t* launches )
     B2_CUDA( cudaGetLastError() );
     B2_CUDA( cudaStreamSynchronize( st ) );
 
-    cudaFree( sortTmp ); cudaFree( dValid ); cudaFree( dLeaves ); cudaFree( dKeys ); cudaFree( dSegA ); cudaFree( dSegB );
-    cudaFree( dSegBox ); cudaFree( dSkip ); cudaFree( dLeafNodeOfPos ); cudaFree( dLeafSlotOfNode );
-    t.nodeDepth = dDepth; // kept for refitTree
+    temps.keep( dDepth );
+    t.nodeDepth = dDepth; // kept for refitTree; everything else is released by temps
+#undef T_ALLOC
     if ( launches ) *launches += nl;
     return B2FWN_OK;
 }

@@ -273,3 +273,25 @@ def test_offset_mesh_to_half_edges_without_leaving_the_device(torus):
     he, epv, epf = fwn.build_topology()
     assert len(epf) == len(t) and len(epv) == len(v)
     _check_tables(t, len(v), he, epv, epf)
+
+
+def test_suggest_voxel_size_and_malformed_triangulation(torus):
+    pts, tris, fwn = torus
+    f = np.float32
+    ext = (pts.max(0) - pts.min(0)).astype(f)
+    vol = f(f(f(f(1) * ext[0]) * ext[1]) * ext[2])  # Box::volume, MRBox.h:112-119
+    want = np.cbrt(f(vol / f(5e6)))                  # suggestVoxelSize, MROffset.cpp:25-31
+    assert abs(fwn.suggest_voxel_size(5e6) - float(want)) <= 1e-7 * float(want)
+    # a vertex id beyond the vertex array is an error of the build, not an out-of-bounds read on the device
+    bad = tris.copy()
+    bad[11, 1] = len(pts) + 3
+    with pytest.raises(mb.B2Error) as e:
+        mb.FastWindingNumber(pts, bad)
+    assert "vertex ids beyond" in str(e.value)
+    # the context survives: the next build works
+    ok = mb.FastWindingNumber(pts, tris)
+    assert ok.stats().num_leaves == len(tris)
+    ok.close()
+    # device forms refuse a null output
+    with pytest.raises(mb.B2Error):
+        fwn.calc_from_grid_with_distances_device((8, 8, 8), mb.make_basis_xf((-3, -3, -1), 0.5), 0)
