@@ -1093,6 +1093,10 @@ __global__ void __launch_bounds__( GRID_TB, MINB ) kGridFwn6( const TravNode* __
 
     int fR[FX];
     int i = 0;
+    // (r02: classifying 32 consecutive nodes at once -- lane l takes node i + l, two ballots, the warp then walks the window on
+    // the bits -- was built and measured: bit-identical results, but c5_band 1069 ms against 857 ms for this node-by-node loop.
+    // A window is thrown away whenever a skip link leaves it, which is what most ALL_FAR and MIXED nodes do, and the two
+    // ballots plus the second fetch of the node sit on the critical path of every step.)
     while ( i < N )
     {
         const float4* np = reinterpret_cast<const float4*>( nodes + i );
@@ -1315,7 +1319,12 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
     {
         if ( distPass )
         {
-            if ( aa ) kGridDist<true, false><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, nullptr );
+            // dev switch: blocks per SM of the distance walk on axis-aligned grids (8 = 64 registers, the default; 6 = 80; 5 = 96; 4 = 128)
+            static const int distMinB = getenv( "B2FWN_DIST_MINB" ) ? atoi( getenv( "B2FWN_DIST_MINB" ) ) : 8;
+            if ( aa && distMinB == 6 ) kGridDist<true, false, 6><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, nullptr );
+            else if ( aa && distMinB == 5 ) kGridDist<true, false, 5><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, nullptr );
+            else if ( aa && distMinB == 4 ) kGridDist<true, false, 4><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, nullptr );
+            else if ( aa ) kGridDist<true, false><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, nullptr );
             else kGridDist<false, false><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, nullptr );
         }
         if ( sideEst ) B2_CUDA( cudaStreamWaitEvent( st, t.evJoin, 0 ) );
