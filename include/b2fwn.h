@@ -303,7 +303,10 @@ int b2fwn_mesh_to_distance_volume_by_projection_normal( b2fwn_handle h, const b2
 /* MR::mcOffsetMesh / generalOffsetMesh( Mode::Standard ) with SignDetectionMode::HoleWindingRule
  * (source/MRVoxels/MROffset.cpp:117-246, grid by calcOriginAndDimensions, source/MRVoxels/MRCalcDims.h:18-27):
  * the signed-distance band is computed into HBM and meshed there (marching cubes at iso = offset, lessInside = true);
- * the volume never leaves the device.  Fetch the mesh with b2fwn_marching_cubes_fetch. */
+ * the volume never leaves the device.  A grid that does not fit the free device memory is worked through in z-slabs (the
+ * reference's MarchingCubesByParts, MRMarchingCubes.h:96-122, fed in HBM); a multi-device handle gives every device a z-range of
+ * the grid and numbers the vertices by the exclusive prefix of the devices' counts.  The mesh is identical in every case.
+ * Fetch it with b2fwn_marching_cubes_fetch. */
 typedef struct b2fwn_offset_params
 {
     float voxel_size;               /* OffsetParameters::voxelSize, > 0 */
@@ -311,7 +314,8 @@ typedef struct b2fwn_offset_params
     int32_t close_holes;            /* OffsetParameters::closeHolesInHoleWindingNumber (default 1) */
     float winding_number_threshold; /* default 0.5 */
     float winding_number_beta;      /* default 2 */
-    int32_t reserved[3];
+    int32_t max_layers_per_slab;    /* 0: as many z-layers per slab as the free device memory allows (normally the whole grid) */
+    int32_t reserved[2];
 } b2fwn_offset_params;
 typedef struct b2fwn_offset_result
 {

@@ -67,7 +67,8 @@ class VolumeParams(C.Structure):
 class OffsetParams(C.Structure):
     """the fields of MR::OffsetParameters that mcOffsetMesh reads in HoleWindingRule mode (source/MRVoxels/MROffset.h)"""
     _fields_ = [("voxel_size", C.c_float), ("offset", C.c_float), ("close_holes", C.c_int32),
-                ("winding_number_threshold", C.c_float), ("winding_number_beta", C.c_float), ("reserved", C.c_int32 * 3)]
+                ("winding_number_threshold", C.c_float), ("winding_number_beta", C.c_float), ("max_layers_per_slab", C.c_int32),
+                ("reserved", C.c_int32 * 2)]
 
 
 # b2fwn_projection (include/b2fwn.h)
@@ -520,10 +521,10 @@ class FastWindingNumber:
                                                                        C.byref(lo), C.byref(hi), _progress(cb), None))
         return res, lo.value, hi.value
 
-    def mc_offset_mesh(self, offset, voxel_size, close_holes=True, threshold=0.5, beta=2.0, cb=None, fetch=True):
+    def mc_offset_mesh(self, offset, voxel_size, close_holes=True, threshold=0.5, beta=2.0, cb=None, fetch=True, max_layers_per_slab=0):
         """MR::mcOffsetMesh with HoleWindingRule (source/MRVoxels/MROffset.cpp:117-246), distance band and marching cubes
         both on the device.  Returns (verts, tris, info) -- verts/tris None when fetch is False"""
-        p = OffsetParams(float(voxel_size), float(offset), int(close_holes), float(threshold), float(beta))
+        p = OffsetParams(float(voxel_size), float(offset), int(close_holes), float(threshold), float(beta), int(max_layers_per_slab))
         r = OffsetResult()
         _check(_lib.b2fwn_mc_offset_mesh(self._h, C.byref(p), C.byref(r), _progress(cb), None))
         info = dict(origin=np.array(r.origin[:], np.float32), dims=tuple(r.dims[:]), n_verts=r.n_verts, n_tris=r.n_tris,

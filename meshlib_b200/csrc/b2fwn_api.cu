@@ -914,14 +914,6 @@ int b2fwn_mc_offset_mesh( b2fwn_handle h, const b2fwn_offset_params* p, b2fwn_of
         dims[c] = (int32_t)q + 1;
         res->origin[c] = o; res->dims[c] = dims[c];
     }
-    const size_t total = (size_t)dims[0] * dims[1] * dims[2];
-    size_t freeB = 0, totalB = 0;
-    B2_CUDA( cudaMemGetInfo( &freeB, &totalB ) );
-    if ( total * 6 + ( (size_t)256 << 20 ) > freeB ) // volume (4 B) + codes (1 B) + segment totals and scan scratch
-    {
-        setError( "offset volume does not fit into device memory; use calcFromGridWithDistancesByParts" );
-        return B2FWN_ERR_INVALID;
-    }
     b2fwn_dist_options o{};
     {
         // MROffset.cpp:176-183 (1.001f guards against rounding, as there)
@@ -939,31 +931,98 @@ int b2fwn_mc_offset_mesh( b2fwn_handle h, const b2fwn_offset_params* p, b2fwn_of
         volatile float half = 0.5f * v;
         xf[9 + c] = origin[c] + half; // basis = ( scale( voxelSize ), origin + 0.5f * voxelSize ), MROffset.cpp:202
     }
-    float* dVol = nullptr;
-    B2_CUDA( cudaMalloc( &dVol, total * sizeof( float ) ) );
-    cudaEventRecord( h->evA, h->stream );
-    int rc = launchSdfGrid( h->tree, dims, toXf( xf ), o, 0, dims[2], dVol, h->stream, &h->stats.kernel_launches );
-    cudaEventRecord( h->evB, h->stream );
-    if ( rc == B2FWN_OK && cudaEventSynchronize( h->evB ) != cudaSuccess ) rc = cudaFail( cudaGetLastError(), "offset: distance volume" );
-    if ( rc ) { cudaFree( dVol ); return rc; }
-    float ms = 0;
-    cudaEventElapsedTime( &ms, h->evA, h->evB );
-    res->sdf_ms = ms;
-    if ( !report( cb, user, 0.4f ) ) { cudaFree( dVol ); return canceled(); }
     b2fwn_mc_params mp{};
     for ( int c = 0; c < 3; ++c ) { mp.origin[c] = origin[c]; mp.voxel_size[c] = v; }
     mp.iso = p->offset;
     mp.less_inside = 1;
-    cudaEventRecord( h->evA, h->stream );
-    rc = marchingCubesDevice( dVol, dims, mp, h->mc, h->stream, &h->stats.kernel_launches, h->tree.pool );
-    cudaEventRecord( h->evB, h->stream );
-    cudaEventSynchronize( h->evB );
-    cudaEventElapsedTime( &ms, h->evA, h->evB );
-    res->mc_ms = ms;
+    const GridXf gxf = toXf( xf );
+
+    // Every device of the handle takes a contiguous z-range of the grid and works through it in slabs: the distance band of the
+    // slab's layers plus the two after them into a buffer, marching cubes on the slab (b2fwn_mc.cu), on to the next.  One slab
+    // is the whole range when it fits the safe share of the free device memory (the usual case on a B200: 2048^3 needs 45 GB);
+    // otherwise, or when the caller caps it (max_layers_per_slab), as many layers as fit -- the reference's MarchingCubesByParts
+    // (MRMarchingCubes.h:96-122, MROffset.cpp:205-221) without the volume ever leaving HBM.  Ids are local to a device until
+    // every device has counted; then the exclusive prefix of the counts is added to its triangles.
+    std::vector<b2fwn_ctx*> devs{ h };
+    devs.insert( devs.end(), h->replicas.begin(), h->replicas.end() );
+    const int nd = (int)std::min<size_t>( devs.size(), (size_t)std::max( 1, dims[2] / 4 ) );
+    devs.resize( nd );
+    const size_t layer = (size_t)dims[0] * dims[1];
+    struct DevRun { int z0 = 0, z1 = 0; double sdfMs = 0, totalMs = 0; int rc = B2FWN_OK; std::string err; };
+    std::vector<DevRun> run( nd );
+    for ( int d = 0; d < nd; ++d ) { run[d].z0 = (int)( (int64_t)dims[2] * d / nd ); run[d].z1 = (int)( (int64_t)dims[2] * ( d + 1 ) / nd ); }
+    const int cap = p->max_layers_per_slab;
+    auto work = [&]( int d )
+    {
+        b2fwn_ctx* c = devs[d];
+        DevRun& R = run[d];
+        auto fail = [&]( int rc ) { R.rc = rc; R.err = b2fwn_last_error(); };
+        if ( cudaSetDevice( c->device ) != cudaSuccess ) { fail( cudaFail( cudaGetLastError(), "cudaSetDevice" ) ); return; }
+        // values 4 B x (n + 2) layers, codes 1 B x (n + 1) layers, segment totals and scan scratch ~ 0.3 B: 5.5 B per voxel of a slab
+        const size_t budget = safeMemoryLimit( c->device );
+        int n = R.z1 - R.z0;
+        const size_t fit = layer ? (size_t)( (double)budget / ( 5.5 * (double)layer ) ) : (size_t)n;
+        if ( fit < (size_t)n + 2 ) n = fit > 3 ? (int)fit - 2 : 1;
+        if ( cap > 0 ) n = std::min( n, cap );
+        float* dBuf = nullptr;
+        const size_t bufLayers = (size_t)std::min( dims[2] - R.z0, n + 2 );
+        cudaError_t ce = cudaMalloc( &dBuf, std::max<size_t>( bufLayers * layer, 1 ) * sizeof( float ) );
+        if ( ce != cudaSuccess ) { fail( cudaFail( ce, "offset: slab buffer" ) ); return; }
+        cudaEvent_t e0 = nullptr, e1 = nullptr, s0 = nullptr, s1 = nullptr;
+        cudaEventCreate( &e0 ); cudaEventCreate( &e1 ); cudaEventCreate( &s0 ); cudaEventCreate( &s1 );
+        cudaEventRecord( e0, c->stream );
+        const int rc = marchingCubesSlabs( [&]( int z0, int z1, const float** dl ) -> int
+        {
+            cudaEventRecord( s0, c->stream );
+            if ( int e = launchSdfGrid( c->tree, dims, gxf, o, z0, z1, dBuf, c->stream, &c->stats.kernel_launches ) ) return e;
+            cudaEventRecord( s1, c->stream );
+            if ( cudaEventSynchronize( s1 ) != cudaSuccess ) return cudaFail( cudaGetLastError(), "offset: distance slab" );
+            float ms = 0;
+            cudaEventElapsedTime( &ms, s0, s1 );
+            R.sdfMs += ms;
+            *dl = dBuf;
+            return B2FWN_OK;
+        }, dims, mp, n, R.z0, R.z1, 0, 0, c->mc, c->stream, &c->stats.kernel_launches, c->tree.pool );
+        cudaEventRecord( e1, c->stream );
+        cudaEventSynchronize( e1 );
+        float ms = 0;
+        cudaEventElapsedTime( &ms, e0, e1 );
+        R.totalMs = ms;
+        cudaEventDestroy( e0 ); cudaEventDestroy( e1 ); cudaEventDestroy( s0 ); cudaEventDestroy( s1 );
+        cudaFree( dBuf );
+        if ( rc ) fail( rc );
+    };
+    {
+        std::vector<std::thread> th;
+        for ( int d = 1; d < nd; ++d ) th.emplace_back( work, d );
+        work( 0 );
+        for ( auto& t : th ) t.join();
+    }
+    B2_CUDA( cudaSetDevice( h->device ) );
+    for ( int d = 0; d < nd; ++d )
+        if ( run[d].rc ) { setError( run[d].err ); return run[d].rc; }
+    if ( !report( cb, user, 0.9f ) ) return canceled();
+    // global ids: every device's triangles get the number of vertices of the devices before it
+    uint64_t baseV = 0, totV = 0, totT = 0;
+    for ( int d = 0; d < nd; ++d ) { totV += devs[d]->mc.nVerts; totT += devs[d]->mc.nTris; }
+    if ( totV > 0x7FFFFFFFull ) { setError( "more than 2^31 vertices" ); return B2FWN_ERR_INVALID; }
+    for ( int d = 0; d < nd; ++d )
+    {
+        b2fwn_ctx* c = devs[d];
+        if ( d > 0 && c->mc.nTris )
+        {
+            B2_CUDA( cudaSetDevice( c->device ) );
+            if ( int e = marchingCubesAddBase( c->mc, (int32_t)baseV, c->stream, &c->stats.kernel_launches ) ) return e;
+            B2_CUDA( cudaStreamSynchronize( c->stream ) );
+        }
+        baseV += c->mc.nVerts;
+        res->sdf_ms = std::max( res->sdf_ms, run[d].sdfMs );
+        res->mc_ms = std::max( res->mc_ms, run[d].totalMs - run[d].sdfMs );
+    }
+    for ( size_t d = (size_t)nd; d < 1 + h->replicas.size(); ++d ) freeMc( ( d == 0 ? h : h->replicas[d - 1] )->mc ); // devices without a share
+    B2_CUDA( cudaSetDevice( h->device ) );
     h->stats.last_kernel_ms = res->sdf_ms + res->mc_ms;
-    cudaFree( dVol );
-    if ( rc ) return rc;
-    res->n_verts = h->mc.nVerts; res->n_tris = h->mc.nTris;
+    res->n_verts = totV; res->n_tris = totT;
     if ( !report( cb, user, 1.f ) ) return canceled();
     return B2FWN_OK;
 }
@@ -1029,6 +1088,8 @@ int b2fwn_marching_cubes( b2fwn_handle h, const float* volume, int32_t onDevice,
     const size_t total = (size_t)dims[0] * dims[1] * dims[2];
     *nVerts = *nTris = 0;
     freeMc( h->mc );
+    for ( b2fwn_ctx* r : h->replicas ) { cudaSetDevice( r->device ); freeMc( r->mc ); }
+    cudaSetDevice( h->device );
     if ( total == 0 ) return B2FWN_OK;
     if ( !volume ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
     const float* dVol = volume;
@@ -1053,11 +1114,20 @@ int b2fwn_marching_cubes( b2fwn_handle h, const float* volume, int32_t onDevice,
 int b2fwn_marching_cubes_fetch( b2fwn_handle h, float* outVerts, int32_t* outTris )
 {
     if ( !h ) { setError( "null handle" ); return B2FWN_ERR_INVALID; }
+    // the result of a multi-device offset lies on the devices in z order: the primary's share first
+    std::vector<b2fwn_ctx*> devs{ h };
+    devs.insert( devs.end(), h->replicas.begin(), h->replicas.end() );
+    size_t v0 = 0, t0 = 0;
+    for ( b2fwn_ctx* c : devs )
+    {
+        B2_CUDA( cudaSetDevice( c->device ) );
+        if ( c->mc.nVerts && outVerts )
+            B2_CUDA( cudaMemcpy( outVerts + 3 * v0, c->mc.dVerts, c->mc.nVerts * 3 * sizeof( float ), cudaMemcpyDeviceToHost ) );
+        if ( c->mc.nTris && outTris )
+            B2_CUDA( cudaMemcpy( outTris + 3 * t0, c->mc.dTris, c->mc.nTris * 3 * sizeof( int32_t ), cudaMemcpyDeviceToHost ) );
+        v0 += c->mc.nVerts; t0 += c->mc.nTris;
+    }
     B2_CUDA( cudaSetDevice( h->device ) );
-    if ( h->mc.nVerts && outVerts )
-        B2_CUDA( cudaMemcpy( outVerts, h->mc.dVerts, h->mc.nVerts * 3 * sizeof( float ), cudaMemcpyDeviceToHost ) );
-    if ( h->mc.nTris && outTris )
-        B2_CUDA( cudaMemcpy( outTris, h->mc.dTris, h->mc.nTris * 3 * sizeof( int32_t ), cudaMemcpyDeviceToHost ) );
     return B2FWN_OK;
 }
 
@@ -1074,6 +1144,23 @@ int b2fwn_build_topology( b2fwn_handle h, const int32_t* tris, size_t nTris, int
     if ( !tris )
     {
         dTris = h->mc.dTris; nTris = h->mc.nTris; nVerts = h->mc.nVerts; // the marching-cubes result of this handle
+        size_t moreT = 0, moreV = 0;
+        for ( const b2fwn_ctx* r : h->replicas ) { moreT += r->mc.nTris; moreV += r->mc.nVerts; }
+        if ( moreT || moreV )
+        {
+            // a multi-device offset: the other devices' triangles come over (peer copies; staged by the driver without peer access)
+            B2_CUDA( cudaMalloc( &dTmp, ( nTris + moreT ) * 3 * sizeof( int32_t ) ) );
+            cudaError_t e = nTris ? cudaMemcpyAsync( dTmp, h->mc.dTris, nTris * 3 * sizeof( int32_t ), cudaMemcpyDeviceToDevice, h->stream ) : cudaSuccess;
+            size_t at = nTris;
+            for ( const b2fwn_ctx* r : h->replicas )
+            {
+                if ( e == cudaSuccess && r->mc.nTris )
+                    e = cudaMemcpyPeerAsync( dTmp + 3 * at, h->device, r->mc.dTris, r->device, r->mc.nTris * 3 * sizeof( int32_t ), h->stream );
+                at += r->mc.nTris;
+            }
+            if ( e != cudaSuccess ) { cudaFree( dTmp ); return cudaFail( e, "gathering the triangles" ); }
+            dTris = dTmp; nTris += moreT; nVerts += moreV;
+        }
     }
     else if ( !onDevice && nTris )
     {

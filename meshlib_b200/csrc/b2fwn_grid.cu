@@ -1319,12 +1319,9 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
     {
         if ( distPass )
         {
-            // dev switch: blocks per SM of the distance walk on axis-aligned grids (8 = 64 registers, the default; 6 = 80; 5 = 96; 4 = 128)
-            static const int distMinB = getenv( "B2FWN_DIST_MINB" ) ? atoi( getenv( "B2FWN_DIST_MINB" ) ) : 8;
-            if ( aa && distMinB == 6 ) kGridDist<true, false, 6><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, nullptr );
-            else if ( aa && distMinB == 5 ) kGridDist<true, false, 5><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, nullptr );
-            else if ( aa && distMinB == 4 ) kGridDist<true, false, 4><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, nullptr );
-            else if ( aa ) kGridDist<true, false><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, nullptr );
+            // (r02: 6 / 5 / 4 blocks per SM -- 80 / 96 / 118 registers, fewer or no spills -- measured again on the full-range walk:
+            //  c3_full 533 ms at 8 blocks, 571 at 5, 602 at 4; c1 6.1 / 6.0 / 6.2 / 6.5 ms; c3_band 34.5 -> 38.6 ms: 8 stays)
+            if ( aa ) kGridDist<true, false><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, nullptr );
             else kGridDist<false, false><<<blocksFor( oD ), GRID_TB, 0, st>>>( t.nodes, t.leafTris, t.leafFilt, P, dOut, cullCost, oD, nullptr );
         }
         if ( sideEst ) B2_CUDA( cudaStreamWaitEvent( st, t.evJoin, 0 ) );

@@ -5,6 +5,7 @@
 #include <stdint.h>
 #include <stddef.h>
 #include <string>
+#include <functional>
 #include "../../include/b2fwn.h"
 
 namespace b2
@@ -159,9 +160,19 @@ struct McResult
     int32_t* dTris = nullptr;  // nTris*3
     uint64_t nVerts = 0, nTris = 0;
 };
+// layersPerSlab > 0: the volume is meshed in slabs of that many owner layers (identical output; bounds the scratch memory)
 int marchingCubesDevice( const float* dVolume, const int32_t dims[3], const b2fwn_mc_params& p, McResult& out,
-                         cudaStream_t stream, uint64_t* launches, cudaMemPool_t pool = nullptr );
+                         cudaStream_t stream, uint64_t* launches, cudaMemPool_t pool = nullptr, int layersPerSlab = 0 );
+// The same for a volume that is produced slab by slab: src( z0, z1, &dPtr ) must make the values of the layers [z0, z1) of the grid
+// available on the device (dPtr = layer z0) until its next call; it is asked for the owner layers of a slab plus the two layers
+// after them.  Meshes the owner layers [zBegin, zEnd); vertex / triangle ids start at baseV / baseT (several devices each mesh
+// a z-range of one grid: the bases are the exclusive prefix of their counts).
+using McVolumeSource = std::function<int( int z0, int z1, const float** dLayers )>;
+int marchingCubesSlabs( const McVolumeSource& src, const int32_t dims[3], const b2fwn_mc_params& p, int layersPerSlab, int zBegin, int zEnd,
+                        uint32_t baseV, uint32_t baseT, McResult& out, cudaStream_t stream, uint64_t* launches, cudaMemPool_t pool );
 void freeMc( McResult& r );
+// adds base to every vertex id of the triangles (a device's share of a multi-device mesh gets its global ids)
+int marchingCubesAddBase( McResult& r, int32_t base, cudaStream_t stream, uint64_t* launches );
 
 // half-edge tables of a triangle mesh (b2fwn_topology.cu) ----------------------------------------------------------------
 struct TopoResult

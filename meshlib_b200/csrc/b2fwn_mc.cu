@@ -43,15 +43,37 @@ __constant__ unsigned char cEdgeDir[12] = { 0, 1, 0, 1, 0, 1, 0, 1, 2, 2, 2, 2 }
 __constant__ unsigned char cCornerBit[8] = { 0, 1, 3, 2, 4, 5, 7, 6 };
 __constant__ unsigned char cNeiOrder[7] = { 1, 2, 4, 3, 5, 6, 7 }; // NaN substitution order (:951-959)
 
+// The mesher works on a SLAB of the grid: the voxels of the layers [zo0, zo1) ("owners": each owns the vertices on its +X/+Y/+Z
+// edges and the triangles of the cell whose lowest corner it is) get vertex / triangle ids baseV.. / baseT.. in voxel-id order.
+// Their triangles also use vertices owned by voxels of layer zo1, so that layer is classified as well ("extra" layer: its codes
+// give the ranks of its vertices, which continue the numbering: the next slab starts exactly there).  Values must be present for
+// the layers [zv0, ..) up to min(dz, zo1 + 2).  The whole grid is the slab zo0 = 0, zo1 = dz.
+// Thread / code index t: owners t in [0, nOwn) = voxel id minus zo0 * layer; the extra layer at [extraBase, extraBase + layer),
+// extraBase = nOwn rounded up to the block size, so that a block never mixes the two.
 struct McGrid
 {
     int dx, dy, dz;
-    size_t layer, total;
+    size_t layer, total; // total = number of code slots (owners, padding, extra layer)
     float iso;
     float zero[3];  // origin + 0.5 * voxelSize (zeroPoint of a SimpleVolume, :566; MRVoxelsVolumeAccess.h:78)
     float vs[3];
     int lessInside;
+    int zv0, zo0, zo1;
+    size_t nOwn, extraBase;
+    uint32_t baseV, baseT;
 };
+
+// code slot -> index into the slab's value array (layer zv0 first); slot must be an owner or an extra-layer voxel
+__device__ __forceinline__ size_t valueIndex( const McGrid& g, size_t t )
+{
+    return t < g.nOwn ? t + (size_t)( g.zo0 - g.zv0 ) * g.layer : ( t - g.extraBase ) + (size_t)( g.zo1 - g.zv0 ) * g.layer;
+}
+// code slot of the voxel `off` voxel ids after owner slot t (off = +1, +dx, +layer and sums): layer zo1 lives at extraBase
+__device__ __forceinline__ size_t slotAfter( const McGrid& g, size_t t, size_t off )
+{
+    const size_t r = t + off;
+    return r < g.nOwn ? r : g.extraBase + ( r - g.nOwn );
+}
 
 __device__ __forceinline__ bool lowerThan( float v, float iso ) { return v < iso; }
 __device__ __forceinline__ bool invalidVal( float v, float iso ) { return !( v < iso ) && !( v >= iso ); }
@@ -135,12 +157,16 @@ __device__ __forceinline__ int cellCase( const Cell& c, float iso )
     return (int)cfg;
 }
 
-__device__ __forceinline__ void voxelPos( const McGrid& g, size_t i, int& x, int& y, int& z )
+// grid position of code slot t (owners: layers from zo0 on; extra layer: zo1)
+__device__ __forceinline__ void voxelPos( const McGrid& g, size_t t, int& x, int& y, int& z )
 {
-    z = (int)( i / g.layer );
-    const size_t r = i - (size_t)z * g.layer;
+    const bool extra = t >= g.extraBase;
+    const size_t i = extra ? t - g.extraBase : t;
+    const int lz = (int)( i / g.layer );
+    const size_t r = i - (size_t)lz * g.layer;
     y = (int)( r / (size_t)g.dx );
     x = (int)( r - (size_t)y * g.dx );
+    z = extra ? g.zo1 : g.zo0 + lz;
 }
 
 // (x, y, z) of the block's voxels without a 64-bit division per thread (ncu r02: kMcClassify was ALU-bound at 290 thread
@@ -157,6 +183,11 @@ __device__ __forceinline__ void blockVoxelPos( const McGrid& g, int* sPos, int& 
     x = sPos[0] + (int)threadIdx.x; y = sPos[1]; z = sPos[2];
     while ( x >= g.dx ) { x -= g.dx; ++y; }
     while ( y >= g.dy ) { y -= g.dy; ++z; }
+}
+// does code slot t hold a voxel (owner or extra layer)?
+__device__ __forceinline__ bool slotInGrid( const McGrid& g, size_t t )
+{
+    return t < g.nOwn || ( t >= g.extraBase && t < g.total );
 }
 
 // The +x corners of a voxel are the own-x corners of the next voxel: inside a row the lane to the right has them already
@@ -190,9 +221,9 @@ __global__ void __launch_bounds__( MC_TB ) kMcClassify( const float* __restrict_
     unsigned vm = 0, nt = 0;
     int x, y, z;
     blockVoxelPos( g, sPos, x, y, z );
-    const bool inGrid = i < g.total;
+    const bool inGrid = slotInGrid( g, i );
     Cell c;
-    loadCellShared( vol, g, i, x, y, z, inGrid, c );
+    loadCellShared( vol, g, inGrid ? valueIndex( g, i ) : 0, x, y, z, inGrid, c );
     if ( inGrid )
     {
         const bool full = c.hasX && c.hasY && c.hasZ;
@@ -218,8 +249,8 @@ __global__ void __launch_bounds__( MC_TB ) kMcClassify( const float* __restrict_
             const int cfg = cellCase( c, g.iso );
             nt = cfg < 0 ? 0 : cTriCount[cfg];
         }
-        code[i] = (uint8_t)( vm | ( nt << 3 ) );
     }
+    if ( i < g.total ) code[i] = (uint8_t)( vm | ( nt << 3 ) ); // padding slots between the owners and the extra layer: 0
     const unsigned sv = __reduce_add_sync( FULL, __popc( vm ) );
     const unsigned stt = __reduce_add_sync( FULL, nt );
     if ( ( threadIdx.x & 31 ) == 0 && i < g.total )
@@ -271,7 +302,7 @@ __global__ void __launch_bounds__( MC_TB ) kMcEmit( const float* __restrict__ vo
     __shared__ int sPos[3];
     const size_t i = blockIdx.x * (size_t)MC_TB + threadIdx.x;
     const unsigned lane = threadIdx.x & 31;
-    const unsigned cd = i < g.total ? code[i] : 0u;
+    const unsigned cd = i < g.nOwn ? code[i] : 0u; // owners only: the extra layer belongs to the next slab
     int x, y, z;
     blockVoxelPos( g, sPos, x, y, z );
     if ( __ballot_sync( FULL, cd != 0 ) == 0 ) return; // nothing on the surface in this segment
@@ -283,11 +314,11 @@ __global__ void __launch_bounds__( MC_TB ) kMcEmit( const float* __restrict__ vo
                            + 4 * __popc( __ballot_sync( FULL, cd & 32 ) & lt );
     if ( cd == 0 ) return;
     Cell c;
-    loadCell( vol, g, i, x, y, z, c );
+    loadCell( vol, g, valueIndex( g, i ), x, y, z, c );
     const unsigned vm = cd & 7u;
     if ( vm )
     {
-        size_t vid = (size_t)segV[i >> 5] + vRank;
+        size_t vid = (size_t)segV[i >> 5] + vRank; // slab-local: outVerts starts at the slab's first vertex
         float coords[3];
         coords[0] = FA( g.zero[0], FM( g.vs[0], (float)x ) );
         coords[1] = FA( g.zero[1], FM( g.vs[1], (float)y ) );
@@ -322,8 +353,8 @@ __global__ void __launch_bounds__( MC_TB ) kMcEmit( const float* __restrict__ vo
             {
                 const int e = plan[3 * t + k];
                 const int cn = cEdgeCorner[e], dir = cEdgeDir[e];
-                const size_t owner = i + ( cn & 1 ) + ( ( cn >> 1 ) & 1 ) * (size_t)g.dx + ( ( cn >> 2 ) & 1 ) * g.layer;
-                vv[k] = (int32_t)( segV[owner >> 5] + rankInSegment( code, owner, dir, g.total ) );
+                const size_t owner = slotAfter( g, i, ( cn & 1 ) + ( ( cn >> 1 ) & 1 ) * (size_t)g.dx + ( ( cn >> 2 ) & 1 ) * g.layer );
+                vv[k] = (int32_t)( g.baseV + segV[owner >> 5] + rankInSegment( code, owner, dir, g.total ) );
             }
             outTris[3 * tid] = vv[0];
             outTris[3 * tid + 1] = g.lessInside ? vv[2] : vv[1]; // :1058-1069
@@ -358,19 +389,34 @@ void freeMc( McResult& r )
     r = McResult{};
 }
 
-int marchingCubesDevice( const float* dVolume, const int32_t dims[3], const b2fwn_mc_params& p, McResult& out,
-                         cudaStream_t st, uint64_t* launches, cudaMemPool_t pool )
+namespace
 {
-    freeMc( out );
-    if ( dims[0] <= 0 || dims[1] <= 0 || dims[2] <= 0 ) return B2FWN_OK; // VolumeMesher::run :383-384
-    if ( dims[2] <= 1 ) { setError( "a part must have at least two Z slices" ); return B2FWN_ERR_INVALID; } // :443-444
-    int device = 0;
-    B2_CUDA( cudaGetDevice( &device ) );
-    if ( int e = uploadTables( device ) ) return e;
+
+// one slab between its two phases: count (classify + scans: how many vertices and triangles the owners yield) and emit
+struct McPass
+{
+    McGrid g{};
+    uint8_t* dCode = nullptr;
+    uint32_t *dSegV = nullptr, *dSegT = nullptr;
+    void* dTmp = nullptr;
+    cudaMemPool_t pool = nullptr;
+    uint32_t nV = 0, nT = 0;
+};
+
+void mcRelease( McPass& ps, cudaStream_t st )
+{
+    void* all[4] = { ps.dCode, ps.dSegV, ps.dSegT, ps.dTmp };
+    for ( void* q : all )
+        if ( q ) { if ( ps.pool ) cudaFreeAsync( q, st ); else cudaFree( q ); }
+    if ( ps.pool ) { cudaStreamSynchronize( st ); cudaMemPoolTrimTo( ps.pool, (size_t)1 << 30 ); } // keep at most 1 GiB cached
+    ps.dCode = nullptr; ps.dSegV = ps.dSegT = nullptr; ps.dTmp = nullptr;
+}
+
+McGrid makeGrid( const int32_t dims[3], const b2fwn_mc_params& p, int zv0, int zo0, int zo1 )
+{
     McGrid g{};
     g.dx = dims[0]; g.dy = dims[1]; g.dz = dims[2];
     g.layer = (size_t)dims[0] * dims[1];
-    g.total = g.layer * dims[2];
     g.iso = p.iso;
     g.lessInside = p.less_inside;
     for ( int c = 0; c < 3; ++c )
@@ -379,54 +425,145 @@ int marchingCubesDevice( const float* dVolume, const int32_t dims[3], const b2fw
         volatile float half = 0.5f * p.voxel_size[c]; // separate rounding, as mult(shift, voxelSize) then +
         g.zero[c] = p.origin[c] + half;
     }
+    g.zv0 = zv0; g.zo0 = zo0; g.zo1 = zo1;
+    g.nOwn = (size_t)( zo1 - zo0 ) * g.layer;
+    g.extraBase = ( g.nOwn + MC_TB - 1 ) / MC_TB * MC_TB;
+    g.total = g.extraBase + ( zo1 < g.dz ? g.layer : 0 );
+    return g;
+}
+
+// phase 1: dVol = values of the layers [zv0, min(dz, zo1 + 2)); fills ps.nV / ps.nT (synchronises the stream)
+int mcCount( const float* dVol, McPass& ps, cudaStream_t st, uint64_t* launches )
+{
+    McGrid& g = ps.g;
     const size_t S = ( g.total + 31 ) / 32;
     if ( S + 1 > 0x7FFFFFFFull ) { setError( "volume too large for one marching-cubes pass" ); return B2FWN_ERR_INVALID; }
-    uint8_t* dCode = nullptr; uint32_t *dSegV = nullptr, *dSegT = nullptr; void* dTmp = nullptr;
     // scratch from the handle's stream-ordered pool: cached between calls, no device-wide synchronisation per allocation
     // (r02: of 6.9 ms for marching cubes at 512^3 the two kernels took 2.6 ms, cudaMalloc / cudaFree most of the rest)
-    // -- for volumes whose scratch fits the part of the pool that stays cached (1 GiB); larger ones pay cudaMalloc once per call
+    // -- for slabs whose scratch fits the part of the pool that stays cached (1 GiB); larger ones pay cudaMalloc once per call
     // either way (c5_offset, 2050^3: 225 ms with plain allocations, 307 ms through a pool that is trimmed after every call)
-    if ( g.total + 2 * ( S + 1 ) * sizeof( uint32_t ) > ( (size_t)1 << 30 ) - ( (size_t)64 << 20 ) ) pool = nullptr;
-    auto alloc = [&]( void** ptr, size_t bytes ) { return pool ? cudaMallocFromPoolAsync( ptr, bytes, pool, st ) : cudaMalloc( ptr, bytes ); };
-    auto cleanup = [&]()
-    {
-        void* all[4] = { dCode, dSegV, dSegT, dTmp };
-        for ( void* q : all )
-            if ( q ) { if ( pool ) cudaFreeAsync( q, st ); else cudaFree( q ); }
-        if ( pool ) { cudaStreamSynchronize( st ); cudaMemPoolTrimTo( pool, (size_t)1 << 30 ); } // keep at most 1 GiB cached
-    };
-#define MC_TRY( expr ) do { cudaError_t _e = ( expr ); if ( _e != cudaSuccess ) { cleanup(); return cudaFail( _e, #expr ); } } while ( 0 )
-    MC_TRY( alloc( (void**)&dCode, ( g.total + 31 ) & ~(size_t)31 ) );
-    MC_TRY( alloc( (void**)&dSegV, ( S + 1 ) * sizeof( uint32_t ) ) );
-    MC_TRY( alloc( (void**)&dSegT, ( S + 1 ) * sizeof( uint32_t ) ) );
-    MC_TRY( cudaMemsetAsync( dSegV + S, 0, sizeof( uint32_t ), st ) );
-    MC_TRY( cudaMemsetAsync( dSegT + S, 0, sizeof( uint32_t ), st ) );
+    if ( g.total + 2 * ( S + 1 ) * sizeof( uint32_t ) > ( (size_t)1 << 30 ) - ( (size_t)64 << 20 ) ) ps.pool = nullptr;
+    auto alloc = [&]( void** ptr, size_t bytes ) { return ps.pool ? cudaMallocFromPoolAsync( ptr, bytes, ps.pool, st ) : cudaMalloc( ptr, bytes ); };
+#define MC_TRY( expr ) do { cudaError_t _e = ( expr ); if ( _e != cudaSuccess ) { mcRelease( ps, st ); return cudaFail( _e, #expr ); } } while ( 0 )
+    MC_TRY( alloc( (void**)&ps.dCode, ( g.total + 31 ) & ~(size_t)31 ) );
+    MC_TRY( alloc( (void**)&ps.dSegV, ( S + 1 ) * sizeof( uint32_t ) ) );
+    MC_TRY( alloc( (void**)&ps.dSegT, ( S + 1 ) * sizeof( uint32_t ) ) );
+    MC_TRY( cudaMemsetAsync( ps.dSegV + S, 0, sizeof( uint32_t ), st ) );
+    MC_TRY( cudaMemsetAsync( ps.dSegT + S, 0, sizeof( uint32_t ), st ) );
     const size_t blocks = ( g.total + MC_TB - 1 ) / MC_TB;
-    if ( blocks > 0x7FFFFFFFull ) { cleanup(); setError( "volume too large for one launch" ); return B2FWN_ERR_INVALID; }
-    kMcClassify<<<(unsigned)blocks, MC_TB, 0, st>>>( dVolume, g, dCode, dSegV, dSegT );
+    if ( blocks > 0x7FFFFFFFull ) { mcRelease( ps, st ); setError( "volume too large for one launch" ); return B2FWN_ERR_INVALID; }
+    kMcClassify<<<(unsigned)blocks, MC_TB, 0, st>>>( dVol, g, ps.dCode, ps.dSegV, ps.dSegT );
     size_t tmpBytes = 0;
-    MC_TRY( cub::DeviceScan::ExclusiveSum( nullptr, tmpBytes, dSegV, dSegV, (int)( S + 1 ), st ) );
-    MC_TRY( alloc( &dTmp, tmpBytes ) );
-    MC_TRY( cub::DeviceScan::ExclusiveSum( dTmp, tmpBytes, dSegV, dSegV, (int)( S + 1 ), st ) );
-    MC_TRY( cub::DeviceScan::ExclusiveSum( dTmp, tmpBytes, dSegT, dSegT, (int)( S + 1 ), st ) );
-    uint32_t totV = 0, totT = 0;
-    MC_TRY( cudaMemcpyAsync( &totV, dSegV + S, sizeof( uint32_t ), cudaMemcpyDeviceToHost, st ) );
-    MC_TRY( cudaMemcpyAsync( &totT, dSegT + S, sizeof( uint32_t ), cudaMemcpyDeviceToHost, st ) );
+    MC_TRY( cub::DeviceScan::ExclusiveSum( nullptr, tmpBytes, ps.dSegV, ps.dSegV, (int)( S + 1 ), st ) );
+    MC_TRY( alloc( &ps.dTmp, tmpBytes ) );
+    MC_TRY( cub::DeviceScan::ExclusiveSum( ps.dTmp, tmpBytes, ps.dSegV, ps.dSegV, (int)( S + 1 ), st ) );
+    MC_TRY( cub::DeviceScan::ExclusiveSum( ps.dTmp, tmpBytes, ps.dSegT, ps.dSegT, (int)( S + 1 ), st ) );
+    // what the owners yield = the prefix at the first slot after them (extraBase is a multiple of 32)
+    const size_t sOwn = g.extraBase / 32;
+    MC_TRY( cudaMemcpyAsync( &ps.nV, ps.dSegV + sOwn, sizeof( uint32_t ), cudaMemcpyDeviceToHost, st ) );
+    MC_TRY( cudaMemcpyAsync( &ps.nT, ps.dSegT + sOwn, sizeof( uint32_t ), cudaMemcpyDeviceToHost, st ) );
     MC_TRY( cudaStreamSynchronize( st ) );
     if ( launches ) *launches += 5; // classify + 2 x (cub scan = 2 kernels)
-    out.nVerts = totV; out.nTris = totT;
-    if ( totV ) MC_TRY( cudaMalloc( &out.dVerts, (size_t)totV * 3 * sizeof( float ) ) );
-    if ( totT ) MC_TRY( cudaMalloc( &out.dTris, (size_t)totT * 3 * sizeof( int32_t ) ) );
-    if ( totV || totT )
+    return B2FWN_OK;
+}
+
+// phase 2: the owners' vertices and triangles to dVerts / dTris (this slab's first vertex / triangle first), ids from g.baseV on
+int mcEmit( const float* dVol, McPass& ps, float* dVerts, int32_t* dTris, cudaStream_t st, uint64_t* launches )
+{
+    if ( ps.nV || ps.nT )
     {
-        kMcEmit<<<(unsigned)blocks, MC_TB, 0, st>>>( dVolume, g, dCode, dSegV, dSegT, out.dVerts, out.dTris );
+        const size_t blocks = ( ps.g.nOwn + MC_TB - 1 ) / MC_TB;
+        kMcEmit<<<(unsigned)blocks, MC_TB, 0, st>>>( dVol, ps.g, ps.dCode, ps.dSegV, ps.dSegT, dVerts, dTris );
         if ( launches ) ++*launches;
     }
     MC_TRY( cudaGetLastError() );
-    MC_TRY( cudaStreamSynchronize( st ) );
-#undef MC_TRY
-    cleanup();
     return B2FWN_OK;
+#undef MC_TRY
+}
+
+} // anonymous namespace
+
+// growing output arrays of a mesh that arrives slab by slab
+int mcReserve( McResult& out, size_t& capV, size_t& capT, size_t needV, size_t needT, cudaStream_t st )
+{
+    auto grow = [&]( void** p, size_t& cap, size_t used, size_t need, size_t elem ) -> cudaError_t
+    {
+        if ( need <= cap ) return cudaSuccess;
+        const size_t nc = std::max( need, cap + cap / 2 );
+        void* q = nullptr;
+        cudaError_t e = cudaMalloc( &q, std::max<size_t>( nc, 1 ) * elem );
+        if ( e != cudaSuccess ) return e;
+        if ( used ) e = cudaMemcpyAsync( q, *p, used * elem, cudaMemcpyDeviceToDevice, st );
+        if ( e == cudaSuccess ) e = cudaStreamSynchronize( st );
+        cudaFree( *p );
+        *p = q; cap = nc;
+        return e;
+    };
+    B2_CUDA( grow( (void**)&out.dVerts, capV, out.nVerts, needV, 3 * sizeof( float ) ) );
+    B2_CUDA( grow( (void**)&out.dTris, capT, out.nTris, needT, 3 * sizeof( int32_t ) ) );
+    return B2FWN_OK;
+}
+
+int marchingCubesSlabs( const McVolumeSource& src, const int32_t dims[3], const b2fwn_mc_params& p, int layersPerSlab, int zBegin, int zEnd,
+                        uint32_t baseV, uint32_t baseT, McResult& out, cudaStream_t st, uint64_t* launches, cudaMemPool_t pool )
+{
+    freeMc( out );
+    if ( dims[0] <= 0 || dims[1] <= 0 || dims[2] <= 0 ) return B2FWN_OK; // VolumeMesher::run :383-384
+    if ( dims[2] <= 1 ) { setError( "a part must have at least two Z slices" ); return B2FWN_ERR_INVALID; } // :443-444
+    int device = 0;
+    B2_CUDA( cudaGetDevice( &device ) );
+    if ( int e = uploadTables( device ) ) return e;
+    if ( layersPerSlab <= 0 ) layersPerSlab = zEnd - zBegin;
+    size_t capV = 0, capT = 0;
+    for ( int z = zBegin; z < zEnd; z += layersPerSlab )
+    {
+        const int zo1 = std::min( zEnd, z + layersPerSlab );
+        const int zv1 = std::min( dims[2], zo1 + 2 );
+        const float* dVol = nullptr;
+        if ( int e = src( z, zv1, &dVol ) ) return e; // values of the layers [z, zv1), pointer to layer z
+        McPass ps;
+        ps.pool = pool;
+        ps.g = makeGrid( dims, p, z, z, zo1 );
+        if ( int e = mcCount( dVol, ps, st, launches ) ) return e;
+        if ( (uint64_t)baseV + out.nVerts + ps.nV > 0x7FFFFFFFull ) { mcRelease( ps, st ); setError( "more than 2^31 vertices" ); return B2FWN_ERR_INVALID; }
+        ps.g.baseV = baseV + (uint32_t)out.nVerts;
+        ps.g.baseT = baseT + (uint32_t)out.nTris;
+        if ( int e = mcReserve( out, capV, capT, out.nVerts + ps.nV, out.nTris + ps.nT, st ) ) { mcRelease( ps, st ); return e; }
+        const int rc = mcEmit( dVol, ps, out.dVerts + 3 * out.nVerts, out.dTris + 3 * out.nTris, st, launches );
+        const cudaError_t se = cudaStreamSynchronize( st );
+        mcRelease( ps, st );
+        if ( rc ) return rc;
+        if ( se != cudaSuccess ) return cudaFail( se, "marching cubes slab" );
+        out.nVerts += ps.nV; out.nTris += ps.nT;
+    }
+    return B2FWN_OK;
+}
+
+namespace
+{
+__global__ void __launch_bounds__( 256 ) kAddBase( int32_t* __restrict__ ids, size_t n, int32_t base )
+{
+    const size_t i = blockIdx.x * (size_t)256 + threadIdx.x;
+    if ( i < n ) ids[i] += base;
+}
+} // namespace
+
+int marchingCubesAddBase( McResult& r, int32_t base, cudaStream_t st, uint64_t* launches )
+{
+    const size_t n = 3 * (size_t)r.nTris;
+    if ( n == 0 || base == 0 ) return B2FWN_OK;
+    kAddBase<<<(unsigned)( ( n + 255 ) / 256 ), 256, 0, st>>>( r.dTris, n, base );
+    if ( launches ) ++*launches;
+    B2_CUDA( cudaGetLastError() );
+    return B2FWN_OK;
+}
+
+int marchingCubesDevice( const float* dVolume, const int32_t dims[3], const b2fwn_mc_params& p, McResult& out,
+                         cudaStream_t st, uint64_t* launches, cudaMemPool_t pool, int layersPerSlab )
+{
+    const size_t layer = (size_t)std::max( dims[0], 0 ) * std::max( dims[1], 0 );
+    return marchingCubesSlabs( [&]( int z0, int, const float** d ) { *d = dVolume + (size_t)z0 * layer; return B2FWN_OK; }, dims, p, layersPerSlab,
+                               0, dims[2], 0, 0, out, st, launches, pool );
 }
 
 } // namespace b2

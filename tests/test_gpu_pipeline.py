@@ -295,3 +295,44 @@ def test_suggest_voxel_size_and_malformed_triangulation(torus):
     # device forms refuse a null output
     with pytest.raises(mb.B2Error):
         fwn.calc_from_grid_with_distances_device((8, 8, 8), mb.make_basis_xf((-3, -3, -1), 0.5), 0)
+
+
+# ---- marching cubes by slabs and over several devices (the reference's MarchingCubesByParts, in HBM) ------------------------
+@pytest.mark.parametrize("close_holes", [True, False])
+def test_offset_mesh_in_slabs_is_identical_to_one_shot(torus, close_holes):
+    """slabs of 1, 2, 3, 5 ... owner layers (each with the two layers after it) must give the one-shot TriMesh bit for bit:
+    vertices, their order, triangles, their order -- with NaN outside the band (close_holes False) and without"""
+    _p, _t, fwn = torus
+    want_v, want_t, info = fwn.mc_offset_mesh(0.15, 0.11, close_holes=close_holes)
+    assert len(want_t) > 1000
+    for n in (1, 2, 3, 5, 16, info["dims"][2] - 1, info["dims"][2] + 7):
+        v, t, i2 = fwn.mc_offset_mesh(0.15, 0.11, close_holes=close_holes, max_layers_per_slab=n)
+        assert i2["dims"] == info["dims"] and (i2["n_verts"], i2["n_tris"]) == (len(want_v), len(want_t)), n
+        assert v.tobytes() == want_v.tobytes() and t.tobytes() == want_t.tobytes(), n
+    # the half-edge tables of a slabbed result
+    he, epv, epf = fwn.build_topology()
+    _check_tables(want_t, len(want_v), he, epv, epf)
+
+
+def test_offset_mesh_over_several_devices():
+    L = mb.load_library()
+    if L.b2fwn_device_count() < 2:
+        pytest.skip("one CUDA device")
+    pts, tris = meshgen.make_torus(2, 1, 96, 48)
+    n = min(L.b2fwn_device_count(), 4)
+    one = mb.FastWindingNumber(pts, tris)
+    many = mb.FastWindingNumber(pts, tris, devices=list(range(n)))
+    for kw in (dict(), dict(max_layers_per_slab=3), dict(close_holes=False)):
+        want_v, want_t, info = one.mc_offset_mesh(-0.1, 0.09, **kw)
+        v, t, i2 = many.mc_offset_mesh(-0.1, 0.09, **kw)
+        assert i2["dims"] == info["dims"]
+        assert v.tobytes() == want_v.tobytes() and t.tobytes() == want_t.tobytes(), kw
+    he, epv, epf = many.build_topology()  # triangles gathered from every device
+    _check_tables(want_t, len(want_v), he, epv, epf)
+    # a plain marching-cubes call afterwards forgets the multi-device result
+    vol = np.linspace(-1, 1, 8 * 8 * 8, dtype=np.float32)
+    v1, t1 = many.marching_cubes(vol, (8, 8, 8), (0, 0, 0), 1.0, 0.0)
+    v2, t2 = one.marching_cubes(vol, (8, 8, 8), (0, 0, 0), 1.0, 0.0)
+    assert v1.tobytes() == v2.tobytes() and t1.tobytes() == t2.tobytes()
+    one.close()
+    many.close()
