@@ -97,6 +97,7 @@ void destroyCtx( b2fwn_ctx* h )
     cudaDeviceSynchronize();
     freeTree( h->tree );
     freeMc( h->mc );
+    freeMcWorkspace( h->mcWork );
     freeTopology( h->topo );
     for ( int s = 0; s < 2; ++s )
     {
@@ -959,15 +960,16 @@ int b2fwn_mc_offset_mesh( b2fwn_handle h, const b2fwn_offset_params* p, b2fwn_of
         auto fail = [&]( int rc ) { R.rc = rc; R.err = b2fwn_last_error(); };
         if ( cudaSetDevice( c->device ) != cudaSuccess ) { fail( cudaFail( cudaGetLastError(), "cudaSetDevice" ) ); return; }
         // values 4 B x (n + 2) layers, codes 1 B x (n + 1) layers, segment totals and scan scratch ~ 0.3 B: 5.5 B per voxel of a slab
-        const size_t budget = safeMemoryLimit( c->device );
+        freeMc( c->mc ); // the previous result goes before the budget is taken
+        const size_t budget = safeMemoryLimit( c->device ) + c->scratchFloats[0] * sizeof( float ) + c->mcWork.codeBytes
+                              + 2 * c->mcWork.segEntries * sizeof( uint32_t );
         int n = R.z1 - R.z0;
         const size_t fit = layer ? (size_t)( (double)budget / ( 5.5 * (double)layer ) ) : (size_t)n;
         if ( fit < (size_t)n + 2 ) n = fit > 3 ? (int)fit - 2 : 1;
         if ( cap > 0 ) n = std::min( n, cap );
-        float* dBuf = nullptr;
         const size_t bufLayers = (size_t)std::min( dims[2] - R.z0, n + 2 );
-        cudaError_t ce = cudaMalloc( &dBuf, std::max<size_t>( bufLayers * layer, 1 ) * sizeof( float ) );
-        if ( ce != cudaSuccess ) { fail( cudaFail( ce, "offset: slab buffer" ) ); return; }
+        if ( int e = ensureScratch( c, 0, std::max<size_t>( bufLayers * layer, 1 ) ) ) { fail( e ); return; }
+        float* dBuf = c->dScratch[0]; // the handle's cached slot: no 34-GB cudaMalloc / cudaFree per call
         cudaEvent_t e0 = nullptr, e1 = nullptr, s0 = nullptr, s1 = nullptr;
         cudaEventCreate( &e0 ); cudaEventCreate( &e1 ); cudaEventCreate( &s0 ); cudaEventCreate( &s1 );
         cudaEventRecord( e0, c->stream );
@@ -982,14 +984,13 @@ int b2fwn_mc_offset_mesh( b2fwn_handle h, const b2fwn_offset_params* p, b2fwn_of
             R.sdfMs += ms;
             *dl = dBuf;
             return B2FWN_OK;
-        }, dims, mp, n, R.z0, R.z1, 0, 0, c->mc, c->stream, &c->stats.kernel_launches, c->tree.pool );
+        }, dims, mp, n, R.z0, R.z1, 0, 0, c->mc, c->stream, &c->stats.kernel_launches, &c->mcWork );
         cudaEventRecord( e1, c->stream );
         cudaEventSynchronize( e1 );
         float ms = 0;
         cudaEventElapsedTime( &ms, e0, e1 );
         R.totalMs = ms;
         cudaEventDestroy( e0 ); cudaEventDestroy( e1 ); cudaEventDestroy( s0 ); cudaEventDestroy( s1 );
-        cudaFree( dBuf );
         if ( rc ) fail( rc );
     };
     {
@@ -1102,7 +1103,7 @@ int b2fwn_marching_cubes( b2fwn_handle h, const float* volume, int32_t onDevice,
         dVol = dTmp;
     }
     KernelTimer tm( h );
-    const int rc = marchingCubesDevice( dVol, dims, *p, h->mc, h->stream, &h->stats.kernel_launches, h->tree.pool );
+    const int rc = marchingCubesDevice( dVol, dims, *p, h->mc, h->stream, &h->stats.kernel_launches, &h->mcWork );
     tm.stop();
     cudaStreamSynchronize( h->stream );
     if ( dTmp ) cudaFree( dTmp );

@@ -15,6 +15,7 @@ struct b2fwn_ctx
     b2::DeviceTree tree;
     b2fwn_stats stats{};
     b2::McResult mc;
+    b2::McWorkspace mcWork;            // scratch of the mesher, grow-only, released by b2fwn_destroy or when memory runs short
     b2::TopoResult topo;
     // scratch for the host-pointer entry points
     float* dScratch[2] = { nullptr, nullptr };

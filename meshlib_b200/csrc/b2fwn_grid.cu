@@ -683,9 +683,12 @@ __device__ __forceinline__ void fwnInner( const int i, const int link, const flo
 }
 
 // walks the tree for the NV voxels of every lane; pc, rad = centre and padded radius of all voxels of the warp
-template <int NV>
+// SKIP: skip[v] = face whose exact solid angle voxel v leaves out (calcFromVector's skipFace, calcSelfIntersections' own face:
+// MRDipole.cpp:113-116 -- the leaf's dipole test still runs, only the triangle term is dropped)
+template <int NV, bool SKIP = false>
 __device__ __forceinline__ void fwnWalk( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris, const int N, const float betaSq,
-                                         const float3 ( &p )[NV], const float3 pc, const float rad, float ( &sum )[NV], int ( &fR )[NV] )
+                                         const float3 ( &p )[NV], const float3 pc, const float rad, float ( &sum )[NV], int ( &fR )[NV],
+                                         const int* skip = nullptr )
 {
     int i = __reduce_min_sync( FULL, minOf( fR ) );
     while ( i < N )
@@ -724,7 +727,8 @@ __device__ __forceinline__ void fwnWalk( const TravNode* __restrict__ nodes, con
                 const float4 ta = __ldg( tp ), tb = __ldg( tp + 1 ), tc = __ldg( tp + 2 );
 #pragma unroll
                 for ( int v = 0; v < NV; ++v )
-                    if ( go[v] ) sum[v] = FA( sum[v], triangleSolidAngle( p[v], ta, tb, tc ) ); // (all NV angles + predicated adds measured slower)
+                    if ( go[v] && !( SKIP && __float_as_int( ta.w ) == skip[v] ) )
+                        sum[v] = FA( sum[v], triangleSolidAngle( p[v], ta, tb, tc ) ); // (all NV angles + predicated adds measured slower)
             }
         }
         i = max( __reduce_min_sync( FULL, minOf( fR ) ), i + 1 );
@@ -826,6 +830,102 @@ __global__ void __launch_bounds__( GRID_TB, MINB ) kGridFwn5( const TravNode* __
                     if ( B.x0 + v < P.dx ) po[B.id + v] = res[v];
             }
         }
+    }
+}
+
+// ---- winding numbers of query vectors, warp-cooperative ---------------------------------------------------------------------
+// calcFromVector / calcSelfIntersections for large vectors: the queries arrive in an order in which neighbours in the vector are
+// neighbours in space (Morton order of the points, b2fwn_kernels.cu; leaf order of the faces), a warp takes 32 x QV consecutive
+// ones as its "brick" and walks the tree for them with the grid kernel's code: one fetch and one all-near test per node for 128
+// queries, per-query resume indices, the reference's exactly rounded decisions.  One thread per query (kFwnVector / kFwnFaces)
+// walked every node once per query, each lane its own way: C2 4.3 ms, C4 16.7 ms (r02).
+constexpr int QV = 4;
+
+// order: query index of slot t (nullptr: t itself); FACES: the queries are the centres of the leaf triangles (slot t = leaf t),
+// each skipping its own face, bits set where w < 0 || w > 1 (MRFastWindingNumber.cpp:40-52)
+template <bool FACES>
+__global__ void __launch_bounds__( GRID_TB, 8 ) kFwnQueriesWarp( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris, const int N,
+    const float* __restrict__ pts, const int32_t* __restrict__ faces, const uint32_t* __restrict__ order, const size_t n, const float betaSq,
+    const int skipFace, float* __restrict__ outW, uint32_t* __restrict__ outBits32 )
+{
+    const unsigned lane = threadIdx.x & 31;
+    const size_t base = ( blockIdx.x * (size_t)( GRID_TB / 32 ) + ( threadIdx.x >> 5 ) ) * ( 32 * QV );
+    if ( base >= n ) return;
+    float3 p[QV];
+    float sum[QV];
+    int fR[QV], skip[QV];
+    size_t idx[QV];
+    float lo[3] = { FLT_MAX, FLT_MAX, FLT_MAX }, hi[3] = { -FLT_MAX, -FLT_MAX, -FLT_MAX };
+#pragma unroll
+    for ( int v = 0; v < QV; ++v )
+    {
+        const size_t t = base + (size_t)v * 32 + lane;
+        const bool valid = t < n;
+        idx[v] = 0; skip[v] = skipFace; p[v] = make_float3( 0.f, 0.f, 0.f );
+        if ( valid )
+        {
+            if ( FACES )
+            {
+                const size_t f = (size_t)__float_as_int( __ldg( reinterpret_cast<const float4*>( tris + t ) ).w );
+                const int32_t ia = faces[3 * f], ib = faces[3 * f + 1], ic = faces[3 * f + 2];
+                const float third = 1 / 3.0f; // triCenter: (1/3.0f) * (a + b + c), MRMeshMath.cpp:119-124
+                p[v].x = FM( third, FA( FA( pts[3 * (size_t)ia], pts[3 * (size_t)ib] ), pts[3 * (size_t)ic] ) );
+                p[v].y = FM( third, FA( FA( pts[3 * (size_t)ia + 1], pts[3 * (size_t)ib + 1] ), pts[3 * (size_t)ic + 1] ) );
+                p[v].z = FM( third, FA( FA( pts[3 * (size_t)ia + 2], pts[3 * (size_t)ib + 2] ), pts[3 * (size_t)ic + 2] ) );
+                idx[v] = f; skip[v] = (int)f;
+            }
+            else
+            {
+                idx[v] = order ? order[t] : t;
+                p[v] = make_float3( pts[3 * idx[v]], pts[3 * idx[v] + 1], pts[3 * idx[v] + 2] );
+            }
+            const float c[3] = { p[v].x, p[v].y, p[v].z };
+#pragma unroll
+            for ( int k = 0; k < 3; ++k )
+                if ( fabsf( c[k] ) <= FLT_MAX ) { lo[k] = fminf( lo[k], c[k] ); hi[k] = fmaxf( hi[k], c[k] ); }
+        }
+        // a query with a non-finite coordinate gets NaN from the reference's arithmetic (every dd is NaN or inf: the terms are);
+        // it is kept out of the walk and of the warp's ball, its sum starts and stays NaN
+        const bool finite = fabsf( p[v].x ) <= FLT_MAX && fabsf( p[v].y ) <= FLT_MAX && fabsf( p[v].z ) <= FLT_MAX;
+        sum[v] = finite ? 0.f : __int_as_float( 0x7fc00000 );
+        fR[v] = valid && finite ? 0 : INT_MAX;
+    }
+    // ball of the warp's queries: centre of their box, radius to the farthest one (padded like the grid bricks')
+    float3 pc;
+    {
+        float c[3];
+#pragma unroll
+        for ( int k = 0; k < 3; ++k )
+        {
+            float a = lo[k], b = hi[k];
+#pragma unroll
+            for ( int o = 16; o > 0; o >>= 1 ) { a = fminf( a, __shfl_xor_sync( FULL, a, o ) ); b = fmaxf( b, __shfl_xor_sync( FULL, b, o ) ); }
+            c[k] = 0.5f * ( a + b );
+        }
+        pc = make_float3( c[0], c[1], c[2] );
+    }
+    float rad = 0.f;
+#pragma unroll
+    for ( int v = 0; v < QV; ++v )
+        if ( fR[v] == 0 )
+        {
+            const float ex = p[v].x - pc.x, ey = p[v].y - pc.y, ez = p[v].z - pc.z;
+            rad = fmaxf( rad, ex * ex + ey * ey + ez * ez );
+        }
+    rad = sqrtf( __uint_as_float( __reduce_max_sync( FULL, __float_as_uint( rad ) ) ) ) * 1.00001f;
+    if ( !( pc.x == pc.x && pc.y == pc.y && pc.z == pc.z ) || !( rad < FLT_MAX ) ) { pc = make_float3( 0.f, 0.f, 0.f ); rad = FLT_MAX; } // no all-near shortcut then
+
+    fwnWalk<QV, true>( nodes, tris, N, betaSq, p, pc, rad, sum, fR, skip );
+
+    constexpr float INV_4PI = 1.0f / ( 4 * 3.14159265358979323846f ); // MRDipole.cpp:126
+#pragma unroll
+    for ( int v = 0; v < QV; ++v )
+    {
+        const size_t t = base + (size_t)v * 32 + lane;
+        if ( t >= n ) continue;
+        const float w = FM( INV_4PI, sum[v] );
+        if ( outW ) outW[idx[v]] = w;
+        if ( FACES && outBits32 && ( w < 0 || w > 1 ) ) atomicOr( outBits32 + ( idx[v] >> 5 ), 1u << ( idx[v] & 31 ) );
     }
 }
 
@@ -1418,6 +1518,24 @@ int launchSdfGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf,
                    int zBegin, int zEnd, float* dOut, cudaStream_t st, uint64_t* launches, const ZChunks* zc, const PeerOut* peers )
 {
     return launchGrid<1>( t, dims, xf, opt.winding_number_beta, &opt, zBegin, zEnd, zc, peers, dOut, st, launches );
+}
+
+// warp-cooperative winding numbers of a query vector in a spatially coherent order (b2fwn_kernels.cu decides when to use it)
+int launchFwnQueriesWarp( const DeviceTree& t, const float* dPts, const uint32_t* dOrder, size_t n, bool faces, float beta, int32_t skipFace,
+                          float* dOutW, uint32_t* dBits32, cudaStream_t st, uint64_t* launches )
+{
+    if ( n == 0 || t.numNodes == 0 ) return B2FWN_OK;
+    const size_t warps = ( n + 32 * QV - 1 ) / ( 32 * QV );
+    const size_t blocks = ( warps + GRID_TB / 32 - 1 ) / ( GRID_TB / 32 );
+    if ( blocks > 0x7FFFFFFFull ) { setError( "too many queries for one launch" ); return B2FWN_ERR_INVALID; }
+    if ( faces )
+        kFwnQueriesWarp<true><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, (int)t.numNodes, t.points, t.tris, nullptr, n, beta * beta, -1, dOutW, dBits32 );
+    else
+        kFwnQueriesWarp<false><<<(unsigned)blocks, GRID_TB, 0, st>>>( t.nodes, t.leafTris, (int)t.numNodes, dPts, nullptr, dOrder, n, beta * beta,
+                                                                      skipFace < 0 ? -1 : skipFace, dOutW, nullptr );
+    if ( launches ) ++*launches;
+    B2_CUDA( cudaGetLastError() );
+    return B2FWN_OK;
 }
 
 // In-place sign of a distance slab: value -> -value where the winding number of the voxel exceeds the threshold

@@ -113,6 +113,10 @@ int launchFwnVector( const DeviceTree& t, const float* dPts, size_t n, float bet
                      cudaStream_t stream, uint64_t* launches );
 int launchFwnFaces( const DeviceTree& t, float beta, float* dOutWOrNull, uint64_t* dBits, cudaStream_t stream,
                     uint64_t* launches );
+// warp-cooperative form for large vectors in a spatially coherent order (b2fwn_grid.cu): dOrder = query index per slot (Morton order)
+// or nullptr; faces: the queries are the centres of the leaf triangles, in leaf order, each skipping its own face
+int launchFwnQueriesWarp( const DeviceTree& t, const float* dPts, const uint32_t* dOrder, size_t n, bool faces, float beta, int32_t skipFace,
+                          float* dOutW, uint32_t* dBits32, cudaStream_t stream, uint64_t* launches );
 // z-interleaved layer set of one launch (multi-GPU partition): chunks of `chunk` consecutive layers, `stride` layers apart
 struct ZChunks
 {
@@ -160,16 +164,25 @@ struct McResult
     int32_t* dTris = nullptr;  // nTris*3
     uint64_t nVerts = 0, nTris = 0;
 };
+// classification codes, segment totals and scan scratch of the mesher: grow-only, kept by the handle between slabs and calls
+// (r02, 2050^3: cudaMalloc / cudaFree of 10 GB of scratch per call cost more than the two kernels -- 170 .. 480 ms against ~110 ms)
+struct McWorkspace
+{
+    uint8_t* dCode = nullptr; size_t codeBytes = 0;
+    uint32_t *dSegV = nullptr, *dSegT = nullptr; size_t segEntries = 0;
+    void* dTmp = nullptr; size_t tmpBytes = 0;
+};
+void freeMcWorkspace( McWorkspace& w );
 // layersPerSlab > 0: the volume is meshed in slabs of that many owner layers (identical output; bounds the scratch memory)
 int marchingCubesDevice( const float* dVolume, const int32_t dims[3], const b2fwn_mc_params& p, McResult& out,
-                         cudaStream_t stream, uint64_t* launches, cudaMemPool_t pool = nullptr, int layersPerSlab = 0 );
+                         cudaStream_t stream, uint64_t* launches, McWorkspace* work = nullptr, int layersPerSlab = 0 );
 // The same for a volume that is produced slab by slab: src( z0, z1, &dPtr ) must make the values of the layers [z0, z1) of the grid
 // available on the device (dPtr = layer z0) until its next call; it is asked for the owner layers of a slab plus the two layers
 // after them.  Meshes the owner layers [zBegin, zEnd); vertex / triangle ids start at baseV / baseT (several devices each mesh
 // a z-range of one grid: the bases are the exclusive prefix of their counts).
 using McVolumeSource = std::function<int( int z0, int z1, const float** dLayers )>;
 int marchingCubesSlabs( const McVolumeSource& src, const int32_t dims[3], const b2fwn_mc_params& p, int layersPerSlab, int zBegin, int zEnd,
-                        uint32_t baseV, uint32_t baseT, McResult& out, cudaStream_t stream, uint64_t* launches, cudaMemPool_t pool );
+                        uint32_t baseV, uint32_t baseT, McResult& out, cudaStream_t stream, uint64_t* launches, McWorkspace* work );
 void freeMc( McResult& r );
 // adds base to every vertex id of the triangles (a device's share of a multi-device mesh gets its global ids)
 int marchingCubesAddBase( McResult& r, int32_t base, cudaStream_t stream, uint64_t* launches );

@@ -143,9 +143,18 @@ int launchFwnVector( const DeviceTree& t, const float* dPts, size_t n, float bet
         order = vals2;
         if ( launches ) *launches += 5; // keys + 4 radix passes
     }
-    kFwnVector<<<(unsigned)blocks, 128, 0, st>>>( t.nodes, t.leafTris, (int)t.numNodes, dPts, n, beta * beta,
-                                                  skipFace < 0 ? -1 : skipFace, dOut, order );
-    if ( launches ) ++*launches;
+    // sorted vectors: 32 x 4 neighbours per warp walk together (b2fwn_grid.cu); B2FWN_QUERY_THREADS=1: one thread per query
+    static const bool perThread = getenv( "B2FWN_QUERY_THREADS" ) && atoi( getenv( "B2FWN_QUERY_THREADS" ) );
+    if ( order && !perThread )
+    {
+        if ( int e = launchFwnQueriesWarp( t, dPts, order, n, false, beta, skipFace, dOut, nullptr, st, launches ) ) return e;
+    }
+    else
+    {
+        kFwnVector<<<(unsigned)blocks, 128, 0, st>>>( t.nodes, t.leafTris, (int)t.numNodes, dPts, n, beta * beta,
+                                                      skipFace < 0 ? -1 : skipFace, dOut, order );
+        if ( launches ) ++*launches;
+    }
     if ( scratch ) B2_CUDA( cudaFreeAsync( scratch, st ) );
     B2_CUDA( cudaGetLastError() );
     return B2FWN_OK;
@@ -159,6 +168,9 @@ int launchFwnFaces( const DeviceTree& t, float beta, float* dOutW, uint64_t* dBi
     if ( dOutW ) B2_CUDA( cudaMemsetAsync( dOutW, 0, n * sizeof( float ), st ) );
     const size_t L = t.numLeaves;
     if ( L == 0 ) return B2FWN_OK;
+    static const bool perThread = getenv( "B2FWN_QUERY_THREADS" ) && atoi( getenv( "B2FWN_QUERY_THREADS" ) );
+    if ( L >= ( 1u << 15 ) && !perThread )
+        return launchFwnQueriesWarp( t, nullptr, nullptr, L, true, beta, -1, dOutW, reinterpret_cast<uint32_t*>( dBits ), st, launches );
     kFwnFaces<<<(unsigned)( ( L + 127 ) / 128 ), 128, 0, st>>>( t.nodes, t.leafTris, (int)t.numNodes, t.points, t.tris, L, beta * beta, dOutW,
                                                               reinterpret_cast<uint32_t*>( dBits ) );
     if ( launches ) ++*launches;

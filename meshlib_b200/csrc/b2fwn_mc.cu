@@ -389,6 +389,12 @@ void freeMc( McResult& r )
     r = McResult{};
 }
 
+void freeMcWorkspace( McWorkspace& w )
+{
+    cudaFree( w.dCode ); cudaFree( w.dSegV ); cudaFree( w.dSegT ); cudaFree( w.dTmp );
+    w = McWorkspace{};
+}
+
 namespace
 {
 
@@ -396,20 +402,18 @@ namespace
 struct McPass
 {
     McGrid g{};
-    uint8_t* dCode = nullptr;
-    uint32_t *dSegV = nullptr, *dSegT = nullptr;
-    void* dTmp = nullptr;
-    cudaMemPool_t pool = nullptr;
+    McWorkspace* w = nullptr;
     uint32_t nV = 0, nT = 0;
 };
 
-void mcRelease( McPass& ps, cudaStream_t st )
+cudaError_t growBuffer( void** p, size_t& have, size_t need )
 {
-    void* all[4] = { ps.dCode, ps.dSegV, ps.dSegT, ps.dTmp };
-    for ( void* q : all )
-        if ( q ) { if ( ps.pool ) cudaFreeAsync( q, st ); else cudaFree( q ); }
-    if ( ps.pool ) { cudaStreamSynchronize( st ); cudaMemPoolTrimTo( ps.pool, (size_t)1 << 30 ); } // keep at most 1 GiB cached
-    ps.dCode = nullptr; ps.dSegV = ps.dSegT = nullptr; ps.dTmp = nullptr;
+    if ( need <= have ) return cudaSuccess;
+    cudaFree( *p );
+    *p = nullptr; have = 0;
+    const cudaError_t e = cudaMalloc( p, need );
+    if ( e == cudaSuccess ) have = need;
+    return e;
 }
 
 McGrid makeGrid( const int32_t dims[3], const b2fwn_mc_params& p, int zv0, int zo0, int zo1 )
@@ -436,32 +440,33 @@ McGrid makeGrid( const int32_t dims[3], const b2fwn_mc_params& p, int zv0, int z
 int mcCount( const float* dVol, McPass& ps, cudaStream_t st, uint64_t* launches )
 {
     McGrid& g = ps.g;
+    McWorkspace& w = *ps.w;
     const size_t S = ( g.total + 31 ) / 32;
     if ( S + 1 > 0x7FFFFFFFull ) { setError( "volume too large for one marching-cubes pass" ); return B2FWN_ERR_INVALID; }
-    // scratch from the handle's stream-ordered pool: cached between calls, no device-wide synchronisation per allocation
-    // (r02: of 6.9 ms for marching cubes at 512^3 the two kernels took 2.6 ms, cudaMalloc / cudaFree most of the rest)
-    // -- for slabs whose scratch fits the part of the pool that stays cached (1 GiB); larger ones pay cudaMalloc once per call
-    // either way (c5_offset, 2050^3: 225 ms with plain allocations, 307 ms through a pool that is trimmed after every call)
-    if ( g.total + 2 * ( S + 1 ) * sizeof( uint32_t ) > ( (size_t)1 << 30 ) - ( (size_t)64 << 20 ) ) ps.pool = nullptr;
-    auto alloc = [&]( void** ptr, size_t bytes ) { return ps.pool ? cudaMallocFromPoolAsync( ptr, bytes, ps.pool, st ) : cudaMalloc( ptr, bytes ); };
-#define MC_TRY( expr ) do { cudaError_t _e = ( expr ); if ( _e != cudaSuccess ) { mcRelease( ps, st ); return cudaFail( _e, #expr ); } } while ( 0 )
-    MC_TRY( alloc( (void**)&ps.dCode, ( g.total + 31 ) & ~(size_t)31 ) );
-    MC_TRY( alloc( (void**)&ps.dSegV, ( S + 1 ) * sizeof( uint32_t ) ) );
-    MC_TRY( alloc( (void**)&ps.dSegT, ( S + 1 ) * sizeof( uint32_t ) ) );
-    MC_TRY( cudaMemsetAsync( ps.dSegV + S, 0, sizeof( uint32_t ), st ) );
-    MC_TRY( cudaMemsetAsync( ps.dSegT + S, 0, sizeof( uint32_t ), st ) );
+#define MC_TRY( expr ) do { cudaError_t _e = ( expr ); if ( _e != cudaSuccess ) return cudaFail( _e, #expr ); } while ( 0 )
+    MC_TRY( growBuffer( (void**)&w.dCode, w.codeBytes, ( g.total + 31 ) & ~(size_t)31 ) );
+    if ( S + 1 > w.segEntries )
+    {
+        cudaFree( w.dSegV ); cudaFree( w.dSegT );
+        w.dSegV = w.dSegT = nullptr; w.segEntries = 0;
+        MC_TRY( cudaMalloc( &w.dSegV, ( S + 1 ) * sizeof( uint32_t ) ) );
+        MC_TRY( cudaMalloc( &w.dSegT, ( S + 1 ) * sizeof( uint32_t ) ) );
+        w.segEntries = S + 1;
+    }
+    MC_TRY( cudaMemsetAsync( w.dSegV + S, 0, sizeof( uint32_t ), st ) );
+    MC_TRY( cudaMemsetAsync( w.dSegT + S, 0, sizeof( uint32_t ), st ) );
     const size_t blocks = ( g.total + MC_TB - 1 ) / MC_TB;
-    if ( blocks > 0x7FFFFFFFull ) { mcRelease( ps, st ); setError( "volume too large for one launch" ); return B2FWN_ERR_INVALID; }
-    kMcClassify<<<(unsigned)blocks, MC_TB, 0, st>>>( dVol, g, ps.dCode, ps.dSegV, ps.dSegT );
+    if ( blocks > 0x7FFFFFFFull ) { setError( "volume too large for one launch" ); return B2FWN_ERR_INVALID; }
+    kMcClassify<<<(unsigned)blocks, MC_TB, 0, st>>>( dVol, g, w.dCode, w.dSegV, w.dSegT );
     size_t tmpBytes = 0;
-    MC_TRY( cub::DeviceScan::ExclusiveSum( nullptr, tmpBytes, ps.dSegV, ps.dSegV, (int)( S + 1 ), st ) );
-    MC_TRY( alloc( &ps.dTmp, tmpBytes ) );
-    MC_TRY( cub::DeviceScan::ExclusiveSum( ps.dTmp, tmpBytes, ps.dSegV, ps.dSegV, (int)( S + 1 ), st ) );
-    MC_TRY( cub::DeviceScan::ExclusiveSum( ps.dTmp, tmpBytes, ps.dSegT, ps.dSegT, (int)( S + 1 ), st ) );
+    MC_TRY( cub::DeviceScan::ExclusiveSum( nullptr, tmpBytes, w.dSegV, w.dSegV, (int)( S + 1 ), st ) );
+    MC_TRY( growBuffer( &w.dTmp, w.tmpBytes, tmpBytes ) );
+    MC_TRY( cub::DeviceScan::ExclusiveSum( w.dTmp, tmpBytes, w.dSegV, w.dSegV, (int)( S + 1 ), st ) );
+    MC_TRY( cub::DeviceScan::ExclusiveSum( w.dTmp, tmpBytes, w.dSegT, w.dSegT, (int)( S + 1 ), st ) );
     // what the owners yield = the prefix at the first slot after them (extraBase is a multiple of 32)
     const size_t sOwn = g.extraBase / 32;
-    MC_TRY( cudaMemcpyAsync( &ps.nV, ps.dSegV + sOwn, sizeof( uint32_t ), cudaMemcpyDeviceToHost, st ) );
-    MC_TRY( cudaMemcpyAsync( &ps.nT, ps.dSegT + sOwn, sizeof( uint32_t ), cudaMemcpyDeviceToHost, st ) );
+    MC_TRY( cudaMemcpyAsync( &ps.nV, w.dSegV + sOwn, sizeof( uint32_t ), cudaMemcpyDeviceToHost, st ) );
+    MC_TRY( cudaMemcpyAsync( &ps.nT, w.dSegT + sOwn, sizeof( uint32_t ), cudaMemcpyDeviceToHost, st ) );
     MC_TRY( cudaStreamSynchronize( st ) );
     if ( launches ) *launches += 5; // classify + 2 x (cub scan = 2 kernels)
     return B2FWN_OK;
@@ -473,7 +478,7 @@ int mcEmit( const float* dVol, McPass& ps, float* dVerts, int32_t* dTris, cudaSt
     if ( ps.nV || ps.nT )
     {
         const size_t blocks = ( ps.g.nOwn + MC_TB - 1 ) / MC_TB;
-        kMcEmit<<<(unsigned)blocks, MC_TB, 0, st>>>( dVol, ps.g, ps.dCode, ps.dSegV, ps.dSegT, dVerts, dTris );
+        kMcEmit<<<(unsigned)blocks, MC_TB, 0, st>>>( dVol, ps.g, ps.w->dCode, ps.w->dSegV, ps.w->dSegT, dVerts, dTris );
         if ( launches ) ++*launches;
     }
     MC_TRY( cudaGetLastError() );
@@ -505,8 +510,11 @@ int mcReserve( McResult& out, size_t& capV, size_t& capT, size_t needV, size_t n
 }
 
 int marchingCubesSlabs( const McVolumeSource& src, const int32_t dims[3], const b2fwn_mc_params& p, int layersPerSlab, int zBegin, int zEnd,
-                        uint32_t baseV, uint32_t baseT, McResult& out, cudaStream_t st, uint64_t* launches, cudaMemPool_t pool )
+                        uint32_t baseV, uint32_t baseT, McResult& out, cudaStream_t st, uint64_t* launches, McWorkspace* work )
 {
+    McWorkspace local; // without a handle's workspace: scratch of this call only
+    struct Guard { McWorkspace* w; ~Guard() { if ( w ) freeMcWorkspace( *w ); } } guard{ work ? nullptr : &local };
+    if ( !work ) work = &local;
     freeMc( out );
     if ( dims[0] <= 0 || dims[1] <= 0 || dims[2] <= 0 ) return B2FWN_OK; // VolumeMesher::run :383-384
     if ( dims[2] <= 1 ) { setError( "a part must have at least two Z slices" ); return B2FWN_ERR_INVALID; } // :443-444
@@ -522,16 +530,15 @@ int marchingCubesSlabs( const McVolumeSource& src, const int32_t dims[3], const 
         const float* dVol = nullptr;
         if ( int e = src( z, zv1, &dVol ) ) return e; // values of the layers [z, zv1), pointer to layer z
         McPass ps;
-        ps.pool = pool;
+        ps.w = work;
         ps.g = makeGrid( dims, p, z, z, zo1 );
         if ( int e = mcCount( dVol, ps, st, launches ) ) return e;
-        if ( (uint64_t)baseV + out.nVerts + ps.nV > 0x7FFFFFFFull ) { mcRelease( ps, st ); setError( "more than 2^31 vertices" ); return B2FWN_ERR_INVALID; }
+        if ( (uint64_t)baseV + out.nVerts + ps.nV > 0x7FFFFFFFull ) { setError( "more than 2^31 vertices" ); return B2FWN_ERR_INVALID; }
         ps.g.baseV = baseV + (uint32_t)out.nVerts;
         ps.g.baseT = baseT + (uint32_t)out.nTris;
-        if ( int e = mcReserve( out, capV, capT, out.nVerts + ps.nV, out.nTris + ps.nT, st ) ) { mcRelease( ps, st ); return e; }
+        if ( int e = mcReserve( out, capV, capT, out.nVerts + ps.nV, out.nTris + ps.nT, st ) ) return e;
         const int rc = mcEmit( dVol, ps, out.dVerts + 3 * out.nVerts, out.dTris + 3 * out.nTris, st, launches );
         const cudaError_t se = cudaStreamSynchronize( st );
-        mcRelease( ps, st );
         if ( rc ) return rc;
         if ( se != cudaSuccess ) return cudaFail( se, "marching cubes slab" );
         out.nVerts += ps.nV; out.nTris += ps.nT;
@@ -559,11 +566,11 @@ int marchingCubesAddBase( McResult& r, int32_t base, cudaStream_t st, uint64_t* 
 }
 
 int marchingCubesDevice( const float* dVolume, const int32_t dims[3], const b2fwn_mc_params& p, McResult& out,
-                         cudaStream_t st, uint64_t* launches, cudaMemPool_t pool, int layersPerSlab )
+                         cudaStream_t st, uint64_t* launches, McWorkspace* work, int layersPerSlab )
 {
     const size_t layer = (size_t)std::max( dims[0], 0 ) * std::max( dims[1], 0 );
     return marchingCubesSlabs( [&]( int z0, int, const float** d ) { *d = dVolume + (size_t)z0 * layer; return B2FWN_OK; }, dims, p, layersPerSlab,
-                               0, dims[2], 0, 0, out, st, launches, pool );
+                               0, dims[2], 0, 0, out, st, launches, work );
 }
 
 } // namespace b2
