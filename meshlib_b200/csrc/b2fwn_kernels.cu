@@ -143,9 +143,12 @@ int launchFwnVector( const DeviceTree& t, const float* dPts, size_t n, float bet
         order = vals2;
         if ( launches ) *launches += 5; // keys + 4 radix passes
     }
-    // sorted vectors: 32 x 4 neighbours per warp walk together (b2fwn_grid.cu); B2FWN_QUERY_THREADS=1: one thread per query
-    static const bool perThread = getenv( "B2FWN_QUERY_THREADS" ) && atoi( getenv( "B2FWN_QUERY_THREADS" ) );
-    if ( order && !perThread )
+    // One thread per query, in Morton order.  The warp-cooperative walk of the grid kernels (32 x 4 neighbours per warp,
+    // launchFwnQueriesWarp) is kept for the faces of calcSelfIntersections, where it wins (C4: 16.7 -> 10.9 ms); for scattered
+    // points it loses (C2, 10 M random points: 5.69 ms against 4.29 ms -- the ball of 128 random neighbours is ten triangles
+    // wide, few nodes are near or far for all of them).  B2FWN_QUERY_WARPS=1 selects it here as well.
+    static const bool warps = getenv( "B2FWN_QUERY_WARPS" ) && atoi( getenv( "B2FWN_QUERY_WARPS" ) );
+    if ( order && warps )
     {
         if ( int e = launchFwnQueriesWarp( t, dPts, order, n, false, beta, skipFace, dOut, nullptr, st, launches ) ) return e;
     }
