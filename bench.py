@@ -55,11 +55,11 @@ OFFSET_WORKLOADS = {
     "c5_offset": dict(mesh=("noisy_sphere", 3162, 1581, 1e-3), voxel=2.04 / 2040.0, offset=0.005, close_holes=True),
 }
 
-# DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of ONE launch of the dominant kernel (kGridFwn5, whole grid on one
+# DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of ONE launch of the dominant kernel (kGridFwn6, whole grid on one
 # GPU) from an `ncu --set full` capture on B200; not measurable inside a timed run, so quoted from the committed capture
 NCU_TRAFFIC = {
-    "c5_band": (41.609227e9 + 34.414311e9, "profiles/r01/ncu_full_kGridFwn5_c5_band_v6.csv"),
-    "c3_band": (1.002902e9 + 0.504868e9, "profiles/r01/ncu_full_kGridDist_kGridFwn5_c3_band_v6.csv"),
+    "c5_band": (40.156268e9 + 34.851371e9, "profiles/r02/ncu_full_kGridFwn6_c5_band.csv"),
+    "c3_band": (1.002902e9 + 0.504868e9, "profiles/r01/ncu_full_kGridDist_kGridFwn5_c3_band_v6.csv (kGridFwn5, r01)"),
 }
 
 
@@ -342,8 +342,9 @@ def run_queries(args, name):
     fwn.close()
     # e2e: host mesh + host queries -> create -> call with host buffers (pageable) -> destroy
     e_steps = max(1, min(args.steps, 3))
-    t0 = time.perf_counter()
-    for _ in range(e_steps):
+    for it in range(e_steps + 1):  # the first round is a warm-up (staging ring, allocator state)
+        if it == 1:
+            t0 = time.perf_counter()
         f2 = mb.FastWindingNumber(pts, tris)
         res = f2.calc_from_vector(q) if vector else f2.calc_self_intersections()
         f2.close()
@@ -448,8 +449,9 @@ def run_offset(args, name):
     # e2e: host mesh -> create -> offset -> TriMesh on the host (pageable numpy), create + fetch + destroy inside
     fwn.close()
     e_steps = max(1, min(args.steps, 3))
-    t0 = time.perf_counter()
-    for _ in range(e_steps):
+    for it in range(e_steps + 1):  # the first round is a warm-up
+        if it == 1:
+            t0 = time.perf_counter()
         f2 = mb.FastWindingNumber(pts, tris)
         v, t, info2 = f2.mc_offset_mesh(w["offset"], w["voxel"], close_holes=w["close_holes"], fetch=True)
         f2.close()
@@ -733,14 +735,14 @@ def run_ours(args, wl):
     }
     if e2e:
         out["e2e"] = e2e
-    # roofline of the step (kGridDist + kGridFwn5, the latter ~87 % of it): FP32 pipe, per north_star; HBM figures beside it
+    # roofline of the step (kGridDist + kGridFwn6, the latter ~84 % of it): FP32 pipe, per north_star; HBM figures beside it
     out["roofline"] = {"bound": "fp32", "achieved": None, "peak": fp32_peak, "unit": "TFLOP/s", "frac": None, "traffic": None,
                        "peak_source": "FFMA micro-benchmark run on this GPU just now (b2fwn_measure_fp32_peak)",
                        "hbm": {"algorithmic_bytes_per_voxel": 4.0 + (st0.num_nodes * 64 + st0.num_leaves * 64) * world / total,
                                "peak": hbm_peak, "peak_source": hbm_src, "unit": "GB/s"}}
     if world == 1 and wl["name"] in NCU_TRAFFIC and not args.grid:
         out["roofline"]["traffic"], out["roofline"]["traffic_source"] = NCU_TRAFFIC[wl["name"]]
-        out["roofline"]["traffic_note"] = ("dominant kernel kGridFwn5 alone; its algorithmic bytes are 8 B/voxel (|d| read, signed d written) "
+        out["roofline"]["traffic_note"] = ("dominant kernel (the winding walk) alone; its algorithmic bytes are 8 B/voxel (|d| read, signed d written) "
                                            "+ one read of the tree")
     nslab0 = (dims[2] // world) * layer  # voxels of one launch (rank 0's slab)
     out["roofline"]["hbm"]["achieved"] = (4.0 * nslab0 + st0.num_nodes * 64 + st0.num_leaves * 64) / (k_ms * 1e-3) / 1e9

@@ -63,6 +63,7 @@ struct DeviceTree
     size_t numVerts = 0, numFaces = 0, numLeaves = 0, numNodes = 0;
     int depth = 0;
     float bbox[6] = { 0, 0, 0, 0, 0, 0 }; // exact box of the vertices of valid faces (min xyz, max xyz); valid iff numLeaves > 0
+    void* arena = nullptr;       // one allocation behind refNodes, refDipoles, nodes, leafTris, leafFilt, nodeDepth
     float* points = nullptr;     // numVerts*3
     int32_t* tris = nullptr;     // numFaces*3
     RefNode* refNodes = nullptr; // numNodes

@@ -17,6 +17,8 @@
 #include <thrust/iterator/counting_iterator.h>
 #include <cfloat>
 #include <cstring>
+#include <cstdlib>
+#include <algorithm>
 #include <vector>
 
 namespace b2
@@ -279,6 +281,199 @@ __global__ void kEmitLevel( uint32_t nSegs, int level, const Seg* __restrict__ s
     next[2 * (size_t)s + 1] = r;
 }
 
+// ---- the lower levels of the build, one thread block per subtree --------------------------------------------------------
+// Once the segments of a level hold at most SUB_CAP leaves, a block takes one segment and finishes its whole subtree in shared
+// memory: per level the same steps as above (segment boxes, keys, sort by (segment, k1, k2, k3, face), emit, descend), the sort
+// being a bitonic network over the block's leaves.  The global passes sort ALL leaves once per level whatever the segment sizes
+// (2.9 ms per level at 10 M leaves); for the last 10 of 24 levels this kernel replaces them.  Same comparator, same strict
+// total order, same closed-form node numbering: the tree is bit-identical (test_tree_and_dipoles_bit_exact, golden fixtures).
+constexpr int SUB_CAP = 1024;
+constexpr int SUB_TB = 256;
+
+struct SubSeg
+{
+    uint16_t first, n;
+    int32_t node;
+    uint32_t done;
+};
+
+struct SubShared
+{
+    float mn[3][SUB_CAP], mx[3][SUB_CAP];
+    float k1[SUB_CAP], k2[SUB_CAP], k3[SUB_CAP];
+    int32_t face[SUB_CAP], leaf[SUB_CAP];
+    uint32_t box[SUB_CAP][6];
+    SubSeg seg[2][SUB_CAP];
+    uint16_t segOf[SUB_CAP]; // by element
+    uint16_t ord[SUB_CAP];   // position -> element, 0xFFFF = padding
+};
+
+__device__ __forceinline__ bool subLess( const SubShared& S, unsigned a, unsigned b )
+{
+    if ( a == 0xFFFFu ) return false;
+    if ( b == 0xFFFFu ) return true;
+    if ( S.segOf[a] != S.segOf[b] ) return S.segOf[a] < S.segOf[b];
+    if ( S.k1[a] != S.k1[b] ) return S.k1[a] < S.k1[b]; // MRAABBTreeMaker.hpp:56-69
+    if ( S.k2[a] != S.k2[b] ) return S.k2[a] < S.k2[b];
+    if ( S.k3[a] != S.k3[b] ) return S.k3[a] < S.k3[b];
+    return S.face[a] < S.face[b];
+}
+
+__global__ void __launch_bounds__( SUB_TB ) kSubtrees( const Seg* __restrict__ segs, int level0, int levels, LevelKey* __restrict__ keys,
+                                                       const LeafBox* __restrict__ leaves, RefNode* __restrict__ nodes, int32_t* __restrict__ skip,
+                                                       uint8_t* __restrict__ depth, int32_t* __restrict__ leafNodeOfPos )
+{
+    extern __shared__ __align__( 16 ) unsigned char subRaw[];
+    SubShared& S = *reinterpret_cast<SubShared*>( subRaw );
+    const Seg root = segs[blockIdx.x];
+    const int n = root.n;
+    if ( n <= 0 || ( n == 1 && root.done ) ) return;
+    const int tid = threadIdx.x;
+    int P = 1;
+    while ( P < n ) P <<= 1;
+    for ( int i = tid; i < P; i += SUB_TB )
+    {
+        if ( i < n )
+        {
+            const LevelKey k = keys[root.first + i];
+            const LeafBox lb = leaves[k.leaf];
+#pragma unroll
+            for ( int c = 0; c < 3; ++c ) { S.mn[c][i] = lb.mn[c]; S.mx[c][i] = lb.mx[c]; }
+            S.face[i] = lb.face; S.leaf[i] = k.leaf;
+            S.segOf[i] = 0;
+            S.ord[i] = (uint16_t)i;
+        }
+        else S.ord[i] = 0xFFFFu;
+    }
+    if ( tid == 0 ) S.seg[0][0] = SubSeg{ 0, (uint16_t)n, root.node, (uint32_t)root.done };
+    __syncthreads();
+    int cur = 0;
+    for ( int lev = level0; lev <= levels; ++lev )
+    {
+        const int nSegs = 1 << ( lev - level0 );
+        const bool split = lev < levels;
+        if ( split )
+        {
+            for ( int i = tid; i < nSegs * 6; i += SUB_TB ) S.box[i / 6][i % 6] = ( i % 6 < 3 ) ? 0xFFFFFFFFu : 0u;
+            __syncthreads();
+            // union of the leaf boxes of every segment that will be split (makeNode_, MRAABBTreeMaker.hpp:80-83)
+            for ( int e = tid; e < n; e += SUB_TB )
+            {
+                const int sg = S.segOf[e];
+                if ( S.seg[cur][sg].n > 1 )
+                {
+#pragma unroll
+                    for ( int c = 0; c < 3; ++c ) { atomicMin( &S.box[sg][c], f2ord( S.mn[c][e] ) ); atomicMax( &S.box[sg][3 + c], f2ord( S.mx[c][e] ) ); }
+                }
+            }
+            __syncthreads();
+            // keys: findSortedBoxDims (MRBox.h:376-396) + the comparator of partitionLeaves_ (as kMakeKeys)
+            for ( int e = tid; e < n; e += SUB_TB )
+            {
+                const int sg = S.segOf[e];
+                float a1 = 0, a2 = 0, a3 = 0;
+                if ( S.seg[cur][sg].n > 1 )
+                {
+                    float ext[3]; int dim[3] = { 0, 1, 2 };
+#pragma unroll
+                    for ( int c = 0; c < 3; ++c ) ext[c] = ord2f( S.box[sg][3 + c] ) - ord2f( S.box[sg][c] );
+#pragma unroll
+                    for ( int a = 0; a + 1 < 3; ++a )
+#pragma unroll
+                        for ( int b = a + 1; b < 3; ++b )
+                            if ( ext[b] < ext[a] || ( !( ext[a] < ext[b] ) && dim[b] < dim[a] ) )
+                            {
+                                float te = ext[a]; ext[a] = ext[b]; ext[b] = te;
+                                int td = dim[a]; dim[a] = dim[b]; dim[b] = td;
+                            }
+                    float c2[3];
+#pragma unroll
+                    for ( int c = 0; c < 3; ++c ) c2[c] = S.mn[c][e] + S.mx[c][e];
+                    a1 = dim[2] == 0 ? c2[0] : dim[2] == 1 ? c2[1] : c2[2];
+                    a2 = dim[1] == 0 ? c2[0] : dim[1] == 1 ? c2[1] : c2[2];
+                    a3 = dim[0] == 0 ? c2[0] : dim[0] == 1 ? c2[1] : c2[2];
+                }
+                S.k1[e] = a1; S.k2[e] = a2; S.k3[e] = a3;
+            }
+            __syncthreads();
+            // bitonic sort of the positions by (segment, k1, k2, k3, face)
+            for ( int k = 2; k <= P; k <<= 1 )
+                for ( int j = k >> 1; j > 0; j >>= 1 )
+                {
+                    for ( int i = tid; i < P; i += SUB_TB )
+                    {
+                        const int ixj = i ^ j;
+                        if ( ixj > i )
+                        {
+                            const unsigned a = S.ord[i], b = S.ord[ixj];
+                            const bool up = ( i & k ) == 0;
+                            if ( subLess( S, b, a ) == up ) { S.ord[i] = (uint16_t)b; S.ord[ixj] = (uint16_t)a; }
+                        }
+                    }
+                    __syncthreads();
+                }
+        }
+        // nodes of this level and the segment table of the next (as kEmitLevel)
+        for ( int sidx = tid; sidx < nSegs; sidx += SUB_TB )
+        {
+            const SubSeg sg = S.seg[cur][sidx];
+            SubSeg l = { 0, 0, 0, 0 }, r = { 0, 0, 0, 0 };
+            if ( sg.n == 1 )
+            {
+                if ( !sg.done )
+                {
+                    const int e = S.ord[sg.first];
+                    RefNode nd;
+#pragma unroll
+                    for ( int c = 0; c < 3; ++c ) { nd.bmin[c] = S.mn[c][e]; nd.bmax[c] = S.mx[c][e]; }
+                    nd.l = S.face[e]; nd.r = -1; // setLeafId (MRAABBTreeNode.h:41)
+                    nodes[sg.node] = nd;
+                    skip[sg.node] = sg.node + 1;
+                    depth[sg.node] = (uint8_t)lev;
+                    leafNodeOfPos[root.first + sg.first] = sg.node;
+                }
+                l = SubSeg{ sg.first, 1, sg.node, 1 };
+            }
+            else if ( sg.n > 1 )
+            {
+                const int nl = sg.n / 2; // midLeaf = first + n/2 (MRAABBTreeMaker.hpp:71)
+                RefNode nd;
+#pragma unroll
+                for ( int c = 0; c < 3; ++c ) { nd.bmin[c] = ord2f( S.box[sidx][c] ); nd.bmax[c] = ord2f( S.box[sidx][3 + c] ); }
+                nd.l = sg.node + 1;
+                nd.r = sg.node + 2 * nl; // root + 1 + getNumNodes(leftNumLeaves) (MRAABBTreeMaker.hpp:88-89)
+                nodes[sg.node] = nd;
+                skip[sg.node] = sg.node + 2 * sg.n - 1;
+                depth[sg.node] = (uint8_t)lev;
+                l = SubSeg{ sg.first, (uint16_t)nl, sg.node + 1, 0 };
+                r = SubSeg{ (uint16_t)( sg.first + nl ), (uint16_t)( sg.n - nl ), sg.node + 2 * nl, 0 };
+            }
+            if ( split ) { S.seg[cur ^ 1][2 * sidx] = l; S.seg[cur ^ 1][2 * sidx + 1] = r; }
+        }
+        __syncthreads();
+        if ( !split ) break;
+        // every leaf moves into the left or right child segment (as kDescend)
+        for ( int pos = tid; pos < n; pos += SUB_TB )
+        {
+            const int e = S.ord[pos];
+            const int sidx = S.segOf[e];
+            const SubSeg sg = S.seg[cur][sidx];
+            int ns = 2 * sidx;
+            if ( sg.n > 1 && pos - sg.first >= sg.n / 2 ) ns += 1;
+            S.segOf[e] = (uint16_t)ns;
+        }
+        __syncthreads();
+        cur ^= 1;
+    }
+    // final leaf order of the subtree
+    for ( int pos = tid; pos < n; pos += SUB_TB )
+    {
+        const int e = S.ord[pos];
+        keys[root.first + pos].face = S.face[e];
+        keys[root.first + pos].leaf = S.leaf[e];
+    }
+}
+
 // ---- dipoles (MRDipole.cpp:23-71) ---------------------------------------------------------------------------------
 
 // leaves: da = 0.5f*cross(b-a, c-a); area = |da|; pos = area * ((1/3.0f)*(a+b+c))   (MRDipole.cpp:29-45,
@@ -499,9 +694,8 @@ int initTreeAux( DeviceTree& t, int device )
 
 void freeTree( DeviceTree& t )
 {
-    cudaFree( t.points ); cudaFree( t.tris ); cudaFree( t.refNodes ); cudaFree( t.refDipoles );
-    cudaFree( t.nodes ); cudaFree( t.leafTris ); cudaFree( t.leafFilt );
-    cudaFree( t.faceNormals ); cudaFree( t.vertNormals ); cudaFree( t.faceAdj ); cudaFree( t.nodeDepth );
+    cudaFree( t.points ); cudaFree( t.tris ); cudaFree( t.arena ); // refNodes, refDipoles, nodes, leafTris, leafFilt, nodeDepth
+    cudaFree( t.faceNormals ); cudaFree( t.vertNormals ); cudaFree( t.faceAdj );
     if ( t.sideStream ) cudaStreamDestroy( t.sideStream );
     if ( t.evFork ) cudaEventDestroy( t.evFork );
     if ( t.evJoin ) cudaEventDestroy( t.evJoin );
@@ -572,24 +766,44 @@ int buildTree( DeviceTree& t, cudaStream_t st, uint64_t* launches )
     LeafBox* dLeaves = nullptr; LevelKey *dKeys = nullptr; Seg *dSegA = nullptr, *dSegB = nullptr;
     uint32_t* dSegBox = nullptr; int32_t *dSkip = nullptr, *dLeafNodeOfPos = nullptr, *dLeafSlotOfNode = nullptr;
     uint8_t* dDepth = nullptr;
-    const size_t maxSegs = (size_t)1 << levels;
-    T_ALLOC( dLeaves, (size_t)L * sizeof( LeafBox ) );
-    T_ALLOC( dKeys, (size_t)L * sizeof( LevelKey ) );
-    T_ALLOC( dSegA, 2 * maxSegs * sizeof( Seg ) );
-    T_ALLOC( dSegB, 2 * maxSegs * sizeof( Seg ) );
-    T_ALLOC( dSegBox, maxSegs * 6 * sizeof( uint32_t ) );
-    T_ALLOC( dSkip, N * sizeof( int32_t ) );
-    T_ALLOC( dDepth, N );
-    T_ALLOC( dLeafNodeOfPos, (size_t)L * sizeof( int32_t ) );
-    T_ALLOC( dLeafSlotOfNode, N * sizeof( int32_t ) );
-    B2_CUDA( cudaMalloc( &t.refNodes, N * sizeof( RefNode ) ) );
-    B2_CUDA( cudaMalloc( &t.refDipoles, N * sizeof( RefDipole ) ) );
-    B2_CUDA( cudaMalloc( &t.nodes, N * sizeof( TravNode ) ) );
-    B2_CUDA( cudaMalloc( &t.leafTris, (size_t)L * sizeof( LeafTri ) ) );
-    B2_CUDA( cudaMalloc( &t.leafFilt, (size_t)L * sizeof( LeafFilt ) ) );
-
+    // the global passes stop at level0 (below it one block finishes each subtree): the segment tables only grow that far
+    static const bool noSubtrees = getenv( "B2FWN_NO_SUBTREES" ) != nullptr; // dev switch: global passes down to the leaves
+    const int level0 = noSubtrees ? levels + 1 : std::max( 0, levels - 10 ); // segments of level0 hold <= SUB_CAP = 2^10 leaves
+    const size_t maxSegs = (size_t)1 << std::min( levels, level0 );
+    size_t sortTmpBytes = 0; void* sortTmp = nullptr;
+    cub::DeviceMergeSort::SortKeys( nullptr, sortTmpBytes, dKeys, L, LevelKeyLess(), st );
+    // ONE allocation for all temporaries of the build and one for the arrays the tree keeps: cudaMalloc / cudaFree are slow and
+    // device-synchronising, and their cost varies from box to box (r02, 10 M faces: 16 ms of the build on one box, ~70 ms on another,
+    // with twenty separate allocations)
     uint32_t* dBBox = nullptr;
-    T_ALLOC( dBBox, 6 * sizeof( uint32_t ) );
+    {
+        size_t off = 0;
+        auto span = [&]( size_t bytes ) { const size_t at = off; off += ( bytes + 255 ) & ~(size_t)255; return at; };
+        const size_t oLeaves = span( (size_t)L * sizeof( LeafBox ) ), oKeys = span( (size_t)L * sizeof( LevelKey ) );
+        const size_t oSegA = span( 2 * maxSegs * sizeof( Seg ) ), oSegB = span( 2 * maxSegs * sizeof( Seg ) );
+        const size_t oSegBox = span( maxSegs * 6 * sizeof( uint32_t ) ), oSkip = span( N * sizeof( int32_t ) );
+        const size_t oPos = span( (size_t)L * sizeof( int32_t ) ), oSlot = span( N * sizeof( int32_t ) );
+        const size_t oBBox = span( 6 * sizeof( uint32_t ) ), oSort = span( sortTmpBytes );
+        uint8_t* arena = nullptr;
+        T_ALLOC( arena, off );
+        dLeaves = reinterpret_cast<LeafBox*>( arena + oLeaves ); dKeys = reinterpret_cast<LevelKey*>( arena + oKeys );
+        dSegA = reinterpret_cast<Seg*>( arena + oSegA ); dSegB = reinterpret_cast<Seg*>( arena + oSegB );
+        dSegBox = reinterpret_cast<uint32_t*>( arena + oSegBox ); dSkip = reinterpret_cast<int32_t*>( arena + oSkip );
+        dLeafNodeOfPos = reinterpret_cast<int32_t*>( arena + oPos ); dLeafSlotOfNode = reinterpret_cast<int32_t*>( arena + oSlot );
+        dBBox = reinterpret_cast<uint32_t*>( arena + oBBox ); sortTmp = arena + oSort;
+    }
+    {
+        size_t off = 0;
+        auto span = [&]( size_t bytes ) { const size_t at = off; off += ( bytes + 255 ) & ~(size_t)255; return at; };
+        const size_t oRefN = span( N * sizeof( RefNode ) ), oRefD = span( N * sizeof( RefDipole ) ), oNodes = span( N * sizeof( TravNode ) );
+        const size_t oTris = span( (size_t)L * sizeof( LeafTri ) ), oFilt = span( (size_t)L * sizeof( LeafFilt ) ), oDepth = span( N );
+        B2_CUDA( cudaMalloc( &t.arena, off ) );
+        uint8_t* a = static_cast<uint8_t*>( t.arena );
+        t.refNodes = reinterpret_cast<RefNode*>( a + oRefN ); t.refDipoles = reinterpret_cast<RefDipole*>( a + oRefD );
+        t.nodes = reinterpret_cast<TravNode*>( a + oNodes ); t.leafTris = reinterpret_cast<LeafTri*>( a + oTris );
+        t.leafFilt = reinterpret_cast<LeafFilt*>( a + oFilt ); dDepth = a + oDepth;
+    }
+
     kClearSegBoxes<<<1, 32, 0, st>>>( dBBox, 1 ); ++nl;
     kFaceBoxes<<<nblk( L ), TB, 0, st>>>( t.points, t.tris, dValid, L, dLeaves, dBBox ); ++nl;
     {
@@ -601,20 +815,21 @@ int buildTree( DeviceTree& t, cudaStream_t st, uint64_t* launches )
             const uint32_t u = ( hb[c] & 0x80000000u ) ? ( hb[c] & 0x7fffffffu ) : ~hb[c];
             memcpy( &t.bbox[c], &u, 4 );
         }
-        temps.release( dBBox );
     }
     kInitPerm<<<nblk( L ), TB, 0, st>>>( L, dKeys, dLeaves ); ++nl;
     const Seg root = { 0, L, 0, 0 };
     B2_CUDA( cudaMemcpyAsync( dSegA, &root, sizeof( Seg ), cudaMemcpyHostToDevice, st ) );
 
-    size_t sortTmpBytes = 0; void* sortTmp = nullptr;
-    cub::DeviceMergeSort::SortKeys( nullptr, sortTmpBytes, dKeys, L, LevelKeyLess(), st );
-    T_ALLOC( sortTmp, sortTmpBytes );
-
-    // 2. breadth-first build, one segmented sort per level
+    // 2. breadth-first build: one segmented sort per level while the segments are large, then one block per subtree
     for ( int lev = 0; lev <= levels; ++lev )
     {
         const size_t nSegs = (size_t)1 << lev;
+        if ( lev == level0 )
+        {
+            B2_CUDA( cudaFuncSetAttribute( kSubtrees, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof( SubShared ) ) );
+            kSubtrees<<<(unsigned)nSegs, SUB_TB, sizeof( SubShared ), st>>>( dSegA, level0, levels, dKeys, dLeaves, t.refNodes, dSkip, dDepth, dLeafNodeOfPos ); ++nl;
+            break;
+        }
         if ( lev < levels )
         {
             kClearSegBoxes<<<nblk( nSegs * 6 ), TB, 0, st>>>( dSegBox, nSegs ); ++nl;
@@ -642,8 +857,7 @@ int buildTree( DeviceTree& t, cudaStream_t st, uint64_t* launches )
     B2_CUDA( cudaGetLastError() );
     B2_CUDA( cudaStreamSynchronize( st ) );
 
-    temps.keep( dDepth );
-    t.nodeDepth = dDepth; // kept for refitTree; everything else is released by temps
+    t.nodeDepth = dDepth; // part of t.arena, kept for refitTree; the temporaries are released by temps
 #undef T_ALLOC
     if ( launches ) *launches += nl;
     return B2FWN_OK;
