@@ -1218,6 +1218,7 @@ __global__ void __launch_bounds__( GRID_TB, MINB ) kGridFwn6( const TravNode* __
     }
 
     if ( !rowValid ) return;
+    float4 r8[2] = { make_float4( 0.f, 0.f, 0.f, 0.f ), make_float4( 0.f, 0.f, 0.f, 0.f ) };
 #pragma unroll
     for ( int h = 0; h < 2; ++h )
     {
@@ -1231,7 +1232,15 @@ __global__ void __launch_bounds__( GRID_TB, MINB ) kGridFwn6( const TravNode* __
                                            fwnResult( MODE, s4[2], d4.z, P.threshold ), fwnResult( MODE, s4[3], d4.w, P.threshold ) );
             *reinterpret_cast<float4*>( out + id + 4 * h ) = r4;
             if ( PEERS )
-                for ( int k = 0; k < peers.n; ++k ) *reinterpret_cast<float4*>( peers.p[k] + id + 4 * h ) = r4;
+            {
+                r8[h] = r4;
+                // rows of whole 32-byte sectors (dx % 8 == 0, all volumes 32-B aligned: P.vecStore == 2): the lane's 8 results go to
+                // every peer as ONE 256-bit store after the loop.  Two 16-byte stores per row, issued by two different
+                // instructions, reached the peers as two partial-sector writes each: r02, N = 8: 234 ms per rank for 107 ms of
+                // work, 30 GB of posted writes per GPU at 128 GB/s (profiles/r02/scale/)
+                if ( P.vecStore != 2 )
+                    for ( int k = 0; k < peers.n; ++k ) *reinterpret_cast<float4*>( peers.p[k] + id + 4 * h ) = r4;
+            }
         }
         else
         {
@@ -1247,6 +1256,10 @@ __global__ void __launch_bounds__( GRID_TB, MINB ) kGridFwn6( const TravNode* __
                 }
         }
     }
+    if ( PEERS && P.vecStore == 2 ) // dx % 8 == 0: both halves of the row lie inside the grid
+        for ( int k = 0; k < peers.n; ++k )
+            asm volatile( "st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" :: "l"( peers.p[k] + id ), "f"( r8[0].x ), "f"( r8[0].y ),
+                          "f"( r8[0].z ), "f"( r8[0].w ), "f"( r8[1].x ), "f"( r8[1].y ), "f"( r8[1].z ), "f"( r8[1].w ) : "memory" );
 }
 
 inline int checkDims( const int32_t dims[3], int zBegin, int zEnd )
@@ -1432,6 +1445,13 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
             po = *peers;
             for ( int k = 0; k < po.n; ++k )
                 if ( reinterpret_cast<uintptr_t>( po.p[k] ) % 16 != 0 ) PF.vecStore = 0;
+            if ( v6 && PF.vecStore && dims[0] % 8 == 0 )
+            {
+                bool a32 = true; // the peer volumes (the only targets of the 256-bit stores)
+                for ( int k = 0; k < po.n; ++k ) a32 = a32 && reinterpret_cast<uintptr_t>( po.p[k] ) % 32 == 0;
+                static const bool noV8 = getenv( "B2FWN_NO_V8" ) != nullptr; // dev switch: two 16-byte stores per row, as before
+                if ( a32 && !noV8 ) PF.vecStore = 2;
+            }
         }
         if ( v6 )
         {

@@ -237,15 +237,17 @@ def test_z_interleaved_chunks_match_full_grid(world, chunk, stages, dz):
         fwn.calc_from_grid_with_distances_device_chunks(dims, xf, out.data_ptr(), z_chunk=6, z_stride=12)
 
 
-def test_fused_gather_stores_every_result_into_the_peer_volumes():
+@pytest.mark.parametrize("dims", [(36, 40, 48), (40, 36, 48)])
+def test_fused_gather_stores_every_result_into_the_peer_volumes(dims):
     """the _p2p form (multi-GPU gather fused into the kernel): two further volumes stand in for the other ranks' memory;
-    after all ranks' calls each of them equals the full-grid result"""
+    after all ranks' calls each of them equals the full-grid result.  dx = 36: rows of 16-byte pieces (float4 stores); dx = 40:
+    rows of whole 32-byte sectors, the peers receive one 256-bit store per lane"""
     import torch
     from meshlib_b200 import slabs
     pts, tris = _mesh("noisy")
     fwn = mb.FastWindingNumber(pts, tris)
-    dims, world = (36, 40, 48), 3
-    xf = mb.make_basis_xf((-1.3, -1.3, -1.3), (2.6 / 36, 2.6 / 40, 2.6 / 48))
+    world = 3
+    xf = mb.make_basis_xf((-1.3, -1.3, -1.3), (2.6 / dims[0], 2.6 / dims[1], 2.6 / dims[2]))
     opts = mb.DistOptions(0.0, 0.04, False, 0.5, 2.0)
     full = fwn.calc_from_grid_with_distances(dims, xf, opts)
     layer = dims[0] * dims[1]
