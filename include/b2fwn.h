@@ -231,6 +231,13 @@ int b2fwn_calc_from_grid_with_distances_by_parts_into( b2fwn_handle h, const int
                                                        int32_t max_layers_per_part, b2fwn_part_buffer_cb buffer,
                                                        b2fwn_part_cb part, void* part_user, b2fwn_progress cb, void* user );
 
+/* The partition the by-parts / host-output calls use, without running anything (no device needed): splitByChunks
+ * (source/MRMesh/MRChunkIterator.cpp:25-49) over whole layers -- part k begins at k * (layers_per_part - layer_overlap) and has
+ * layers_per_part layers, the last one fewer -- and the device (index into the handle's device list) each part is computed on:
+ * k mod min(n_devices, n_parts).  Writes at most `capacity` entries; *n_parts = the number of parts. */
+int b2fwn_plan_parts( int32_t n_layers, int32_t layers_per_part, int32_t layer_overlap, int32_t n_devices, int32_t capacity,
+                      int32_t* out_begin, int32_t* out_layers, int32_t* out_device, int32_t* n_parts );
+
 /* getCudaSafeMemoryLimit (source/MRCuda/MRCudaBasic.cpp:75-90) of a device: 80 % of (free - 128 MB), in bytes; 0 on failure */
 size_t b2fwn_safe_memory_limit( int32_t device );
 

@@ -103,7 +103,7 @@ EXPORTS = [
     "b2fwn_signed_distances_by_projection_normal", "b2fwn_signed_distances_by_projection_normal_device",
     "b2fwn_mesh_to_distance_volume_by_projection_normal", "b2fwn_update_points",
     "b2fwn_calc_from_grid_by_parts_into", "b2fwn_calc_from_grid_with_distances_by_parts_into", "b2fwn_safe_memory_limit",
-    "b2fwn_build_topology", "b2fwn_build_topology_fetch", "b2fwn_suggest_voxel_size",
+    "b2fwn_build_topology", "b2fwn_build_topology_fetch", "b2fwn_suggest_voxel_size", "b2fwn_plan_parts",
 ]
 
 
@@ -158,6 +158,7 @@ def load_library():
     L.b2fwn_build_topology.argtypes = [vp, vp, C.c_size_t, C.c_int32, C.c_size_t, u64p, u64p, u64p]
     L.b2fwn_build_topology_fetch.argtypes = [vp, vp, vp, vp]
     L.b2fwn_suggest_voxel_size.argtypes = [vp, C.c_float, f32p]
+    L.b2fwn_plan_parts.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, i32p, i32p, i32p, i32p]
     L.b2fwn_safe_memory_limit.argtypes = [C.c_int32]
     L.b2fwn_safe_memory_limit.restype = C.c_size_t
     L.b2fwn_get_tree.argtypes = [vp, vp, vp, C.c_size_t, C.POINTER(C.c_size_t)]
@@ -204,6 +205,16 @@ def make_basis_xf(origin, voxel_size):
     v = np.asarray(voxel_size, np.float32) * np.ones(3, np.float32)
     b = o + np.float32(0.5) * v
     return np.array([v[0], 0, 0, 0, v[1], 0, 0, 0, v[2], b[0], b[1], b[2]], np.float32)
+
+
+def plan_parts(n_layers, layers_per_part, layer_overlap=0, n_devices=1):
+    """[(first layer, layers, device index), ...]: the partition of the by-parts / host-output calls (b2fwn_plan_parts; needs no GPU)"""
+    L = load_library()
+    n = C.c_int32()
+    _check(L.b2fwn_plan_parts(n_layers, layers_per_part, layer_overlap, n_devices, 0, None, None, None, C.byref(n)))
+    b, s, d = ((C.c_int32 * max(n.value, 1))() for _ in range(3))
+    _check(L.b2fwn_plan_parts(n_layers, layers_per_part, layer_overlap, n_devices, n.value, b, s, d, C.byref(n)))
+    return [(b[k], s[k], d[k]) for k in range(n.value)]
 
 
 def measure_fp32_peak(device=0):

@@ -271,6 +271,24 @@ int b2fwn_update_points( b2fwn_handle h, const float* points, size_t nVerts )
 
 size_t b2fwn_safe_memory_limit( int32_t device ) { return safeMemoryLimit( device ); }
 
+int b2fwn_plan_parts( int32_t nLayers, int32_t layersPerPart, int32_t overlap, int32_t nDevices, int32_t capacity, int32_t* outBegin,
+                      int32_t* outLayers, int32_t* outDevice, int32_t* nParts )
+{
+    if ( !nParts ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    if ( overlap < 0 ) { setError( "negative layer overlap" ); return B2FWN_ERR_INVALID; }
+    if ( nLayers > 0 && layersPerPart <= overlap ) { setError( "part must be larger than the overlap" ); return B2FWN_ERR_INVALID; }
+    const int count = partCount( nLayers, std::min( layersPerPart, std::max( nLayers, 1 ) ), overlap );
+    *nParts = count;
+    const int nd = std::max( 1, std::min( nDevices, count ) ), step = std::min( layersPerPart, std::max( nLayers, 1 ) ) - overlap;
+    for ( int k = 0; k < count && k < capacity; ++k )
+    {
+        if ( outBegin ) outBegin[k] = k * step;
+        if ( outLayers ) outLayers[k] = std::min( nLayers, k * step + std::min( layersPerPart, nLayers ) ) - k * step;
+        if ( outDevice ) outDevice[k] = k % nd; // chunks are dealt round-robin: index into the handle's device list
+    }
+    return B2FWN_OK;
+}
+
 int b2fwn_get_stats( b2fwn_handle h, b2fwn_stats* out )
 {
     if ( !h || !out ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }

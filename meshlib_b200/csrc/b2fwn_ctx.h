@@ -36,6 +36,9 @@ namespace b2
 int ensureScratch( b2fwn_ctx* h, int slot, size_t floats );
 int ensurePinned( b2fwn_ctx* h, int slot, size_t floats );
 
+// number of parts of nLayers layers in parts of layersPerPart with `overlap` shared layers (0 when the part is not larger than the overlap)
+int partCount( int nLayers, int layersPerPart, int overlap );
+
 // getCudaSafeMemoryLimit (source/MRCuda/MRCudaBasic.cpp:75-90): 80 % of ( free - 128 MB ) of the device, in bytes
 size_t safeMemoryLimit( int device );
 

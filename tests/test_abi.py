@@ -96,3 +96,28 @@ def test_cpp_adapter_compiles_against_reference_headers():
            f"-I{ref}/thirdparty/parallel-hashmap", f"-I{ref}/thirdparty/expected/include", f"-I{ROOT}/include", src]
     r = subprocess.run(cmd, capture_output=True, text=True)
     assert r.returncode == 0, r.stderr[-3000:]
+
+
+def test_part_plan_matches_split_by_chunks():
+    """b2fwn_plan_parts (the partition runChunked uses; no device needed) against the restated splitByChunks of the oracle and the
+    reference's own known answers (/root/reference/source/MRMesh/MRChunkIterator.cpp:52-80), plus the round-robin deal over devices"""
+    from oracle import portlib
+    assert [(b, s) for b, s, _d in mb.plan_parts(8, 4, 0)] == [(0, 4), (4, 4)]
+    assert [(b, s) for b, s, _d in mb.plan_parts(9, 4, 0)] == [(0, 4), (4, 4), (8, 1)]
+    assert [(b, s) for b, s, _d in mb.plan_parts(10, 4, 1)] == [(0, 4), (3, 4), (6, 4)]
+    assert [(b, s) for b, s, _d in mb.plan_parts(11, 4, 1)] == [(0, 4), (3, 4), (6, 4), (9, 2)]
+    assert mb.plan_parts(0, 4, 0) == []
+    for total in (1, 2, 7, 19, 64, 2048):
+        for part in (1, 2, 3, 5, 8, 64, 5000):
+            for overlap in (0, 1, 2):
+                if part <= overlap:
+                    with pytest.raises(mb.B2Error):
+                        mb.plan_parts(total, part, overlap)
+                    continue
+                want = portlib.split_by_chunks(total, min(part, total), overlap)
+                if total <= overlap:
+                    continue  # the reference yields no chunk there; the pipeline computes the few layers as one part
+                got = mb.plan_parts(total, part, overlap, n_devices=3)
+                assert [(b, s) for b, s, _d in got] == want, (total, part, overlap)
+                nd = min(3, len(got))
+                assert [d for _b, _s, d in got] == [k % nd for k in range(len(got))]
