@@ -101,6 +101,27 @@ int b2fwn_calc_from_vector( b2fwn_handle h, const float* pts_xyz, size_t n, floa
 int b2fwn_calc_from_vector_device( b2fwn_handle h, const float* d_pts_xyz, size_t n, float beta, int32_t skip_face,
                                    float* d_out_w );
 
+/* b2fwn_calc_from_vector_device for callers that must not trigger a device allocation.  It has no counterpart in the
+ * reference (whose calcFromVector resizes its DynamicArrays on every call, MRCudaFastWindingNumber.cpp:87-127).
+ * Who needs it: a host application that gave all but a sliver of the GPU's memory to its own arena at start-up (a later
+ * cudaMalloc or memory-pool growth inside a plug-in then fails, or pushes the application's own data out), and loops with a
+ * latency budget, for which an allocation is a synchronisation point of the whole device that stalls their other streams.
+ * b2fwn_calc_from_vector_device borrows the index arrays of its Morton sort from the handle's memory pool; this call keeps them
+ * in a fixed array inside the library image instead, and calls neither cudaMalloc / cudaFree nor any routine that allocates.
+ *  - Same arguments, same results bit for bit (the order in which queries are walked does not enter the arithmetic).
+ *  - n > B2FWN_NOALLOC_MAX_QUERIES is rejected with B2FWN_ERR_INVALID and a message that names the limit: split the vector.
+ *  - Cost: 4 * 4 B * B2FWN_NOALLOC_MAX_QUERIES + 1 MiB = 17 MiB of device memory on EVERY GPU the process uses with this
+ *    library loaded, from module load to process exit, whether or not the call is ever made.
+ *  - The first call on a device looks up the array's address on that device (cudaGetSymbolAddress) and keeps it; make that first
+ *    call before any stream capture begins.
+ *  - All calls on one device share the one array, and it keeps whatever the previous call left there.  Nothing in it has to
+ *    start at zero (each call writes every word before reading it), but two calls in flight on the same GPU at once would
+ *    overwrite each other's sort: the library therefore lets one call per device through at a time, the others wait for it
+ *    to finish.  Processes do not share the array. */
+#define B2FWN_NOALLOC_MAX_QUERIES ( 1u << 20 )
+int b2fwn_calc_from_vector_device_noalloc( b2fwn_handle h, const float* d_pts_xyz, size_t n, float beta, int32_t skip_face,
+                                           float* d_out_w );
+
 /* IFastWindingNumber::calcSelfIntersections (MRFastWindingNumber.h:31; CPU .cpp:40-52; GPU
  * MRCudaFastWindingNumber.cpp:129-173).  out_bits: ceil(n_faces/64) words, bit f set iff w<0 || w>1. */
 int b2fwn_calc_self_intersections( b2fwn_handle h, float beta, uint64_t* out_bits, b2fwn_progress cb, void* user );

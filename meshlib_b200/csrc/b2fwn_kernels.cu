@@ -8,12 +8,13 @@
 //     the per-query order of additions is exactly the reference's.
 // The grid kernels (warp-cooperative brick walk, fused sign + distance) live in b2fwn_grid.cu; this file holds the
 // one-thread-per-query kernels for point vectors and face centroids.
-#include "b2fwn_internal.h"
+#include "b2fwn_ctx.h"
 #include "b2fwn_math.cuh"
 #include <cub/device/device_radix_sort.cuh>
 #include <cfloat>
 #include <climits>
 #include <cstdlib>
+#include <mutex>
 
 namespace b2
 {
@@ -181,4 +182,100 @@ int launchFwnFaces( const DeviceTree& t, float beta, float* dOutW, uint64_t* dBi
     return B2FWN_OK;
 }
 
+// ---- b2fwn_calc_from_vector_device_noalloc: the Morton-ordered query walk with its scratch inside the library image ----------
+//
+// launchFwnVector above borrows 4 index arrays + the radix sort's workspace from the handle's memory pool for the length of the
+// call.  Some hosts of this library cannot let it do that: an application that has handed (nearly) all of the GPU's memory to its own
+// arena at start-up, so that any later cudaMalloc / pool growth inside a plug-in fails or evicts it; and a frame- or
+// latency-bound loop, where an allocation is a device-wide synchronisation point that stalls the caller's other streams.  For those
+// the same walk exists once more with the scratch as a file-scope array in device memory: it is part of the loaded module, so
+// every GPU that loads libb2fwn.so carries these 17 MiB from the first CUDA call of the process to its exit, and no call ever
+// asks the allocator for anything.  The price is the fixed upper limit on the number of queries below.
+//
+// gNoAllocScratch is a HOST-side handle of the symbol in this translation unit's host code -- not a device address.  The
+// address a kernel can use comes from cudaGetSymbolAddress with the device current, once per device (noAllocScratchOf).
+constexpr size_t kNoAllocMaxQueries = B2FWN_NOALLOC_MAX_QUERIES;
+constexpr size_t kNoAllocSortBytes = (size_t)1 << 20; // workspace of cub's radix sort; what cub really asks for is checked per call
+constexpr size_t kNoAllocScratchBytes = 4 * kNoAllocMaxQueries * sizeof( uint32_t ) + kNoAllocSortBytes;
+static __device__ __align__( 256 ) unsigned char gNoAllocScratch[kNoAllocScratchBytes];
+
+namespace
+{
+
+constexpr int kNoAllocMaxDeviceOrdinal = 64;
+std::mutex gNoAllocMutex[kNoAllocMaxDeviceOrdinal];              // one call at a time per device: every call uses the same array
+unsigned char* gNoAllocScratchAddr[kNoAllocMaxDeviceOrdinal] = {}; // device address of gNoAllocScratch on that device, once resolved
+
+// device address of the scratch array on `device`, which must be the current device; caller holds gNoAllocMutex[device]
+int noAllocScratchOf( int device, unsigned char** out )
+{
+    if ( !gNoAllocScratchAddr[device] )
+    {
+        unsigned char* p = nullptr;
+        B2_CUDA( cudaGetSymbolAddress( (void**)&p, gNoAllocScratch ) );
+        if ( !p ) { setError( "no device address for the static scratch array" ); return B2FWN_ERR_CUDA; }
+        gNoAllocScratchAddr[device] = p; // a failed look-up is not remembered: the next call tries again
+    }
+    *out = gNoAllocScratchAddr[device];
+    return B2FWN_OK;
+}
+
+} // anonymous namespace
+
 } // namespace b2
+
+#pragma GCC visibility push( default )
+extern "C" int b2fwn_calc_from_vector_device_noalloc( b2fwn_handle h, const float* dPts, size_t n, float beta, int32_t skipFace, float* dOut )
+{
+    using namespace b2;
+    if ( !h || ( n && ( !dPts || !dOut ) ) ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    if ( n > kNoAllocMaxQueries )
+    {
+        setError( "b2fwn_calc_from_vector_device_noalloc: " + std::to_string( n ) + " queries exceed the static scratch (B2FWN_NOALLOC_MAX_QUERIES = "
+                  + std::to_string( kNoAllocMaxQueries ) + "); split the vector or use b2fwn_calc_from_vector_device" );
+        return B2FWN_ERR_INVALID;
+    }
+    if ( h->device < 0 || h->device >= kNoAllocMaxDeviceOrdinal ) { setError( "device ordinal beyond the static scratch table" ); return B2FWN_ERR_INVALID; }
+    if ( n == 0 ) return B2FWN_OK;
+    B2_CUDA( cudaSetDevice( h->device ) );
+    // held until the stream has drained: a second call on this device (another thread, another handle) would sort into the
+    // same array while this one still reads its order from it
+    std::lock_guard<std::mutex> lock( gNoAllocMutex[h->device] );
+    const DeviceTree& t = h->tree;
+    const cudaStream_t st = h->stream;
+    uint32_t* order = nullptr;
+    if ( n >= ( 1u << 15 ) && t.numLeaves > 0 ) // same threshold as launchFwnVector: below it the sort costs more than it saves
+    {
+        unsigned char* scratch = nullptr;
+        if ( int e = noAllocScratchOf( h->device, &scratch ) ) return e;
+        // [keys | keys2 | vals | vals2 | sort workspace]; every word read below is written first in this call (the sort clears
+        // its own counters), so nothing of the previous call's contents has to be zeroed.  The sort ping-pongs between the two
+        // halves (cub::DoubleBuffer): the plain-pointer form would want a second copy of keys and values in its workspace.
+        uint32_t* keys = reinterpret_cast<uint32_t*>( scratch );
+        uint32_t *keys2 = keys + kNoAllocMaxQueries, *vals = keys2 + kNoAllocMaxQueries, *vals2 = vals + kNoAllocMaxQueries;
+        void* sortTmp = vals2 + kNoAllocMaxQueries;
+        cub::DoubleBuffer<uint32_t> dbKeys( keys, keys2 ), dbVals( vals, vals2 );
+        size_t tmpBytes = 0;
+        B2_CUDA( cub::DeviceRadixSort::SortPairs( nullptr, tmpBytes, dbKeys, dbVals, (int)n, 0, 30, st ) );
+        if ( tmpBytes > kNoAllocSortBytes ) { setError( "radix sort workspace exceeds its share of the static scratch" ); return B2FWN_ERR_INVALID; }
+        const float ext[3] = { t.bbox[3] - t.bbox[0], t.bbox[4] - t.bbox[1], t.bbox[5] - t.bbox[2] };
+        const float3 lo = make_float3( t.bbox[0] - 0.5f * ext[0], t.bbox[1] - 0.5f * ext[1], t.bbox[2] - 0.5f * ext[2] );
+        const float3 inv = make_float3( ext[0] > 0 ? 1024.f / ( 2 * ext[0] ) : 0.f, ext[1] > 0 ? 1024.f / ( 2 * ext[1] ) : 0.f, ext[2] > 0 ? 1024.f / ( 2 * ext[2] ) : 0.f );
+        B2_CUDA( cudaEventRecord( h->evA, st ) );
+        kMortonKeys<<<(unsigned)( ( n + 255 ) / 256 ), 256, 0, st>>>( dPts, n, lo, inv, keys, vals );
+        B2_CUDA( cub::DeviceRadixSort::SortPairs( sortTmp, tmpBytes, dbKeys, dbVals, (int)n, 0, 30, st ) );
+        order = dbVals.Current();
+        h->stats.kernel_launches += 5;
+    }
+    else
+        B2_CUDA( cudaEventRecord( h->evA, st ) );
+    kFwnVector<<<(unsigned)( ( n + 127 ) / 128 ), 128, 0, st>>>( t.nodes, t.leafTris, (int)t.numNodes, dPts, n, beta * beta, skipFace < 0 ? -1 : skipFace, dOut, order );
+    ++h->stats.kernel_launches;
+    B2_CUDA( cudaGetLastError() );
+    B2_CUDA( cudaEventRecord( h->evB, st ) );
+    B2_CUDA( cudaStreamSynchronize( st ) );
+    float ms = 0;
+    if ( cudaEventElapsedTime( &ms, h->evA, h->evB ) == cudaSuccess ) h->stats.last_kernel_ms = ms;
+    return B2FWN_OK;
+}
+#pragma GCC visibility pop
