@@ -47,12 +47,19 @@ typedef int ( *b2fwn_progress )( float progress, void* user );
  * return 0 to continue, non-zero to abort (GridByPartsFunc, source/MRMesh/MRFastWindingNumber.h:88) */
 typedef int ( *b2fwn_part_cb )( const float* data, const int32_t dims[3], int32_t z_offset, void* user );
 
-/* Devices of a handle.  n_devices <= 1: the single device `device` (the reference always uses device 0,
- * MRCudaFastWindingNumber.cpp:48).  n_devices > 1: devices[0 .. n_devices) of ONE process; the tree is built on devices[0] and
- * copied to the others (peer copies over NVLink), and the host-output grid calls (b2fwn_calc_from_grid,
- * b2fwn_calc_from_grid_with_distances[_layers], the by-parts calls, b2fwn_make_signed_by_winding_number,
- * b2fwn_mesh_to_distance_volume) deal their z-chunks round-robin over all of them, every device copying its chunks straight
- * into the caller's buffer: no gather.  All other calls (point vectors, *_device forms, marching cubes) run on devices[0]. */
+/* Devices of a handle.  n_devices <= 1: the single device `device`; `devices[]` is not read (the reference always uses device 0,
+ * MRCudaFastWindingNumber.cpp:48).  n_devices > 1: devices[0 .. n_devices) of ONE process, `device` is not read.  b2fwn_create
+ * uploads the mesh to every listed device and each builds its own copy of the tree and the dipoles, all at the same time on one
+ * host thread per device (the builds are deterministic, so the copies are identical; no peer access is needed).  What then
+ * uses all of them:
+ *  - the host-output grid calls (b2fwn_calc_from_grid, b2fwn_calc_from_grid_with_distances[_layers], the by-parts calls,
+ *    b2fwn_make_signed_by_winding_number, b2fwn_mesh_to_distance_volume): z-chunks dealt round-robin, every device copying its
+ *    chunks straight into the caller's buffer, no gather;
+ *  - b2fwn_mc_offset_mesh: one z-range of the grid per device, vertex ids continued by the exclusive prefix of the devices'
+ *    counts; b2fwn_marching_cubes_fetch reads every device's share, b2fwn_build_topology collects the triangles on devices[0];
+ *  - b2fwn_update_points (every copy is refitted).
+ * Everything else -- point vectors, face lists, projections and the ProjectionNormal volume, the *_device forms,
+ * b2fwn_marching_cubes on a caller's volume -- runs on devices[0]; device pointers passed to a *_device call belong to devices[0]. */
 #define B2FWN_MAX_DEVICES 16
 typedef struct b2fwn_config
 {

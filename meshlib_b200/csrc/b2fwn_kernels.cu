@@ -127,7 +127,7 @@ int launchFwnVector( const DeviceTree& t, const float* dPts, size_t n, float bet
     static const bool noSort = getenv( "B2FWN_NO_QUERY_SORT" ) != nullptr; // dev switch
     uint32_t* order = nullptr;
     uint8_t* scratch = nullptr;
-    if ( !noSort && n >= ( 1u << 15 ) && n < 0xFFFFFFFFull && t.numLeaves > 0 && t.pool )
+    if ( !noSort && n >= ( 1u << 15 ) && n <= (size_t)INT_MAX && t.numLeaves > 0 && t.pool ) // cub counts the items in an int; longer vectors are walked in input order
     {
         size_t tmpBytes = 0;
         cub::DeviceRadixSort::SortPairs( nullptr, tmpBytes, (uint32_t*)nullptr, (uint32_t*)nullptr, (uint32_t*)nullptr, (uint32_t*)nullptr, (int)n, 0, 30, st );
