@@ -269,6 +269,19 @@ int b2fwn_plan_parts( int32_t n_layers, int32_t layers_per_part, int32_t layer_o
 /* getCudaSafeMemoryLimit (source/MRCuda/MRCudaBasic.cpp:75-90) of a device: 80 % of (free - 128 MB), in bytes; 0 on failure */
 size_t b2fwn_safe_memory_limit( int32_t device );
 
+/* Memory a handle keeps between calls, and how it is given back.  To spare the allocator (a cudaMalloc / cudaFree pair of tens of GB
+ * costs more than the kernels), a handle caches and only ever grows: two device scratch slots of the host-output / by-parts / offset
+ * calls (up to the whole offset band: 34 GB at 2048^3), the mesher's workspace (~1.3 B per voxel of the largest slab), two pinned
+ * part buffers, and the idle blocks of its stream-ordered memory pool.  The reference frees its DynamicArrays with the object only
+ * (source/MRCuda/MRCudaBasic.cuh:19-70); a long-lived host with several handles or other users of the device needs more:
+ *  - b2fwn_trim releases all of these caches on every device of the handle (after synchronising them).  The tree, the dipoles
+ *    and the last marching-cubes / topology results stay; the next call simply allocates again.  Call it after a large call
+ *    whose like will not follow.
+ *  - Without being asked, an allocation of the handle that fails with "out of memory" releases those caches the running call does
+ *    not use and tries once more; the part-size budget of the host-output calls counts them as available for that reason.
+ * A handle never touches another handle's caches: only b2fwn_trim / b2fwn_destroy of that handle return them. */
+int b2fwn_trim( b2fwn_handle h );
+
 /* debug / parity: download the device-built tree in the reference's layouts:
  * nodes = AABBTreeNode (32 B: box.min xyz, box.max xyz, l, r; source/MRMesh/MRAABBTreeNode.h:29-45),
  * dipoles = Dipole (32 B: pos xyz, area, dirArea xyz, rr; source/MRMesh/MRDipole.h:10-30). */

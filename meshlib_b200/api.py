@@ -104,7 +104,7 @@ EXPORTS = [
     "b2fwn_mesh_to_distance_volume_by_projection_normal", "b2fwn_update_points",
     "b2fwn_calc_from_grid_by_parts_into", "b2fwn_calc_from_grid_with_distances_by_parts_into", "b2fwn_safe_memory_limit",
     "b2fwn_build_topology", "b2fwn_build_topology_fetch", "b2fwn_suggest_voxel_size", "b2fwn_plan_parts",
-    "b2fwn_calc_from_vector_device_noalloc",
+    "b2fwn_calc_from_vector_device_noalloc", "b2fwn_trim",
 ]
 
 
@@ -125,6 +125,7 @@ def load_library():
     L.b2fwn_destroy.restype = None
     L.b2fwn_calc_from_vector.argtypes = [vp, vp, C.c_size_t, C.c_float, C.c_int32, vp, PROGRESS_CB, vp]
     L.b2fwn_calc_from_vector_device.argtypes = [vp, vp, C.c_size_t, C.c_float, C.c_int32, vp]
+    L.b2fwn_trim.argtypes = [vp]
     L.b2fwn_calc_from_vector_device_noalloc.argtypes = [vp, vp, C.c_size_t, C.c_float, C.c_int32, vp]
     L.b2fwn_calc_self_intersections.argtypes = [vp, C.c_float, vp, PROGRESS_CB, vp]
     L.b2fwn_calc_self_intersections_device.argtypes = [vp, C.c_float, vp, vp]
@@ -381,6 +382,10 @@ class FastWindingNumber:
     # ---- device-pointer forms (multi-GPU slabs, benches) ----
     def calc_from_vector_device(self, d_points_ptr, n, d_out_ptr, beta=2.0, skip_face=-1):
         _check(_lib.b2fwn_calc_from_vector_device(self._h, d_points_ptr, n, beta, skip_face, d_out_ptr))
+
+    def trim(self):
+        """gives the handle's cached scratch (device slots, mesher workspace, pinned part buffers, idle pool blocks) back"""
+        _check(_lib.b2fwn_trim(self._h))
 
     def calc_from_vector_device_noalloc(self, d_points_ptr, n, d_out_ptr, beta=2.0, skip_face=-1):
         """calc_from_vector_device without any device allocation: the sort's scratch is a fixed array inside the library

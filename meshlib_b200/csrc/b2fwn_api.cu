@@ -13,13 +13,16 @@ namespace b2
 {
 
 static thread_local std::string g_lastError;
+static thread_local cudaError_t g_lastCudaError = cudaSuccess;
 
-void setError( const std::string& msg ) { g_lastError = msg; }
+void setError( const std::string& msg ) { g_lastError = msg; g_lastCudaError = cudaSuccess; }
+cudaError_t lastCudaError() { return g_lastCudaError; }
 
 int cudaFail( cudaError_t e, const char* where )
 {
     // reference wording: source/MRCuda/MRCudaBasic.cpp:109-112
     g_lastError = std::string( "NVIDIA GPU error: " ) + cudaGetErrorString( e ) + " [" + where + "]";
+    g_lastCudaError = e;
     (void)cudaGetLastError();
     return B2FWN_ERR_CUDA;
 }
@@ -270,6 +273,19 @@ int b2fwn_update_points( b2fwn_handle h, const float* points, size_t nVerts )
 }
 
 size_t b2fwn_safe_memory_limit( int32_t device ) { return safeMemoryLimit( device ); }
+
+int b2fwn_trim( b2fwn_handle h )
+{
+    if ( !h ) { setError( "null handle" ); return B2FWN_ERR_INVALID; }
+    const int rc = onAllDevices( h, [&]( b2fwn_ctx* d ) -> int
+    {
+        B2_CUDA( cudaSetDevice( d->device ) );
+        reclaimCaches( d, RECLAIM_ALL );
+        return B2FWN_OK;
+    } );
+    cudaSetDevice( h->device );
+    return rc;
+}
 
 int b2fwn_plan_parts( int32_t nLayers, int32_t layersPerPart, int32_t overlap, int32_t nDevices, int32_t capacity, int32_t* outBegin,
                       int32_t* outLayers, int32_t* outDevice, int32_t* nParts )
@@ -979,10 +995,19 @@ int b2fwn_mc_offset_mesh( b2fwn_handle h, const b2fwn_offset_params* p, b2fwn_of
         if ( cudaSetDevice( c->device ) != cudaSuccess ) { fail( cudaFail( cudaGetLastError(), "cudaSetDevice" ) ); return; }
         // values 4 B x (n + 2) layers, codes 1 B x (n + 1) layers, segment totals and scan scratch ~ 0.3 B: 5.5 B per voxel of a slab
         freeMc( c->mc ); // the previous result goes before the budget is taken
-        const size_t budget = safeMemoryLimit( c->device ) + c->scratchFloats[0] * sizeof( float ) + c->mcWork.codeBytes
-                              + 2 * c->mcWork.segEntries * sizeof( uint32_t );
+        // slot 0 and the mesher's workspace are reused; slot 1 and idle pool blocks are of no use here and go when the range does not fit
+        auto fitLayers = [&]() -> size_t
+        {
+            const size_t budget = safeMemoryLimit( c->device ) + reclaimableBytes( c, RECLAIM_SCRATCH0 | RECLAIM_MC_WORK );
+            return layer ? (size_t)( (double)budget / ( 5.5 * (double)layer ) ) : (size_t)( R.z1 - R.z0 ) + 2;
+        };
         int n = R.z1 - R.z0;
-        const size_t fit = layer ? (size_t)( (double)budget / ( 5.5 * (double)layer ) ) : (size_t)n;
+        size_t fit = fitLayers();
+        if ( fit < (size_t)n + 2 && reclaimableBytes( c, RECLAIM_SCRATCH1 | RECLAIM_POOL ) > 0 )
+        {
+            reclaimCaches( c, RECLAIM_SCRATCH1 | RECLAIM_POOL );
+            fit = fitLayers();
+        }
         if ( fit < (size_t)n + 2 ) n = fit > 3 ? (int)fit - 2 : 1;
         if ( cap > 0 ) n = std::min( n, cap );
         const size_t bufLayers = (size_t)std::min( dims[2] - R.z0, n + 2 );
@@ -1121,7 +1146,9 @@ int b2fwn_marching_cubes( b2fwn_handle h, const float* volume, int32_t onDevice,
         dVol = dTmp;
     }
     KernelTimer tm( h );
-    const int rc = marchingCubesDevice( dVol, dims, *p, h->mc, h->stream, &h->stats.kernel_launches, &h->mcWork );
+    // the volume is the caller's or dTmp: both scratch slots can go when the mesher's own buffers do not fit
+    const int rc = retryAfterReclaim( h, RECLAIM_SCRATCH0 | RECLAIM_SCRATCH1 | RECLAIM_POOL, [&]
+    { return marchingCubesDevice( dVol, dims, *p, h->mc, h->stream, &h->stats.kernel_launches, &h->mcWork ); } );
     tm.stop();
     cudaStreamSynchronize( h->stream );
     if ( dTmp ) cudaFree( dTmp );
@@ -1189,7 +1216,9 @@ int b2fwn_build_topology( b2fwn_handle h, const int32_t* tris, size_t nTris, int
         dTris = dTmp;
     }
     KernelTimer tm( h );
-    const int rc = buildTopologyDevice( dTris, nTris, nVerts, h->topo, h->stream, &h->stats.kernel_launches );
+    // the triangles are the mesher's result or dTmp: every cache of the handle can go when the sort's buffers do not fit
+    const int rc = retryAfterReclaim( h, RECLAIM_SCRATCH0 | RECLAIM_SCRATCH1 | RECLAIM_MC_WORK | RECLAIM_POOL, [&]
+    { return buildTopologyDevice( dTris, nTris, nVerts, h->topo, h->stream, &h->stats.kernel_launches ); } );
     tm.stop();
     cudaStreamSynchronize( h->stream );
     if ( dTmp ) cudaFree( dTmp );

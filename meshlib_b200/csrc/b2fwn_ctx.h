@@ -15,7 +15,8 @@ struct b2fwn_ctx
     b2::DeviceTree tree;
     b2fwn_stats stats{};
     b2::McResult mc;
-    b2::McWorkspace mcWork;            // scratch of the mesher, grow-only, released by b2fwn_destroy or when memory runs short
+    b2::McWorkspace mcWork;            // scratch of the mesher, grow-only; released by b2fwn_destroy, b2fwn_trim, and by reclaimCaches
+                                       // when an allocation of this handle fails for lack of memory
     b2::TopoResult topo;
     // scratch for the host-pointer entry points
     float* dScratch[2] = { nullptr, nullptr };
@@ -32,6 +33,27 @@ struct b2fwn_ctx
 
 namespace b2
 {
+
+// The caches a handle keeps between calls (the two scratch slots, the mesher's workspace, the pinned part buffers, the unused
+// blocks of its memory pool) are given back in three ways: b2fwn_destroy, b2fwn_trim, and -- the parts named in `what` -- by the
+// allocation sites of the handle themselves when cudaMalloc reports cudaErrorMemoryAllocation, before they try once more.
+// A site names only what the running call does not use.  The device of h must be current; the device is synchronised first.
+enum : unsigned { RECLAIM_SCRATCH0 = 1, RECLAIM_SCRATCH1 = 2, RECLAIM_MC_WORK = 4, RECLAIM_PINNED = 8, RECLAIM_POOL = 16, RECLAIM_ALL = 31 };
+void reclaimCaches( b2fwn_ctx* h, unsigned what );
+// device bytes reclaimCaches( h, what ) would release: part of the memory a call of this handle can count on
+size_t reclaimableBytes( const b2fwn_ctx* h, unsigned what );
+// fn() once more after reclaimCaches( h, what ) when it failed with cudaErrorMemoryAllocation
+template <class Fn>
+int retryAfterReclaim( b2fwn_ctx* h, unsigned what, Fn fn )
+{
+    int rc = fn();
+    if ( rc == B2FWN_ERR_CUDA && lastCudaError() == cudaErrorMemoryAllocation && reclaimableBytes( h, what ) > 0 )
+    {
+        reclaimCaches( h, what );
+        rc = fn();
+    }
+    return rc;
+}
 
 int ensureScratch( b2fwn_ctx* h, int slot, size_t floats );
 int ensurePinned( b2fwn_ctx* h, int slot, size_t floats );

@@ -93,6 +93,8 @@ struct GridXf
 // errors -------------------------------------------------------------------------------------------------------
 void setError( const std::string& msg );
 int cudaFail( cudaError_t e, const char* where );
+// the CUDA error code behind the calling thread's last cudaFail (cudaSuccess when its last failure was none of CUDA's)
+cudaError_t lastCudaError();
 #define B2_CUDA( expr )                                        \
     do {                                                       \
         cudaError_t _e = ( expr );                             \

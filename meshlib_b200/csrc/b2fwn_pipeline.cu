@@ -27,14 +27,65 @@
 namespace b2
 {
 
+namespace
+{
+size_t poolIdleBytes( cudaMemPool_t pool )
+{
+    if ( !pool ) return 0;
+    uint64_t reserved = 0, used = 0;
+    if ( cudaMemPoolGetAttribute( pool, cudaMemPoolAttrReservedMemCurrent, &reserved ) != cudaSuccess
+         || cudaMemPoolGetAttribute( pool, cudaMemPoolAttrUsedMemCurrent, &used ) != cudaSuccess )
+    {
+        (void)cudaGetLastError();
+        return 0;
+    }
+    return reserved > used ? (size_t)( reserved - used ) : 0;
+}
+}
+
+size_t reclaimableBytes( const b2fwn_ctx* h, unsigned what )
+{
+    size_t bytes = 0;
+    if ( what & RECLAIM_SCRATCH0 ) bytes += h->scratchFloats[0] * sizeof( float );
+    if ( what & RECLAIM_SCRATCH1 ) bytes += h->scratchFloats[1] * sizeof( float );
+    if ( what & RECLAIM_MC_WORK ) bytes += h->mcWork.codeBytes + 2 * h->mcWork.segEntries * sizeof( uint32_t ) + h->mcWork.tmpBytes;
+    if ( what & RECLAIM_POOL ) bytes += poolIdleBytes( h->tree.pool );
+    return bytes;
+}
+
+void reclaimCaches( b2fwn_ctx* h, unsigned what )
+{
+    cudaDeviceSynchronize(); // nothing in flight still reads what goes
+    for ( int s = 0; s < 2; ++s )
+    {
+        if ( ( what & ( s ? RECLAIM_SCRATCH1 : RECLAIM_SCRATCH0 ) ) && h->dScratch[s] )
+        {
+            cudaFree( h->dScratch[s] );
+            h->dScratch[s] = nullptr; h->scratchFloats[s] = 0;
+        }
+        if ( ( what & RECLAIM_PINNED ) && h->hPinned[s] )
+        {
+            cudaFreeHost( h->hPinned[s] );
+            h->hPinned[s] = nullptr; h->pinnedFloats[s] = 0;
+        }
+    }
+    if ( what & RECLAIM_MC_WORK ) freeMcWorkspace( h->mcWork );
+    if ( ( what & RECLAIM_POOL ) && h->tree.pool ) cudaMemPoolTrimTo( h->tree.pool, 0 );
+    (void)cudaGetLastError();
+}
+
 int ensureScratch( b2fwn_ctx* h, int slot, size_t floats )
 {
     if ( h->scratchFloats[slot] >= floats ) return B2FWN_OK;
     if ( h->dScratch[slot] ) cudaFree( h->dScratch[slot] );
     h->dScratch[slot] = nullptr; h->scratchFloats[slot] = 0;
-    B2_CUDA( cudaMalloc( &h->dScratch[slot], floats * sizeof( float ) ) );
-    h->scratchFloats[slot] = floats;
-    return B2FWN_OK;
+    // the other slot may hold the running call's data; the mesher never runs while a slot is being sized
+    return retryAfterReclaim( h, RECLAIM_MC_WORK | RECLAIM_POOL, [&]() -> int
+    {
+        B2_CUDA( cudaMalloc( &h->dScratch[slot], floats * sizeof( float ) ) );
+        h->scratchFloats[slot] = floats;
+        return B2FWN_OK;
+    } );
 }
 
 int ensurePinned( b2fwn_ctx* h, int slot, size_t floats )
@@ -233,8 +284,9 @@ int chooseLayersPerPart( const std::vector<b2fwn_ctx*>& devs, const int32_t dims
     size_t budgetFloats = ~(size_t)0;
     for ( const b2fwn_ctx* d : devs )
     {
-        // scratch slots this device already holds count as available (they are reused)
-        const size_t have = ( d->scratchFloats[0] + d->scratchFloats[1] ) * sizeof( float );
+        // scratch slots this device already holds count as available (they are reused), and so does what ensureScratch takes back
+        // from the handle's other caches when the allocation fails
+        const size_t have = reclaimableBytes( d, RECLAIM_SCRATCH0 | RECLAIM_SCRATCH1 | RECLAIM_MC_WORK | RECLAIM_POOL );
         budgetFloats = std::min( budgetFloats, ( safeMemoryLimit( d->device ) + have ) / ( 2 * sizeof( float ) ) );
     }
     const size_t budgetLayers = std::max<size_t>( budgetFloats / layer, 1 );

@@ -336,3 +336,67 @@ def test_offset_mesh_over_several_devices():
     assert v1.tobytes() == v2.tobytes() and t1.tobytes() == t2.tobytes()
     one.close()
     many.close()
+
+
+def test_trim_and_reclaim_of_the_handle_caches_when_memory_runs_out():
+    """the caches of a handle (scratch slots, mesher workspace, pool) are given back by b2fwn_trim, and by the handle's own
+    allocation sites when cudaMalloc reports out-of-memory -- with the device filled up to 96 MB by somebody else, calls that need
+    more than that go through, and give the same results as with an empty device"""
+    import torch
+    pts, tris = meshgen.make_uv_sphere(1, 96, 48)
+    dims = (512, 512, 512)
+    vs = 2.6 / 512
+    xf = mb.make_basis_xf((-1.3, -1.3, -1.3), vs)
+    opt = mb.DistOptions(0.0, (3 * vs) ** 2, False)
+    ref = mb.FastWindingNumber(pts, tris)
+    vol_ref = ref.calc_from_grid_with_distances(dims, xf, opt)
+    ref.close()
+    torch.zeros(1, device="cuda")
+    MB = 1 << 20
+
+    def free_bytes():
+        torch.cuda.synchronize()
+        torch.cuda.empty_cache()
+        return torch.cuda.mem_get_info()[0]
+
+    def fill_device_up_to(leave):
+        return torch.empty(free_bytes() - leave, dtype=torch.uint8, device="cuda")
+
+    fwn = mb.FastWindingNumber(pts, tris)
+    try:
+        q = meshgen.query_points(5000, -1.5, 1.5, seed=3)
+        w0 = fwn.calc_from_vector(q)
+        free_start = free_bytes()
+        v0, t0, _info = fwn.mc_offset_mesh(0.05, 0.0035)
+        topo0 = fwn.build_topology()
+        held = free_start - free_bytes()
+        assert held > 1000 * MB, held  # the band of ~606^3 voxels and the mesher's workspace stay cached
+        assert len(t0) * 3 * 32 > 128 * MB  # the tables' sort needs more than what is left free below
+
+        # (1) the half-edge build cannot allocate its sort buffers: every cache of the handle goes, second attempt succeeds
+        hog = fill_device_up_to(96 * MB)
+        topo1 = fwn.build_topology()
+        for a, b in zip(topo0, topo1):
+            assert a.tobytes() == b.tobytes()
+        del hog
+
+        # (2) the second scratch slot of a host-output call cannot be allocated: the mesher's workspace goes
+        v1, t1, _info = fwn.mc_offset_mesh(0.05, 0.0035)  # caches grown again
+        assert v1.tobytes() == v0.tobytes() and t1.tobytes() == t0.tobytes()
+        hog = fill_device_up_to(96 * MB)
+        vol = fwn.calc_from_grid_with_distances(dims, xf, opt)
+        del hog
+        assert vol.tobytes() == vol_ref.tobytes()
+
+        # (3) b2fwn_trim: the device is as free as before the calls, up to the results the handle still holds (mesh + tables)
+        before_trim = free_bytes()
+        fwn.trim()
+        after_trim = free_bytes()
+        assert after_trim - before_trim > 800 * MB, (before_trim, after_trim)
+        assert free_start - after_trim < 512 * MB, (free_start, after_trim)
+        # and the handle works as before
+        assert fwn.calc_from_vector(q).tobytes() == w0.tobytes()
+        v2, t2, _info = fwn.mc_offset_mesh(0.05, 0.0035)
+        assert v2.tobytes() == v0.tobytes() and t2.tobytes() == t0.tobytes()
+    finally:
+        fwn.close()
