@@ -56,11 +56,40 @@ OFFSET_WORKLOADS = {
 }
 
 # DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of ONE launch of the dominant kernel (kGridFwn6, whole grid on one
-# GPU) from an `ncu --set full` capture on B200; not measurable inside a timed run, so quoted from the committed capture
-NCU_TRAFFIC = {
-    "c5_band": (40.156268e9 + 34.851371e9, "profiles/r02/ncu_full_kGridFwn6_c5_band.csv"),
-    "c3_band": (1.002902e9 + 0.504868e9, "profiles/r01/ncu_full_kGridDist_kGridFwn5_c3_band_v6.csv (kGridFwn5, r01)"),
+# GPU): not measurable inside a timed run, so READ from the committed raw page of the `ncu --set full` capture on B200
+# (scripts/gpu_r3.sh stages fwn6 / c3; c5_band by application replay so that all counter passes complete)
+NCU_CAPTURES = {
+    "c5_band": ("profiles/r03/ncu_full_kGridFwn6_c5_band.csv", "kGridFwn6"),
+    "c3_band": ("profiles/r03/ncu_full_c3_band.csv", "kGridFwn6"),
 }
+# flops per voxel by SURVEY 8(d)'s weights over the reference algorithm's counters, as the N = 1 run measures them on its sample
+# layers (roofline.flops_per_voxel of that line): carried to the lines that have no CPU leg (N > 1, --no-cpu)
+FLOPS_PER_VOXEL = {
+    "c5_band": (2645.5708909032824, "BENCH_r02.json parsed.roofline.flops_per_voxel (N = 1, 200336-voxel sample of 16 layers)"),
+}
+_NCU_UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+
+
+def ncu_traffic(workload):
+    """(bytes per launch, source) of the workload's dominant kernel from its committed capture; (None, reason) without one"""
+    if workload not in NCU_CAPTURES:
+        return None, "no capture of this workload"
+    rel, kernel = NCU_CAPTURES[workload]
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), rel)
+    if not os.path.exists(path):
+        return None, f"{rel} is missing"
+    import csv
+    with open(path, newline="") as f:
+        rows = list(csv.reader(f))
+    head, units = rows[0], rows[1]
+    for r in rows[2:]:
+        if kernel in r[head.index("Kernel Name")]:
+            total = 0.0
+            for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                c = head.index(k)
+                total += float(r[c].replace(",", "")) * _NCU_UNIT[units[c]]
+            return total, f"{rel} ({kernel}: dram__bytes_read.sum + dram__bytes_write.sum)"
+    return None, f"{rel} holds no {kernel}"
 
 
 def build_workload(name, grid_override=None):
@@ -665,21 +694,28 @@ def run_ours(args, wl):
         barrier(host_only=True)
         if rank == 0:
             devices = list(range(world))
-            e_steps = max(1, min(args.steps, 3))
+            # every round is timed on its own and the MEDIAN is the e2e figure: one stalled cudaMalloc inside b2fwn_create (2 s, once,
+            # in the r02 driver run) moved a three-round mean by 39 %; max and all rounds are reported beside it
+            e_steps = max(1, min(args.steps, 5))
+            e_rounds = {}
 
-            def run(out, steps):
-                t0 = time.perf_counter()
+            def run(out, steps, key=None):
+                ms = []
                 for _ in range(steps):
+                    t0 = time.perf_counter()
                     f2 = mb.FastWindingNumber(wl["points"], wl["tris"], devices=devices)
                     f2.calc_from_grid_with_distances(dims, xf, opts, out=out)
                     st = f2.stats()
                     f2.close()
-                return 1e3 * (time.perf_counter() - t0) / steps, st
+                    ms.append(1e3 * (time.perf_counter() - t0))
+                if key:
+                    e_rounds[key] = ms
+                return float(np.median(ms)), st
 
             host_np = np.empty(total, np.float32)
             host_np.fill(0)  # touched, like the vector a caller resized
             run(host_np, 1)  # warm-up: contexts on the other devices, staging rings
-            e_ms, st2 = run(host_np, e_steps)
+            e_ms, st2 = run(host_np, e_steps, "pageable")
             # the host-output call must deliver what the device-resident call left in HBM (same kernels, chunked): bit for bit
             e2e_same = None
             if gpu_layers is not None:
@@ -690,13 +726,17 @@ def run_ours(args, wl):
             if not args.no_pinned and (world == 1 or args.pinned):  # N > 1: only on request (--pinned), it pins 34 GB once more
                 host = torch.empty(total, dtype=torch.float32, pin_memory=True)
                 run(host.numpy(), 1)
-                pinned_ms, _ = run(host.numpy(), e_steps)
+                pinned_ms, _ = run(host.numpy(), min(e_steps, 3), "pinned")
                 del host
             e2e = {"value": total / (e_ms * 1e-3), "unit": UNIT, "ms_per_step": e_ms, "steps": e_steps,
+                   "statistic": "median over the rounds, each timed on its own (host wall clock)",
+                   "ms_max": max(e_rounds["pageable"]), "ms_min": min(e_rounds["pageable"]),
+                   "ms_mean": float(np.mean(e_rounds["pageable"])), "ms_rounds": [round(v, 1) for v in e_rounds["pageable"]],
                    "h2d_bytes_per_step": int(wl["points"].nbytes + wl["tris"].nbytes + 12 * 4 + 20),
                    "d2h_bytes_per_step": int(4 * total), "equals_resident_volume_on_sample_layers": e2e_same, "checksum": e2e_checksum,
                    "host_buffer": "pageable (numpy, sized and touched by the caller): pinned staging ring + copier threads inside the library",
-                   "pinned_buffer": None if pinned_ms is None else {"value": total / (pinned_ms * 1e-3), "ms_per_step": pinned_ms},
+                   "pinned_buffer": None if pinned_ms is None else {"value": total / (pinned_ms * 1e-3), "ms_per_step": pinned_ms,
+                                                                    "ms_rounds": [round(v, 1) for v in e_rounds["pinned"]]},
                    "kernel_ms_of_the_call": st2.last_kernel_ms, "tree_build_ms": st2.tree_build_ms,
                    "includes": f"one process, {world} GPU(s): b2fwn_create (mesh H2D + device tree/dipole build"
                                + (", on every GPU at once" if world > 1 else "")
@@ -740,8 +780,10 @@ def run_ours(args, wl):
                        "peak_source": "FFMA micro-benchmark run on this GPU just now (b2fwn_measure_fp32_peak)",
                        "hbm": {"algorithmic_bytes_per_voxel": 4.0 + (st0.num_nodes * 64 + st0.num_leaves * 64) * world / total,
                                "peak": hbm_peak, "peak_source": hbm_src, "unit": "GB/s"}}
-    if world == 1 and wl["name"] in NCU_TRAFFIC and not args.grid:
-        out["roofline"]["traffic"], out["roofline"]["traffic_source"] = NCU_TRAFFIC[wl["name"]]
+    if world == 1 and not args.grid:
+        traffic, source = ncu_traffic(wl["name"])
+        if traffic is not None:
+            out["roofline"]["traffic"], out["roofline"]["traffic_source"] = traffic, source
         out["roofline"]["traffic_note"] = ("dominant kernel (the winding walk) alone; its algorithmic bytes are 8 B/voxel (|d| read, signed d written) "
                                            "+ one read of the tree")
     nslab0 = (dims[2] // world) * layer  # voxels of one launch (rank 0's slab)
@@ -763,6 +805,14 @@ def run_ours(args, wl):
         ach = fpv * nslab0 / (k_ms * 1e-3) / 1e12
         out["roofline"].update({"achieved": ach, "frac": ach / fp32_peak, "flops_per_voxel": fpv, "ops_per_voxel": per_voxel,
                                 "ops_sample": f"{n} voxels (stride sample of the cpu_baseline layers), reference algorithm counters"})
+    if out["roofline"]["achieved"] is None and wl["name"] in FLOPS_PER_VOXEL and not args.grid:
+        # N > 1 (or --no-cpu): the flop count per voxel is a property of the workload, not of the run -- the N = 1 figure with its
+        # source; one rank's launch does 1/N of the grid in the slowest rank's kernel time, against ONE GPU's peak
+        fpv, src = FLOPS_PER_VOXEL[wl["name"]]
+        t_ms = max(per_rank_kernel_ms) if per_rank_kernel_ms else k_ms
+        ach = fpv * (total / world) / (t_ms * 1e-3) / 1e12
+        out["roofline"].update({"achieved": ach, "frac": ach / fp32_peak, "flops_per_voxel": fpv, "flops_per_voxel_source": src,
+                                "per": "one rank's launch (1/N of the grid) in the slowest rank's kernel time, one GPU's peak"})
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
