@@ -189,7 +189,7 @@ struct HostRing
         {
             cudaError_t e = cudaMallocHost( &slot[s], PIECE * sizeof( float ) );
             if ( e == cudaSuccess ) e = cudaEventCreateWithFlags( &ev[s], cudaEventDisableTiming );
-            if ( e != cudaSuccess ) { error = cudaGetErrorString( e ); (void)cudaGetLastError(); return; }
+            if ( e != cudaSuccess ) { error = cudaGetErrorString( e ); (void)cudaGetLastError(); release(); return; }
         }
         // measured on the 16-thread host of a B200 box (c5_band, 34 GB into pageable memory): 2 threads 1577 ms, 4 threads 1345 ms,
         // 8 threads 1133 ms against 1116 ms into pinned memory (profiles/r02)
@@ -197,6 +197,18 @@ struct HostRing
         if ( const char* t = getenv( "B2FWN_COPY_THREADS" ) ) threads = std::max( 1, std::min( atoi( t ), R ) );
         for ( int t = 0; t < threads; ++t ) std::thread( [this] { threadMain(); } ).detach();
         ok = true;
+    }
+
+    // a ring whose set-up failed half way gives back what it got (no thread has been started yet)
+    void release()
+    {
+        for ( int s = 0; s < R; ++s )
+        {
+            if ( slot[s] ) cudaFreeHost( slot[s] );
+            if ( ev[s] ) cudaEventDestroy( ev[s] );
+            slot[s] = nullptr; ev[s] = nullptr;
+        }
+        (void)cudaGetLastError();
     }
 
     int acquire()
@@ -243,7 +255,7 @@ struct HostRing
 };
 
 // one ring per device for the life of the process (384 MiB of pinned memory, allocated at the first pageable host-output call
-// on that device; never freed: its threads outlive every handle)
+// on that device; never freed once it stands: its threads outlive every handle)
 HostRing* ringOf( int device, std::string& err )
 {
     static std::mutex gm;
@@ -251,7 +263,15 @@ HostRing* ringOf( int device, std::string& err )
     std::lock_guard<std::mutex> l( gm );
     auto it = rings.find( device );
     if ( it == rings.end() ) it = rings.emplace( device, new HostRing( device ) ).first;
-    if ( !it->second->ok ) { err = "NVIDIA GPU error: " + it->second->error + " [pinned staging ring]"; return nullptr; }
+    if ( !it->second->ok )
+    {
+        // the failed ring is not kept: the call that needed it fails with the reason, the next one tries again (pinned memory may
+        // have been short only for a moment)
+        err = "NVIDIA GPU error: " + it->second->error + " [pinned staging ring]";
+        delete it->second;
+        rings.erase( it );
+        return nullptr;
+    }
     return it->second;
 }
 
