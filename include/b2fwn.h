@@ -266,6 +266,18 @@ int b2fwn_calc_from_grid_with_distances_by_parts_into( b2fwn_handle h, const int
 int b2fwn_plan_parts( int32_t n_layers, int32_t layers_per_part, int32_t layer_overlap, int32_t n_devices, int32_t capacity,
                       int32_t* out_begin, int32_t* out_layers, int32_t* out_device, int32_t* n_parts );
 
+/* b2fwn_plan_parts is arithmetic only: it is the partition of a call exactly when layers_per_part is the part size that call ends up
+ * with.  The calls themselves may choose another one: max_layers_per_part <= 0 means "choose", and a wish that does not fit twice into
+ * the memory the handle's devices can count on is cut (never below layer_overlap + 1).  b2fwn_plan_parts_for asks the handle: it runs
+ * the same code as the host-output / by-parts calls do on entry, for the layers [z_begin, z_end) of a dims grid, and returns the
+ * parts (out_begin = absolute first layer) and the part size it settled on (*layers_per_part, may be NULL).  The answer holds
+ * for a call made in the same memory situation; a caller that sizes buffers from it should make the call next.  Both functions
+ * refuse 0 < layers <= layer_overlap, as the calls do; no layers = no parts.  (No counterpart in the reference, which derives the
+ * part size inside calcFromGridByParts, MRCudaFastWindingNumber.cpp:299-312, and does not tell.) */
+int b2fwn_plan_parts_for( b2fwn_handle h, const int32_t dims[3], int32_t z_begin, int32_t z_end, int32_t layer_overlap,
+                          int32_t max_layers_per_part, int32_t capacity, int32_t* out_begin, int32_t* out_layers, int32_t* out_device,
+                          int32_t* n_parts, int32_t* layers_per_part );
+
 /* getCudaSafeMemoryLimit (source/MRCuda/MRCudaBasic.cpp:75-90) of a device: 80 % of (free - 128 MB), in bytes; 0 on failure */
 size_t b2fwn_safe_memory_limit( int32_t device );
 

@@ -104,7 +104,7 @@ EXPORTS = [
     "b2fwn_mesh_to_distance_volume_by_projection_normal", "b2fwn_update_points",
     "b2fwn_calc_from_grid_by_parts_into", "b2fwn_calc_from_grid_with_distances_by_parts_into", "b2fwn_safe_memory_limit",
     "b2fwn_build_topology", "b2fwn_build_topology_fetch", "b2fwn_suggest_voxel_size", "b2fwn_plan_parts",
-    "b2fwn_calc_from_vector_device_noalloc", "b2fwn_trim",
+    "b2fwn_calc_from_vector_device_noalloc", "b2fwn_trim", "b2fwn_plan_parts_for",
 ]
 
 
@@ -126,6 +126,7 @@ def load_library():
     L.b2fwn_calc_from_vector.argtypes = [vp, vp, C.c_size_t, C.c_float, C.c_int32, vp, PROGRESS_CB, vp]
     L.b2fwn_calc_from_vector_device.argtypes = [vp, vp, C.c_size_t, C.c_float, C.c_int32, vp]
     L.b2fwn_trim.argtypes = [vp]
+    L.b2fwn_plan_parts_for.argtypes = [vp, i32p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, i32p, i32p, i32p, i32p, i32p]
     L.b2fwn_calc_from_vector_device_noalloc.argtypes = [vp, vp, C.c_size_t, C.c_float, C.c_int32, vp]
     L.b2fwn_calc_self_intersections.argtypes = [vp, C.c_float, vp, PROGRESS_CB, vp]
     L.b2fwn_calc_self_intersections_device.argtypes = [vp, C.c_float, vp, vp]
@@ -382,6 +383,18 @@ class FastWindingNumber:
     # ---- device-pointer forms (multi-GPU slabs, benches) ----
     def calc_from_vector_device(self, d_points_ptr, n, d_out_ptr, beta=2.0, skip_face=-1):
         _check(_lib.b2fwn_calc_from_vector_device(self._h, d_points_ptr, n, beta, skip_face, d_out_ptr))
+
+    def plan_parts(self, dims, layer_overlap=0, max_layers_per_part=0, z_begin=0, z_end=None):
+        """([(first layer, layers, device index), ...], layers per part): the partition a by-parts / host-output call of this handle
+        would use right now (b2fwn_plan_parts_for: the calls' own part-size choice incl. the free-memory cut)"""
+        z_end = dims[2] if z_end is None else z_end
+        n, lpp = C.c_int32(), C.c_int32()
+        _check(_lib.b2fwn_plan_parts_for(self._h, _dims(dims), z_begin, z_end, layer_overlap, max_layers_per_part, 0, None, None, None,
+                                         C.byref(n), C.byref(lpp)))
+        b, s, d = ((C.c_int32 * max(n.value, 1))() for _ in range(3))
+        _check(_lib.b2fwn_plan_parts_for(self._h, _dims(dims), z_begin, z_end, layer_overlap, max_layers_per_part, n.value, b, s, d,
+                                         C.byref(n), C.byref(lpp)))
+        return [(b[k], s[k], d[k]) for k in range(n.value)], lpp.value
 
     def trim(self):
         """gives the handle's cached scratch (device slots, mesher workspace, pinned part buffers, idle pool blocks) back"""

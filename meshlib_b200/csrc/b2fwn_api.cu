@@ -293,6 +293,8 @@ int b2fwn_plan_parts( int32_t nLayers, int32_t layersPerPart, int32_t overlap, i
     if ( !nParts ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
     if ( overlap < 0 ) { setError( "negative layer overlap" ); return B2FWN_ERR_INVALID; }
     if ( nLayers > 0 && layersPerPart <= overlap ) { setError( "part must be larger than the overlap" ); return B2FWN_ERR_INVALID; }
+    // a grid with no more layers than the overlap: the calls refuse it (their one part could not be larger than the overlap), so does the plan
+    if ( nLayers > 0 && nLayers <= overlap ) { setError( "part must be larger than the overlap" ); return B2FWN_ERR_INVALID; }
     const int count = partCount( nLayers, std::min( layersPerPart, std::max( nLayers, 1 ) ), overlap );
     *nParts = count;
     const int nd = std::max( 1, std::min( nDevices, count ) ), step = std::min( layersPerPart, std::max( nLayers, 1 ) ) - overlap;
@@ -302,6 +304,25 @@ int b2fwn_plan_parts( int32_t nLayers, int32_t layersPerPart, int32_t overlap, i
         if ( outLayers ) outLayers[k] = std::min( nLayers, k * step + std::min( layersPerPart, nLayers ) ) - k * step;
         if ( outDevice ) outDevice[k] = k % nd; // chunks are dealt round-robin: index into the handle's device list
     }
+    return B2FWN_OK;
+}
+
+int b2fwn_plan_parts_for( b2fwn_handle h, const int32_t dims[3], int32_t zBegin, int32_t zEnd, int32_t overlap, int32_t maxLayersPerPart,
+                          int32_t capacity, int32_t* outBegin, int32_t* outLayers, int32_t* outDevice, int32_t* nParts, int32_t* layersPerPart )
+{
+    if ( !h || !dims || !nParts ) { setError( "null argument" ); return B2FWN_ERR_INVALID; }
+    if ( dims[0] < 0 || dims[1] < 0 || zBegin < 0 || zEnd > dims[2] || zBegin > zEnd ) { setError( "invalid layer range" ); return B2FWN_ERR_INVALID; }
+    if ( overlap < 0 ) { setError( "negative layer overlap" ); return B2FWN_ERR_INVALID; }
+    *nParts = 0;
+    if ( layersPerPart ) *layersPerPart = 0;
+    const int nz = zEnd - zBegin;
+    if ( nz == 0 || (size_t)dims[0] * dims[1] == 0 ) return B2FWN_OK; // the calls return at once as well
+    const int lpp = layersPerPartOf( h, dims, nz, overlap, maxLayersPerPart );
+    cudaSetDevice( h->device );
+    if ( layersPerPart ) *layersPerPart = lpp;
+    if ( int e = b2fwn_plan_parts( nz, lpp, overlap, 1 + (int)h->replicas.size(), capacity, outBegin, outLayers, outDevice, nParts ) ) return e;
+    if ( outBegin )
+        for ( int k = 0; k < *nParts && k < capacity; ++k ) outBegin[k] += zBegin;
     return B2FWN_OK;
 }
 

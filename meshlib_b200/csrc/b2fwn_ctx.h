@@ -61,6 +61,10 @@ int ensurePinned( b2fwn_ctx* h, int slot, size_t floats );
 // number of parts of nLayers layers in parts of layersPerPart with `overlap` shared layers (0 when the part is not larger than the overlap)
 int partCount( int nLayers, int layersPerPart, int overlap );
 
+// layers per part runChunked uses for nz layers of a dims grid on this handle right now: the caller's wish (<= 0: chosen from the grid),
+// cut to what fits twice into the memory its devices can count on, at least overlap + 1, at most nz
+int layersPerPartOf( b2fwn_ctx* h, const int32_t dims[3], int nz, int overlap, int wanted );
+
 // getCudaSafeMemoryLimit (source/MRCuda/MRCudaBasic.cpp:75-90): 80 % of ( free - 128 MB ) of the device, in bytes
 size_t safeMemoryLimit( int device );
 

@@ -450,6 +450,13 @@ void driveDevice( b2fwn_ctx* dev, const int d, const int nd, const ChunkedCall& 
 
 } // anonymous namespace
 
+int layersPerPartOf( b2fwn_ctx* h, const int32_t dims[3], int nz, int overlap, int wanted )
+{
+    std::vector<b2fwn_ctx*> devs{ h };
+    devs.insert( devs.end(), h->replicas.begin(), h->replicas.end() );
+    return chooseLayersPerPart( devs, dims, nz, overlap, wanted );
+}
+
 int runChunked( b2fwn_ctx* h, const ChunkedCall& c, const ChunkLaunch& launch )
 {
     const int32_t* dims = c.dims;

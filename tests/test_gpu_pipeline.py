@@ -76,16 +76,20 @@ def test_by_parts_into_caller_owned_buffers(torus, small_chunks):
     full = _device_volume(fwn, dims, xf, mb.DistOptions())
     layer = dims[0] * dims[1]
     for overlap, per_part in ((0, 0), (1, 4), (2, 7), (1, 31)):
-        seen, vol = [], np.full(full.size, np.float32(7e33))
+        seen, delivered, vol = [], [], np.full(full.size, np.float32(7e33))
 
         def part(arr, d, z0):
             assert arr.size == layer * d[2] and arr.flags.owndata  # the consumer owns the memory it receives
             seen.append(z0)
+            delivered.append((z0, d[2]))
             vol[z0 * layer:(z0 + d[2]) * layer] = arr
             return True
 
+        plan, per_part_used = fwn.plan_parts(dims, overlap, per_part)  # b2fwn_plan_parts_for: what the call is about to do
         fwn.calc_from_grid_with_distances_by_parts_into(part, dims, xf, layer_overlap=overlap, max_layers_per_part=per_part)
         assert seen == sorted(seen) and len(set(seen)) == len(seen) and seen[0] == 0
+        assert [(b, n) for b, n, _d in plan] == delivered, (overlap, per_part, plan, delivered)
+        assert per_part_used == delivered[0][1] and (per_part <= 0 or per_part_used == min(per_part, dims[2]))
         assert vol.tobytes() == full.tobytes()
     # winding numbers alone, consumer failure
     w = fwn.calc_from_grid(dims, xf)
@@ -385,6 +389,11 @@ def test_trim_and_reclaim_of_the_handle_caches_when_memory_runs_out():
         assert v1.tobytes() == v0.tobytes() and t1.tobytes() == t0.tobytes()
         hog = fill_device_up_to(96 * MB)
         vol = fwn.calc_from_grid_with_distances(dims, xf, opt)
+        # with the device this full, a wish of 512 layers of 1024^2 per part (2 GiB, twice) is cut to what the handle can count on; the
+        # plan says so before the call would
+        plan, per_part = fwn.plan_parts((1024, 1024, 1024), 1, 512)
+        assert 2 <= per_part < 512 and plan[0][:2] == (0, per_part) and plan[-1][0] + plan[-1][1] == 1024
+        assert all(b1 == b0 + per_part - 1 for (b0, _n0, _d0), (b1, _n1, _d1) in zip(plan, plan[1:]))
         del hog
         assert vol.tobytes() == vol_ref.tobytes()
 
