@@ -755,7 +755,7 @@ __device__ __forceinline__ float fwnResult( const int MODE, const float sum, con
 // 9 blocks per SM (56 registers) measured 1.8 % faster than 8 (63 registers); 10 (48 registers, 60 B spills) slower again
 template <int MODE, bool AA, bool PEERS, int MINB = 9>
 __global__ void __launch_bounds__( GRID_TB, MINB ) kGridFwn5( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
-                                                        const GridParams P, float* __restrict__ out, const BrickOrder O, const PeerOut peers )
+                                                        const GridParams P, float* __restrict__ out, const BrickOrder O, const __grid_constant__ PeerOut peers )
 {
     Brick B;
     if ( !brickOfWarp( P, O, B ) ) return;
@@ -1113,7 +1113,7 @@ __device__ __forceinline__ int fwn6Section( const TravNode* __restrict__ nodes, 
 
 template <int MODE, bool PEERS, int MINB = 7>
 __global__ void __launch_bounds__( GRID_TB, MINB ) kGridFwn6( const TravNode* __restrict__ nodes, const LeafTri* __restrict__ tris,
-                                                        const GridParams P, float* __restrict__ out, const BrickOrder O, const PeerOut peers )
+                                                        const GridParams P, float* __restrict__ out, const BrickOrder O, const __grid_constant__ PeerOut peers )
 {
     // work items of a leaf's exact solid angles and their results (fwn6Section), per warp
     __shared__ unsigned char sList[GRID_TB / 32][32 * FX];
@@ -1292,7 +1292,7 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
 {
     const bool distPass = MODE == 1 && !signOnly;
     if ( int e = checkDims( dims, zBegin, zEnd ) ) return e;
-    if ( peers && peers->n > 0 && getenv( "B2FWN_STATS" ) ) { setError( "peer output is not available in stats mode" ); return B2FWN_ERR_INVALID; }
+    if ( peers && peers->n > 0 && devSwitch( "B2FWN_STATS" ) ) { setError( "peer output is not available in stats mode" ); return B2FWN_ERR_INVALID; }
     if ( dims[0] == 0 || dims[1] == 0 || zEnd == zBegin ) return B2FWN_OK;
     GridParams P{};
     P.dx = dims[0]; P.dy = dims[1]; P.zBegin = zBegin;
@@ -1326,9 +1326,9 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
     const size_t blocks = ( numBricks + GRID_TB / 32 - 1 ) / ( GRID_TB / 32 );
     if ( blocks > 0x7FFFFFFFull ) { setError( "grid too large for one launch" ); return B2FWN_ERR_INVALID; }
     const bool aa = xf.A[1] == 0 && xf.A[2] == 0 && xf.A[3] == 0 && xf.A[5] == 0 && xf.A[6] == 0 && xf.A[7] == 0;
-    static const bool wantStats = getenv( "B2FWN_STATS" ) != nullptr;
-    static const bool heavyFirst = !( getenv( "B2FWN_LINEAR" ) && atoi( getenv( "B2FWN_LINEAR" ) ) ); // dev switch: plain linear order
-    static const bool forceV5 = getenv( "B2FWN_FWN5" ) && atoi( getenv( "B2FWN_FWN5" ) ); // dev switch: v5 winding walk on axis-aligned grids too
+    static const bool wantStats = devSwitch( "B2FWN_STATS" ) != nullptr;
+    static const bool heavyFirst = !( devSwitch( "B2FWN_LINEAR" ) && atoi( devSwitch( "B2FWN_LINEAR" ) ) ); // dev switch: plain linear order
+    static const bool forceV5 = devSwitch( "B2FWN_FWN5" ) && atoi( devSwitch( "B2FWN_FWN5" ) ); // dev switch: v5 winding walk on axis-aligned grids too
     // winding walk: v6 (8 x 8 x 4 bricks) on axis-aligned grids, v5 (8 x 4 x 4) on general affine grids; the stats build counts v4's walk
     const bool v6 = aa && !forceV5 && !wantStats;
     GridParams PF = P; // brick layout of the winding kernel
@@ -1449,7 +1449,7 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
             {
                 bool a32 = true; // the peer volumes (the only targets of the 256-bit stores)
                 for ( int k = 0; k < po.n; ++k ) a32 = a32 && reinterpret_cast<uintptr_t>( po.p[k] ) % 32 == 0;
-                static const bool noV8 = getenv( "B2FWN_NO_V8" ) != nullptr; // dev switch: two 16-byte stores per row, as before
+                static const bool noV8 = devSwitch( "B2FWN_NO_V8" ) != nullptr; // dev switch: two 16-byte stores per row, as before
                 if ( a32 && !noV8 ) PF.vecStore = 2;
             }
         }
@@ -1467,7 +1467,7 @@ int launchGrid( const DeviceTree& t, const int32_t dims[3], const GridXf& xf, fl
         else kGridFwn5<MODE, false, false><<<blocksF, GRID_TB, 0, st>>>( t.nodes, t.leafTris, PF, dOut, oF, po );
     }
     if ( launches ) *launches += ( distPass ? 2 : 1 );
-    static const bool debugOrder = getenv( "B2FWN_DEBUG" ) != nullptr;
+    static const bool debugOrder = devSwitch( "B2FWN_DEBUG" ) != nullptr;
     if ( debugOrder && scratch )
     {
         unsigned long long h[8];
