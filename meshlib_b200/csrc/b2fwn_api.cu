@@ -894,7 +894,7 @@ int b2fwn_mesh_to_distance_volume_by_projection_normal( b2fwn_handle h, const b2
         // (non-manifold: the pole of a UV sphere with faces removed) the duplicates have different pseudonormals -- 1 voxel of
         // 34,891 got the other sign (profiles/r01/diag_projbricks_n2.txt); (2) it measured 2 x faster over the full range of a
         // sphere but 3.5 x slower in a narrow band than the Morton-ordered per-point search (r01).
-        const char* envBricks = getenv( "B2FWN_PROJ_BRICKS" );
+        const char* envBricks = devSwitch( "B2FWN_PROJ_BRICKS" );
         const bool bricks = envBricks && atoi( envBricks ) && ( !opt->null_outside_min_max || opt->min_dist_sq <= 0.f );
         const int layers = (int)std::min<size_t>( std::max<size_t>( ( (size_t)8 << 20 ) / layer, 1 ), (size_t)dims[2] );
         if ( layer * layers > 0xFFFFFFFFull ) { setError( "grid layer too large" ); return B2FWN_ERR_INVALID; }

@@ -5,6 +5,7 @@
 #include <stdint.h>
 #include <stddef.h>
 #include <string>
+#include <cstdlib>
 #include <functional>
 #include "../../include/b2fwn.h"
 
@@ -91,6 +92,18 @@ struct GridXf
 };
 
 // errors -------------------------------------------------------------------------------------------------------
+// Development switches (alternative kernels and orders kept for measurements: B2FWN_FWN5, _LINEAR, _NO_V8, _PROJ_BRICKS, _NO_SUBTREES,
+// _QUERY_THREADS, _QUERY_WARPS, _NO_QUERY_SORT, _HOST_OUT, _STATS, _DEBUG) are read from the environment ONLY in a library built with
+// `make DEV=1` (-DB2FWN_DEV_SWITCHES).  The product library ignores them: a plug-in must not let its host process's environment pick its
+// kernels (B2FWN_PROJ_BRICKS=1 selects a walk that differs from the reference in a tie-dependent voxel).  What the product build still
+// reads are three sizing knobs that cannot change a result: B2FWN_PIECE_FLOATS, B2FWN_COPY_THREADS (staging ring), B2FWN_MIN_CHUNK_VOXELS
+// (smallest automatic part) -- the tests use them to drive small grids through the many-pieces / many-parts paths.
+#ifdef B2FWN_DEV_SWITCHES
+inline const char* devSwitch( const char* name ) { return getenv( name ); }
+#else
+inline const char* devSwitch( const char* ) { return nullptr; }
+#endif
+
 void setError( const std::string& msg );
 int cudaFail( cudaError_t e, const char* where );
 // the CUDA error code behind the calling thread's last cudaFail (cudaSuccess when its last failure was none of CUDA's)

@@ -124,7 +124,7 @@ int launchFwnVector( const DeviceTree& t, const float* dPts, size_t n, float bet
     if ( n == 0 ) return B2FWN_OK;
     const size_t blocks = ( n + 127 ) / 128;
     // Morton order for vectors large enough to pay for the sort (r02, C2: 10 M random points against 1 M triangles)
-    static const bool noSort = getenv( "B2FWN_NO_QUERY_SORT" ) != nullptr; // dev switch
+    static const bool noSort = devSwitch( "B2FWN_NO_QUERY_SORT" ) != nullptr; // dev switch
     uint32_t* order = nullptr;
     uint8_t* scratch = nullptr;
     if ( !noSort && n >= ( 1u << 15 ) && n <= (size_t)INT_MAX && t.numLeaves > 0 && t.pool ) // cub counts the items in an int; longer vectors are walked in input order
@@ -148,7 +148,7 @@ int launchFwnVector( const DeviceTree& t, const float* dPts, size_t n, float bet
     // launchFwnQueriesWarp) is kept for the faces of calcSelfIntersections, where it wins (C4: 16.7 -> 10.9 ms); for scattered
     // points it loses (C2, 10 M random points: 5.69 ms against 4.29 ms -- the ball of 128 random neighbours is ten triangles
     // wide, few nodes are near or far for all of them).  B2FWN_QUERY_WARPS=1 selects it here as well.
-    static const bool warps = getenv( "B2FWN_QUERY_WARPS" ) && atoi( getenv( "B2FWN_QUERY_WARPS" ) );
+    static const bool warps = devSwitch( "B2FWN_QUERY_WARPS" ) && atoi( devSwitch( "B2FWN_QUERY_WARPS" ) );
     if ( order && warps )
     {
         if ( int e = launchFwnQueriesWarp( t, dPts, order, n, false, beta, skipFace, dOut, nullptr, st, launches ) ) return e;
@@ -172,7 +172,7 @@ int launchFwnFaces( const DeviceTree& t, float beta, float* dOutW, uint64_t* dBi
     if ( dOutW ) B2_CUDA( cudaMemsetAsync( dOutW, 0, n * sizeof( float ), st ) );
     const size_t L = t.numLeaves;
     if ( L == 0 ) return B2FWN_OK;
-    static const bool perThread = getenv( "B2FWN_QUERY_THREADS" ) && atoi( getenv( "B2FWN_QUERY_THREADS" ) );
+    static const bool perThread = devSwitch( "B2FWN_QUERY_THREADS" ) && atoi( devSwitch( "B2FWN_QUERY_THREADS" ) );
     if ( L >= ( 1u << 15 ) && !perThread )
         return launchFwnQueriesWarp( t, nullptr, nullptr, L, true, beta, -1, dOutW, reinterpret_cast<uint32_t*>( dBits ), st, launches );
     kFwnFaces<<<(unsigned)( ( L + 127 ) / 128 ), 128, 0, st>>>( t.nodes, t.leafTris, (int)t.numNodes, t.points, t.tris, L, beta * beta, dOutW,

@@ -491,7 +491,7 @@ int runChunked( b2fwn_ctx* h, const ChunkedCall& c, const ChunkLaunch& launch )
         outPinned = isPinned( c.hostOut );
         // dev switch: pin the caller's buffer for the duration of the call instead of staging (page-locking tens of GB costs
         // seconds; measured against the staging ring in profiles/r02)
-        static const bool wantRegister = getenv( "B2FWN_HOST_OUT" ) && !strcmp( getenv( "B2FWN_HOST_OUT" ), "register" );
+        static const bool wantRegister = devSwitch( "B2FWN_HOST_OUT" ) && !strcmp( devSwitch( "B2FWN_HOST_OUT" ), "register" );
         if ( !outPinned && wantRegister )
         {
             if ( cudaHostRegister( c.hostOut, (size_t)g.nz * g.layer * sizeof( float ), cudaHostRegisterPortable ) == cudaSuccess )

@@ -767,7 +767,7 @@ int buildTree( DeviceTree& t, cudaStream_t st, uint64_t* launches )
     uint32_t* dSegBox = nullptr; int32_t *dSkip = nullptr, *dLeafNodeOfPos = nullptr, *dLeafSlotOfNode = nullptr;
     uint8_t* dDepth = nullptr;
     // the global passes stop at level0 (below it one block finishes each subtree): the segment tables only grow that far
-    static const bool noSubtrees = getenv( "B2FWN_NO_SUBTREES" ) != nullptr; // dev switch: global passes down to the leaves
+    static const bool noSubtrees = devSwitch( "B2FWN_NO_SUBTREES" ) != nullptr; // dev switch: global passes down to the leaves
     const int level0 = noSubtrees ? levels + 1 : std::max( 0, levels - 10 ); // segments of level0 hold <= SUB_CAP = 2^10 leaves
     const size_t maxSegs = (size_t)1 << std::min( levels, level0 );
     size_t sortTmpBytes = 0; void* sortTmp = nullptr;

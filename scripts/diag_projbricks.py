@@ -1,5 +1,6 @@
 #!/usr/bin/env python
-"""dev diagnostics: ProjectionNormal volume through the brick walk (B2FWN_PROJ_BRICKS=1) against the per-point search and the
+"""(needs a library built with `make DEV=1`: the product build ignores B2FWN_PROJ_BRICKS)
+dev diagnostics: ProjectionNormal volume through the brick walk (B2FWN_PROJ_BRICKS=1) against the per-point search and the
 reference, on the open-boundary test mesh; prints the voxels whose sign differs"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))

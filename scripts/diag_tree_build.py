@@ -1,5 +1,6 @@
 #!/usr/bin/env python
-"""tree + dipole build time on the device (b2fwn_stats.tree_build_ms) for the bench meshes; B2FWN_NO_SUBTREES=1 = global passes only"""
+"""(needs a library built with `make DEV=1`: the product build ignores B2FWN_NO_SUBTREES)
+tree + dipole build time on the device (b2fwn_stats.tree_build_ms) for the bench meshes; B2FWN_NO_SUBTREES=1 = global passes only"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
