@@ -552,7 +552,8 @@ def run_ours(args, wl):
     fwn = mb.FastWindingNumber(wl["points"], wl["tris"], device=local)
     st0 = fwn.stats()
     # full volume on every GPU (north_star: the slabs of all ranks gathered on every GPU); rank r writes its share in place
-    p2p = world > 1 and args.gather == "p2p"
+    p2p = world > 1 and args.gather in ("p2p", "ce")  # both need the peer-mapped volumes
+    ce = world > 1 and args.gather == "ce"
     peer_ptrs, my_ptr = [], None
     if p2p:
         # peer-visible volumes: every rank maps the volumes of the others; the kernels store each result into all of them.
@@ -578,7 +579,7 @@ def run_ours(args, wl):
                 fwn.shared_close(q)
             if my_ptr:
                 fwn.shared_free(my_ptr)
-            p2p, peer_ptrs, my_ptr = False, [], None
+            p2p, ce, peer_ptrs, my_ptr = False, False, [], None
     if p2p:
         volume = torch.as_tensor(mb.DeviceBuffer(my_ptr, total), device=dev)
     else:
@@ -602,7 +603,14 @@ def run_ours(args, wl):
     # N > 1: z-interleaved chunks (equal cost per rank).  --gather p2p (default): one call per step, the gather fused into the
     # kernel (stores into every rank's volume over NVLink), then a barrier.  --gather nccl: the z-range cut into stages, the
     # all-gather of one stage issued on NCCL's stream while the next stage is computed.  N = 1: one plain call.
-    plan = slabs.ChunkPlan(world, dims[2], chunk=args.z_chunk, stages=1 if p2p else args.stages) if world > 1 else None
+    plan = slabs.ChunkPlan(world, dims[2], chunk=args.z_chunk, stages=1 if (p2p and not ce) else args.stages) if world > 1 else None
+    if ce:
+        # --gather ce: the kernels write the rank's own volume only; every finished stage's chunks (contiguous blocks of z_chunk
+        # layers) are pushed into the peers' volumes by the COPY ENGINES (cudaMemcpyAsync on the peer-mapped pointers, two copy
+        # streams) while the next stage is computed -- no SM issues a remote store; exposed: the last stage's copies + barrier
+        from cuda.bindings import runtime as cudart
+        copy_streams = [torch.cuda.Stream(device=dev) for _ in range(max(1, min(args.copy_streams, world - 1)))]
+        D2D = cudart.cudaMemcpyKind.cudaMemcpyDeviceToDevice
     if p2p and plan.call_args(rank, 0) is None:
         raise SystemExit("grid too small for this many ranks")
 
@@ -611,6 +619,30 @@ def run_ours(args, wl):
         if world == 1:
             fwn.calc_from_grid_with_distances_device(dims, xf, slab.data_ptr(), opts, z_begin=z0, z_end=z1)
             return fwn.stats().last_kernel_ms, 0.0
+        if ce:
+            k_ms, n_copy = 0.0, 0
+            for s in range(plan.stages):
+                a = plan.call_args(rank, s)
+                if not a:
+                    continue
+                zb, ze, zc, zs = a
+                fwn.calc_from_grid_with_distances_device_chunks(dims, xf, my_ptr + 4 * zb * layer, opts, z_begin=zb, z_end=ze,
+                                                                z_chunk=zc, z_stride=zs)  # returns when the kernels are done
+                k_ms += fwn.stats().last_kernel_ms
+                for z in range(zb, ze, zs):
+                    off, nbytes = 4 * z * layer, 4 * layer * min(zc, ze - z)
+                    for i in range(len(peer_ptrs)):
+                        q = peer_ptrs[(i + rank) % len(peer_ptrs)]  # the ranks start with different peers
+                        err, = cudart.cudaMemcpyAsync(q + off, my_ptr + off, nbytes, D2D, copy_streams[n_copy % len(copy_streams)].cuda_stream)
+                        if err != cudart.cudaError_t.cudaSuccess:
+                            raise RuntimeError(f"cudaMemcpyAsync to a peer volume: {err}")
+                        n_copy += 1
+            t = time.perf_counter()
+            for cs in copy_streams:
+                cs.synchronize()
+            dist.barrier()  # every rank's copies have landed: the volume is complete everywhere
+            torch.cuda.synchronize()
+            return k_ms, 1e3 * (time.perf_counter() - t)
         if p2p:
             zb, ze, zc, zs = plan.call_args(rank, 0)
             off = 4 * zb * layer
@@ -761,6 +793,9 @@ def run_ours(args, wl):
         "ms_per_step": dev_ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": {"workload": wl["desc"], "sharding": "single GPU" if world == 1 else
+                   (f"z-interleaved chunks of {args.z_chunk} layers x{world} ranks in {plan.stages} stages, mesh+tree replicated, every "
+                    "finished stage pushed into the peers' volumes by the copy engines (cudaMemcpyAsync over NVLink) behind the next "
+                    "stage's kernels + barrier") if ce else
                    (f"z-interleaved chunks of {args.z_chunk} layers x{world} ranks, mesh+tree replicated, gather fused into the kernel "
                     "(peer stores over NVLink into every rank's volume) + barrier") if p2p else
                    (f"z-interleaved chunks of {args.z_chunk} layers x{world} ranks in {plan.stages} stages, mesh+tree replicated, NCCL "
@@ -827,7 +862,9 @@ def main():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS) + sorted(OFFSET_WORKLOADS) + sorted(QUERY_WORKLOADS))
     ap.add_argument("--grid", type=int, default=None, help="override the grid size (diagnostics only; not the headline)")
     ap.add_argument("--z-chunk", type=int, default=8, help="N > 1: layers per interleaved chunk (multiple of 4)")
-    ap.add_argument("--gather", default="p2p", choices=["p2p", "nccl"], help="N > 1: fused peer stores, or NCCL all-gather")
+    ap.add_argument("--gather", default="p2p", choices=["p2p", "ce", "nccl"],
+                    help="N > 1: fused peer stores; copy-engine pushes of finished stages into the peers' volumes; or NCCL all-gather")
+    ap.add_argument("--copy-streams", type=int, default=7, help="--gather ce: copy streams the pushes are dealt over (at most one per peer)")
     ap.add_argument("--stages", type=int, default=4, help="N > 1: compute/gather pipeline stages over z")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-pinned", action="store_true", help="skip the pinned-buffer variant of the e2e leg")
